@@ -1,0 +1,113 @@
+"""Shared test plumbing: ctypes loaders for the oracle, the reference build (when
+present) and small helpers.  TEST INFRASTRUCTURE ONLY."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+REF_LIB = os.path.join(ORACLE_DIR, "_ref", "libaomref.so")
+
+TX_W = [4, 8, 16, 32, 64, 4, 8, 8, 16, 16, 32, 32, 64, 4, 16, 8, 32, 16, 64]
+TX_H = [4, 8, 16, 32, 64, 8, 4, 16, 8, 32, 16, 64, 32, 16, 4, 32, 8, 64, 16]
+TX_NAMES = ["%dx%d" % (w, h) for w, h in zip(TX_W, TX_H)]
+N_TX_SIZES = 19
+N_TX_TYPES = 16
+
+# SAD / variance block sizes of aom_dsp_rtcd_defs.pl:42-58
+BLOCK_SIZES = [(128, 128), (128, 64), (64, 128), (64, 64), (64, 32), (32, 64), (32, 32),
+               (32, 16), (16, 32), (16, 16), (16, 8), (8, 16), (8, 8), (8, 4), (4, 8),
+               (4, 4), (4, 16), (16, 4), (8, 32), (32, 8), (16, 64), (64, 16)]
+
+i16p = C.POINTER(C.c_int16)
+i32p = C.POINTER(C.c_int32)
+u8p = C.POINTER(C.c_uint8)
+u16p = C.POINTER(C.c_uint16)
+u32p = C.POINTER(C.c_uint32)
+i64p = C.POINTER(C.c_int64)
+
+
+def ptr(a, t):
+    return a.ctypes.data_as(t)
+
+
+_oracle = None
+
+
+def oracle():
+    """Build (if needed) and load oracle/liboracle.so."""
+    global _oracle
+    if _oracle is None:
+        subprocess.run(["make", "-s", "-C", ORACLE_DIR], check=True)
+        lib = C.CDLL(os.path.join(ORACLE_DIR, "liboracle.so"))
+        lib.av1o_scan.restype = i16p
+        lib.av1o_iscan.restype = i16p
+        lib.av1o_cospi.restype = i32p
+        lib.av1o_sinpi.restype = i32p
+        lib.av1o_dc_q.restype = C.c_int16
+        lib.av1o_ac_q.restype = C.c_int16
+        for n in ("av1o_block_error", "av1o_block_error_lp", "av1o_highbd_block_error",
+                  "av1o_block_error_qm", "av1o_sse", "av1o_highbd_sse"):
+            getattr(lib, n).restype = C.c_int64
+        for n in ("av1o_sad", "av1o_sad_skip", "av1o_sad_avg", "av1o_highbd_sad",
+                  "av1o_highbd_sad_skip", "av1o_variance", "av1o_mse",
+                  "av1o_sub_pixel_variance", "av1o_highbd_variance",
+                  "av1o_highbd_sub_pixel_variance"):
+            getattr(lib, n).restype = C.c_uint
+        _oracle = lib
+    return _oracle
+
+
+_ref = None
+
+
+def have_ref():
+    return os.path.exists(REF_LIB)
+
+
+def ref():
+    """The reference's own C functions (oracle/_ref), or None when not built."""
+    global _ref
+    if _ref is None and have_ref():
+        _ref = C.CDLL(REF_LIB)
+    return _ref
+
+
+class QRow(C.Structure):
+    _fields_ = [(n, C.c_int16 * 8) for n in
+                ("quant", "quant_shift", "zbin", "round", "quant_fp", "round_fp", "dequant")]
+
+
+def oracle_qrow(bd, qindex, plane=0, sharpness=0):
+    row = QRow()
+    oracle().av1o_build_qrow(bd, qindex, plane, sharpness, C.byref(row))
+    return row
+
+
+def oracle_scan(tx_size, tx_type):
+    n = oracle().av1o_max_eob(tx_size)
+    s = np.ctypeslib.as_array(oracle().av1o_scan(tx_size, tx_type), shape=(n,)).copy()
+    i = np.ctypeslib.as_array(oracle().av1o_iscan(tx_size, tx_type), shape=(n,)).copy()
+    return s, i
+
+
+def max_eob(tx_size):
+    return min(TX_W[tx_size], 32) * min(TX_H[tx_size], 32)
+
+
+def tx_valid(tx_size, tx_type):
+    return bool(oracle().av1o_tx_valid(tx_size, tx_type))
+
+
+def log_scale(tx_size):
+    """av1_get_tx_scale, av1/common/idct.c:24"""
+    pels = TX_W[tx_size] * TX_H[tx_size]
+    return int(pels > 256) + int(pels > 1024)
+
+
+def oracle_fwd_txfm2d(resid, stride, tx_size, tx_type, bd=8):
+    out = np.zeros(max_eob(tx_size), np.int32)
+    oracle().av1o_fwd_txfm2d(ptr(resid, i16p), ptr(out, i32p), stride, tx_size, tx_type, bd)
+    return out
