@@ -1,0 +1,180 @@
+/*
+ * b200av1.h -- C ABI of libb200av1.so: the B200 (sm_100a) implementation of the
+ * aom-av1-lavish encoder's data-parallel hot path (forward transform + quantisation,
+ * block error, subtract, SAD / variance, motion search).
+ *
+ * Plain C, plain pointers and sizes; no torch or CUDA types in any signature
+ * (streams are passed as void*, device buffers as void* / typed device pointers).
+ *
+ * Three tiers:
+ *   1. frame tier    -- context, device buffers, table upload            (this file)
+ *   2. batched tier  -- descriptor arrays -> one launch per kernel class  (this file)
+ *   3. drop-in tier  -- the reference's RTCD prototypes, one block per call:
+ *                       include/b200av1_rtcd.h
+ *
+ * Every entry point cites the reference interface it replaces as
+ * (path:line relative to the aom-av1-lavish tree).
+ *
+ * Error model: RTCD-shaped functions cannot return errors (reference DSP kernels are
+ * void / value functions), so a CUDA failure there is fatal:
+ * the message is stored for b200_last_error(), printed to stderr, and abort() is
+ * called.  Tier 1/2 functions return 0 on success and a negative B200_E* code on
+ * failure.  There is no CPU fallback anywhere in this library.
+ */
+#ifndef B200AV1_H_
+#define B200AV1_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK 0
+#define B200_ECUDA (-1)   /* a CUDA runtime call failed; see b200_last_error() */
+#define B200_EINVAL (-2)  /* bad argument (size/type combination, null pointer) */
+#define B200_ENODEV (-3)  /* no CUDA device / device is not sm_100 */
+
+/* TX_SIZE and TX_TYPE numbering: aom_dsp/txfm_common.h:25-71 */
+enum {
+  B200_TX_4X4, B200_TX_8X8, B200_TX_16X16, B200_TX_32X32, B200_TX_64X64,
+  B200_TX_4X8, B200_TX_8X4, B200_TX_8X16, B200_TX_16X8, B200_TX_16X32,
+  B200_TX_32X16, B200_TX_32X64, B200_TX_64X32, B200_TX_4X16, B200_TX_16X4,
+  B200_TX_8X32, B200_TX_32X8, B200_TX_16X64, B200_TX_64X16, B200_TX_SIZES_ALL
+};
+enum {
+  B200_DCT_DCT, B200_ADST_DCT, B200_DCT_ADST, B200_ADST_ADST, B200_FLIPADST_DCT,
+  B200_DCT_FLIPADST, B200_FLIPADST_FLIPADST, B200_ADST_FLIPADST, B200_FLIPADST_ADST,
+  B200_IDTX, B200_V_DCT, B200_H_DCT, B200_V_ADST, B200_H_ADST, B200_V_FLIPADST,
+  B200_H_FLIPADST, B200_TX_TYPES
+};
+
+/* ------------------------------------------------------------------ frame tier */
+
+typedef struct b200_ctx b200_ctx;
+
+int b200_device_count(void);
+/* Create a context on `device` (one per GPU; one process per GPU is the intended
+ * deployment, several contexts per process also work).  Uploads the constant tables
+ * (cospi/sinpi av1_txfm.c:18-69, scan orders scan.c:1666, tx configuration
+ * av1_fwd_txfm2d.c:314-381).  Fails with B200_ENODEV when no sm_100 device exists. */
+int b200_ctx_create(int device, b200_ctx **ctx);
+void b200_ctx_destroy(b200_ctx *ctx);
+/* Context used by the drop-in tier (created lazily on device $B200AV1_DEVICE or 0). */
+b200_ctx *b200_default_ctx(void);
+const char *b200_last_error(void);
+/* The context's own stream as a cudaStream_t cast to void*. */
+void *b200_ctx_stream(b200_ctx *ctx);
+int b200_sync(b200_ctx *ctx);
+
+/* Device memory helpers (thin wrappers so that C callers need no CUDA headers). */
+int b200_malloc(b200_ctx *ctx, size_t bytes, void **dptr);
+int b200_free(b200_ctx *ctx, void *dptr);
+int b200_malloc_host(size_t bytes, void **hptr); /* pinned */
+int b200_free_host(void *hptr);
+int b200_h2d(b200_ctx *ctx, void *dst, const void *src, size_t bytes); /* async on ctx stream */
+int b200_d2h(b200_ctx *ctx, void *dst, const void *src, size_t bytes); /* async on ctx stream */
+
+/* Introspection used by tests: geometry helpers mirroring tx_size_wide/high
+ * (av1/common/common_data.h) and av1_get_max_eob (av1/common/blockd.h:1596). */
+int b200_tx_wide(int tx_size);
+int b200_tx_high(int tx_size);
+int b200_tx_max_eob(int tx_size);
+int b200_tx_valid(int tx_size, int tx_type);
+/* Host copy of scan / iscan of av1_scan_orders[tx_size][tx_type] (scan.c:1666). */
+const int16_t *b200_scan(int tx_size, int tx_type);
+const int16_t *b200_iscan(int tx_size, int tx_type);
+
+/* ---------------------------------------------------------------- batched tier */
+
+/* One quantiser row: the [0]=DC / [1]=AC entries of the reference's per-qindex
+ * tables (QUANTS / Dequants, av1/encoder/av1_quantize.h:45-84), as the encoder
+ * keeps them in MACROBLOCK_PLANE (av1/encoder/block.h:129-167).  The encoder builds
+ * them (av1_build_quantizer, av1_quantize.c:602); this library only consumes them. */
+typedef struct {
+  int16_t zbin[2], round[2], quant[2], quant_shift[2]; /* "B" quantiser */
+  int16_t round_fp[2], quant_fp[2];                    /* "FP" quantiser */
+  int16_t dequant[2];
+  int16_t reserved[2];
+} B200QRow; /* 32 bytes */
+
+/* One transform block of a batch. */
+typedef struct {
+  uint32_t src_offset; /* elements from the input base to the block's top-left sample */
+  uint32_t out_offset; /* int32 elements into coeff / qcoeff / dqcoeff (BLOCK_OFFSET,
+                          av1/common/blockd.h:489) */
+  uint16_t src_stride; /* elements per input row (diff_stride / plane stride) */
+  uint16_t qrow;       /* index into the B200QRow table */
+  uint8_t tx_size;     /* B200_TX_* ; all blocks of one launch share it */
+  uint8_t tx_type;     /* B200_*_* */
+  uint16_t reserved;
+} B200TxBlock; /* 16 bytes */
+
+/* Companion entry when the kernel forms the residual itself (fused
+ * aom_subtract_block, aom_dsp/subtract.c:20): location of the prediction block. */
+typedef struct {
+  uint32_t pred_offset;
+  uint16_t pred_stride;
+  uint16_t reserved;
+} B200TxPred; /* 8 bytes */
+
+/* what the fused kernel reads */
+enum {
+  B200_IN_RESIDUAL = 0, /* int16 src_diff, as av1_fwd_txfm (hybrid_fwd_txfm.c:233) */
+  B200_IN_PIXELS8 = 1,  /* uint8 source + prediction planes (fused subtract) */
+  B200_IN_PIXELS16 = 2  /* uint16 source + prediction planes (high bit depth) */
+};
+/* which quantiser runs on the coefficients while they are still in registers */
+enum {
+  B200_Q_NONE = 0,      /* transform only */
+  B200_Q_FP = 1,        /* av1_quantize_fp / _32x32 / _64x64 (av1_quantize.c:201-264) */
+  B200_Q_FP_HBD = 2,    /* av1_highbd_quantize_fp (av1_quantize.c:565) */
+  B200_Q_B = 3,         /* aom_quantize_b / _32x32 / _64x64 (aom_dsp/quantize.c:399-433) */
+  B200_Q_B_HBD = 4      /* aom_highbd_quantize_b* (aom_dsp/quantize.c:435-470) */
+};
+#define B200_TXQ_STORE_COEFF 1u /* write the transform coefficients (p->coeff) */
+#define B200_TXQ_BLOCK_ERROR 2u /* also av1_block_error / av1_highbd_block_error */
+#define B200_TXQ_FAST32 4u      /* all-32-bit butterflies (arithmetic) */
+
+typedef struct {
+  int tx_size;             /* all n_blocks blocks have this size */
+  int in_kind;             /* B200_IN_* */
+  int q_kind;              /* B200_Q_* */
+  int bd;                  /* 8, 10 or 12 (block-error rounding, rdopt.c:663) */
+  unsigned flags;          /* B200_TXQ_* */
+  int n_blocks;
+  const B200TxBlock *blocks; /* device */
+  const B200TxPred *preds;   /* device, or NULL for B200_IN_RESIDUAL */
+  const void *src;           /* device: int16 residual or pixel plane base */
+  const void *pred;          /* device: prediction plane base, or NULL */
+  const B200QRow *qrows;     /* device */
+  int32_t *coeff;            /* device, may be NULL without B200_TXQ_STORE_COEFF */
+  int32_t *qcoeff;           /* device */
+  int32_t *dqcoeff;          /* device */
+  uint16_t *eob;             /* device, n_blocks entries */
+  int64_t *dist;             /* device, 2*n_blocks entries {error, ssz}, or NULL */
+} B200TxqLaunch;
+
+/* Enqueue one fused (subtract +) transform (+ quantise) (+ block error) launch on
+ * `stream` (void* cudaStream_t; NULL = the context's stream).  All pointers are
+ * DEVICE pointers.  Replaces the per-block sequence av1_subtract_block ->
+ * av1_xform -> av1_quant -> dist_block_tx_domain (encodemb.c:38,295,308;
+ * tx_search.c:1077) for a whole batch of same-size blocks. */
+int b200_txq_launch(b200_ctx *ctx, const B200TxqLaunch *launch, void *stream);
+
+/* Host-buffer convenience wrapper over b200_txq_launch: copies descriptors, input and
+ * tables to the device, launches once per tx_size present in `blocks`, copies the
+ * results back and synchronises.  `src_elems` / `pred_elems` are the input buffer
+ * lengths in elements, `out_elems` the length of each coefficient buffer. */
+int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int bd, unsigned flags,
+                        const B200TxBlock *blocks, const B200TxPred *preds, int n_blocks,
+                        const void *src, size_t src_elems, const void *pred,
+                        size_t pred_elems, const B200QRow *qrows, int n_qrows,
+                        int32_t *coeff, int32_t *qcoeff, int32_t *dqcoeff,
+                        size_t out_elems, uint16_t *eob, int64_t *dist);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200AV1_H_ */

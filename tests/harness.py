@@ -111,3 +111,64 @@ def oracle_fwd_txfm2d(resid, stride, tx_size, tx_type, bd=8):
     out = np.zeros(max_eob(tx_size), np.int32)
     oracle().av1o_fwd_txfm2d(ptr(resid, i16p), ptr(out, i32p), stride, tx_size, tx_type, bd)
     return out
+
+
+# ---------------------------------------------------------------- batch oracle ----
+def oracle_txq_batch(src, blocks, rows, q_kind, bd, out_elems, in_kind=0, pred=None, preds=None,
+                     with_err=True):
+    """Run the oracle over a descriptor batch exactly like b200_txq_batch_host would.
+    `rows` is a list of harness.QRow (oracle rows) indexed by block['qrow'].
+    q_kind / in_kind use the B200_* numbering of include/b200av1.h."""
+    O = oracle()
+    coeff = np.zeros(out_elems, np.int32)
+    qc = np.zeros(out_elems, np.int32)
+    dq = np.zeros(out_elems, np.int32)
+    eob = np.zeros(len(blocks), np.uint16)
+    dist = np.zeros((len(blocks), 2), np.int64)
+    for i, b in enumerate(blocks):
+        ts, tt = int(b["tx_size"]), int(b["tx_type"])
+        W, Hh = TX_W[ts], TX_H[ts]
+        n = max_eob(ts)
+        so, st = int(b["src_offset"]), int(b["src_stride"])
+        if in_kind == 0:
+            resid = src[so: so + (Hh - 1) * st + W]
+            rstride = st
+        else:
+            po, ps = int(preds[i]["pred_offset"]), int(preds[i]["pred_stride"])
+            resid = np.zeros((Hh, W), np.int16)
+            s2 = np.lib.stride_tricks.as_strided(src[so:], (Hh, W), (st * src.itemsize, src.itemsize))
+            p2 = np.lib.stride_tricks.as_strided(pred[po:], (Hh, W), (ps * pred.itemsize, pred.itemsize))
+            resid[:] = (s2.astype(np.int32) - p2.astype(np.int32)).astype(np.int16)
+            resid = resid.reshape(-1)
+            rstride = W
+        resid = np.ascontiguousarray(resid)
+        oo = int(b["out_offset"])
+        c = np.zeros(n, np.int32)
+        O.av1o_fwd_txfm2d(ptr(resid, i16p), ptr(c, i32p), rstride, ts, tt, bd)
+        coeff[oo:oo + n] = c
+        if q_kind == 0:
+            continue
+        row = rows[int(b["qrow"])]
+        scan, iscan = oracle_scan(ts, tt)
+        q = np.zeros(n, np.int32)
+        d = np.zeros(n, np.int32)
+        e = C.c_uint16(0)
+        ls = log_scale(ts)
+        fp = q_kind in (1, 2)
+        fn = {1: O.av1o_quantize_fp, 2: O.av1o_highbd_quantize_fp, 3: O.av1o_quantize_b,
+              4: O.av1o_highbd_quantize_b}[q_kind]
+        fn(ptr(c, i32p), C.c_ssize_t(n), row.zbin, row.round_fp if fp else row.round,
+           row.quant_fp if fp else row.quant, row.quant_shift, ptr(q, i32p), ptr(d, i32p),
+           row.dequant, C.byref(e), ptr(scan, i16p), ptr(iscan, i16p), None, None, ls)
+        qc[oo:oo + n] = q
+        dq[oo:oo + n] = d
+        eob[i] = e.value
+        if with_err:
+            ssz = C.c_int64(0)
+            if q_kind in (2, 4):
+                err = O.av1o_highbd_block_error(ptr(c, i32p), ptr(d, i32p), C.c_ssize_t(n),
+                                                C.byref(ssz), bd)
+            else:
+                err = O.av1o_block_error(ptr(c, i32p), ptr(d, i32p), C.c_ssize_t(n), C.byref(ssz))
+            dist[i] = (err, ssz.value)
+    return coeff, qc, dq, eob, dist

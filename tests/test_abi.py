@@ -1,0 +1,66 @@
+"""CPU-side checks of the product library: it loads, exports every symbol declared in
+include/*.h, its host tables match the oracle, and it fails loudly without a GPU."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import harness as H
+
+ROOT = H.ROOT
+
+
+def _declared_symbols():
+    syms = set()
+    inc = os.path.join(ROOT, "include")
+    for fn in sorted(os.listdir(inc)):
+        if not fn.endswith(".h"):
+            continue
+        text = open(os.path.join(inc, fn)).read()
+        text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+        text = re.sub(r"//[^\n]*", "", text)
+        for m in re.finditer(r"\b([A-Za-z_][A-Za-z0-9_]*)\s*\(", text):
+            name = m.group(1)
+            if name.startswith(("b200_", "av1_", "aom_")) and not name.isupper():
+                syms.add(name)
+        # macro-generated families are listed explicitly in a B200_EXPORTS comment block
+    return syms
+
+
+def test_library_exports_declared_symbols():
+    import b200av1
+    L = b200av1.lib()
+    missing = [s for s in sorted(_declared_symbols()) if not hasattr(L, s)]
+    assert not missing, missing
+
+
+def test_struct_sizes():
+    import b200av1
+    assert C.sizeof(b200av1.QRow) == 32
+    assert b200av1.TXBLOCK_DTYPE.itemsize == 16
+
+
+def test_host_tables_match_oracle():
+    import b200av1
+    L, O = b200av1.lib(), H.oracle()
+    for ts in range(19):
+        assert L.b200_tx_wide(ts) == O.av1o_tx_wide(ts)
+        assert L.b200_tx_high(ts) == O.av1o_tx_high(ts)
+        n = L.b200_tx_max_eob(ts)
+        assert n == O.av1o_max_eob(ts)
+        for tt in range(16):
+            assert L.b200_tx_valid(ts, tt) == O.av1o_tx_valid(ts, tt)
+            s, i = H.oracle_scan(ts, tt)
+            assert np.array_equal(np.ctypeslib.as_array(L.b200_scan(ts, tt), shape=(n,)), s)
+            assert np.array_equal(np.ctypeslib.as_array(L.b200_iscan(ts, tt), shape=(n,)), i)
+
+
+def test_no_gpu_fails_loudly():
+    import b200av1
+    if b200av1.lib().b200_device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(b200av1.B200Error) as e:
+        b200av1.Context(0)
+    assert "no CPU fallback" in str(e.value)

@@ -1,0 +1,155 @@
+"""GPU parity: fused transform + quantise (+ block error) through the C ABI vs the
+oracle, bit-exact.  Inputs replay the reference tests' distributions
+(test/av1_fwd_txfm2d_test.cc:243-297,518-576; test/quantize_func_test.cc:209-259)."""
+import numpy as np
+import pytest
+
+import harness as H
+import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import b200av1
+    c = b200av1.Context(0)
+    yield c
+    c.close()
+
+
+def _make_batch(rng, ts, n_per_type, bd, mode, qindexes):
+    import b200av1
+    W, Hh = H.TX_W[ts], H.TX_H[ts]
+    n = H.max_eob(ts)
+    types = [t for t in range(16) if H.tx_valid(ts, t)]
+    nb = n_per_type * len(types)
+    stride = W * 3 + 5  # deliberately odd pitch: blocks side by side with gaps
+    rows_per_block = Hh + 1
+    hi = (1 << bd) - 1
+    src = np.zeros(nb // 3 * rows_per_block * stride + rows_per_block * stride * 2 + 64, np.int16)
+    blocks = np.zeros(nb, b200av1.TXBLOCK_DTYPE)
+    for i in range(nb):
+        brow, bcol = divmod(i, 3)
+        off = brow * rows_per_block * stride + bcol * W + (i % 2)
+        blk = np.lib.stride_tricks.as_strided(src[off:], (Hh, W), (stride * 2, 2))
+        if mode == "max":
+            blk[:] = hi if i % 2 == 0 else -hi
+        elif mode == "small":
+            blk[:] = rng.integers(-40, 41, (Hh, W))
+        else:
+            blk[:] = rng.integers(-hi, hi + 1, (Hh, W))
+        blocks[i] = (off, i * n, stride, i % len(qindexes), ts, types[i % len(types)], 0)
+    rng.shuffle(blocks)  # tx types and offsets in arbitrary order
+    return src, blocks, nb * n
+
+
+CASES = [(8, "rand", 1), (8, "max", 1), (8, "small", 1), (10, "rand", 2), (12, "rand", 2),
+         (12, "max", 2), (8, "rand", 3), (10, "small", 4), (12, "rand", 4)]
+
+
+@pytest.mark.parametrize("ts", range(19), ids=H.TX_NAMES)
+def test_txq_all_types(ctx, ts):
+    import b200av1
+    rng = np.random.default_rng(1000 + ts)
+    qidx = [0, 1, 20, 60, 128, 200, 255]
+    for bd, mode, q_kind in CASES:
+        rows = [H.oracle_qrow(bd, q) for q in qidx]
+        qrows = np.array([b200av1.qrow_from_oracle(r) for r in rows], b200av1.QROW_DTYPE)
+        src, blocks, out_elems = _make_batch(rng, ts, 3 if H.TX_W[ts] * H.TX_H[ts] >= 1024 else 6,
+                                             bd, mode, qidx)
+        for fast in (0, b200av1.TXQ_FAST32):
+            coeff = np.full(out_elems, 123, np.int32)
+            qc = np.full(out_elems, 123, np.int32)
+            dq = np.full(out_elems, 123, np.int32)
+            eob = np.full(len(blocks), 9999, np.uint16)
+            dist = np.full((len(blocks), 2), -1, np.int64)
+            flags = b200av1.TXQ_STORE_COEFF | b200av1.TXQ_BLOCK_ERROR | fast
+            ctx.txq_batch_host(b200av1.IN_RESIDUAL, q_kind, bd, flags, blocks, None, src, None,
+                               qrows, coeff, qc, dq, eob, dist)
+            r = H.oracle_txq_batch(src, blocks, rows, q_kind, bd, out_elems)
+            tag = (H.TX_NAMES[ts], bd, mode, q_kind, fast)
+            assert np.array_equal(coeff, r[0]), tag
+            assert np.array_equal(qc, r[1]), tag
+            assert np.array_equal(dq, r[2]), tag
+            assert np.array_equal(eob, r[3]), tag
+            assert np.array_equal(dist, r[4]), tag
+
+
+def test_txq_transform_only_and_empty(ctx):
+    import b200av1
+    rng = np.random.default_rng(5)
+    src, blocks, out_elems = _make_batch(rng, 2, 2, 8, "rand", [0])
+    coeff = np.zeros(out_elems, np.int32)
+    ctx.txq_batch_host(b200av1.IN_RESIDUAL, b200av1.Q_NONE, 8, b200av1.TXQ_STORE_COEFF, blocks,
+                       None, src, None, None, coeff, None, None, None, None)
+    r = H.oracle_txq_batch(src, blocks, [], 0, 8, out_elems)
+    assert np.array_equal(coeff, r[0])
+    # empty batch is a no-op
+    ctx.txq_batch_host(b200av1.IN_RESIDUAL, b200av1.Q_NONE, 8, b200av1.TXQ_STORE_COEFF,
+                       blocks[:0], None, src, None, None, coeff, None, None, None, None)
+
+
+def test_txq_mixed_sizes_one_call(ctx):
+    """b200_txq_batch_host groups a ragged batch of mixed tx sizes into per-size launches"""
+    import b200av1
+    rng = np.random.default_rng(6)
+    parts, srcs, off_src, off_out = [], [], 0, 0
+    for ts in (0, 5, 1, 13, 2, 9, 3, 17, 4):
+        src, blocks, out_elems = _make_batch(rng, ts, 1, 8, "rand", [0, 1, 2])
+        blocks["src_offset"] += off_src
+        blocks["out_offset"] += off_out
+        off_src += len(src)
+        off_out += out_elems
+        parts.append(blocks)
+        srcs.append(src)
+    blocks = np.concatenate(parts)
+    rng.shuffle(blocks)
+    src = np.concatenate(srcs)
+    rows = [H.oracle_qrow(8, q) for q in (10, 90, 220)]
+    qrows = np.array([b200av1.qrow_from_oracle(r) for r in rows], b200av1.QROW_DTYPE)
+    coeff, qc, dq = (np.zeros(off_out, np.int32) for _ in range(3))
+    eob = np.zeros(len(blocks), np.uint16)
+    dist = np.zeros((len(blocks), 2), np.int64)
+    ctx.txq_batch_host(b200av1.IN_RESIDUAL, b200av1.Q_FP, 8,
+                       b200av1.TXQ_STORE_COEFF | b200av1.TXQ_BLOCK_ERROR, blocks, None, src, None,
+                       qrows, coeff, qc, dq, eob, dist)
+    r = H.oracle_txq_batch(src, blocks, rows, 1, 8, off_out)
+    for a, b in zip((coeff, qc, dq, eob, dist), r):
+        assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+def test_txq_fused_subtract_from_planes(ctx, bd):
+    """pixels in (src, pred planes) -> residual formed in-kernel (aom_subtract_block)"""
+    import b200av1
+    rng = np.random.default_rng(7 + bd)
+    w, h, stride = 192, 128, 224
+    srcp = np.zeros((h, stride), np.uint8 if bd == 8 else np.uint16)
+    srcp[:, :w] = synth.smooth_frame(rng, w, h, bd)
+    predp = np.zeros((h, stride + 32), srcp.dtype)
+    predp[:, :w] = synth.pred_from(rng, srcp[:, :w], bd)
+    src, pred = srcp.reshape(-1), predp.reshape(-1)
+    rows = [H.oracle_qrow(bd, q) for q in (40, 120)]
+    qrows = np.array([b200av1.qrow_from_oracle(r) for r in rows], b200av1.QROW_DTYPE)
+    for ts in (0, 1, 2, 3, 4, 7, 10, 12):
+        W, Hh, n = H.TX_W[ts], H.TX_H[ts], H.max_eob(ts)
+        offs = synth.tile_blocks(w, h, stride, W, Hh)
+        poffs = synth.tile_blocks(w, h, stride + 32, W, Hh)
+        types = [t for t in range(16) if H.tx_valid(ts, t)]
+        blocks = np.zeros(len(offs), b200av1.TXBLOCK_DTYPE)
+        preds = np.zeros(len(offs), b200av1.TXPRED_DTYPE)
+        for i in range(len(offs)):
+            blocks[i] = (offs[i], i * n, stride, i % 2, ts, types[i % len(types)], 0)
+            preds[i] = (poffs[i], stride + 32, 0)
+        out_elems = len(offs) * n
+        coeff, qc, dq = (np.zeros(out_elems, np.int32) for _ in range(3))
+        eob = np.zeros(len(blocks), np.uint16)
+        dist = np.zeros((len(blocks), 2), np.int64)
+        q_kind = b200av1.Q_FP if bd == 8 else b200av1.Q_FP_HBD
+        in_kind = b200av1.IN_PIXELS8 if bd == 8 else b200av1.IN_PIXELS16
+        ctx.txq_batch_host(in_kind, q_kind, bd, b200av1.TXQ_STORE_COEFF | b200av1.TXQ_BLOCK_ERROR,
+                           blocks, preds, src, pred, qrows, coeff, qc, dq, eob, dist)
+        r = H.oracle_txq_batch(src, blocks, rows, q_kind, bd, out_elems, in_kind, pred, preds)
+        for a, b in zip((coeff, qc, dq, eob, dist), r):
+            assert np.array_equal(a, b), (H.TX_NAMES[ts], bd)
