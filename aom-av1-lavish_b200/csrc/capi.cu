@@ -224,12 +224,11 @@ extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int b
   if (has_q)
     B200_CUDA_TRY(cudaMemcpyAsync(base + o_q, qrows, sizeof(B200QRow) * n_qrows,
                                   cudaMemcpyHostToDevice, s));
-  // outputs that the kernels do not fully cover keep the caller's bytes
-  if (want_coeff)
-    B200_CUDA_TRY(cudaMemcpyAsync(base + o_coeff, coeff, out_elems * 4, cudaMemcpyHostToDevice, s));
+  // regions of the output buffers that no block covers read back as zero
+  if (want_coeff) B200_CUDA_TRY(cudaMemsetAsync(base + o_coeff, 0, out_elems * 4, s));
   if (has_q) {
-    B200_CUDA_TRY(cudaMemcpyAsync(base + o_qc, qcoeff, out_elems * 4, cudaMemcpyHostToDevice, s));
-    B200_CUDA_TRY(cudaMemcpyAsync(base + o_dq, dqcoeff, out_elems * 4, cudaMemcpyHostToDevice, s));
+    B200_CUDA_TRY(cudaMemsetAsync(base + o_qc, 0, out_elems * 4, s));
+    B200_CUDA_TRY(cudaMemsetAsync(base + o_dq, 0, out_elems * 4, s));
   }
   for (int i = 0; i < n_blocks;) {
     int j = i;

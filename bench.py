@@ -1,0 +1,493 @@
+#!/usr/bin/env python3
+"""bench.py -- headline benchmark of the B200 AV1 hot path (BASELINE.json configs[1]).
+
+Workload ("txq_sweep_1080p_8bit"): a batch of F synthetic 1080p 8-bit 4:2:0 frames
+(int16 residual planes = source - prediction, seeded) goes through the fused
+forward-transform + quantize_fp kernel once for EACH of the 19 AV1 transform sizes
+(every plane tiled with WxH blocks, tx_type drawn per block from the valid set, qindex
+drawn per block from {0,32,96,160,255}).  One step = 19 launches = 19*F frame
+equivalents (FE, 3 110 400 samples each).  Inputs are resident in HBM for `value`;
+`e2e` runs the same sweep through the host-buffer C-ABI call (H2D + D2H inside).
+
+Contract: python bench.py --gpus N --steps K --warmup W   (torchrun for N > 1)
+prints ONE JSON line on rank 0.  `--impl reference` times the reference's own C
+functions (oracle/_ref) on the host cores instead.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "aom-av1-lavish_b200", "python"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+FE_SAMPLES = 1920 * 1080 * 3 // 2
+TX_W = [4, 8, 16, 32, 64, 4, 8, 8, 16, 16, 32, 32, 64, 4, 16, 8, 32, 16, 64]
+TX_H = [4, 8, 16, 32, 64, 8, 4, 16, 8, 32, 16, 64, 32, 16, 4, 32, 8, 64, 16]
+VTX = [0, 1, 0, 1, 2, 0, 2, 1, 2, 3, 0, 3, 1, 3, 2, 3]
+HTX = [0, 0, 1, 1, 0, 2, 2, 2, 1, 3, 3, 0, 3, 1, 3, 2]
+QINDEXES = [0, 32, 96, 160, 255]
+
+TXBLOCK_DTYPE = np.dtype([("src_offset", "<u4"), ("out_offset", "<u4"), ("src_stride", "<u2"),
+                          ("qrow", "<u2"), ("tx_size", "u1"), ("tx_type", "u1"),
+                          ("reserved", "<u2")])
+
+
+def valid_types(ts):
+    out = []
+    for tt in range(16):
+        ok = True
+        for dim, kind in ((TX_H[ts], VTX[tt]), (TX_W[ts], HTX[tt])):
+            if dim == 64 and kind != 0:
+                ok = False
+            if dim == 32 and kind in (1, 2):
+                ok = False
+        if ok:
+            out.append(tt)
+    return out
+
+
+def max_eob(ts):
+    return min(TX_W[ts], 32) * min(TX_H[ts], 32)
+
+
+def make_residual_frames(n_frames, seed):
+    """int16 residual of a 1080p 4:2:0 frame: planes Y 1920x1080, U, V 960x540 stored
+    back to back (strides = widths).  Smooth source, prediction = shifted source + noise."""
+    import synth
+    rng = np.random.default_rng(seed)
+    planes = [(1920, 1080), (960, 540), (960, 540)]
+    frame_elems = sum(w * h for w, h in planes)
+    out = np.zeros((n_frames, frame_elems), np.int16)
+    base = []
+    for (w, h) in planes:
+        s = synth.smooth_frame(rng, w, h, 8)
+        base.append(s)
+    for f in range(n_frames):
+        o = 0
+        for (w, h), s in zip(planes, base):
+            src = np.roll(s, (f * 2, f * 3), (0, 1))
+            pred = synth.pred_from(rng, src, 8)
+            out[f, o:o + w * h] = (src.astype(np.int16) - pred.astype(np.int16)).reshape(-1)
+            o += w * h
+    return out, planes
+
+
+def make_descriptors(ts, n_frames, planes, frame_elems, seed):
+    """all blocks of size ts tiling every plane of every frame; sorted by tx_type so that
+    the lanes of a warp share one code path (the batch queue's job)."""
+    rng = np.random.default_rng(seed * 100 + ts)
+    W, Hh = TX_W[ts], TX_H[ts]
+    offs, strides, planes_id = [], [], []
+    o = 0
+    for pi, (w, h) in enumerate(planes):
+        xs = np.arange(w // W) * W
+        ys = np.arange(h // Hh) * Hh
+        po = (o + ys[:, None] * w + xs[None, :]).reshape(-1)
+        offs.append(po)
+        strides.append(np.full(po.size, w))
+        planes_id.append(np.full(po.size, pi))
+        o += w * h
+    offs = np.concatenate(offs)
+    strides = np.concatenate(strides)
+    planes_id = np.concatenate(planes_id)
+    per_frame = offs.size
+    n = per_frame * n_frames
+    blocks = np.zeros(n, TXBLOCK_DTYPE)
+    blocks["src_offset"] = (offs[None, :] + (np.arange(n_frames) * frame_elems)[:, None]).reshape(-1)
+    blocks["src_stride"] = np.tile(strides, n_frames)
+    vt = np.array(valid_types(ts), np.uint8)
+    blocks["tx_type"] = vt[rng.integers(0, vt.size, n)]
+    blocks["tx_size"] = ts
+    # quantiser row = plane * 5 + qindex slot
+    blocks["qrow"] = np.tile(planes_id, n_frames) * len(QINDEXES) + rng.integers(0, len(QINDEXES), n)
+    order = np.argsort(blocks["tx_type"], kind="stable")
+    blocks = blocks[order]
+    blocks["out_offset"] = np.arange(n, dtype=np.uint64) * max_eob(ts)
+    samples = n * W * Hh
+    return blocks, samples
+
+
+def algorithmic_bytes(ts, n_blocks):
+    """int16 in + coeff/qcoeff/dqcoeff int32 out (kept region) + eob"""
+    return n_blocks * (TX_W[ts] * TX_H[ts] * 2 + max_eob(ts) * 12 + 2)
+
+
+class ClockSampler:
+    """nvidia-smi clocks during the timed region (B200_PROFILING.md clocks line)"""
+
+    def __init__(self, gpu):
+        self.gpu = gpu
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._read, daemon=True)
+            self.thr.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 7:
+                continue
+            try:
+                sm.append(float(p[0]))
+                smax = float(p[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, p[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------- CPU arm ----
+def load_cpu_libs():
+    import harness as H
+    O = H.oracle()
+    R = H.ref()
+    return H, O, R
+
+
+def cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed, n_threads, sizes=range(19),
+                  keep_outputs=False):
+    """One frame per size through the CPU path.  Returns (seconds, samples, outputs)."""
+    rows = (H.QRow * (3 * len(QINDEXES)))()
+    for pl in range(3):
+        for qi, q in enumerate(QINDEXES):
+            O.av1o_build_qrow(8, q, pl, 0, C.byref(rows[pl * len(QINDEXES) + qi]))
+    total_t, total_samples, outs = 0.0, 0, {}
+    src = np.ascontiguousarray(frames[:1].reshape(-1))
+    for ts in sizes:
+        blocks, samples = make_descriptors(ts, 1, planes, frame_elems, seed)
+        n = blocks.size
+        ne = n * max_eob(ts)
+        coeff = np.zeros(ne, np.int32)
+        qc = np.zeros(ne, np.int32)
+        dq = np.zeros(ne, np.int32)
+        eob = np.zeros(n, np.uint16)
+        if R is not None:
+            fwd = C.cast(getattr(R, "av1_fwd_txfm2d_%dx%d_c" % (TX_W[ts], TX_H[ts])), C.c_void_p)
+            ls = H.log_scale(ts)
+            qn = ["av1_quantize_fp_c", "av1_quantize_fp_32x32_c", "av1_quantize_fp_64x64_c"][ls]
+            quant = C.cast(getattr(R, qn), C.c_void_p)
+        else:
+            fwd, quant = None, None
+        t0 = time.perf_counter()
+        O.av1o_drv_txq_fp(fwd, quant, 0, 8, ts, C.c_void_p(blocks.ctypes.data), n,
+                          C.c_void_p(src.ctypes.data), rows, C.c_void_p(coeff.ctypes.data),
+                          C.c_void_p(qc.ctypes.data), C.c_void_p(dq.ctypes.data),
+                          C.c_void_p(eob.ctypes.data), n_threads)
+        total_t += time.perf_counter() - t0
+        total_samples += samples
+        if keep_outputs:
+            outs[ts] = (blocks, coeff, qc, dq, eob)
+    return total_t, total_samples, outs
+
+
+def build_qrows_product():
+    """3 planes x 5 qindexes, all delta_q = 0 (av1_build_quantizer, av1_quantize.c:602)"""
+    import b200av1
+    import harness as H
+    rows = []
+    for pl in range(3):
+        for q in QINDEXES:
+            rows.append(b200av1.qrow_from_oracle(H.oracle_qrow(8, q, pl)))
+    return np.array(rows, b200av1.QROW_DTYPE)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--frames", type=int, default=32, help="frames per rank per launch")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--fast32", action="store_true", help="all-32-bit butterflies (DESIGN.md)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--sizes", default="", help="comma list of tx sizes (debug)")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    sizes = [int(s) for s in args.sizes.split(",")] if args.sizes else list(range(19))
+    seed = 2001
+    metric = "1080p frame-equiv/s for txfm+quant+ME SAD; HBM GB/s as % of B200 peak"
+    config = {"workload": "txq_sweep_1080p_8bit: fused fwd txfm + quantize_fp over all %d TX sizes, "
+                          "%d synthetic 1080p 4:2:0 frames per GPU per launch" % (len(sizes), args.frames),
+              "frames_per_gpu": args.frames, "tx_sizes": len(sizes), "quantizer": "av1_quantize_fp",
+              "qindex_set": QINDEXES, "l2": "inputs (%.0f MB/GPU) larger than L2; outputs streamed"
+                                            % (args.frames * FE_SAMPLES * 2 / 1e6),
+              "parallelism": "frames sharded over %d GPU(s), no collective" % world,
+              "butterflies": "fast32" if args.fast32 else "exact64"}
+
+    # ----------------------------------------------------------- reference arm
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        H, O, R = load_cpu_libs()
+        frames, planes = make_residual_frames(1, seed)
+        frame_elems = frames.shape[1]
+        n_threads = os.cpu_count() or 1
+        for _ in range(min(args.warmup, 1)):
+            cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed, n_threads, sizes)
+        tt, ss = 0.0, 0
+        for _ in range(args.steps):
+            t, s, _o = cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed, n_threads, sizes)
+            tt += t
+            ss += s
+        val = ss / FE_SAMPLES / tt
+        kind = "reference" if R is not None else "port"
+        line = {"impl": "reference", "metric": metric, "value": val, "unit": "1080p frame-equiv/s",
+                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": tt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "int32", "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": val, "unit": "1080p frame-equiv/s", "cores": n_threads,
+                                 "kind": kind,
+                                 "sample": "per step: 1 frame x %d TX sizes (%.1f FE) through "
+                                           "av1_fwd_txfm2d_*_c + av1_quantize_fp*_c"
+                                           % (len(sizes), ss / args.steps / FE_SAMPLES)},
+                "e2e": {"value": val, "unit": "1080p frame-equiv/s", "h2d_bytes_per_step": 0,
+                        "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    # ---------------------------------------------------------------- b200 arm
+    import torch
+    import b200av1
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    ctx = b200av1.Context(local_rank)
+    stream = torch.cuda.Stream(device=dev)
+
+    frames, planes = make_residual_frames(args.frames, seed + rank)
+    frame_elems = frames.shape[1]
+    d_src = torch.from_numpy(frames.reshape(-1)).to(dev)
+    qrows = build_qrows_product()
+    d_qrows = torch.from_numpy(qrows.view(np.uint8)).to(dev)
+    launches, keep = [], []
+    max_out = 0
+    total_samples, total_bytes = 0, 0
+    per_size = []
+    for ts in sizes:
+        blocks, samples = make_descriptors(ts, args.frames, planes, frame_elems, seed + rank)
+        max_out = max(max_out, blocks.size * max_eob(ts))
+        d_blocks = torch.from_numpy(blocks.view(np.uint8)).to(dev)
+        d_eob = torch.zeros(blocks.size, dtype=torch.int16, device=dev)
+        keep += [d_blocks, d_eob]
+        per_size.append({"ts": ts, "n_blocks": int(blocks.size), "samples": int(samples),
+                         "bytes": int(algorithmic_bytes(ts, blocks.size)), "d_blocks": d_blocks,
+                         "d_eob": d_eob})
+        total_samples += samples
+        total_bytes += algorithmic_bytes(ts, blocks.size)
+    d_coeff = torch.empty(max_out, dtype=torch.int32, device=dev)
+    d_qc = torch.empty(max_out, dtype=torch.int32, device=dev)
+    d_dq = torch.empty(max_out, dtype=torch.int32, device=dev)
+    flags = b200av1.TXQ_STORE_COEFF | (b200av1.TXQ_FAST32 if args.fast32 else 0)
+    for ps in per_size:
+        l = b200av1.TxqLaunch()
+        l.tx_size, l.in_kind, l.q_kind, l.bd, l.flags = ps["ts"], 0, b200av1.Q_FP, 8, flags
+        l.n_blocks = ps["n_blocks"]
+        l.blocks = ps["d_blocks"].data_ptr()
+        l.src = d_src.data_ptr()
+        l.qrows = d_qrows.data_ptr()
+        l.coeff, l.qcoeff, l.dqcoeff = d_coeff.data_ptr(), d_qc.data_ptr(), d_dq.data_ptr()
+        l.eob = ps["d_eob"].data_ptr()
+        launches.append(l)
+    sptr = stream.cuda_stream
+
+    def step(events=None):
+        for i, l in enumerate(launches):
+            if events is not None:
+                events[i].record(stream)
+            ctx.txq_launch(l, sptr)
+        if events is not None:
+            events[len(launches)].record(stream)
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    with torch.cuda.stream(stream):
+        for _ in range(args.warmup):
+            step()
+    barrier()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(launches) + 1)]
+          for _ in range(args.steps)]
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    for k in range(args.steps):
+        step(ev[k])
+    barrier()
+    clocks = sampler.stop()
+    step_ms = [ev[k][0].elapsed_time(ev[k][len(launches)]) for k in range(args.steps)]
+    total_ms = ev[0][0].elapsed_time(ev[args.steps - 1][len(launches)])
+    kern_ms = np.zeros(len(launches))
+    for k in range(args.steps):
+        for i in range(len(launches)):
+            kern_ms[i] += ev[k][i].elapsed_time(ev[k][i + 1])
+    kern_ms /= args.steps
+    t_local = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_local, op=dist.ReduceOp.MAX)
+    total_ms_max = float(t_local.item())
+    fe_per_step_rank = total_samples / FE_SAMPLES
+    value = fe_per_step_rank * world * args.steps / (total_ms_max / 1e3)
+
+    # ---- e2e: the same sweep through the host-buffer C-ABI call (1 frame / step)
+    e2e = None
+    if args.e2e_steps > 0:
+        eb, e_samples = [], 0
+        out_off = 0
+        for ts in sizes:
+            b, s = make_descriptors(ts, 1, planes, frame_elems, seed + rank)
+            b["out_offset"] += out_off
+            out_off += b.size * max_eob(ts)
+            eb.append(b)
+            e_samples += s
+        eblocks = np.concatenate(eb)
+        lib = b200av1.lib()
+
+        def pinned(nbytes, dtype):
+            p = C.c_void_p()
+            b200av1.check(lib.b200_malloc_host(C.c_size_t(nbytes), C.byref(p)))
+            n = nbytes // np.dtype(dtype).itemsize
+            return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(nbytes,)).view(dtype)[:n], p
+
+        h_src, p1 = pinned(frame_elems * 2, np.int16)
+        h_src[:] = frames[0]
+        h_coeff, p2 = pinned(out_off * 4, np.int32)
+        h_qc, p3 = pinned(out_off * 4, np.int32)
+        h_dq, p4 = pinned(out_off * 4, np.int32)
+        h_eob = np.zeros(eblocks.size, np.uint16)
+
+        def e2e_step():
+            ctx.txq_batch_host(0, b200av1.Q_FP, 8, flags, eblocks, None, h_src, None, qrows,
+                               h_coeff, h_qc, h_dq, h_eob, None)
+
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            e2e_step()
+        torch.cuda.synchronize(dev)
+        dt = time.perf_counter() - t0
+        t_e = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
+        e2e = {"value": e_samples / FE_SAMPLES * world * args.e2e_steps / float(t_e.item()),
+               "unit": "1080p frame-equiv/s",
+               "h2d_bytes_per_step": int(frame_elems * 2 + eblocks.nbytes + qrows.nbytes),
+               "d2h_bytes_per_step": int(out_off * 12 + eblocks.size * 2),
+               "note": "b200_txq_batch_host: pinned host buffers, 1 frame x %d sizes per step, "
+                       "descriptor sort + H2D + 19 launches + D2H inside the timed region" % len(sizes)}
+        for p in (p1, p2, p3, p4):
+            pass  # pinned buffers live until process exit
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = total_bytes / (kern_ms.sum() / 1e3) / 1e9
+    kernels = []
+    for ps, ms in zip(per_size, kern_ms):
+        kernels.append({"tx": "%dx%d" % (TX_W[ps["ts"]], TX_H[ps["ts"]]), "ms": round(float(ms), 4),
+                        "GBps": round(ps["bytes"] / (ms / 1e3) / 1e9, 1),
+                        "frac": round(ps["bytes"] / (ms / 1e3) / 1e9 / peak, 3)})
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        try:
+            traffic = json.load(open(tp)).get("txq_kernel_dram_bytes_per_launch")
+        except (OSError, ValueError):
+            traffic = None
+    line = {"metric": metric, "value": value, "unit": "1080p frame-equiv/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms_max / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
+            "data": "synthetic", "config": config, "clocks": clocks,
+            "gpu_launches": len(launches) * args.steps,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+                         "kernel": "txq_kernel<W,H> (19 instances, one launch each per step); "
+                                   "algorithmic bytes = 2 B/sample in + 12 B/kept coeff out + 2 B/block",
+                         "bytes_per_step": int(total_bytes)},
+            "kernels": kernels, "e2e": e2e,
+            "step_ms_min_max": [float(min(step_ms)), float(max(step_ms))]}
+
+    # ---- cpu_baseline (rank 0, N = 1 only) + full-size parity of frame 0
+    if world == 1 and not args.no_cpu:
+        H, O, R = load_cpu_libs()
+        n_threads = os.cpu_count() or 1
+        t, s, outs = cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed + rank, n_threads,
+                                   sizes, keep_outputs=True)
+        line["cpu_baseline"] = {"value": s / FE_SAMPLES / t, "unit": "1080p frame-equiv/s",
+                                "cores": n_threads, "kind": "reference" if R is not None else "port",
+                                "sample": "1 frame x %d TX sizes (%.1f FE), av1_fwd_txfm2d_*_c + "
+                                          "av1_quantize_fp*_c on %d host threads"
+                                          % (len(sizes), s / FE_SAMPLES, n_threads)}
+        # parity at full size: GPU (host-buffer call, frame 0) vs CPU outputs, bit-exact
+        ok = True
+        for ts in sizes:
+            blocks, coeff, qc, dq, eob = outs[ts]
+            g = [np.zeros_like(coeff), np.zeros_like(qc), np.zeros_like(dq), np.zeros_like(eob)]
+            ctx.txq_batch_host(0, b200av1.Q_FP, 8, flags, blocks, None,
+                               np.ascontiguousarray(frames[0]), None, qrows, g[0], g[1], g[2], g[3],
+                               None)
+            ok = ok and all(np.array_equal(a, b) for a, b in zip(g, (coeff, qc, dq, eob)))
+        line["parity_full_frame"] = "bit-exact" if ok else "MISMATCH"
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

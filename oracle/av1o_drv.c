@@ -1,0 +1,150 @@
+/*
+ * av1o_drv.c -- ORACLE / CPU-BASELINE DRIVER (test infrastructure only).
+ *
+ * Runs a batch of same-size transform blocks through "forward transform, then
+ * quantize_fp" on the host CPU with a pthread pool, calling through FUNCTION POINTERS
+ * so that the same driver times either the reference's own C functions
+ * (oracle/_ref/libaomref.so: av1_fwd_txfm2d_WxH_c + av1_quantize_fp*_c /
+ * av1_highbd_quantize_fp_c) or this oracle's restatement.  It is what bench.py's
+ * `cpu_baseline` leg and `--impl reference` arm execute; the product never links it.
+ */
+#include <pthread.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "av1o.h"
+
+typedef void (*fwd_txfm_fn)(const int16_t *input, int32_t *output, int stride,
+                            uint8_t tx_type, int bd);
+/* av1_quantize_fp_c family: 12 arguments; av1_highbd_quantize_fp_c: + log_scale */
+typedef void (*quant_fp_fn)(const int32_t *coeff, intptr_t n, const int16_t *zbin,
+                            const int16_t *round, const int16_t *quant,
+                            const int16_t *quant_shift, int32_t *qcoeff, int32_t *dqcoeff,
+                            const int16_t *dequant, uint16_t *eob, const int16_t *scan,
+                            const int16_t *iscan);
+typedef void (*quant_fp_hbd_fn)(const int32_t *coeff, intptr_t n, const int16_t *zbin,
+                                const int16_t *round, const int16_t *quant,
+                                const int16_t *quant_shift, int32_t *qcoeff,
+                                int32_t *dqcoeff, const int16_t *dequant, uint16_t *eob,
+                                const int16_t *scan, const int16_t *iscan, int log_scale);
+
+typedef struct {
+  uint32_t src_offset, out_offset;
+  uint16_t src_stride, qrow;
+  uint8_t tx_size, tx_type;
+  uint16_t reserved;
+} DrvBlock; /* same layout as B200TxBlock */
+
+typedef struct {
+  fwd_txfm_fn fwd;
+  void *quant;
+  int highbd, log_scale, bd, n_coeffs, full_coeffs;
+  const DrvBlock *blocks;
+  int n_blocks;
+  const int16_t *src;
+  const Av1oQRow *rows;
+  const int16_t *scan[3], *iscan[3];
+  int32_t *coeff, *qcoeff, *dqcoeff;
+  uint16_t *eob;
+  int tid, n_threads;
+} DrvJob;
+
+static void *drv_worker(void *arg) {
+  DrvJob *j = (DrvJob *)arg;
+  /* the reference transform uses its output as scratch for the full W*H block */
+  int32_t *tmp = (int32_t *)malloc(sizeof(int32_t) * (size_t)(j->full_coeffs + 64));
+  const int per = (j->n_blocks + j->n_threads - 1) / j->n_threads;
+  const int lo = j->tid * per, hi = lo + per > j->n_blocks ? j->n_blocks : lo + per;
+  for (int i = lo; i < hi; ++i) {
+    const DrvBlock *b = &j->blocks[i];
+    const int cls = b->tx_type < 10 ? 0 : ((b->tx_type & 1) ? 2 : 1);
+    const Av1oQRow *r = &j->rows[b->qrow];
+    int32_t *c = j->coeff + b->out_offset;
+    j->fwd(j->src + b->src_offset, tmp, b->src_stride, b->tx_type, j->bd);
+    memcpy(c, tmp, sizeof(int32_t) * (size_t)j->n_coeffs);
+    if (j->highbd)
+      ((quant_fp_hbd_fn)j->quant)(c, j->n_coeffs, r->zbin, r->round_fp, r->quant_fp,
+                                  r->quant_shift, j->qcoeff + b->out_offset,
+                                  j->dqcoeff + b->out_offset, r->dequant, &j->eob[i],
+                                  j->scan[cls], j->iscan[cls], j->log_scale);
+    else
+      ((quant_fp_fn)j->quant)(c, j->n_coeffs, r->zbin, r->round_fp, r->quant_fp,
+                              r->quant_shift, j->qcoeff + b->out_offset,
+                              j->dqcoeff + b->out_offset, r->dequant, &j->eob[i],
+                              j->scan[cls], j->iscan[cls]);
+  }
+  free(tmp);
+  return NULL;
+}
+
+/* adapters so that the oracle's own functions fit the reference prototypes */
+static int g_oracle_tx_size;
+static void oracle_fwd(const int16_t *input, int32_t *output, int stride, uint8_t tx_type,
+                       int bd) {
+  av1o_fwd_txfm2d(input, output, stride, g_oracle_tx_size, tx_type, bd);
+}
+static void oracle_qfp_hbd(const int32_t *coeff, intptr_t n, const int16_t *zbin,
+                           const int16_t *round, const int16_t *quant,
+                           const int16_t *quant_shift, int32_t *qcoeff, int32_t *dqcoeff,
+                           const int16_t *dequant, uint16_t *eob, const int16_t *scan,
+                           const int16_t *iscan, int log_scale) {
+  av1o_highbd_quantize_fp(coeff, n, zbin, round, quant, quant_shift, qcoeff, dqcoeff, dequant,
+                          eob, scan, iscan, NULL, NULL, log_scale);
+}
+static int g_oracle_ls;
+static void oracle_qfp(const int32_t *coeff, intptr_t n, const int16_t *zbin,
+                       const int16_t *round, const int16_t *quant, const int16_t *quant_shift,
+                       int32_t *qcoeff, int32_t *dqcoeff, const int16_t *dequant,
+                       uint16_t *eob, const int16_t *scan, const int16_t *iscan) {
+  av1o_quantize_fp(coeff, n, zbin, round, quant, quant_shift, qcoeff, dqcoeff, dequant, eob,
+                   scan, iscan, NULL, NULL, g_oracle_ls);
+}
+
+/* fwd / quant == NULL selects the oracle's own restatement. */
+int av1o_drv_txq_fp(void *fwd, void *quant, int highbd, int bd, int tx_size,
+                    const DrvBlock *blocks, int n_blocks, const int16_t *src,
+                    const Av1oQRow *rows, int32_t *coeff, int32_t *qcoeff, int32_t *dqcoeff,
+                    uint16_t *eob, int n_threads) {
+  if (n_threads < 1) n_threads = 1;
+  if (n_threads > 256) n_threads = 256;
+  const int pels = av1o_tx_wide(tx_size) * av1o_tx_high(tx_size);
+  const int ls = (pels > 256) + (pels > 1024);
+  g_oracle_tx_size = tx_size;
+  g_oracle_ls = ls;
+  DrvJob proto;
+  memset(&proto, 0, sizeof(proto));
+  proto.fwd = fwd ? (fwd_txfm_fn)fwd : oracle_fwd;
+  proto.quant = quant ? quant : (highbd ? (void *)oracle_qfp_hbd : (void *)oracle_qfp);
+  proto.highbd = highbd;
+  proto.log_scale = ls;
+  proto.bd = bd;
+  proto.n_coeffs = av1o_max_eob(tx_size);
+  proto.full_coeffs = pels;
+  proto.blocks = blocks;
+  proto.n_blocks = n_blocks;
+  proto.src = src;
+  proto.rows = rows;
+  for (int cls = 0; cls < 3; ++cls) {
+    const int tt = cls == 0 ? 0 : (cls == 1 ? 10 : 11);
+    proto.scan[cls] = av1o_scan(tx_size, tt);
+    proto.iscan[cls] = av1o_iscan(tx_size, tt);
+  }
+  proto.coeff = coeff;
+  proto.qcoeff = qcoeff;
+  proto.dqcoeff = dqcoeff;
+  proto.eob = eob;
+  proto.n_threads = n_threads;
+  DrvJob *jobs = (DrvJob *)malloc(sizeof(DrvJob) * (size_t)n_threads);
+  pthread_t *th = (pthread_t *)malloc(sizeof(pthread_t) * (size_t)n_threads);
+  for (int t = 0; t < n_threads; ++t) {
+    jobs[t] = proto;
+    jobs[t].tid = t;
+    if (t > 0) pthread_create(&th[t], NULL, drv_worker, &jobs[t]);
+  }
+  drv_worker(&jobs[0]);
+  for (int t = 1; t < n_threads; ++t) pthread_join(th[t], NULL);
+  free(jobs);
+  free(th);
+  return 0;
+}
