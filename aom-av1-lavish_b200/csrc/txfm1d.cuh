@@ -21,10 +21,10 @@ namespace b200 {
 
 // cos(j*pi/128) * 2^bit for bit = 10..13 and the negated values (so that a negative
 // weight is also a plain constant-bank operand), plus the ADST4 sine table.
-// (defined here: include this header from exactly one translation unit)
-__constant__ int32_t c_cospi[4][64];
-__constant__ int32_t c_ncospi[4][64];
-__constant__ int32_t c_sinpi[4][5];
+// (one private copy per translation unit; each TU uploads its own, see txq_inst.cuh)
+static __constant__ int32_t c_cospi[4][64];
+static __constant__ int32_t c_ncospi[4][64];
+static __constant__ int32_t c_sinpi[4][5];
 
 __host__ __device__ constexpr int cx_log2(int n) { return n <= 1 ? 0 : 1 + cx_log2(n >> 1); }
 __host__ __device__ constexpr int cx_bitrev(int v, int bits) {

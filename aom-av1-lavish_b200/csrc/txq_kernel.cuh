@@ -1,0 +1,577 @@
+// txq_kernel.cuh -- fused (subtract +) forward 2-D transform (+ quantise) (+ block error)
+// kernel, version 2.
+//
+// Replaces, for a whole batch of same-size transform blocks in one launch, the
+// reference's per-block chain
+//   aom_subtract_block        aom_dsp/subtract.c:20
+//   av1_fwd_txfm2d_WxH        av1/encoder/av1_fwd_txfm2d.c:56-312
+//   av1_quantize_fp* / aom_quantize_b* (+highbd)   av1/encoder/av1_quantize.c:36-264,
+//                                                  aom_dsp/quantize.c:108-316
+//   av1_block_error / av1_highbd_block_error       av1/encoder/rdopt.c:635-682
+//
+// Mapping: a transform block is owned by NT <= 32 lanes of ONE
+// warp; a warp works on BPW = 32/NT blocks ("a tile") at a time and strides over the
+// tiles of the launch (persistent grid).  Per tile:
+//   1. input rows arrive in shared memory through cp.async (16/8/4-byte chunks, one
+//      address computation per chunk, ring of S stages filled S-1 tiles ahead; the
+//      upside-down flip of FLIPADST columns is applied by the copy);
+//   2. lane c reads column c with immediate-offset LDS and runs the whole H-point
+//      column transform in registers;
+//   3. the column results cross to row ownership through a padded per-warp int32 tile
+//      (__syncwarp only -- there is no CTA-wide barrier in this kernel);
+//   4. lane r reads row r with LDS.128, runs the W-point row transform, quantises its
+//      W coefficients in registers and stores coeff / qcoeff / dqcoeff -- which the
+//      codec keeps column-major, i.e. lane-contiguous -- with coalesced 32-bit stores;
+//   5. eob and the error sums are shuffle-reduced over the block's lanes.
+// Arithmetic: butterflies use the 3-instruction all-32-bit form when every residual of
+// the warp's tile satisfies |x| <= kGuard (proved exact by tools/range_proof.py), and
+// the literal 64-bit-sum form of half_btf otherwise; results are bit-identical to the
+// reference either way.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string.h>
+
+#include "internal.h"
+#include "txfm1d.cuh"
+
+namespace b200 {
+
+__host__ __device__ constexpr int cx_min(int a, int b) { return a < b ? a : b; }
+__host__ __device__ constexpr int cx_max(int a, int b) { return a > b ? a : b; }
+__host__ __device__ constexpr int cx_round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+constexpr int kGuard = 4094;  // tools/range_proof.py: fast butterflies exact for |x| <= 4094
+constexpr int kWarpsPerCta = 4;
+
+// ---------------------------------------------------------------- configuration --
+// av1_fwd_txfm_shift_ls (av1_fwd_txfm2d.c:314-340): shift[0] is an up-shift, shift[1]
+// and shift[2] are rounding down-shifts; stored here as non-negative amounts.
+template <int W, int H>
+struct TxCfg {
+  static constexpr int kPels = W * H;
+  static constexpr int kMaxDim = cx_max(W, H), kMinDim = cx_min(W, H);
+  static constexpr int kUp =
+      (kMaxDim == 64 && !(W == 64 && H == 32) && !(W == 64 && H == 16)) ? 0 : 2;
+  static constexpr int kDown1 =
+      (W == 4 && H == 4)                                   ? 0
+      : (kMaxDim == 64 && kUp == 0)                        ? 2 /* 64x64 32x64 16x64 */
+      : (W == 64)                                          ? 4 /* 64x32 64x16 */
+      : (kMaxDim == 8 || (kMaxDim == 16 && kMinDim == 4))  ? 1
+      : (kMaxDim == 16 || (kMaxDim == 32 && kMinDim == 8)) ? 2
+                                                           : 4; /* 32x32 16x32 32x16 */
+  static constexpr int kDown2 =
+      ((W == 64 && H == 64) || (W == 32 && H == 64) || (W == 64 && H == 32)) ? 2 : 0;
+  static constexpr bool kRect = (W == 2 * H) || (H == 2 * W);
+  static constexpr int kLogScale = (kPels > 256) + (kPels > 1024);
+  // av1_fwd_cos_bit_col/_row[log2(W)-2][log2(H)-2] (av1_fwd_txfm2d.c:342-358)
+  static constexpr int cosbit_col() {
+    constexpr int8_t t[5][5] = { { 13, 13, 13, 0, 0 }, { 13, 13, 13, 12, 0 }, { 13, 13, 13, 12, 13 },
+                                 { 0, 13, 13, 12, 13 }, { 0, 0, 13, 12, 13 } };
+    return t[cx_log2(W) - 2][cx_log2(H) - 2];
+  }
+  static constexpr int cosbit_row() {
+    constexpr int8_t t[5][5] = { { 13, 13, 12, 0, 0 }, { 13, 13, 13, 12, 0 }, { 13, 13, 12, 13, 12 },
+                                 { 0, 12, 13, 12, 11 }, { 0, 0, 12, 11, 10 } };
+    return t[cx_log2(W) - 2][cx_log2(H) - 2];
+  }
+  static constexpr int kCosCol = cosbit_col(), kCosRow = cosbit_row();
+
+  // kept region and lane mapping
+  static constexpr int Wk = cx_min(W, 32), Hk = cx_min(H, 32);
+  static constexpr int CW = cx_min(W, 32);   // columns handled per column iteration
+  static constexpr int CI = W / CW;          // column iterations (2 for 64-wide)
+  static constexpr int NT = cx_max(CW, Hk);  // lanes per transform block
+  static constexpr int BPW = 32 / NT;        // transform blocks per warp ("tile")
+  // transpose tile (int32): pitch = 4 (mod 8) words -> LDS.128 row reads and the
+  // column-wise STS are both bank-conflict free
+  static constexpr int LDX = W == 4 ? 4 : W + 4;
+  static constexpr int XS = BPW > 1 ? cx_round_up(Hk * LDX, 32) + CW : Hk * LDX;  // words / slot
+};
+
+// Input staging geometry for element size ESZ (2: int16 residual / uint16 pixels, 1: uint8)
+template <int W, int H, int ESZ>
+struct StageCfg {
+  using C = TxCfg<W, H>;
+  static constexpr int kRowBytes = W * ESZ;
+  static constexpr int kChunk = cx_min(16, kRowBytes);        // bytes per cp.async
+  static constexpr int kCpr = kRowBytes / kChunk;             // chunks per row
+  static constexpr int kCpb = H * kCpr;                       // chunks per block
+  static constexpr int kChunksPerTile = C::BPW * kCpb;
+  static constexpr int kCpl = (kChunksPerTile + 31) / 32;     // chunks per lane
+  static constexpr int kTileBytes = H * kRowBytes;
+  // slot pitch: distinct banks for the column reads of the BPW slots of a warp
+  static constexpr int kSlotBytes =
+      C::BPW > 1 ? cx_round_up(kTileBytes, 128) + C::NT * ESZ : cx_round_up(kTileBytes, 16);
+  static constexpr int kPlaneBytes = C::BPW * kSlotBytes;     // one operand, all slots
+};
+
+template <int W, int H, int IN>
+struct SmemCfg {
+  using C = TxCfg<W, H>;
+  static constexpr int ESZ = IN == B200_IN_PIXELS8 ? 1 : 2;
+  using S = StageCfg<W, H, ESZ>;
+  static constexpr int kOperands = IN == B200_IN_RESIDUAL ? 1 : 2;  // src (+ pred)
+  static constexpr int kStageBytes = cx_round_up(kOperands * S::kPlaneBytes, 16);
+  // deeper prefetch for small tiles (bytes in flight per warp)
+  static constexpr int kStages = S::kPlaneBytes >= 2048 ? 2 : (S::kPlaneBytes >= 1024 ? 3 : 4);
+  static constexpr int kXposeBytes = C::BPW * C::XS * 4;
+  static constexpr int kWarpBytes = cx_round_up(kStages * kStageBytes + kXposeBytes, 16);
+  static constexpr int kCtaBytes = kWarpsPerCta * kWarpBytes;
+};
+
+struct TxqArgs {
+  const B200TxBlock *blocks;
+  const B200TxPred *preds;
+  const void *src;
+  const void *pred;
+  const B200QRow *qrows;
+  const int16_t *iscan3;  // default, mrow, mcol inverse scans of this tx size
+  int32_t *coeff, *qcoeff, *dqcoeff;
+  uint16_t *eob;
+  int64_t *dist;
+  int n_blocks;
+  int q_kind, bd;
+  unsigned flags;
+};
+
+// 1-D kind per 2-D type: 0 DCT, 1 ADST, 2 FLIPADST, 3 IDENTITY
+// (vtx_tab / htx_tab, av1/common/common_data.h:149-159), packed 2 bits per type
+constexpr uint32_t kVtxPacked = 0u | (1u << 2) | (0u << 4) | (1u << 6) | (2u << 8) | (0u << 10) |
+                                (2u << 12) | (1u << 14) | (2u << 16) | (3u << 18) | (0u << 20) |
+                                (3u << 22) | (1u << 24) | (3u << 26) | (2u << 28) | (3u << 30);
+constexpr uint32_t kHtxPacked = 0u | (0u << 2) | (1u << 4) | (1u << 6) | (0u << 8) | (2u << 10) |
+                                (2u << 12) | (2u << 14) | (1u << 16) | (3u << 18) | (3u << 20) |
+                                (0u << 22) | (3u << 24) | (1u << 26) | (3u << 28) | (2u << 30);
+__host__ __device__ __forceinline__ int vtx_of(int tx_type) { return (kVtxPacked >> (2 * tx_type)) & 3; }
+__host__ __device__ __forceinline__ int htx_of(int tx_type) { return (kHtxPacked >> (2 * tx_type)) & 3; }
+
+// --------------------------------------------------------------- small helpers --
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+template <int BYTES>
+__device__ __forceinline__ void cp_async(uint32_t dst, const void *src) {
+  if constexpr (BYTES == 16)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+  else if constexpr (BYTES == 8)
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+  else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+__device__ __forceinline__ B200TxBlock load_desc(const B200TxBlock *p) {
+  const uint4 raw = __ldg(reinterpret_cast<const uint4 *>(p));
+  B200TxBlock d;
+  memcpy(&d, &raw, sizeof(d));
+  return d;
+}
+
+// Arithmetic flavour of one pass: EXACT = literal reference widths everywhere.
+template <bool EXACT, int K>
+__device__ __forceinline__ int32_t down_shift(int32_t x) {
+  if constexpr (K == 0) return x;
+  else if constexpr (EXACT) return rshift_round<K>(x);
+  else return (x + (1 << (K - 1))) >> K;  // cannot overflow under the guard
+}
+// round_shift((int64)v * 5793 * MUL, 12)
+template <bool EXACT, int MUL>
+__device__ __forceinline__ int32_t sqrt2_scale(int32_t v) {
+  if constexpr (EXACT) {
+    return scale_sqrt2<MUL>(v);
+  } else {
+    // 5793*MUL = MUL*4096 + R  ->  MUL*v + ((v*R + 2048) >> 12), all in 32 bits
+    constexpr int R = 5793 * MUL - 4096 * MUL;
+    return MUL * v + ((v * R + 2048) >> 12);
+  }
+}
+
+template <int N, int BIT, bool EXACT, int KEEP>
+__device__ __forceinline__ void txfm1d(int kind, int32_t *x, int32_t *y) {
+  using B = Btf<BIT, EXACT>;
+  if constexpr (N == 64) {
+    fdct<64, B, KEEP>(x, y);  // only DCT exists at 64 (av1_txfm.c:89-100)
+  } else if constexpr (N == 32) {
+    if (kind == 3) {
+      fidentity<32>(x, y);
+    } else {
+      fdct<32, B, KEEP>(x, y);
+    }
+  } else {
+    if (kind == 0) {
+      fdct<N, B, KEEP>(x, y);
+    } else if (kind == 3) {
+      if constexpr (EXACT || N == 8) {
+        fidentity<N>(x, y);
+      } else {
+        static_for<0, N>([&](auto ic) {
+          constexpr int i = decltype(ic)::value;
+          y[i] = sqrt2_scale<false, N == 4 ? 1 : 2>(x[i]);
+        });
+      }
+    } else {
+      fadst<N, B>(x, y);
+    }
+  }
+}
+
+// ------------------------------------------------------------------- staging -----
+// Issue the cp.async copies of one tile (all BPW blocks of warp-tile `wt`) into `stage`.
+template <int W, int H, int IN>
+__device__ __forceinline__ void stage_tile(const TxqArgs &a, int wt, unsigned char *stage, int lane) {
+  using C = TxCfg<W, H>;
+  using M = SmemCfg<W, H, IN>;
+  using S = typename M::S;
+  constexpr int ESZ = M::ESZ;
+#pragma unroll
+  for (int i = 0; i < S::kCpl; ++i) {
+    const int k = lane + 32 * i;
+    if (S::kChunksPerTile % 32 != 0 && k >= S::kChunksPerTile) break;
+    const int slot = k / S::kCpb, rem = k % S::kCpb;
+    const int row = rem / S::kCpr, part = rem % S::kCpr;
+    const int bi = wt * C::BPW + slot;
+    if (bi >= a.n_blocks) continue;
+    const B200TxBlock d = load_desc(a.blocks + bi);
+    const int drow = vtx_of(d.tx_type & 15) == 2 ? H - 1 - row : row;  // ud_flip
+    unsigned char *dst = stage + slot * S::kSlotBytes + drow * S::kRowBytes + part * S::kChunk;
+    const unsigned char *g = static_cast<const unsigned char *>(a.src) +
+                             ((size_t)d.src_offset + (size_t)row * d.src_stride) * ESZ + part * S::kChunk;
+    if ((reinterpret_cast<uintptr_t>(g) & (S::kChunk - 1)) == 0) {
+      cp_async<S::kChunk>(smem_u32(dst), g);
+    } else {  // unaligned source: element-wise copy (rare)
+#pragma unroll
+      for (int e = 0; e < S::kChunk; ++e) dst[e] = g[e];
+    }
+    if constexpr (IN != B200_IN_RESIDUAL) {
+      const B200TxPred pd = a.preds[bi];
+      unsigned char *dstp = dst + S::kPlaneBytes;
+      const unsigned char *gp = static_cast<const unsigned char *>(a.pred) +
+                                ((size_t)pd.pred_offset + (size_t)row * pd.pred_stride) * ESZ +
+                                part * S::kChunk;
+      if ((reinterpret_cast<uintptr_t>(gp) & (S::kChunk - 1)) == 0) {
+        cp_async<S::kChunk>(smem_u32(dstp), gp);
+      } else {
+#pragma unroll
+        for (int e = 0; e < S::kChunk; ++e) dstp[e] = gp[e];
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------- the passes -----
+// Row pass + final scalings: y[c] = coefficient (c, t) of the block, c < Wk.
+template <int W, int H, bool EXACT>
+__device__ __forceinline__ void row_pass(int ht, const int32_t *xrow, int32_t *y) {
+  using C = TxCfg<W, H>;
+  int32_t x[W];
+  if constexpr (W == 4) {
+    const int4 v = *reinterpret_cast<const int4 *>(xrow);
+    x[0] = v.x, x[1] = v.y, x[2] = v.z, x[3] = v.w;
+  } else {
+#pragma unroll
+    for (int c = 0; c < W; c += 4) {
+      const int4 v = *reinterpret_cast<const int4 *>(xrow + c);
+      x[c] = v.x, x[c + 1] = v.y, x[c + 2] = v.z, x[c + 3] = v.w;
+    }
+  }
+  txfm1d<W, C::kCosRow, EXACT, C::Wk>(ht, x, y);
+#pragma unroll
+  for (int c = 0; c < C::Wk; ++c) {
+    int32_t v = down_shift<EXACT, C::kDown2>(y[c]);
+    if constexpr (C::kRect) v = sqrt2_scale<EXACT, 1>(v);
+    y[c] = v;
+  }
+}
+
+// Read column c of the staged block (residual formed here for pixel inputs), track the
+// value range for the guard, apply the up-shift (av1_round_shift_array(temp_in, H,
+// -shift[0]); the input is int16 so the reference's clamp can never trigger).
+template <int W, int H, int IN>
+__device__ __forceinline__ void load_column(const unsigned char *stg, int c, int32_t *x,
+                                            int32_t &mx, int32_t &mn) {
+  using C = TxCfg<W, H>;
+  constexpr int PB = SmemCfg<W, H, IN>::S::kPlaneBytes;
+#pragma unroll
+  for (int r = 0; r < H; ++r) {
+    int32_t v;
+    if constexpr (IN == B200_IN_RESIDUAL) {
+      v = reinterpret_cast<const int16_t *>(stg)[r * W + c];
+    } else if constexpr (IN == B200_IN_PIXELS8) {
+      v = (int)stg[r * W + c] - (int)stg[PB + r * W + c];
+    } else {
+      v = (int16_t)((int)reinterpret_cast<const uint16_t *>(stg)[r * W + c] -
+                    (int)reinterpret_cast<const uint16_t *>(stg + PB)[r * W + c]);
+    }
+    if constexpr (IN != B200_IN_PIXELS8) {
+      mx = v > mx ? v : mx;
+      mn = v < mn ? v : mn;
+    }
+    x[r] = (int32_t)((uint32_t)v << C::kUp);
+  }
+}
+
+// Column transform(s) of lane t.  x0 holds column t already (loaded for the guard);
+// 64-wide blocks reload per iteration to keep the register footprint at one column.
+template <int W, int H, int IN, bool EXACT>
+__device__ __forceinline__ void column_pass(int vt, int ht, const unsigned char *stg, int32_t *x0,
+                                            int32_t *tile, int t) {
+  using C = TxCfg<W, H>;
+#pragma unroll
+  for (int ci = 0; ci < C::CI; ++ci) {
+    const int c = t + ci * C::CW;
+    int32_t y[C::Hk];
+    if constexpr (C::CI == 1) {
+      txfm1d<H, C::kCosCol, EXACT, C::Hk>(vt, x0, y);
+    } else {
+      int32_t x[H], m0 = 0, m1 = 0;
+      load_column<W, H, IN>(stg, c, x, m0, m1);
+      txfm1d<H, C::kCosCol, EXACT, C::Hk>(vt, x, y);
+    }
+    const int cc = (ht == 2) ? (W - 1 - c) : c;  // lr_flip (av1_fwd_txfm2d.c:99-105)
+#pragma unroll
+    for (int r = 0; r < C::Hk; ++r) tile[r * C::LDX + cc] = down_shift<EXACT, C::kDown1>(y[r]);
+  }
+}
+
+// ------------------------------------------------------------------- epilogue ----
+template <int W, int H, int QK, bool ERR>
+__device__ __forceinline__ void quant_epilogue(const TxqArgs &a, const B200TxBlock &d, int t,
+                                               const int32_t *y, int32_t *qc, int32_t *dqc,
+                                               int &last_c, int64_t &err, int64_t &ssz) {
+  using C = TxCfg<W, H>;
+  constexpr int LS = C::kLogScale;
+  constexpr bool fp = QK == B200_Q_FP || QK == B200_Q_FP_HBD;
+  constexpr bool hbd = QK == B200_Q_FP_HBD || QK == B200_Q_B_HBD;
+  // one 32-byte quantiser row per block (broadcast load)
+  const uint4 q0 = __ldg(reinterpret_cast<const uint4 *>(a.qrows + d.qrow));
+  const uint4 q1 = __ldg(reinterpret_cast<const uint4 *>(a.qrows + d.qrow) + 1);
+  B200QRow qr;
+  memcpy(&qr, &q0, 16);
+  memcpy(reinterpret_cast<char *>(&qr) + 16, &q1, 16);
+  auto rpo2 = [](int v) { return LS ? ((v + (1 << (LS - 1))) >> LS) : v; };  // ROUND_POWER_OF_TWO
+  const int rnd0 = rpo2(fp ? qr.round_fp[0] : qr.round[0]);
+  const int rnd1 = rpo2(fp ? qr.round_fp[1] : qr.round[1]);
+  const int qnt0 = fp ? qr.quant_fp[0] : qr.quant[0];
+  const int qnt1 = fp ? qr.quant_fp[1] : qr.quant[1];
+  const int deq0 = qr.dequant[0], deq1 = qr.dequant[1];
+  const int qsh0 = qr.quant_shift[0], qsh1 = qr.quant_shift[1];
+  // dead-zone test rewritten as |coeff| >= threshold:
+  //   FP: (abs << (1+LS)) >= dequant  <=>  abs >= ceil(dequant / 2^(1+LS))
+  //   B : abs*32 >= zbin*32           <=>  abs >= zbin
+  constexpr int K = 1 + LS;
+  const int thr0 = fp ? ((deq0 + (1 << K) - 1) >> K) : rpo2(qr.zbin[0]);
+  const int thr1 = fp ? ((deq1 + (1 << K) - 1) >> K) : rpo2(qr.zbin[1]);
+#pragma unroll
+  for (int c = 0; c < C::Wk; ++c) {
+    const bool dc = (c == 0) && (t == 0);  // compile-time false for c > 0
+    const int rnd_k = dc ? rnd0 : rnd1, qnt_k = dc ? qnt0 : qnt1, deq_k = dc ? deq0 : deq1;
+    const int qsh_k = dc ? qsh0 : qsh1, thr_k = dc ? thr0 : thr1;
+    (void)qsh_k;
+    const int32_t cf = y[c];
+    const int32_t ab = cf < 0 ? -cf : cf;
+    const int32_t sgn = cf < 0 ? -1 : 1;
+    int32_t q, dq;
+    if constexpr (fp) {
+      if constexpr (!hbd) {
+        // clamp64(abs + round, INT16_MIN, INT16_MAX): abs >= 0 so only the upper bound acts
+        int32_t tt = (ab > 32767 ? 32767 : ab) + rnd_k;
+        tt = tt > 32767 ? 32767 : tt;
+        tt = ab >= thr_k ? tt : 0;
+        q = (tt * qnt_k) >> (16 - LS);
+      } else {
+        const uint32_t tt = ab >= thr_k ? (uint32_t)(ab + rnd_k) : 0u;
+        q = (int32_t)(((uint64_t)tt * (uint32_t)qnt_k) >> (16 - LS));
+      }
+      dq = wmul(q, deq_k) >> LS;
+    } else {
+      int64_t tt = (int64_t)ab + rnd_k;
+      if constexpr (!hbd) tt = tt > 32767 ? 32767 : tt;
+      tt = ab >= thr_k ? tt * 32 : 0;
+      q = (int32_t)(((((tt * qnt_k) >> 16) + tt) * qsh_k) >> (16 - LS + 5));
+      dq = wmul(q, deq_k) >> LS;
+    }
+    qc[c] = q * sgn;
+    dqc[c] = dq * sgn;
+    if (q) last_c = c;  // iscan grows with c along a row: the last non-zero c wins
+    if constexpr (ERR) {
+      const int32_t df = wsub(cf, dqc[c]);
+      if constexpr (hbd) {
+        err += (int64_t)df * df;
+        ssz += (int64_t)cf * cf;
+      } else {  // av1_block_error_c squares in 32-bit int (rdopt.c:642-643)
+        err += (int64_t)wmul(df, df);
+        ssz += (int64_t)wmul(cf, cf);
+      }
+    }
+  }
+}
+
+// --------------------------------------------------------------------- kernel ----
+template <int W, int H, int IN>
+__global__ void __launch_bounds__(kWarpsPerCta * 32) txq_kernel(const TxqArgs a) {
+  using C = TxCfg<W, H>;
+  using M = SmemCfg<W, H, IN>;
+  using S = typename M::S;
+  constexpr int NS = M::kStages;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int slot = lane / C::NT, t = lane % C::NT;
+  unsigned char *wbase = smem_raw + warp * M::kWarpBytes;
+  int32_t *tile = reinterpret_cast<int32_t *>(wbase + NS * M::kStageBytes) + slot * C::XS;
+  const int n_tiles = (a.n_blocks + C::BPW - 1) / C::BPW;
+  const int wstride = gridDim.x * kWarpsPerCta;
+  const int wt0 = blockIdx.x * kWarpsPerCta + warp;
+
+  // prologue: fill NS-1 stages
+#pragma unroll
+  for (int s = 0; s < NS - 1; ++s) {
+    const int wt = wt0 + s * wstride;
+    if (wt < n_tiles) stage_tile<W, H, IN>(a, wt, wbase + s * M::kStageBytes, lane);
+    cp_async_commit();
+  }
+
+  int it = 0;
+  for (int wt = wt0; wt < n_tiles; wt += wstride, ++it) {
+    {  // keep the ring full: tile it+NS-1 goes to the stage consumed in the previous round
+      const int wtp = wt + (NS - 1) * wstride;
+      if (wtp < n_tiles)
+        stage_tile<W, H, IN>(a, wtp, wbase + ((it + NS - 1) % NS) * M::kStageBytes, lane);
+      cp_async_commit();
+    }
+    const int bi = wt * C::BPW + slot;
+    const bool active = bi < a.n_blocks;
+    B200TxBlock d;
+    if (active) d = load_desc(a.blocks + bi);
+    else memset(&d, 0, sizeof(d));
+    const int vt = vtx_of(d.tx_type & 15), ht = htx_of(d.tx_type & 15);
+    cp_async_wait<NS - 1>();
+    __syncwarp();
+
+    // ---- column inputs from the stage (immediate-offset LDS) + conformance guard
+    const unsigned char *stg = wbase + (it % NS) * M::kStageBytes + slot * S::kSlotBytes;
+    int32_t x0[C::CI == 1 ? H : 1];
+    int32_t mx = 0, mn = 0;
+    const bool col_lane = active && t < C::CW;
+    if (col_lane) {
+      if constexpr (C::CI == 1) {
+        load_column<W, H, IN>(stg, t, x0, mx, mn);
+      } else if constexpr (IN != B200_IN_PIXELS8) {  // range scan only
+#pragma unroll
+        for (int ci = 0; ci < C::CI; ++ci) {
+          int32_t xs[H];
+          load_column<W, H, IN>(stg, t + ci * C::CW, xs, mx, mn);
+        }
+      }
+    }
+    bool fast = true;
+    if constexpr (IN != B200_IN_PIXELS8)
+      fast = __all_sync(0xffffffffu, mx <= kGuard && mn >= -kGuard);
+    if (a.flags & B200_TXQ_FORCE_EXACT) fast = false;
+
+    // ---- column pass -> transpose tile -> row pass
+    int32_t y[C::Wk];
+    if (fast) {
+      if (col_lane) column_pass<W, H, IN, false>(vt, ht, stg, x0, tile, t);
+      __syncwarp();
+      if (active && t < C::Hk) row_pass<W, H, false>(ht, tile + t * C::LDX, y);
+    } else {
+      if (col_lane) column_pass<W, H, IN, true>(vt, ht, stg, x0, tile, t);
+      __syncwarp();
+      if (active && t < C::Hk) row_pass<W, H, true>(ht, tile + t * C::LDX, y);
+    }
+
+    // ---- epilogue: stores, quantiser, eob, block error
+    int last_c = -1;
+    int64_t err = 0, ssz = 0;
+    const bool row_lane = active && t < C::Hk;
+    if (row_lane) {
+      const size_t obase = (size_t)d.out_offset + t;
+      if (a.flags & B200_TXQ_STORE_COEFF) {
+#pragma unroll
+        for (int c = 0; c < C::Wk; ++c) a.coeff[obase + c * C::Hk] = y[c];
+      }
+      if (a.q_kind != B200_Q_NONE) {
+        int32_t qc[C::Wk], dqc[C::Wk];
+        const bool we = (a.flags & B200_TXQ_BLOCK_ERROR) != 0;
+        switch (a.q_kind) {
+          case B200_Q_FP:
+            if (we) quant_epilogue<W, H, B200_Q_FP, true>(a, d, t, y, qc, dqc, last_c, err, ssz);
+            else quant_epilogue<W, H, B200_Q_FP, false>(a, d, t, y, qc, dqc, last_c, err, ssz);
+            break;
+          case B200_Q_FP_HBD:
+            if (we) quant_epilogue<W, H, B200_Q_FP_HBD, true>(a, d, t, y, qc, dqc, last_c, err, ssz);
+            else quant_epilogue<W, H, B200_Q_FP_HBD, false>(a, d, t, y, qc, dqc, last_c, err, ssz);
+            break;
+          case B200_Q_B:
+            if (we) quant_epilogue<W, H, B200_Q_B, true>(a, d, t, y, qc, dqc, last_c, err, ssz);
+            else quant_epilogue<W, H, B200_Q_B, false>(a, d, t, y, qc, dqc, last_c, err, ssz);
+            break;
+          default:
+            if (we) quant_epilogue<W, H, B200_Q_B_HBD, true>(a, d, t, y, qc, dqc, last_c, err, ssz);
+            else quant_epilogue<W, H, B200_Q_B_HBD, false>(a, d, t, y, qc, dqc, last_c, err, ssz);
+            break;
+        }
+#pragma unroll
+        for (int c = 0; c < C::Wk; ++c) a.qcoeff[obase + c * C::Hk] = qc[c];
+#pragma unroll
+        for (int c = 0; c < C::Wk; ++c) a.dqcoeff[obase + c * C::Hk] = dqc[c];
+      }
+    }
+    if (a.q_kind != B200_Q_NONE) {
+      int eob = 0;
+      if (last_c >= 0) {
+        const int cls = d.tx_type < 10 ? 0 : ((d.tx_type & 1) ? 2 : 1);
+        eob = a.iscan3[cls * (C::Wk * C::Hk) + last_c * C::Hk + t] + 1;
+      }
+#pragma unroll
+      for (int o = C::NT / 2; o > 0; o >>= 1) {
+        const int e2 = __shfl_xor_sync(0xffffffffu, eob, o);
+        eob = e2 > eob ? e2 : eob;
+      }
+      if (a.flags & B200_TXQ_BLOCK_ERROR) {
+#pragma unroll
+        for (int o = C::NT / 2; o > 0; o >>= 1) {
+          err += __shfl_xor_sync(0xffffffffu, err, o);
+          ssz += __shfl_xor_sync(0xffffffffu, ssz, o);
+        }
+      }
+      if (active && t == 0) {
+        a.eob[bi] = (uint16_t)eob;
+        if ((a.flags & B200_TXQ_BLOCK_ERROR) && a.dist) {
+          if (a.q_kind == B200_Q_FP_HBD || a.q_kind == B200_Q_B_HBD) {
+            const int sh = 2 * (a.bd - 8);
+            const int64_t r = sh > 0 ? ((int64_t)1 << (sh - 1)) : 0;
+            err = (err + r) >> sh;
+            ssz = (ssz + r) >> sh;
+          }
+          a.dist[2 * (size_t)bi] = err;
+          a.dist[2 * (size_t)bi + 1] = ssz;
+        }
+      }
+    }
+    __syncwarp();  // stage and transpose tile are reused by the next round
+  }
+  cp_async_wait<0>();
+}
+
+// one launcher per (size, input kind); defined in txq_inst_*.cu
+struct TxqKernelInfo {
+  void (*fn)(const TxqArgs);
+  int smem_bytes;
+  int bpw;
+};
+template <int W, int H, int IN>
+TxqKernelInfo txq_kernel_info() {
+  TxqKernelInfo k;
+  k.fn = txq_kernel<W, H, IN>;
+  k.smem_bytes = SmemCfg<W, H, IN>::kCtaBytes;
+  k.bpw = TxCfg<W, H>::BPW;
+  return k;
+}
+
+}  // namespace b200

@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(PKG_DIR, "libb200av1.so")
 OK = 0
 IN_RESIDUAL, IN_PIXELS8, IN_PIXELS16 = 0, 1, 2
 Q_NONE, Q_FP, Q_FP_HBD, Q_B, Q_B_HBD = 0, 1, 2, 3, 4
-TXQ_STORE_COEFF, TXQ_BLOCK_ERROR, TXQ_FAST32 = 1, 2, 4
+TXQ_STORE_COEFF, TXQ_BLOCK_ERROR, TXQ_FORCE_EXACT = 1, 2, 4
 
 
 class QRow(C.Structure):

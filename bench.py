@@ -81,8 +81,7 @@ def make_residual_frames(n_frames, seed):
 
 
 def make_descriptors(ts, n_frames, planes, frame_elems, seed):
-    """all blocks of size ts tiling every plane of every frame; sorted by tx_type so that
-    the lanes of a warp share one code path (the batch queue's job)."""
+    """all blocks of size ts tiling every plane of every frame, in batch-queue order"""
     rng = np.random.default_rng(seed * 100 + ts)
     W, Hh = TX_W[ts], TX_H[ts]
     offs, strides, planes_id = [], [], []
@@ -108,7 +107,11 @@ def make_descriptors(ts, n_frames, planes, frame_elems, seed):
     blocks["tx_size"] = ts
     # quantiser row = plane * 5 + qindex slot
     blocks["qrow"] = np.tile(planes_id, n_frames) * len(QINDEXES) + rng.integers(0, len(QINDEXES), n)
-    order = np.argsort(blocks["tx_type"], kind="stable")
+    # batch-queue order: within each frame group the blocks by tx_type (warps stay on one
+    # code path) but keep frames apart, so that the 16 type groups of a frame re-touch the
+    # same ~6 MB of residual while it is still in L2
+    frame_id = np.repeat(np.arange(n_frames), per_frame)
+    order = np.lexsort((blocks["tx_type"], frame_id))
     blocks = blocks[order]
     blocks["out_offset"] = np.arange(n, dtype=np.uint64) * max_eob(ts)
     samples = n * W * Hh
@@ -235,7 +238,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--frames", type=int, default=32, help="frames per rank per launch")
     ap.add_argument("--e2e-steps", type=int, default=3)
-    ap.add_argument("--fast32", action="store_true", help="all-32-bit butterflies (DESIGN.md)")
+    ap.add_argument("--force-exact", action="store_true", help="always take the 64-bit half_btf path")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--sizes", default="", help="comma list of tx sizes (debug)")
     args = ap.parse_args()
@@ -251,7 +254,7 @@ def main():
               "qindex_set": QINDEXES, "l2": "inputs (%.0f MB/GPU) larger than L2; outputs streamed"
                                             % (args.frames * FE_SAMPLES * 2 / 1e6),
               "parallelism": "frames sharded over %d GPU(s), no collective" % world,
-              "butterflies": "fast32" if args.fast32 else "exact64"}
+              "butterflies": "exact64 (forced)" if args.force_exact else "guarded (32-bit when |residual|<=4094, proved exact; else 64-bit)"}
 
     # ----------------------------------------------------------- reference arm
     if args.impl == "reference":
@@ -320,7 +323,7 @@ def main():
     d_coeff = torch.empty(max_out, dtype=torch.int32, device=dev)
     d_qc = torch.empty(max_out, dtype=torch.int32, device=dev)
     d_dq = torch.empty(max_out, dtype=torch.int32, device=dev)
-    flags = b200av1.TXQ_STORE_COEFF | (b200av1.TXQ_FAST32 if args.fast32 else 0)
+    flags = b200av1.TXQ_STORE_COEFF | (b200av1.TXQ_FORCE_EXACT if args.force_exact else 0)
     for ps in per_size:
         l = b200av1.TxqLaunch()
         l.tx_size, l.in_kind, l.q_kind, l.bd, l.flags = ps["ts"], 0, b200av1.Q_FP, 8, flags

@@ -135,7 +135,7 @@ enum {
 };
 #define B200_TXQ_STORE_COEFF 1u /* write the transform coefficients (p->coeff) */
 #define B200_TXQ_BLOCK_ERROR 2u /* also av1_block_error / av1_highbd_block_error */
-#define B200_TXQ_FAST32 4u      /* all-32-bit butterflies (arithmetic) */
+#define B200_TXQ_FORCE_EXACT 4u /* always use the literal 64-bit half_btf (arithmetic) */
 
 typedef struct {
   int tx_size;             /* all n_blocks blocks have this size */

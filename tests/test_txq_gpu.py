@@ -37,6 +37,10 @@ def _make_batch(rng, ts, n_per_type, bd, mode, qindexes):
             blk[:] = hi if i % 2 == 0 else -hi
         elif mode == "small":
             blk[:] = rng.integers(-40, 41, (Hh, W))
+        elif mode == "wild":  # non-conformant: any int16 (exercises the exact-path guard)
+            blk[:] = rng.integers(-32768, 32768, (Hh, W))
+        elif mode == "edge":  # just inside / just outside the guard
+            blk[:] = rng.choice(np.array([-4095, -4094, 4094, 4095, 0, 1]), (Hh, W))
         else:
             blk[:] = rng.integers(-hi, hi + 1, (Hh, W))
         blocks[i] = (off, i * n, stride, i % len(qindexes), ts, types[i % len(types)], 0)
@@ -58,7 +62,7 @@ def test_txq_all_types(ctx, ts):
         qrows = np.array([b200av1.qrow_from_oracle(r) for r in rows], b200av1.QROW_DTYPE)
         src, blocks, out_elems = _make_batch(rng, ts, 3 if H.TX_W[ts] * H.TX_H[ts] >= 1024 else 6,
                                              bd, mode, qidx)
-        for fast in (0, b200av1.TXQ_FAST32):
+        for fast in (0, b200av1.TXQ_FORCE_EXACT):
             coeff = np.full(out_elems, 123, np.int32)
             qc = np.full(out_elems, 123, np.int32)
             dq = np.full(out_elems, 123, np.int32)
@@ -74,6 +78,44 @@ def test_txq_all_types(ctx, ts):
             assert np.array_equal(dq, r[2]), tag
             assert np.array_equal(eob, r[3]), tag
             assert np.array_equal(dist, r[4]), tag
+
+
+@pytest.mark.parametrize("ts", range(19), ids=H.TX_NAMES)
+def test_txfm_nonconformant_input_takes_exact_path(ctx, ts):
+    """any int16 residual (far outside what a bd-bit encoder produces) must still match the
+    reference's wrapping 32-bit products / 64-bit sums: the in-kernel guard routes such tiles
+    to the literal half_btf form.  Also +-4094/4095 around the guard threshold."""
+    import b200av1
+    rng = np.random.default_rng(4000 + ts)
+    for mode in ("wild", "edge"):
+        src, blocks, out_elems = _make_batch(rng, ts, 4, 12, mode, [0])
+        coeff = np.zeros(out_elems, np.int32)
+        ctx.txq_batch_host(b200av1.IN_RESIDUAL, b200av1.Q_NONE, 12, b200av1.TXQ_STORE_COEFF,
+                           blocks, None, src, None, None, coeff, None, None, None, None)
+        r = H.oracle_txq_batch(src, blocks, [], 0, 12, out_elems)
+        assert np.array_equal(coeff, r[0]), (H.TX_NAMES[ts], mode)
+
+
+def test_txq_unaligned_sources(ctx):
+    """source offsets / strides that defeat the 16-byte cp.async path (element-wise copy)"""
+    import b200av1
+    rng = np.random.default_rng(77)
+    for ts in (0, 1, 2, 3, 6, 8, 12):
+        W, Hh, n = H.TX_W[ts], H.TX_H[ts], H.max_eob(ts)
+        stride = W + 3
+        src = rng.integers(-255, 256, (Hh + 2) * stride * 6 + 16).astype(np.int16)
+        blocks = np.zeros(6, b200av1.TXBLOCK_DTYPE)
+        for i in range(6):
+            blocks[i] = (i * (Hh + 2) * stride + 1 + i, i * n, stride, 0, ts, 0, 0)
+        rows = [H.oracle_qrow(8, 77)]
+        qrows = np.array([b200av1.qrow_from_oracle(r) for r in rows], b200av1.QROW_DTYPE)
+        coeff, qc, dq = (np.zeros(6 * n, np.int32) for _ in range(3))
+        eob = np.zeros(6, np.uint16)
+        ctx.txq_batch_host(b200av1.IN_RESIDUAL, b200av1.Q_FP, 8, b200av1.TXQ_STORE_COEFF, blocks,
+                           None, src, None, qrows, coeff, qc, dq, eob, None)
+        r = H.oracle_txq_batch(src, blocks, rows, 1, 8, 6 * n, with_err=False)
+        for a, b in zip((coeff, qc, dq, eob), r):
+            assert np.array_equal(a, b), H.TX_NAMES[ts]
 
 
 def test_txq_transform_only_and_empty(ctx):
