@@ -9,17 +9,18 @@
 //                                                  aom_dsp/quantize.c:108-316
 //   av1_block_error / av1_highbd_block_error       av1/encoder/rdopt.c:635-682
 //
-// Mapping: a transform block is owned by NT <= 32 lanes of ONE
-// warp; a warp works on BPW = 32/NT blocks ("a tile") at a time and strides over the
-// tiles of the launch (persistent grid).  Per tile:
+// Mapping: a warp owns a tile of TB = 32/min(W, Hk) transform
+// blocks at a time and strides over the tiles of the launch (persistent grid); the
+// tile's columns, then its rows, are spread over the 32 lanes so that no lane idles in
+// either pass whatever the block shape.  Per tile:
 //   1. input rows arrive in shared memory through cp.async (16/8/4-byte chunks, one
 //      address computation per chunk, ring of S stages filled S-1 tiles ahead; the
 //      upside-down flip of FLIPADST columns is applied by the copy);
-//   2. lane c reads column c with immediate-offset LDS and runs the whole H-point
+//   2. a lane reads its column with immediate-offset LDS and runs the whole H-point
 //      column transform in registers;
 //   3. the column results cross to row ownership through a padded per-warp int32 tile
 //      (__syncwarp only -- there is no CTA-wide barrier in this kernel);
-//   4. lane r reads row r with LDS.128, runs the W-point row transform, quantises its
+//   4. a lane reads its row with LDS.128, runs the W-point row transform, quantises its
 //      W coefficients in registers and stores coeff / qcoeff / dqcoeff -- which the
 //      codec keeps column-major, i.e. lane-contiguous -- with coalesced 32-bit stores;
 //   5. eob and the error sums are shuffle-reduced over the block's lanes.
@@ -77,16 +78,19 @@ struct TxCfg {
   }
   static constexpr int kCosCol = cosbit_col(), kCosRow = cosbit_row();
 
-  // kept region and lane mapping
+  // kept region and lane mapping.  A warp works on a tile of TB blocks.  Column pass:
+  // the TB*W columns of the tile are spread over the 32 lanes (CI rounds); row pass: the
+  // TB*Hk kept rows likewise (RI rounds).  TB is chosen so that the narrower of the two
+  // passes fills the warp exactly -- no lane idles in either pass for any block shape.
   static constexpr int Wk = cx_min(W, 32), Hk = cx_min(H, 32);
-  static constexpr int CW = cx_min(W, 32);   // columns handled per column iteration
-  static constexpr int CI = W / CW;          // column iterations (2 for 64-wide)
-  static constexpr int NT = cx_max(CW, Hk);  // lanes per transform block
-  static constexpr int BPW = 32 / NT;        // transform blocks per warp ("tile")
+  static constexpr int TB = 32 / cx_min(W, Hk);  // blocks per tile
+  static constexpr int BPW = TB;
+  static constexpr int CI = TB * W / 32;         // column rounds
+  static constexpr int RI = TB * Hk / 32;        // row rounds
   // transpose tile (int32): pitch = 4 (mod 8) words -> LDS.128 row reads and the
   // column-wise STS are both bank-conflict free
   static constexpr int LDX = W == 4 ? 4 : W + 4;
-  static constexpr int XS = BPW > 1 ? cx_round_up(Hk * LDX, 32) + CW : Hk * LDX;  // words / slot
+  static constexpr int XS = (TB > 1 && W < 32) ? cx_round_up(Hk * LDX, 32) + W : Hk * LDX;  // words / slot
 };
 
 // Input staging geometry for element size ESZ (2: int16 residual / uint16 pixels, 1: uint8)
@@ -101,8 +105,9 @@ struct StageCfg {
   static constexpr int kCpl = (kChunksPerTile + 31) / 32;     // chunks per lane
   static constexpr int kTileBytes = H * kRowBytes;
   // slot pitch: distinct banks for the column reads of the BPW slots of a warp
-  static constexpr int kSlotBytes =
-      C::BPW > 1 ? cx_round_up(kTileBytes, 128) + C::NT * ESZ : cx_round_up(kTileBytes, 16);
+  static constexpr int kSlotBytes = (C::TB > 1 && kRowBytes < 128)
+                                        ? cx_round_up(kTileBytes, 128) + kRowBytes
+                                        : cx_round_up(kTileBytes, 16);
   static constexpr int kPlaneBytes = C::BPW * kSlotBytes;     // one operand, all slots
 };
 
@@ -315,27 +320,15 @@ __device__ __forceinline__ void load_column(const unsigned char *stg, int c, int
   }
 }
 
-// Column transform(s) of lane t.  x0 holds column t already (loaded for the guard);
-// 64-wide blocks reload per iteration to keep the register footprint at one column.
-template <int W, int H, int IN, bool EXACT>
-__device__ __forceinline__ void column_pass(int vt, int ht, const unsigned char *stg, int32_t *x0,
-                                            int32_t *tile, int t) {
+// Column transform of one column (already in x) -> transpose tile of its block.
+template <int W, int H, bool EXACT>
+__device__ __forceinline__ void column_pass(int vt, int ht, int32_t *x, int32_t *tile, int c) {
   using C = TxCfg<W, H>;
+  int32_t y[C::Hk];
+  txfm1d<H, C::kCosCol, EXACT, C::Hk>(vt, x, y);
+  const int cc = (ht == 2) ? (W - 1 - c) : c;  // lr_flip (av1_fwd_txfm2d.c:99-105)
 #pragma unroll
-  for (int ci = 0; ci < C::CI; ++ci) {
-    const int c = t + ci * C::CW;
-    int32_t y[C::Hk];
-    if constexpr (C::CI == 1) {
-      txfm1d<H, C::kCosCol, EXACT, C::Hk>(vt, x0, y);
-    } else {
-      int32_t x[H], m0 = 0, m1 = 0;
-      load_column<W, H, IN>(stg, c, x, m0, m1);
-      txfm1d<H, C::kCosCol, EXACT, C::Hk>(vt, x, y);
-    }
-    const int cc = (ht == 2) ? (W - 1 - c) : c;  // lr_flip (av1_fwd_txfm2d.c:99-105)
-#pragma unroll
-    for (int r = 0; r < C::Hk; ++r) tile[r * C::LDX + cc] = down_shift<EXACT, C::kDown1>(y[r]);
-  }
+  for (int r = 0; r < C::Hk; ++r) tile[r * C::LDX + cc] = down_shift<EXACT, C::kDown1>(y[r]);
 }
 
 // ------------------------------------------------------------------- epilogue ----
@@ -343,6 +336,7 @@ template <int W, int H, int QK, bool ERR>
 __device__ __forceinline__ void quant_epilogue(const TxqArgs &a, const B200TxBlock &d, int t,
                                                const int32_t *y, int32_t *qc, int32_t *dqc,
                                                int &last_c, int64_t &err, int64_t &ssz) {
+  // qc / dqc: this lane's first output element (global); element c is at [c * Hk]
   using C = TxCfg<W, H>;
   constexpr int LS = C::kLogScale;
   constexpr bool fp = QK == B200_Q_FP || QK == B200_Q_FP_HBD;
@@ -395,11 +389,12 @@ __device__ __forceinline__ void quant_epilogue(const TxqArgs &a, const B200TxBlo
       q = (int32_t)(((((tt * qnt_k) >> 16) + tt) * qsh_k) >> (16 - LS + 5));
       dq = wmul(q, deq_k) >> LS;
     }
-    qc[c] = q * sgn;
-    dqc[c] = dq * sgn;
+    const int32_t dqs = dq * sgn;
+    qc[c * C::Hk] = q * sgn;
+    dqc[c * C::Hk] = dqs;
     if (q) last_c = c;  // iscan grows with c along a row: the last non-zero c wins
     if constexpr (ERR) {
-      const int32_t df = wsub(cf, dqc[c]);
+      const int32_t df = wsub(cf, dqs);
       if constexpr (hbd) {
         err += (int64_t)df * df;
         ssz += (int64_t)cf * cf;
@@ -420,12 +415,12 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) txq_kernel(const TxqArgs a)
   constexpr int NS = M::kStages;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int slot = lane / C::NT, t = lane % C::NT;
   unsigned char *wbase = smem_raw + warp * M::kWarpBytes;
-  int32_t *tile = reinterpret_cast<int32_t *>(wbase + NS * M::kStageBytes) + slot * C::XS;
-  const int n_tiles = (a.n_blocks + C::BPW - 1) / C::BPW;
+  int32_t *xpose = reinterpret_cast<int32_t *>(wbase + NS * M::kStageBytes);
+  const int n_tiles = (a.n_blocks + C::TB - 1) / C::TB;
   const int wstride = gridDim.x * kWarpsPerCta;
   const int wt0 = blockIdx.x * kWarpsPerCta + warp;
+  const bool force_exact = (a.flags & B200_TXQ_FORCE_EXACT) != 0;
 
   // prologue: fill NS-1 stages
 #pragma unroll
@@ -443,114 +438,111 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) txq_kernel(const TxqArgs a)
         stage_tile<W, H, IN>(a, wtp, wbase + ((it + NS - 1) % NS) * M::kStageBytes, lane);
       cp_async_commit();
     }
-    const int bi = wt * C::BPW + slot;
-    const bool active = bi < a.n_blocks;
-    B200TxBlock d;
-    if (active) d = load_desc(a.blocks + bi);
-    else memset(&d, 0, sizeof(d));
-    const int vt = vtx_of(d.tx_type & 15), ht = htx_of(d.tx_type & 15);
     cp_async_wait<NS - 1>();
     __syncwarp();
+    const unsigned char *stage = wbase + (it % NS) * M::kStageBytes;
 
-    // ---- column inputs from the stage (immediate-offset LDS) + conformance guard
-    const unsigned char *stg = wbase + (it % NS) * M::kStageBytes + slot * S::kSlotBytes;
-    int32_t x0[C::CI == 1 ? H : 1];
-    int32_t mx = 0, mn = 0;
-    const bool col_lane = active && t < C::CW;
-    if (col_lane) {
-      if constexpr (C::CI == 1) {
-        load_column<W, H, IN>(stg, t, x0, mx, mn);
-      } else if constexpr (IN != B200_IN_PIXELS8) {  // range scan only
-#pragma unroll
-        for (int ci = 0; ci < C::CI; ++ci) {
-          int32_t xs[H];
-          load_column<W, H, IN>(stg, t + ci * C::CW, xs, mx, mn);
-        }
+    // ---------------------------------------------------------------- column rounds
+    bool tile_fast = !force_exact;
+#pragma unroll 1
+    for (int ci = 0; ci < C::CI; ++ci) {
+      const int item = lane + 32 * ci;
+      const int slot = item / W, c = item % W;
+      const int bi = wt * C::TB + slot;
+      const bool act = bi < a.n_blocks;
+      int tx_type = 0;
+      if (act) tx_type = a.blocks[bi].tx_type & 15;
+      const int vt = vtx_of(tx_type), ht = htx_of(tx_type);
+      int32_t x[H], mx = 0, mn = 0;
+      if (act) load_column<W, H, IN>(stage + slot * S::kSlotBytes, c, x, mx, mn);
+      bool ok = !force_exact;
+      if constexpr (IN != B200_IN_PIXELS8)
+        ok = ok && __all_sync(0xffffffffu, mx <= kGuard && mn >= -kGuard);
+      tile_fast = tile_fast && ok;
+      if (act) {
+        if (ok) column_pass<W, H, false>(vt, ht, x, xpose + slot * C::XS, c);
+        else column_pass<W, H, true>(vt, ht, x, xpose + slot * C::XS, c);
       }
     }
-    bool fast = true;
-    if constexpr (IN != B200_IN_PIXELS8)
-      fast = __all_sync(0xffffffffu, mx <= kGuard && mn >= -kGuard);
-    if (a.flags & B200_TXQ_FORCE_EXACT) fast = false;
+    __syncwarp();
 
-    // ---- column pass -> transpose tile -> row pass
-    int32_t y[C::Wk];
-    if (fast) {
-      if (col_lane) column_pass<W, H, IN, false>(vt, ht, stg, x0, tile, t);
-      __syncwarp();
-      if (active && t < C::Hk) row_pass<W, H, false>(ht, tile + t * C::LDX, y);
-    } else {
-      if (col_lane) column_pass<W, H, IN, true>(vt, ht, stg, x0, tile, t);
-      __syncwarp();
-      if (active && t < C::Hk) row_pass<W, H, true>(ht, tile + t * C::LDX, y);
-    }
-
-    // ---- epilogue: stores, quantiser, eob, block error
-    int last_c = -1;
-    int64_t err = 0, ssz = 0;
-    const bool row_lane = active && t < C::Hk;
-    if (row_lane) {
-      const size_t obase = (size_t)d.out_offset + t;
-      if (a.flags & B200_TXQ_STORE_COEFF) {
+    // ------------------------------------------------------------------- row rounds
+#pragma unroll 1
+    for (int ri = 0; ri < C::RI; ++ri) {
+      const int item = lane + 32 * ri;
+      const int slot = item / C::Hk, t = item % C::Hk;
+      const int bi = wt * C::TB + slot;
+      const bool act = bi < a.n_blocks;
+      B200TxBlock d;
+      if (act) d = load_desc(a.blocks + bi);
+      else memset(&d, 0, sizeof(d));
+      const int ht = htx_of(d.tx_type & 15);
+      int last_c = -1;
+      int64_t err = 0, ssz = 0;
+      if (act) {
+        int32_t y[C::Wk];
+        const int32_t *xrow = xpose + slot * C::XS + t * C::LDX;
+        if (tile_fast) row_pass<W, H, false>(ht, xrow, y);
+        else row_pass<W, H, true>(ht, xrow, y);
+        const size_t obase = (size_t)d.out_offset + t;
+        if (a.flags & B200_TXQ_STORE_COEFF) {
 #pragma unroll
-        for (int c = 0; c < C::Wk; ++c) a.coeff[obase + c * C::Hk] = y[c];
+          for (int c = 0; c < C::Wk; ++c) a.coeff[obase + c * C::Hk] = y[c];
+        }
+        if (a.q_kind != B200_Q_NONE) {
+          int32_t *qc = a.qcoeff + obase, *dqc = a.dqcoeff + obase;
+          const bool we = (a.flags & B200_TXQ_BLOCK_ERROR) != 0;
+          switch (a.q_kind) {
+            case B200_Q_FP:
+              if (we) quant_epilogue<W, H, B200_Q_FP, true>(a, d, t, y, qc, dqc, last_c, err, ssz);
+              else quant_epilogue<W, H, B200_Q_FP, false>(a, d, t, y, qc, dqc, last_c, err, ssz);
+              break;
+            case B200_Q_FP_HBD:
+              if (we) quant_epilogue<W, H, B200_Q_FP_HBD, true>(a, d, t, y, qc, dqc, last_c, err, ssz);
+              else quant_epilogue<W, H, B200_Q_FP_HBD, false>(a, d, t, y, qc, dqc, last_c, err, ssz);
+              break;
+            case B200_Q_B:
+              if (we) quant_epilogue<W, H, B200_Q_B, true>(a, d, t, y, qc, dqc, last_c, err, ssz);
+              else quant_epilogue<W, H, B200_Q_B, false>(a, d, t, y, qc, dqc, last_c, err, ssz);
+              break;
+            default:
+              if (we) quant_epilogue<W, H, B200_Q_B_HBD, true>(a, d, t, y, qc, dqc, last_c, err, ssz);
+              else quant_epilogue<W, H, B200_Q_B_HBD, false>(a, d, t, y, qc, dqc, last_c, err, ssz);
+              break;
+          }
+        }
       }
       if (a.q_kind != B200_Q_NONE) {
-        int32_t qc[C::Wk], dqc[C::Wk];
-        const bool we = (a.flags & B200_TXQ_BLOCK_ERROR) != 0;
-        switch (a.q_kind) {
-          case B200_Q_FP:
-            if (we) quant_epilogue<W, H, B200_Q_FP, true>(a, d, t, y, qc, dqc, last_c, err, ssz);
-            else quant_epilogue<W, H, B200_Q_FP, false>(a, d, t, y, qc, dqc, last_c, err, ssz);
-            break;
-          case B200_Q_FP_HBD:
-            if (we) quant_epilogue<W, H, B200_Q_FP_HBD, true>(a, d, t, y, qc, dqc, last_c, err, ssz);
-            else quant_epilogue<W, H, B200_Q_FP_HBD, false>(a, d, t, y, qc, dqc, last_c, err, ssz);
-            break;
-          case B200_Q_B:
-            if (we) quant_epilogue<W, H, B200_Q_B, true>(a, d, t, y, qc, dqc, last_c, err, ssz);
-            else quant_epilogue<W, H, B200_Q_B, false>(a, d, t, y, qc, dqc, last_c, err, ssz);
-            break;
-          default:
-            if (we) quant_epilogue<W, H, B200_Q_B_HBD, true>(a, d, t, y, qc, dqc, last_c, err, ssz);
-            else quant_epilogue<W, H, B200_Q_B_HBD, false>(a, d, t, y, qc, dqc, last_c, err, ssz);
-            break;
+        int eob = 0;
+        if (last_c >= 0) {
+          const int cls = d.tx_type < 10 ? 0 : ((d.tx_type & 1) ? 2 : 1);
+          eob = a.iscan3[cls * (C::Wk * C::Hk) + last_c * C::Hk + t] + 1;
         }
+        // reduce over the Hk lanes that own the block's rows (xor stays inside the group)
 #pragma unroll
-        for (int c = 0; c < C::Wk; ++c) a.qcoeff[obase + c * C::Hk] = qc[c];
-#pragma unroll
-        for (int c = 0; c < C::Wk; ++c) a.dqcoeff[obase + c * C::Hk] = dqc[c];
-      }
-    }
-    if (a.q_kind != B200_Q_NONE) {
-      int eob = 0;
-      if (last_c >= 0) {
-        const int cls = d.tx_type < 10 ? 0 : ((d.tx_type & 1) ? 2 : 1);
-        eob = a.iscan3[cls * (C::Wk * C::Hk) + last_c * C::Hk + t] + 1;
-      }
-#pragma unroll
-      for (int o = C::NT / 2; o > 0; o >>= 1) {
-        const int e2 = __shfl_xor_sync(0xffffffffu, eob, o);
-        eob = e2 > eob ? e2 : eob;
-      }
-      if (a.flags & B200_TXQ_BLOCK_ERROR) {
-#pragma unroll
-        for (int o = C::NT / 2; o > 0; o >>= 1) {
-          err += __shfl_xor_sync(0xffffffffu, err, o);
-          ssz += __shfl_xor_sync(0xffffffffu, ssz, o);
+        for (int o = C::Hk / 2; o > 0; o >>= 1) {
+          const int e2 = __shfl_xor_sync(0xffffffffu, eob, o);
+          eob = e2 > eob ? e2 : eob;
         }
-      }
-      if (active && t == 0) {
-        a.eob[bi] = (uint16_t)eob;
-        if ((a.flags & B200_TXQ_BLOCK_ERROR) && a.dist) {
-          if (a.q_kind == B200_Q_FP_HBD || a.q_kind == B200_Q_B_HBD) {
-            const int sh = 2 * (a.bd - 8);
-            const int64_t r = sh > 0 ? ((int64_t)1 << (sh - 1)) : 0;
-            err = (err + r) >> sh;
-            ssz = (ssz + r) >> sh;
+        if (a.flags & B200_TXQ_BLOCK_ERROR) {
+#pragma unroll
+          for (int o = C::Hk / 2; o > 0; o >>= 1) {
+            err += __shfl_xor_sync(0xffffffffu, err, o);
+            ssz += __shfl_xor_sync(0xffffffffu, ssz, o);
           }
-          a.dist[2 * (size_t)bi] = err;
-          a.dist[2 * (size_t)bi + 1] = ssz;
+        }
+        if (act && t == 0) {
+          a.eob[bi] = (uint16_t)eob;
+          if ((a.flags & B200_TXQ_BLOCK_ERROR) && a.dist) {
+            if (a.q_kind == B200_Q_FP_HBD || a.q_kind == B200_Q_B_HBD) {
+              const int sh = 2 * (a.bd - 8);
+              const int64_t r = sh > 0 ? ((int64_t)1 << (sh - 1)) : 0;
+              err = (err + r) >> sh;
+              ssz = (ssz + r) >> sh;
+            }
+            a.dist[2 * (size_t)bi] = err;
+            a.dist[2 * (size_t)bi + 1] = ssz;
+          }
         }
       }
     }
@@ -570,7 +562,7 @@ TxqKernelInfo txq_kernel_info() {
   TxqKernelInfo k;
   k.fn = txq_kernel<W, H, IN>;
   k.smem_bytes = SmemCfg<W, H, IN>::kCtaBytes;
-  k.bpw = TxCfg<W, H>::BPW;
+  k.bpw = TxCfg<W, H>::TB;
   return k;
 }
 
