@@ -123,3 +123,73 @@ def qrow_from_oracle(row):
     for name in ("zbin", "round", "quant", "quant_shift", "round_fp", "quant_fp", "dequant"):
         r[name] = [getattr(row, name)[0], getattr(row, name)[1]]
     return r
+
+
+# ------------------------------------------------------------------ device buffers ----
+class DevBuf:
+    """device allocation owned by a Context (b200_malloc / b200_free)"""
+
+    def __init__(self, ctx, nbytes):
+        self.ctx, self.nbytes = ctx, nbytes
+        self.ptr = C.c_void_p()
+        check(lib().b200_malloc(ctx.h, C.c_size_t(max(nbytes, 1)), C.byref(self.ptr)))
+
+    def free(self):
+        if self.ptr and self.ctx.h:  # a closed context has already released its device
+            lib().b200_free(self.ctx.h, self.ptr)
+        self.ptr = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def to_device(ctx, arr):
+    arr = np.ascontiguousarray(arr)
+    buf = DevBuf(ctx, arr.nbytes)
+    check(lib().b200_h2d(ctx.h, buf.ptr, vp(arr), C.c_size_t(arr.nbytes)))
+    ctx.sync()
+    return buf
+
+
+def to_host(ctx, buf, dtype, count):
+    out = np.zeros(count, dtype)
+    check(lib().b200_d2h(ctx.h, vp(out), buf.ptr, C.c_size_t(out.nbytes)))
+    ctx.sync()
+    return out
+
+
+PIXBLOCK_DTYPE = np.dtype([("a_offset", "<u4"), ("b_offset", "<u4"), ("aux_offset", "<u4"),
+                           ("a_stride", "<u2"), ("b_stride", "<u2"), ("w", "u1"), ("h", "u1"),
+                           ("xoff", "u1"), ("yoff", "u1")])
+QUANTBLOCK_DTYPE = np.dtype([("coeff_offset", "<u4"), ("out_offset", "<u4"), ("iscan_offset", "<u4"),
+                             ("qm_offset", "<u4"), ("n_coeffs", "<u2"), ("qrow", "<u2"),
+                             ("log_scale", "u1"), ("reserved", "u1", 3)])
+ERRBLOCK_DTYPE = np.dtype([("coeff_offset", "<u4"), ("dqcoeff_offset", "<u4"), ("n_coeffs", "<u4"),
+                           ("aux_offset", "<u4")])
+assert PIXBLOCK_DTYPE.itemsize == 20 and QUANTBLOCK_DTYPE.itemsize == 24 and ERRBLOCK_DTYPE.itemsize == 16
+
+PIX_SAD, PIX_SAD_SKIP, PIX_SAD_AVG, PIX_VAR, PIX_MSE, PIX_SUBPEL_VAR, PIX_SSE = range(7)
+(QUANT_FP, QUANT_FP_HBD, QUANT_LP, QUANT_B, QUANT_B_HBD, QUANT_B_ADAPT, QUANT_B_ADAPT_HBD) = range(7)
+ERR_LOWBD, ERR_LP, ERR_HBD, ERR_QM = range(4)
+
+
+class PixLaunch(C.Structure):
+    _fields_ = [("op", C.c_int), ("highbd", C.c_int), ("bd", C.c_int), ("n_blocks", C.c_int),
+                ("blocks", C.c_void_p), ("a", C.c_void_p), ("b", C.c_void_p), ("aux", C.c_void_p),
+                ("out", C.c_void_p)]
+
+
+class QuantLaunch(C.Structure):
+    _fields_ = [("kind", C.c_int), ("n_blocks", C.c_int), ("blocks", C.c_void_p),
+                ("coeff", C.c_void_p), ("qrows", C.c_void_p), ("iscan", C.c_void_p),
+                ("qm", C.c_void_p), ("iqm", C.c_void_p), ("qcoeff", C.c_void_p),
+                ("dqcoeff", C.c_void_p), ("eob", C.c_void_p)]
+
+
+class ErrLaunch(C.Structure):
+    _fields_ = [("kind", C.c_int), ("bd", C.c_int), ("n_blocks", C.c_int), ("blocks", C.c_void_p),
+                ("coeff", C.c_void_p), ("dqcoeff", C.c_void_p), ("qm", C.c_void_p),
+                ("scan", C.c_void_p), ("out", C.c_void_p)]

@@ -174,6 +174,118 @@ int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int bd, unsigned
                         int32_t *coeff, int32_t *qcoeff, int32_t *dqcoeff,
                         size_t out_elems, uint16_t *eob, int64_t *dist);
 
+
+/* ------------------------------------------------ stand-alone quantiser batch ---- */
+/* The quantisers as separate launches over coefficient buffers that already sit in
+ * device memory (e.g. re-quantising one transform at several qindexes).  One warp per
+ * block.  Semantics per kind: the reference function named beside it. */
+enum {
+  B200_QUANT_FP = 0,          /* av1_quantize_fp* (av1_quantize.c:70-123,201-264), qm optional */
+  B200_QUANT_FP_HBD = 1,      /* av1_highbd_quantize_fp (av1_quantize.c:125-198,565) */
+  B200_QUANT_LP = 2,          /* av1_quantize_lp (av1_quantize.c:212), int16 in/out */
+  B200_QUANT_B = 3,           /* aom_quantize_b_helper (aom_dsp/quantize.c:108) */
+  B200_QUANT_B_HBD = 4,       /* aom_highbd_quantize_b_helper (aom_dsp/quantize.c:261) */
+  B200_QUANT_B_ADAPT = 5,     /* aom_quantize_b_adaptive_helper (aom_dsp/quantize.c:16) */
+  B200_QUANT_B_ADAPT_HBD = 6  /* aom_highbd_quantize_b_adaptive_helper (quantize.c:173) */
+};
+typedef struct {
+  uint32_t coeff_offset; /* elements into coeff (int32; int16 for B200_QUANT_LP) */
+  uint32_t out_offset;   /* elements into qcoeff / dqcoeff */
+  uint32_t iscan_offset; /* int16 elements into iscan */
+  uint32_t qm_offset;    /* elements into qm / iqm (ignored when those are NULL) */
+  uint16_t n_coeffs;     /* 16 .. 1024 */
+  uint16_t qrow;
+  uint8_t log_scale;     /* 0, 1, 2 (av1_get_tx_scale, av1/common/idct.c:24) */
+  uint8_t reserved[3];
+} B200QuantBlock; /* 24 bytes */
+typedef struct {
+  int kind; /* B200_QUANT_* */
+  int n_blocks;
+  const B200QuantBlock *blocks; /* device */
+  const void *coeff;            /* device */
+  const B200QRow *qrows;        /* device */
+  const int16_t *iscan;         /* device */
+  const uint8_t *qm, *iqm;      /* device or NULL (qm_val_t weights, AOM_QM_BITS = 5) */
+  void *qcoeff, *dqcoeff;       /* device */
+  uint16_t *eob;                /* device */
+} B200QuantLaunch;
+int b200_quant_launch(b200_ctx *ctx, const B200QuantLaunch *launch, void *stream);
+
+/* ------------------------------------------------------ block error batch -------- */
+enum {
+  B200_ERR_LOWBD = 0, /* av1_block_error (rdopt.c:635): squares formed in 32-bit int */
+  B200_ERR_LP = 1,    /* av1_block_error_lp (rdopt.c:650): int16 inputs */
+  B200_ERR_HBD = 2,   /* av1_highbd_block_error (rdopt.c:663): rounded >> 2(bd-8) */
+  B200_ERR_QM = 3     /* av1_block_error_qm (tx_search.c:1049, fork): qmatrix weighted */
+};
+typedef struct {
+  uint32_t coeff_offset, dqcoeff_offset;
+  uint32_t n_coeffs;
+  uint32_t aux_offset; /* B200_ERR_QM: element offset into qm and scan */
+} B200ErrBlock; /* 16 bytes */
+typedef struct {
+  int kind, bd, n_blocks;
+  const B200ErrBlock *blocks; /* device */
+  const void *coeff, *dqcoeff; /* device: int32 (int16 for B200_ERR_LP) */
+  const uint8_t *qm;           /* device, B200_ERR_QM only */
+  const int16_t *scan;         /* device, B200_ERR_QM only */
+  int64_t *out;                /* device: {error, ssz} per block */
+} B200ErrLaunch;
+int b200_block_error_launch(b200_ctx *ctx, const B200ErrLaunch *launch, void *stream);
+
+/* ------------------------------------------- pixel block batch (SAD / variance) -- */
+/* One warp per (a, b) block pair.  `a` follows the first pointer argument of the
+ * reference function, `b` the second (SAD: a = src, b = ref; variance: a = src_ptr,
+ * b = ref_ptr; sub-pel variance: a is the interpolated operand). */
+enum {
+  B200_PIX_SAD = 0,      /* aom_sadWxH (aom_dsp/sad.c:45)                    out0 = sad */
+  B200_PIX_SAD_SKIP = 1, /* aom_sad_skip_WxH (sad.c:65)                      out0 = sad */
+  B200_PIX_SAD_AVG = 2,  /* aom_sadWxH_avg (sad.c:50), aux = second_pred     out0 = sad */
+  B200_PIX_VAR = 3,      /* aom_varianceWxH (variance.c:123)          out0 = var, out1 = sse */
+  B200_PIX_MSE = 4,      /* aom_mseWxH (variance.c:235)               out0 = sse, out1 = sse */
+  B200_PIX_SUBPEL_VAR = 5, /* aom_sub_pixel_varianceWxH (variance.c:132)   out0 = var, out1 = sse */
+  B200_PIX_SSE = 6       /* aom_sse (aom_dsp/sse.c:19)         out0 = low 32, out1 = high 32 */
+};
+typedef struct {
+  uint32_t a_offset, b_offset; /* pixels from the plane bases */
+  uint32_t aux_offset;         /* second_pred offset (B200_PIX_SAD_AVG) */
+  uint16_t a_stride, b_stride;
+  uint8_t w, h;                /* 4 .. 128 */
+  uint8_t xoff, yoff;          /* 1/8-pel bilinear offsets 0..7 (B200_PIX_SUBPEL_VAR) */
+} B200PixBlock; /* 20 bytes */
+typedef struct {
+  int op;      /* B200_PIX_* */
+  int highbd;  /* 0: uint8 pixels, 1: uint16 pixels */
+  int bd;      /* 8 / 10 / 12: variance rounding of aom_highbd_{8,10,12}_variance */
+  int n_blocks;
+  const B200PixBlock *blocks; /* device */
+  const void *a, *b, *aux;    /* device pixel planes */
+  uint32_t *out;              /* device: 2 entries per block */
+} B200PixLaunch;
+int b200_pix_launch(b200_ctx *ctx, const B200PixLaunch *launch, void *stream);
+
+/* aom_subtract_block / aom_highbd_subtract_block (aom_dsp/subtract.c:20,35) over a batch:
+ * diff = a - b for every block (a = src, b = pred); diff rows are `w` apart. */
+typedef struct {
+  int highbd, n_blocks;
+  const B200PixBlock *blocks; /* aux_offset = element offset of the block in diff */
+  const void *a, *b;
+  int16_t *diff;
+} B200SubtractLaunch;
+int b200_subtract_launch(b200_ctx *ctx, const B200SubtractLaunch *launch, void *stream);
+
+/* aom_upsampled_pred / aom_highbd_upsampled_pred (av1/encoder/reconinter_enc.c:424,562),
+ * unscaled references: separable sub-pel interpolation with 2 / 4 / 8 taps; one block
+ * per descriptor: a = reference plane, aux_offset = element offset in comp_pred
+ * (w*h contiguous), xoff / yoff = subpel_x_q3 / subpel_y_q3. */
+typedef struct {
+  int highbd, bd, taps, n_blocks;
+  const B200PixBlock *blocks;
+  const void *ref;
+  void *comp_pred;
+} B200UpsampleLaunch;
+int b200_upsampled_pred_launch(b200_ctx *ctx, const B200UpsampleLaunch *launch, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

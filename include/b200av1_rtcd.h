@@ -1,0 +1,220 @@
+/*
+ * b200av1_rtcd.h -- drop-in tier: the reference's RTCD prototypes with a `_b200` suffix.
+ *
+ * libaom dispatches its DSP kernels through run-time CPU dispatch ("RTCD"): for every
+ * `add_proto` in av1/common/av1_rtcd_defs.pl and aom_dsp/aom_dsp_rtcd_defs.pl the
+ * generated header declares one prototype per flavour (`_c`, `_sse2`, `_avx2`, ...) and
+ * either a `#define name name_c` or a function pointer `name` set in
+ * setup_rtcd_internal() (build/cmake/rtcd.pl:168-290).  This header adds the flavour
+ * `_b200` for the hot-path members, with EXACTLY the reference argument lists, so that
+ * a maintainer can `specialize` them.  Each call moves one block to
+ * the GPU, runs the same kernels as the batched tier on a batch of one, and copies the
+ * result back: correct and complete, but latency-bound -- throughput comes from the
+ * batched tier (b200av1.h).  Calls are serialised on the default context
+ * (b200_default_ctx()); a CUDA failure is fatal (abort) because these signatures have
+ * no error channel.
+ *
+ * High-bit-depth pixel pointers follow the reference convention: uint16_t data passed
+ * as CONVERT_TO_BYTEPTR(ptr) (aom_ports/mem.h:79-80), i.e. (uint8_t *)((uintptr_t)p >> 1).
+ */
+#ifndef B200AV1_RTCD_H_
+#define B200AV1_RTCD_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int32_t b200_tran_low_t; /* tran_low_t, aom_dsp/aom_dsp_common.h:57 */
+typedef uint8_t b200_qm_val_t;   /* qm_val_t */
+
+/* TxfmParam, aom_dsp/txfm_common.h:84-101 (layout-compatible) */
+typedef struct {
+  uint8_t tx_type;     /* TX_TYPE */
+  uint8_t tx_size;     /* TX_SIZE */
+  int lossless;
+  int bd;
+  int is_hbd;
+  uint8_t tx_set_type; /* TxSetType */
+  int eob;
+} B200TxfmParam;
+
+/* ---- forward transforms: av1_rtcd_defs.pl:351-399 (av1_fwd_txfm2d_WxH), :269 ---- */
+#define B200_DECL_FWD_TXFM(W, H)                                                           \
+  void av1_fwd_txfm2d_##W##x##H##_b200(const int16_t *input, int32_t *output, int stride, \
+                                       uint8_t tx_type, int bd);
+B200_DECL_FWD_TXFM(4, 4)
+B200_DECL_FWD_TXFM(8, 8)
+B200_DECL_FWD_TXFM(16, 16)
+B200_DECL_FWD_TXFM(32, 32)
+B200_DECL_FWD_TXFM(64, 64)
+B200_DECL_FWD_TXFM(4, 8)
+B200_DECL_FWD_TXFM(8, 4)
+B200_DECL_FWD_TXFM(8, 16)
+B200_DECL_FWD_TXFM(16, 8)
+B200_DECL_FWD_TXFM(16, 32)
+B200_DECL_FWD_TXFM(32, 16)
+B200_DECL_FWD_TXFM(32, 64)
+B200_DECL_FWD_TXFM(64, 32)
+B200_DECL_FWD_TXFM(4, 16)
+B200_DECL_FWD_TXFM(16, 4)
+B200_DECL_FWD_TXFM(8, 32)
+B200_DECL_FWD_TXFM(32, 8)
+B200_DECL_FWD_TXFM(16, 64)
+B200_DECL_FWD_TXFM(64, 16)
+/* av1_lowbd_fwd_txfm (av1_rtcd_defs.pl:349; hybrid_fwd_txfm.c:241): size switch.
+ * txfm_param->lossless (WHT) is not part of this path and is rejected (abort). */
+void av1_lowbd_fwd_txfm_b200(const int16_t *src_diff, b200_tran_low_t *coeff, int diff_stride,
+                             B200TxfmParam *txfm_param);
+
+/* ---- quantisers: av1_rtcd_defs.pl:334-347,428; aom_dsp_rtcd_defs.pl:655-694 ---- */
+#define B200_QUANT_ARGS                                                                       \
+  const b200_tran_low_t *coeff_ptr, intptr_t n_coeffs, const int16_t *zbin_ptr,               \
+      const int16_t *round_ptr, const int16_t *quant_ptr, const int16_t *quant_shift_ptr,     \
+      b200_tran_low_t *qcoeff_ptr, b200_tran_low_t *dqcoeff_ptr, const int16_t *dequant_ptr,  \
+      uint16_t *eob_ptr, const int16_t *scan, const int16_t *iscan
+void av1_quantize_fp_b200(B200_QUANT_ARGS);
+void av1_quantize_fp_32x32_b200(B200_QUANT_ARGS);
+void av1_quantize_fp_64x64_b200(B200_QUANT_ARGS);
+void av1_highbd_quantize_fp_b200(B200_QUANT_ARGS, int log_scale);
+void av1_quantize_lp_b200(const int16_t *coeff_ptr, intptr_t n_coeffs, const int16_t *round_ptr,
+                          const int16_t *quant_ptr, int16_t *qcoeff_ptr, int16_t *dqcoeff_ptr,
+                          const int16_t *dequant_ptr, uint16_t *eob_ptr, const int16_t *scan,
+                          const int16_t *iscan);
+void aom_quantize_b_b200(B200_QUANT_ARGS);
+void aom_quantize_b_32x32_b200(B200_QUANT_ARGS);
+void aom_quantize_b_64x64_b200(B200_QUANT_ARGS);
+void aom_quantize_b_adaptive_b200(B200_QUANT_ARGS);
+void aom_quantize_b_32x32_adaptive_b200(B200_QUANT_ARGS);
+void aom_quantize_b_64x64_adaptive_b200(B200_QUANT_ARGS);
+void aom_highbd_quantize_b_b200(B200_QUANT_ARGS);
+void aom_highbd_quantize_b_32x32_b200(B200_QUANT_ARGS);
+void aom_highbd_quantize_b_64x64_b200(B200_QUANT_ARGS);
+void aom_highbd_quantize_b_adaptive_b200(B200_QUANT_ARGS);
+void aom_highbd_quantize_b_32x32_adaptive_b200(B200_QUANT_ARGS);
+void aom_highbd_quantize_b_64x64_adaptive_b200(B200_QUANT_ARGS);
+void aom_quantize_b_helper_b200(B200_QUANT_ARGS, const b200_qm_val_t *qm_ptr,
+                                const b200_qm_val_t *iqm_ptr, const int log_scale);
+void aom_highbd_quantize_b_helper_b200(B200_QUANT_ARGS, const b200_qm_val_t *qm_ptr,
+                                       const b200_qm_val_t *iqm_ptr, const int log_scale);
+
+/* ---- transform-domain distortion: av1_rtcd_defs.pl:328-332,423 ---- */
+int64_t av1_block_error_b200(const b200_tran_low_t *coeff, const b200_tran_low_t *dqcoeff,
+                             intptr_t block_size, int64_t *ssz);
+int64_t av1_block_error_lp_b200(const int16_t *coeff, const int16_t *dqcoeff, intptr_t block_size);
+int64_t av1_highbd_block_error_b200(const b200_tran_low_t *coeff, const b200_tran_low_t *dqcoeff,
+                                    intptr_t block_size, int64_t *ssz, int bd);
+
+/* ---- residual / SSE: aom_dsp_rtcd_defs.pl:725-739 ---- */
+void aom_subtract_block_b200(int rows, int cols, int16_t *diff_ptr, ptrdiff_t diff_stride,
+                             const uint8_t *src_ptr, ptrdiff_t src_stride,
+                             const uint8_t *pred_ptr, ptrdiff_t pred_stride);
+void aom_highbd_subtract_block_b200(int rows, int cols, int16_t *diff_ptr, ptrdiff_t diff_stride,
+                                    const uint8_t *src_ptr, ptrdiff_t src_stride,
+                                    const uint8_t *pred_ptr, ptrdiff_t pred_stride);
+int64_t aom_sse_b200(const uint8_t *a, int a_stride, const uint8_t *b, int b_stride, int width,
+                     int height);
+int64_t aom_highbd_sse_b200(const uint8_t *a8, int a_stride, const uint8_t *b8, int b_stride,
+                            int width, int height);
+
+/* ---- SAD / variance: aom_dsp_rtcd_defs.pl:762-768,879-885,1001-1008,1136-1145,
+ *      1303-1323,1349-1367,1466-1516; 22 block sizes (:42-58) ---- */
+#define B200_DECL_BLOCK_FNS(W, H)                                                                 \
+  unsigned int aom_sad##W##x##H##_b200(const uint8_t *src_ptr, int src_stride,                     \
+                                       const uint8_t *ref_ptr, int ref_stride);                    \
+  unsigned int aom_sad_skip_##W##x##H##_b200(const uint8_t *src_ptr, int src_stride,               \
+                                             const uint8_t *ref_ptr, int ref_stride);              \
+  unsigned int aom_sad##W##x##H##_avg_b200(const uint8_t *src_ptr, int src_stride,                 \
+                                           const uint8_t *ref_ptr, int ref_stride,                 \
+                                           const uint8_t *second_pred);                            \
+  void aom_sad##W##x##H##x4d_b200(const uint8_t *src_ptr, int src_stride,                          \
+                                  const uint8_t *const ref_ptr[4], int ref_stride,                 \
+                                  uint32_t sad_array[4]);                                          \
+  void aom_sad##W##x##H##x3d_b200(const uint8_t *src_ptr, int src_stride,                          \
+                                  const uint8_t *const ref_ptr[4], int ref_stride,                 \
+                                  uint32_t sad_array[4]);                                          \
+  void aom_sad_skip_##W##x##H##x4d_b200(const uint8_t *src_ptr, int src_stride,                    \
+                                        const uint8_t *const ref_ptr[4], int ref_stride,           \
+                                        uint32_t sad_array[4]);                                    \
+  unsigned int aom_highbd_sad##W##x##H##_b200(const uint8_t *src_ptr, int src_stride,              \
+                                              const uint8_t *ref_ptr, int ref_stride);             \
+  unsigned int aom_highbd_sad_skip_##W##x##H##_b200(const uint8_t *src_ptr, int src_stride,        \
+                                                    const uint8_t *ref_ptr, int ref_stride);       \
+  void aom_highbd_sad##W##x##H##x4d_b200(const uint8_t *src_ptr, int src_stride,                   \
+                                         const uint8_t *const ref_ptr[4], int ref_stride,          \
+                                         uint32_t sad_array[4]);                                   \
+  unsigned int aom_variance##W##x##H##_b200(const uint8_t *src_ptr, int source_stride,             \
+                                            const uint8_t *ref_ptr, int ref_stride,                \
+                                            unsigned int *sse);                                    \
+  uint32_t aom_sub_pixel_variance##W##x##H##_b200(const uint8_t *src_ptr, int source_stride,       \
+                                                  int xoffset, int yoffset,                        \
+                                                  const uint8_t *ref_ptr, int ref_stride,          \
+                                                  uint32_t *sse);                                  \
+  unsigned int aom_highbd_8_variance##W##x##H##_b200(const uint8_t *src_ptr, int source_stride,    \
+                                                     const uint8_t *ref_ptr, int ref_stride,       \
+                                                     unsigned int *sse);                           \
+  unsigned int aom_highbd_10_variance##W##x##H##_b200(const uint8_t *src_ptr, int source_stride,   \
+                                                      const uint8_t *ref_ptr, int ref_stride,      \
+                                                      unsigned int *sse);                          \
+  unsigned int aom_highbd_12_variance##W##x##H##_b200(const uint8_t *src_ptr, int source_stride,   \
+                                                      const uint8_t *ref_ptr, int ref_stride,      \
+                                                      unsigned int *sse);                          \
+  uint32_t aom_highbd_8_sub_pixel_variance##W##x##H##_b200(                                        \
+      const uint8_t *src_ptr, int source_stride, int xoffset, int yoffset,                         \
+      const uint8_t *ref_ptr, int ref_stride, uint32_t *sse);                                      \
+  uint32_t aom_highbd_10_sub_pixel_variance##W##x##H##_b200(                                       \
+      const uint8_t *src_ptr, int source_stride, int xoffset, int yoffset,                         \
+      const uint8_t *ref_ptr, int ref_stride, uint32_t *sse);                                      \
+  uint32_t aom_highbd_12_sub_pixel_variance##W##x##H##_b200(                                       \
+      const uint8_t *src_ptr, int source_stride, int xoffset, int yoffset,                         \
+      const uint8_t *ref_ptr, int ref_stride, uint32_t *sse);
+B200_DECL_BLOCK_FNS(128, 128)
+B200_DECL_BLOCK_FNS(128, 64)
+B200_DECL_BLOCK_FNS(64, 128)
+B200_DECL_BLOCK_FNS(64, 64)
+B200_DECL_BLOCK_FNS(64, 32)
+B200_DECL_BLOCK_FNS(32, 64)
+B200_DECL_BLOCK_FNS(32, 32)
+B200_DECL_BLOCK_FNS(32, 16)
+B200_DECL_BLOCK_FNS(16, 32)
+B200_DECL_BLOCK_FNS(16, 16)
+B200_DECL_BLOCK_FNS(16, 8)
+B200_DECL_BLOCK_FNS(8, 16)
+B200_DECL_BLOCK_FNS(8, 8)
+B200_DECL_BLOCK_FNS(8, 4)
+B200_DECL_BLOCK_FNS(4, 8)
+B200_DECL_BLOCK_FNS(4, 4)
+B200_DECL_BLOCK_FNS(4, 16)
+B200_DECL_BLOCK_FNS(16, 4)
+B200_DECL_BLOCK_FNS(8, 32)
+B200_DECL_BLOCK_FNS(32, 8)
+B200_DECL_BLOCK_FNS(16, 64)
+B200_DECL_BLOCK_FNS(64, 16)
+/* aom_mse16x16 / 16x8 / 8x16 / 8x8 (aom_dsp_rtcd_defs.pl:1349-1352) */
+unsigned int aom_mse16x16_b200(const uint8_t *src_ptr, int source_stride, const uint8_t *ref_ptr,
+                               int recon_stride, unsigned int *sse);
+unsigned int aom_mse16x8_b200(const uint8_t *src_ptr, int source_stride, const uint8_t *ref_ptr,
+                              int recon_stride, unsigned int *sse);
+unsigned int aom_mse8x16_b200(const uint8_t *src_ptr, int source_stride, const uint8_t *ref_ptr,
+                              int recon_stride, unsigned int *sse);
+unsigned int aom_mse8x8_b200(const uint8_t *src_ptr, int source_stride, const uint8_t *ref_ptr,
+                             int recon_stride, unsigned int *sse);
+
+/* ---- sub-pel predictor: av1_rtcd_defs.pl:282-285,309-312.  xd / cm / mv are only used by
+ * the reference for scaled references; this flavour implements the unscaled branch
+ * (reconinter_enc.c:461-495) and ignores them. ---- */
+void aom_upsampled_pred_b200(void *xd, const void *cm, int mi_row, int mi_col, const void *mv,
+                             uint8_t *comp_pred, int width, int height, int subpel_x_q3,
+                             int subpel_y_q3, const uint8_t *ref, int ref_stride,
+                             int subpel_search);
+void aom_highbd_upsampled_pred_b200(void *xd, const void *cm, int mi_row, int mi_col,
+                                    const void *mv, uint8_t *comp_pred8, int width, int height,
+                                    int subpel_x_q3, int subpel_y_q3, const uint8_t *ref8,
+                                    int ref_stride, int bd, int subpel_search);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200AV1_RTCD_H_ */
