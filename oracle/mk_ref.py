@@ -97,7 +97,8 @@ def main():
     os.makedirs(cfgdir, exist_ok=True)
     lib = os.path.join(OUT, "libaomref.so")
     stubs = os.path.join(OUT, "auto_stubs.c")
-    newest = os.path.getmtime(__file__)
+    newest = max(os.path.getmtime(__file__), os.path.getmtime(os.path.join(HERE, "ref_shim.c")),
+                 os.path.getmtime(os.path.join(HERE, "av1o_me.h")))
     if os.path.exists(lib) and os.path.getmtime(lib) > newest and "--force" not in sys.argv:
         print("mk_ref: up to date")
         return 0
@@ -109,11 +110,12 @@ def main():
     objdir = os.path.join(OUT, "obj")
     os.makedirs(objdir, exist_ok=True)
     procs = []
-    for s in SOURCES:
-        o = os.path.join(objdir, s.replace("/", "_")[:-2] + ".o")
+    srcs = [os.path.join(REF, s) for s in SOURCES] + [os.path.join(HERE, "ref_shim.c")]
+    for s in srcs:
+        o = os.path.join(objdir, os.path.relpath(s, "/").replace("/", "_")[:-2] + ".o")
         objs.append(o)
         procs.append(subprocess.Popen(cmd[:1] + ["-c"] + [c for c in cmd[1:] if c != "-shared"]
-                                      + [os.path.join(REF, s), "-o", o]))
+                                      + ["-I" + HERE, s, "-o", o]))
     for p in procs:
         if p.wait() != 0:
             raise SystemExit("mk_ref: compile failed")

@@ -172,3 +172,60 @@ def oracle_txq_batch(src, blocks, rows, q_kind, bd, out_elems, in_kind=0, pred=N
                 err = O.av1o_block_error(ptr(c, i32p), ptr(d, i32p), C.c_ssize_t(n), C.byref(ssz))
             dist[i] = (err, ssz.value)
     return coeff, qc, dq, eob, dist
+
+
+# ------------------------------------------------------------------ motion search ----
+class MeParams(C.Structure):
+    """oracle/av1o_me.h Av1oMeParams"""
+    _fields_ = [("src", C.c_void_p), ("ref", C.c_void_p), ("src_stride", C.c_int),
+                ("ref_stride", C.c_int), ("bw", C.c_int), ("bh", C.c_int), ("highbd", C.c_int),
+                ("bd", C.c_int), ("col_min", C.c_int), ("col_max", C.c_int), ("row_min", C.c_int),
+                ("row_max", C.c_int), ("search_method", C.c_int), ("step_param", C.c_int),
+                ("run_mesh_search", C.c_int), ("prune_mesh_search", C.c_int),
+                ("mesh_search_mv_diff_threshold", C.c_int), ("force_mesh_thresh", C.c_int),
+                ("mesh_range", C.c_int * 4), ("mesh_interval", C.c_int * 4),
+                ("fine_search_interval", C.c_int), ("use_skip_sad", C.c_int),
+                ("mv_cost_type", C.c_int), ("ref_mv_row", C.c_int), ("ref_mv_col", C.c_int),
+                ("sad_per_bit", C.c_int), ("error_per_bit", C.c_int), ("mvjcost", C.c_void_p),
+                ("mvcost0", C.c_void_p), ("mvcost1", C.c_void_p), ("start_row", C.c_int),
+                ("start_col", C.c_int), ("want_cost_list", C.c_int), ("want_second_best", C.c_int),
+                ("allow_hp", C.c_int), ("forced_stop", C.c_int), ("iters_per_step", C.c_int),
+                ("subpel_search_type", C.c_int), ("sp_col_min", C.c_int), ("sp_col_max", C.c_int),
+                ("sp_row_min", C.c_int), ("sp_row_max", C.c_int), ("sp_start_row", C.c_int),
+                ("sp_start_col", C.c_int)]
+
+
+class MeResult(C.Structure):
+    _fields_ = [("best_row", C.c_int), ("best_col", C.c_int), ("second_row", C.c_int),
+                ("second_col", C.c_int), ("cost_list", C.c_int * 5), ("ret", C.c_int),
+                ("distortion", C.c_int), ("sse", C.c_uint)]
+
+    def key(self, subpel=False):
+        if subpel:
+            return (self.best_row, self.best_col, self.ret, self.distortion, self.sse)
+        return (self.best_row, self.best_col, self.second_row, self.second_col,
+                tuple(self.cost_list), self.ret)
+
+
+MV_TABLE_HALF = 1 << 14
+
+
+def make_mv_cost_tables(seed=0):
+    """synthetic monotone entropy-style cost tables: joint[4], comp[2][2*MV_TABLE_HALF+1]
+    (index by centred pointer), in 1/512-bit units like av1_fill_mv_costs produces"""
+    rng = np.random.default_rng(seed)
+    d = np.abs(np.arange(-MV_TABLE_HALF, MV_TABLE_HALF + 1))
+    base = (np.log2(d + 1.0) * 2 * 512 + 300).astype(np.int32)
+    t0 = (base + rng.integers(0, 40, base.size)).astype(np.int32)
+    t1 = (base + rng.integers(0, 40, base.size)).astype(np.int32)
+    joint = np.array([300, 900, 1000, 1500], np.int32)
+    return joint, t0, t1
+
+
+def mv_cost_ptrs(joint, t0, t1):
+    return (joint.ctypes.data, t0.ctypes.data + 4 * MV_TABLE_HALF, t1.ctypes.data + 4 * MV_TABLE_HALF)
+
+
+def bordered(img, border):
+    """replicate-pad like the encoder's frame border (aom_scale/yv12config.h:28-32)"""
+    return np.ascontiguousarray(np.pad(img, border, mode="edge"))

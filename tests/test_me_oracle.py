@@ -1,0 +1,59 @@
+"""Pin the oracle's motion search (oracle/av1o_mcomp.c) against the reference's own
+av1_full_pixel_search / av1_find_best_sub_pixel_tree called through oracle/ref_shim.c.
+The reference has no unit test for these loops, so the inputs are
+synthetic frames incl. flat regions that force SAD ties."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import harness as H
+import me_common as M
+
+pytestmark = [pytest.mark.ref, pytest.mark.skipif(not H.have_ref(), reason="oracle/_ref not built")]
+
+
+def run_both(fn_o, fn_r, p, subpel=False):
+    a, b = H.MeResult(), H.MeResult()
+    fn_o(C.byref(p), C.byref(a))
+    fn_r(C.byref(p), C.byref(b))
+    return a.key(subpel), b.key(subpel)
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+def test_full_pixel_search_vs_reference(bd):
+    O, R = H.oracle(), H.ref()
+    rng = np.random.default_rng(300 + bd)
+    tables = H.make_mv_cost_tables(1)
+    n = 0
+    for trial in range(10):
+        cur, refb = M.make_frames(rng, 256, 192, bd, flat=(trial % 3 == 2))
+        for (bw, bh) in M.FULLPEL_SIZES:
+            for rep in range(2):
+                p = M.random_fullpel_params(rng, cur, refb, bw, bh, bd, tables)
+                a, b = run_both(O.av1o_full_pixel_search, R.refshim_full_pixel_search, p)
+                assert a == b, (trial, bw, bh, p.search_method, p.step_param, p.run_mesh_search,
+                                p.use_skip_sad, p.mv_cost_type, a, b)
+                n += 1
+    assert n == 200
+
+
+def test_init_search_range():
+    O, R = H.oracle(), H.ref()
+    for size in (1, 8, 16, 32, 64, 128, 500, 1023, 2000):
+        assert O.av1o_init_search_range(size) == R.av1_init_search_range(size)
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+def test_sub_pixel_tree_vs_reference(bd):
+    O, R = H.oracle(), H.ref()
+    rng = np.random.default_rng(400 + bd)
+    tables = H.make_mv_cost_tables(2)
+    for trial in range(6):
+        cur, refb = M.make_frames(rng, 256, 192, bd, flat=(trial % 3 == 2))
+        for (bw, bh) in M.SUBPEL_SIZES:
+            for st in range(4):
+                p = M.random_subpel_params(rng, cur, refb, bw, bh, bd, tables, st)
+                a, b = run_both(O.av1o_find_best_sub_pixel_tree, R.refshim_find_best_sub_pixel_tree,
+                                p, subpel=True)
+                assert a == b, (trial, bw, bh, st, p.allow_hp, p.forced_stop, p.iters_per_step, a, b)
