@@ -63,6 +63,7 @@ extern "C" int b200_ctx_create(int device, b200_ctx **out) {
   B200_CUDA_TRY(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
   int rc = txq_init_device(ctx);
   if (rc == B200_OK) rc = blockops_init_device(ctx);
+  if (rc == B200_OK) rc = me_init_device(ctx);
   if (rc != B200_OK) {
     free(ctx);
     return rc;
@@ -77,6 +78,7 @@ extern "C" void b200_ctx_destroy(b200_ctx *ctx) {
   cudaStreamSynchronize(ctx->stream);
   if (ctx->d_iscan) cudaFree(ctx->d_iscan);
   if (ctx->d_scratch) cudaFree(ctx->d_scratch);
+  if (ctx->d_me_sites) cudaFree(ctx->d_me_sites);
   if (ctx->h_scratch) cudaFreeHost(ctx->h_scratch);
   cudaStreamDestroy(ctx->stream);
   free(ctx);

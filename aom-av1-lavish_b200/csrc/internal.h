@@ -41,6 +41,7 @@ struct b200_ctx {
   size_t scratch_bytes;
   void *h_scratch;
   size_t h_scratch_bytes;
+  void *d_me_sites;   // search-site tables of the four served methods, see me_host.cuh
 };
 
 namespace b200 {
@@ -48,5 +49,6 @@ namespace b200 {
 int txq_init_device(b200_ctx *ctx);
 int txq_launch(b200_ctx *ctx, const B200TxqLaunch &l, cudaStream_t s);
 int blockops_init_device(b200_ctx *ctx);
+int me_init_device(b200_ctx *ctx);
 int scratch_reserve(b200_ctx *ctx, size_t bytes);
 }  // namespace b200

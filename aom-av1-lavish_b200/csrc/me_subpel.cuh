@@ -1,0 +1,238 @@
+// me_subpel.cuh -- av1_find_best_sub_pixel_tree on one CTA (included by me.cu).
+// mcomp.c:2371-2551 (error functions, check_better), :2566-2779 (level checks),
+// :2781-2868 (centre error), :3128-3196 (the tree).  Unscaled references,
+// last_mv_search_list == NULL.
+#pragma once
+
+namespace b200 {
+namespace me {
+
+// Interpolation kernels at 1/8-pel positions: even rows of av1_bilinear_filters,
+// av1_sub_pel_filters_4, av1_sub_pel_filters_8 (av1/common/filter.h:110-135,210-222)
+__constant__ short c_me_taps[3][8][8] = {
+  { { 0, 0, 0, 128, 0, 0, 0, 0 }, { 0, 0, 0, 112, 16, 0, 0, 0 }, { 0, 0, 0, 96, 32, 0, 0, 0 },
+    { 0, 0, 0, 80, 48, 0, 0, 0 }, { 0, 0, 0, 64, 64, 0, 0, 0 }, { 0, 0, 0, 48, 80, 0, 0, 0 },
+    { 0, 0, 0, 32, 96, 0, 0, 0 }, { 0, 0, 0, 16, 112, 0, 0, 0 } },
+  { { 0, 0, 0, 128, 0, 0, 0, 0 }, { 0, 0, -8, 122, 18, -4, 0, 0 }, { 0, 0, -12, 110, 38, -8, 0, 0 },
+    { 0, 0, -14, 94, 58, -10, 0, 0 }, { 0, 0, -12, 76, 76, -12, 0, 0 }, { 0, 0, -10, 58, 94, -14, 0, 0 },
+    { 0, 0, -8, 38, 110, -12, 0, 0 }, { 0, 0, -4, 18, 122, -8, 0, 0 } },
+  { { 0, 0, 0, 128, 0, 0, 0, 0 }, { 0, 2, -10, 122, 18, -4, 0, 0 }, { 0, 2, -14, 110, 38, -10, 2, 0 },
+    { 0, 2, -16, 94, 58, -12, 2, 0 }, { 0, 2, -14, 76, 76, -14, 2, 0 }, { 0, 2, -12, 58, 94, -16, 2, 0 },
+    { 0, 2, -10, 38, 110, -14, 2, 0 }, { 0, 0, -4, 18, 122, -10, 2, 0 } },
+};
+__constant__ unsigned char c_me_bil[8][2] = { { 128, 0 }, { 112, 16 }, { 96, 32 }, { 80, 48 },
+                                              { 64, 64 }, { 48, 80 },  { 32, 96 }, { 16, 112 } };
+
+struct SubCtx {
+  Ctx k;
+  unsigned short *tmp;  // shared: (bh + 7) * bw horizontally filtered samples
+  long long *red;       // shared: 2 * kWarps partial sums
+  int search_type;      // B200_USE_*
+};
+
+__device__ __forceinline__ int ref_px(const Ctx &k, const unsigned char *p, long long idx) {
+  return k.px == 1 ? (int)p[idx] : (int)reinterpret_cast<const unsigned short *>(p)[idx];
+}
+__device__ __forceinline__ int src_px(const Ctx &k, int i) {
+  return k.px == 1 ? (int)k.src[i] : (int)reinterpret_cast<const unsigned short *>(k.src)[i];
+}
+
+// CTA-wide: variance of (pred(mv) - src).  mode 0: pred = full-pel reference block
+// (setup_center_error, vf(y, src)); 1: 2-tap bilinear svf (estimated_pref_error);
+// 2: aom_upsampled_pred with 2/4/8 taps then vf (upsampled_pref_error).
+__device__ unsigned cta_pref_error(const SubCtx &s, Mv mv, int mode, unsigned *sse_out) {
+  const Ctx &k = s.k;
+  const int bw = k.d.bw, bh = k.d.bh, n = bw * bh;
+  const int fr = mv.row >> 3, fc = mv.col >> 3, sx = mv.col & 7, sy = mv.row & 7;
+  const unsigned char *rp = k.ref0 + ((long long)fr * k.ref_pitch + fc) * k.px;
+  const int maxv = k.px == 1 ? 255 : (1 << k.l->bd) - 1;
+  long long sum = 0;
+  unsigned long long sse = 0;
+  __syncthreads();
+  if (mode == 0) {
+    for (int i = threadIdx.x; i < n; i += kThreads) {
+      const int y = i / bw, x = i - y * bw;
+      const int df = ref_px(k, rp, (long long)y * k.ref_pitch + x) - src_px(k, i);
+      sum += df;
+      sse += (unsigned)(df * df);
+    }
+  } else if (mode == 1) {
+    const int f0 = c_me_bil[sx][0], f1 = c_me_bil[sx][1], g0 = c_me_bil[sy][0], g1 = c_me_bil[sy][1];
+    for (int i = threadIdx.x; i < n; i += kThreads) {
+      const int y = i / bw, x = i - y * bw;
+      const long long o = (long long)y * k.ref_pitch + x;
+      const int h0 = (ref_px(k, rp, o) * f0 + ref_px(k, rp, o + 1) * f1 + 64) >> 7;
+      const int h1 = (ref_px(k, rp, o + k.ref_pitch) * f0 + ref_px(k, rp, o + k.ref_pitch + 1) * f1 + 64) >> 7;
+      int pv = (h0 * g0 + h1 * g1 + 64) >> 7;
+      if (k.px == 1) pv &= 0xff;  // uint8 store of the second pass (value <= 255 anyway)
+      const int df = pv - src_px(k, i);
+      sum += df;
+      sse += (unsigned)(df * df);
+    }
+  } else {
+    const int set = s.search_type == B200_USE_2_TAPS ? 0 : (s.search_type == B200_USE_4_TAPS ? 1 : 2);
+    const short *kx = c_me_taps[set][sx], *ky = c_me_taps[set][sy];
+    // horizontal pass (clipped to the pixel range like the reference's pixel-typed temp);
+    // rows -3..bh+3 only when a vertical filter follows
+    const int top = sy ? 3 : 0, ih = sy ? bh + 7 : bh;
+    for (int i = threadIdx.x; i < ih * bw; i += kThreads) {
+      const int y = i / bw, x = i - y * bw;
+      const long long o = (long long)(y - top) * k.ref_pitch + x;
+      int v;
+      if (sx) {
+        int a = 0;
+#pragma unroll
+        for (int t = 0; t < 8; ++t) a += ref_px(k, rp, o + t - 3) * kx[t];
+        v = min(max((a + 64) >> 7, 0), maxv);
+      } else {
+        v = ref_px(k, rp, o);
+      }
+      s.tmp[i] = (unsigned short)v;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += kThreads) {
+      const int y = i / bw, x = i - y * bw;
+      int pv;
+      if (sy) {
+        int a = 0;
+#pragma unroll
+        for (int t = 0; t < 8; ++t) a += (int)s.tmp[(y + t) * bw + x] * ky[t];
+        pv = min(max((a + 64) >> 7, 0), maxv);
+      } else {
+        pv = s.tmp[i];
+      }
+      const int df = pv - src_px(k, i);
+      sum += df;
+      sse += (unsigned)(df * df);
+    }
+  }
+  sum = warp_sum_ll(sum);
+  sse = (unsigned long long)warp_sum_ll((long long)sse);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) {
+    s.red[warp] = sum;
+    s.red[kWarps + warp] = (long long)sse;
+  }
+  __syncthreads();
+  long long tsum = 0;
+  unsigned long long tsse = 0;
+  for (int w = 0; w < kWarps; ++w) {
+    tsum += s.red[w];
+    tsse += (unsigned long long)s.red[kWarps + w];
+  }
+  return finish_var(tsum, tsse, n, k.l->highbd != 0, k.l->bd, sse_out);
+}
+
+struct SubState {
+  Mv best;
+  unsigned besterr, sse;
+  int distortion;
+};
+
+// check_better / check_better_fast (mcomp.c:2496-2551)
+__device__ unsigned check_better(const SubCtx &s, SubState &st, Mv mv, int mode, int *better) {
+  const Ctx &k = s.k;
+  if (mv.col < k.d.col_min || mv.col > k.d.col_max || mv.row < k.d.row_min || mv.row > k.d.row_max)
+    return (unsigned)INT_MAX;
+  unsigned sse;
+  const int mse = (int)cta_pref_error(s, mv, mode, &sse);
+  const unsigned cost = (unsigned)err_cost(k, mv.row, mv.col) + (unsigned)mse;
+  if (cost < st.besterr) {
+    st.besterr = cost;
+    st.best = mv;
+    st.distortion = mse;
+    st.sse = sse;
+    if (better) *better |= 1;
+  }
+  return cost;
+}
+
+__device__ void subpel_search(const SubCtx &s, SubState &st) {
+  const Ctx &k = s.k;
+  const int forced_stop = k.d.subpel & 3, iters_per_step = (k.d.subpel >> 2) & 3;
+  const int allow_hp = (k.d.flags & B200_ME_ALLOW_HP) != 0;
+  const int mode = s.search_type != B200_USE_2_TAPS_ORIG ? 2 : 1;
+  const int round = min(B200_FULL_PEL - forced_stop, 3 - !allow_hp);
+  int hstep = 4;  // INIT_SUBPEL_STEP_SIZE
+  st.best.row = k.d.start_row;
+  st.best.col = k.d.start_col;
+  unsigned sse;
+  const unsigned e = cta_pref_error(s, st.best, mode == 2 ? 2 : 0, &sse);
+  st.distortion = (int)e;
+  st.sse = sse;
+  st.besterr = e + (unsigned)err_cost(k, st.best.row, st.best.col);
+  for (int iter = 0; iter < round; ++iter) {
+    const Mv c = st.best;
+    // first_level_check(_fast): four cardinals, then the diagonal of the better halves
+    const Mv l = { c.row, c.col - hstep }, r = { c.row, c.col + hstep };
+    const Mv t = { c.row - hstep, c.col }, b = { c.row + hstep, c.col };
+    const unsigned left = check_better(s, st, l, mode, nullptr);
+    const unsigned right = check_better(s, st, r, mode, nullptr);
+    const unsigned up = check_better(s, st, t, mode, nullptr);
+    const unsigned down = check_better(s, st, b, mode, nullptr);
+    Mv diag = { up <= down ? -hstep : hstep, left <= right ? -hstep : hstep };
+    const Mv dm = { c.row + diag.row, c.col + diag.col };
+    check_better(s, st, dm, mode, nullptr);
+    // second_level_check_v2
+    if (!(c.row == st.best.row && c.col == st.best.col) && iters_per_step > 1) {
+      if (c.row == st.best.row) diag.row = -diag.row;
+      else if (c.col == st.best.col) diag.col = -diag.col;
+      const Mv rb = { st.best.row + diag.row, st.best.col };
+      const Mv cb = { st.best.row, st.best.col + diag.col };
+      const Mv db = { st.best.row + diag.row, st.best.col + diag.col };
+      int better = 0;
+      check_better(s, st, rb, mode, &better);
+      check_better(s, st, cb, mode, &better);
+      if (better) check_better(s, st, db, mode, &better);
+    }
+    hstep >>= 1;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) {
+  extern __shared__ __align__(16) unsigned char me_smem[];
+  __shared__ long long s_red[2 * kWarps];
+  __shared__ int s_bcast[16];
+  const int bi = blockIdx.x;
+  SubCtx s;
+  s.k.l = &l;
+  s.k.d = l.blocks[bi];
+  s.k.sites = nullptr;
+  s.k.px = l.highbd ? 2 : 1;
+  s.k.sad_shift = 0;
+  s.k.cand = nullptr;
+  s.k.bcast = s_bcast;
+  s.red = s_red;
+  s.search_type = (s.k.d.subpel >> 4) & 3;
+  // the limits are sub-pel here: no window staging (window_budget 0), reference via L1/L2
+  {
+    const int px = s.k.px, bw = s.k.d.bw, bh = s.k.d.bh;
+    const unsigned char *g_src = static_cast<const unsigned char *>(l.cur) + (size_t)s.k.d.src_offset * px;
+    const int row_bytes = bw * px;
+    for (int i = threadIdx.x; i < bh * row_bytes; i += kThreads) {
+      const int y = i / row_bytes, x = i - y * row_bytes;
+      me_smem[i] = g_src[(size_t)y * l.cur_stride * px + x];
+    }
+    s.k.src = me_smem;
+    s.k.ref0 = static_cast<const unsigned char *>(l.ref) + (size_t)s.k.d.ref_offset * px;
+    s.k.ref_pitch = l.ref_stride;
+    s.tmp = reinterpret_cast<unsigned short *>(me_smem + ((bh * row_bytes + 15) & ~15));
+    __syncthreads();
+  }
+  SubState st;
+  subpel_search(s, st);
+  if (threadIdx.x == 0) {
+    B200MeResult r;
+    memset(&r, 0, sizeof(r));
+    r.best_row = (short)st.best.row;
+    r.best_col = (short)st.best.col;
+    r.second_row = r.second_col = -32768;
+    r.ret = (int)st.besterr;
+    r.distortion = st.distortion;
+    r.sse = st.sse;
+    l.results[bi] = r;
+  }
+}
+
+}  // namespace me
+}  // namespace b200

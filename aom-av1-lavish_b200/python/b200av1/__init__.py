@@ -193,3 +193,27 @@ class ErrLaunch(C.Structure):
     _fields_ = [("kind", C.c_int), ("bd", C.c_int), ("n_blocks", C.c_int), ("blocks", C.c_void_p),
                 ("coeff", C.c_void_p), ("dqcoeff", C.c_void_p), ("qm", C.c_void_p),
                 ("scan", C.c_void_p), ("out", C.c_void_p)]
+
+
+# ------------------------------------------------------------------ motion search ----
+MEBLOCK_DTYPE = np.dtype([("src_offset", "<u4"), ("ref_offset", "<u4"), ("col_min", "<i2"),
+                          ("col_max", "<i2"), ("row_min", "<i2"), ("row_max", "<i2"),
+                          ("start_row", "<i2"), ("start_col", "<i2"), ("ref_mv_row", "<i2"),
+                          ("ref_mv_col", "<i2"), ("bw", "u1"), ("bh", "u1"), ("search_method", "u1"),
+                          ("step_param", "u1"), ("flags", "u1"), ("mv_cost_type", "u1"),
+                          ("mesh_mv_diff_threshold", "u1"), ("subpel", "u1"),
+                          ("force_mesh_thresh", "<i4"), ("sad_per_bit", "<i4"),
+                          ("error_per_bit", "<i4")])
+MERESULT_DTYPE = np.dtype([("best_row", "<i2"), ("best_col", "<i2"), ("second_row", "<i2"),
+                           ("second_col", "<i2"), ("cost_list", "<i4", 5), ("ret", "<i4"),
+                           ("distortion", "<i4"), ("sse", "<u4")])
+assert MEBLOCK_DTYPE.itemsize == 44 and MERESULT_DTYPE.itemsize == 40
+ME_RUN_MESH, ME_PRUNE_MESH, ME_FINE_INTERVAL, ME_SKIP_SAD, ME_ALLOW_HP = 1, 2, 4, 8, 16
+
+
+class MeLaunch(C.Structure):
+    _fields_ = [("highbd", C.c_int), ("bd", C.c_int), ("n_blocks", C.c_int), ("blocks", C.c_void_p),
+                ("cur", C.c_void_p), ("ref", C.c_void_p), ("cur_stride", C.c_int),
+                ("ref_stride", C.c_int), ("mesh_range", C.c_int * 4), ("mesh_interval", C.c_int * 4),
+                ("mvjcost", C.c_void_p), ("mvcost", C.c_void_p * 2), ("results", C.c_void_p),
+                ("window_bytes", C.c_int), ("max_bw", C.c_int), ("max_bh", C.c_int)]

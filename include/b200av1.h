@@ -286,6 +286,69 @@ typedef struct {
 } B200UpsampleLaunch;
 int b200_upsampled_pred_launch(b200_ctx *ctx, const B200UpsampleLaunch *launch, void *stream);
 
+
+/* ------------------------------------------------------ motion search batch ------ */
+/* One descriptor = one single-reference translational search of one block: the fields
+ * of FULLPEL_MOTION_SEARCH_PARAMS / SUBPEL_MOTION_SEARCH_PARAMS (av1/encoder/mcomp.h:
+ * 101-141, 301-324) that av1_full_pixel_search (mcomp.c:1755) and
+ * av1_find_best_sub_pixel_tree (mcomp.c:3128) read.  One CTA per descriptor: the
+ * candidates of every search step are evaluated in parallel (SAD / variance per warp),
+ * the decision rule is the reference's "first candidate in scan order with the strictly
+ * smallest sad + mv cost", second_best_mv and the 5-point cost list included. */
+enum { B200_ME_NSTEP = 0, B200_ME_NSTEP_8PT = 1, B200_ME_DIAMOND = 2, B200_ME_CLAMPED_DIAMOND = 3 };
+enum { B200_MV_COST_ENTROPY = 0, B200_MV_COST_L1_LOWRES, B200_MV_COST_L1_MIDRES,
+       B200_MV_COST_L1_HDRES, B200_MV_COST_NONE };           /* MV_COST_TYPE, mcomp.h:32-38 */
+enum { B200_USE_2_TAPS_ORIG = 0, B200_USE_2_TAPS, B200_USE_4_TAPS, B200_USE_8_TAPS };
+enum { B200_EIGHTH_PEL = 0, B200_QUARTER_PEL, B200_HALF_PEL, B200_FULL_PEL };
+#define B200_ME_RUN_MESH 1u      /* run_mesh_search */
+#define B200_ME_PRUNE_MESH 2u    /* prune_mesh_search */
+#define B200_ME_FINE_INTERVAL 4u /* fine_search_interval */
+#define B200_ME_SKIP_SAD 8u      /* ms_params->sdf = vfp->sdsf (row-skipping SAD) */
+#define B200_ME_ALLOW_HP 16u     /* sub-pel: allow_hp */
+typedef struct {
+  uint32_t src_offset; /* pixels from the current-frame base to the block */
+  uint32_t ref_offset; /* pixels from the reference-frame base to the co-located block */
+  int16_t col_min, col_max, row_min, row_max; /* FullMvLimits (full-pel search) or
+                                                 SubpelMvLimits in 1/8 pel (sub-pel search) */
+  int16_t start_row, start_col;               /* full-pel (1/8 pel for the sub-pel search) */
+  int16_t ref_mv_row, ref_mv_col;             /* 1/8 pel */
+  uint8_t bw, bh;                             /* one of the 22 SAD block sizes */
+  uint8_t search_method, step_param;
+  uint8_t flags;                              /* B200_ME_* */
+  uint8_t mv_cost_type;
+  uint8_t mesh_mv_diff_threshold;
+  uint8_t subpel;                             /* forced_stop | iters_per_step << 2 | search_type << 4 */
+  int32_t force_mesh_thresh;
+  int32_t sad_per_bit, error_per_bit;
+} B200MeBlock; /* 44 bytes */
+typedef struct {
+  int16_t best_row, best_col;
+  int16_t second_row, second_col; /* -32768 (INVALID_MV) when the search left it unset */
+  int32_t cost_list[5];           /* full-pel: calc_int_sad_list (mcomp.c:791) */
+  int32_t ret;                    /* the reference function's return value */
+  int32_t distortion;             /* sub-pel: *distortion */
+  uint32_t sse;                   /* sub-pel: *sse1 */
+} B200MeResult; /* 40 bytes */
+typedef struct {
+  int highbd, bd;                /* 0: uint8 planes; 1: uint16 planes of bd bits */
+  int n_blocks;
+  const B200MeBlock *blocks;     /* device */
+  const void *cur, *ref;         /* device planes (the reference plane includes its border) */
+  int cur_stride, ref_stride;    /* pixels */
+  int mesh_range[4], mesh_interval[4]; /* MESH_PATTERN[MAX_MESH_STEP], speed_features.h:27-32 */
+  const int *mvjcost;            /* device, 4 entries (MV_COST_ENTROPY), or NULL */
+  const int *mvcost[2];          /* device, centred pointers: index -MV_MAX..MV_MAX */
+  B200MeResult *results;         /* device */
+  int window_bytes;              /* shared memory reserved per search for the reference window
+                                    (limits box + block, e.g. 192*192 = 36864 for a 64x64 block
+                                    with +-64); searches whose window does not fit read the
+                                    reference through L1/L2 instead.  0 = never stage. */
+  int max_bw, max_bh;            /* largest block of the batch (sizes the per-search shared
+                                    memory); 0 = assume 128 */
+} B200MeLaunch;
+int b200_me_fullpel_launch(b200_ctx *ctx, const B200MeLaunch *launch, void *stream);
+int b200_me_subpel_launch(b200_ctx *ctx, const B200MeLaunch *launch, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,166 @@
+"""GPU parity of the batched motion search (b200_me_fullpel_launch / b200_me_subpel_launch)
+against the oracle (itself pinned to the reference's av1_full_pixel_search /
+av1_find_best_sub_pixel_tree): best mv, second-best mv, cost list, returned variance,
+distortion and sse must be identical."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import harness as H
+import me_common as M
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import b200av1
+    c = b200av1.Context(0)
+    yield c
+    c.close()
+
+
+def upload_tables(ctx, tables):
+    import b200av1
+    joint, t0, t1 = tables
+    dj, d0, d1 = (b200av1.to_device(ctx, t) for t in (joint, t0, t1))
+    return (dj, d0, d1), (dj.ptr.value, d0.ptr.value + 4 * H.MV_TABLE_HALF, d1.ptr.value + 4 * H.MV_TABLE_HALF)
+
+
+def me_launch(ctx, cur, refb, params, tables_dev, subpel, window_bytes):
+    import b200av1
+    n = len(params)
+    blocks = np.zeros(n, b200av1.MEBLOCK_DTYPE)
+    for i, p in enumerate(params):
+        b = blocks[i]
+        b["src_offset"] = p._by * cur.shape[1] + p._bx
+        b["ref_offset"] = (p._by + M.BORDER) * refb.shape[1] + p._bx + M.BORDER
+        if subpel:
+            b["col_min"], b["col_max"], b["row_min"], b["row_max"] = (p.sp_col_min, p.sp_col_max,
+                                                                      p.sp_row_min, p.sp_row_max)
+            b["start_row"], b["start_col"] = p.sp_start_row, p.sp_start_col
+        else:
+            b["col_min"], b["col_max"], b["row_min"], b["row_max"] = (p.col_min, p.col_max,
+                                                                      p.row_min, p.row_max)
+            b["start_row"], b["start_col"] = p.start_row, p.start_col
+        b["ref_mv_row"], b["ref_mv_col"] = p.ref_mv_row, p.ref_mv_col
+        b["bw"], b["bh"] = p.bw, p.bh
+        b["search_method"], b["step_param"] = p.search_method, p.step_param
+        b["flags"] = (p.run_mesh_search * b200av1.ME_RUN_MESH | p.prune_mesh_search * b200av1.ME_PRUNE_MESH |
+                      p.fine_search_interval * b200av1.ME_FINE_INTERVAL |
+                      p.use_skip_sad * b200av1.ME_SKIP_SAD | p.allow_hp * b200av1.ME_ALLOW_HP)
+        b["mv_cost_type"] = p.mv_cost_type
+        b["mesh_mv_diff_threshold"] = p.mesh_search_mv_diff_threshold
+        b["subpel"] = p.forced_stop | (p.iters_per_step << 2) | (p.subpel_search_type << 4)
+        b["force_mesh_thresh"] = p.force_mesh_thresh
+        b["sad_per_bit"], b["error_per_bit"] = p.sad_per_bit, p.error_per_bit
+    d_cur, d_ref = b200av1.to_device(ctx, cur), b200av1.to_device(ctx, refb)
+    d_blk = b200av1.to_device(ctx, blocks)
+    d_res = b200av1.DevBuf(ctx, n * 40)
+    l = b200av1.MeLaunch()
+    l.highbd, l.bd, l.n_blocks = int(cur.itemsize == 2), params[0].bd, n
+    l.blocks, l.cur, l.ref = d_blk.ptr, d_cur.ptr, d_ref.ptr
+    l.cur_stride, l.ref_stride = cur.shape[1], refb.shape[1]
+    for i, (r, it) in enumerate(M.MESH):
+        l.mesh_range[i], l.mesh_interval[i] = r, it
+    l.mvjcost, l.mvcost[0], l.mvcost[1] = tables_dev
+    l.results = d_res.ptr
+    l.window_bytes = window_bytes
+    fn = b200av1.lib().b200_me_subpel_launch if subpel else b200av1.lib().b200_me_fullpel_launch
+    b200av1.check(fn(ctx.h, C.byref(l), None))
+    return b200av1.to_host(ctx, d_res, b200av1.MERESULT_DTYPE, n)
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+def test_fullpel_batch_vs_oracle(ctx, bd):
+    O = H.oracle()
+    rng = np.random.default_rng(700 + bd)
+    tables = H.make_mv_cost_tables(1)
+    keep, tdev = upload_tables(ctx, tables)
+    for trial in range(4):
+        cur, refb = M.make_frames(rng, 256, 192, bd, flat=(trial % 3 == 2))
+        params = [M.random_fullpel_params(rng, cur, refb, bw, bh, bd, tables)
+                  for (bw, bh) in M.FULLPEL_SIZES for _ in range(6)]
+        exp = []
+        for p in params:
+            r = H.MeResult()
+            O.av1o_full_pixel_search(C.byref(p), C.byref(r))
+            exp.append(r)
+        # window staged in shared memory / forced through global memory: same answers
+        for window in (150 * 1024, 0):
+            got = me_launch(ctx, cur, refb, params, tdev, False, window)
+            for i, (p, e) in enumerate(zip(params, exp)):
+                g = got[i]
+                tag = (trial, i, p.bw, p.bh, p.search_method, p.step_param, p.run_mesh_search,
+                       p.use_skip_sad, p.mv_cost_type, window)
+                assert (int(g["best_row"]), int(g["best_col"]), int(g["ret"])) == \
+                    (e.best_row, e.best_col, e.ret), tag
+                if p.want_second_best:
+                    assert (int(g["second_row"]), int(g["second_col"])) == (e.second_row, e.second_col), tag
+                if p.want_cost_list:
+                    assert tuple(int(v) for v in g["cost_list"]) == tuple(e.cost_list), tag
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+def test_subpel_batch_vs_oracle(ctx, bd):
+    O = H.oracle()
+    rng = np.random.default_rng(800 + bd)
+    tables = H.make_mv_cost_tables(2)
+    keep, tdev = upload_tables(ctx, tables)
+    for trial in range(3):
+        cur, refb = M.make_frames(rng, 256, 192, bd, flat=(trial % 3 == 2))
+        params = [M.random_subpel_params(rng, cur, refb, bw, bh, bd, tables, st)
+                  for (bw, bh) in M.SUBPEL_SIZES for st in range(4) for _ in range(2)]
+        got = me_launch(ctx, cur, refb, params, tdev, True, 0)
+        for i, p in enumerate(params):
+            e = H.MeResult()
+            O.av1o_find_best_sub_pixel_tree(C.byref(p), C.byref(e))
+            g = got[i]
+            assert (int(g["best_row"]), int(g["best_col"]), int(g["ret"]), int(g["distortion"]),
+                    int(g["sse"])) == e.key(True), (trial, i, p.bw, p.bh, p.subpel_search_type,
+                                                    p.forced_stop, p.iters_per_step)
+
+
+def test_config3_shape_64x64_pm64_two_refs(ctx):
+    """BASELINE config 3 shape at reduced frame size: 64x64 superblocks, +-64 range, NSTEP +
+    forced mesh {64,8},{28,4},{15,1}, two reference frames, L1 (HD) mv cost; full-pel result
+    feeds the sub-pel tree (8 taps) like av1_single_motion_search chains them."""
+    import b200av1
+    O = H.oracle()
+    rng = np.random.default_rng(33)
+    tables = H.make_mv_cost_tables(3)
+    keep, tdev = upload_tables(ctx, tables)
+    w, h = 448, 256
+    for ref_id in range(2):
+        cur, refb = M.make_frames(rng, w, h, 8, flat=(ref_id == 1))
+        params = []
+        for by in range(0, h, 64):
+            for bx in range(0, w, 64):
+                p = M.base_params(cur, refb, bx, by, 64, 64, 8, tables)
+                p.col_min, p.col_max = max(-64, -(bx + M.BORDER - 8)), min(64, w - 64 - bx + M.BORDER - 8)
+                p.row_min, p.row_max = max(-64, -(by + M.BORDER - 8)), min(64, h - 64 - by + M.BORDER - 8)
+                p.search_method, p.step_param = 0, O.av1o_init_search_range(64)
+                p.run_mesh_search, p.mv_cost_type = 1, 3
+                p.want_cost_list = p.want_second_best = 1
+                params.append(p)
+        got = me_launch(ctx, cur, refb, params, tdev, False, 150 * 1024)
+        sub = []
+        for i, p in enumerate(params):
+            e = H.MeResult()
+            O.av1o_full_pixel_search(C.byref(p), C.byref(e))
+            g = got[i]
+            assert (int(g["best_row"]), int(g["best_col"]), int(g["second_row"]), int(g["second_col"]),
+                    tuple(int(v) for v in g["cost_list"]), int(g["ret"])) == e.key(), (ref_id, i)
+            p.subpel_search_type, p.allow_hp, p.forced_stop, p.iters_per_step = 3, 1, 0, 2
+            p.sp_start_row, p.sp_start_col = e.best_row * 8, e.best_col * 8
+            p.sp_row_min, p.sp_row_max = p.row_min * 8, p.row_max * 8
+            p.sp_col_min, p.sp_col_max = p.col_min * 8, p.col_max * 8
+            sub.append(p)
+        got2 = me_launch(ctx, cur, refb, sub, tdev, True, 0)
+        for i, p in enumerate(sub):
+            e = H.MeResult()
+            O.av1o_find_best_sub_pixel_tree(C.byref(p), C.byref(e))
+            g = got2[i]
+            assert (int(g["best_row"]), int(g["best_col"]), int(g["ret"]), int(g["distortion"]),
+                    int(g["sse"])) == e.key(True), (ref_id, i)
