@@ -115,3 +115,10 @@ extern "C" int b200_me_subpel_launch(b200_ctx *ctx, const B200MeLaunch *l, void 
   B200_CUDA_TRY(cudaGetLastError());
   return B200_OK;
 }
+
+extern "C" int b200_me_init_search_range(int size) {
+  int sr = 0;
+  if (size < 16) size = 16;
+  while ((size << sr) < 1023) sr++;  // MAX_FULL_PEL_VAL
+  return sr < b200::me::kMaxSteps - 2 ? sr : b200::me::kMaxSteps - 2;
+}

@@ -58,24 +58,25 @@ def max_eob(ts):
     return min(TX_W[ts], 32) * min(TX_H[ts], 32)
 
 
-def make_residual_frames(n_frames, seed):
-    """int16 residual of a 1080p 4:2:0 frame: planes Y 1920x1080, U, V 960x540 stored
-    back to back (strides = widths).  Smooth source, prediction = shifted source + noise."""
+def make_residual_frames(frame_ids, seed):
+    """int16 residual of 1080p 4:2:0 frames: planes Y 1920x1080, U, V 960x540 stored back to
+    back (strides = widths).  Smooth source panned per frame, prediction = shifted source +
+    noise.  A frame's content depends only on (seed, frame id), never on the rank owning it."""
     import synth
-    rng = np.random.default_rng(seed)
+    if isinstance(frame_ids, int):
+        frame_ids = list(range(frame_ids))
     planes = [(1920, 1080), (960, 540), (960, 540)]
     frame_elems = sum(w * h for w, h in planes)
-    out = np.zeros((n_frames, frame_elems), np.int16)
-    base = []
-    for (w, h) in planes:
-        s = synth.smooth_frame(rng, w, h, 8)
-        base.append(s)
-    for f in range(n_frames):
+    out = np.zeros((len(frame_ids), frame_elems), np.int16)
+    rng0 = np.random.default_rng(seed)
+    base = [synth.smooth_frame(rng0, w, h, 8) for (w, h) in planes]
+    for i, f in enumerate(frame_ids):
+        rng = np.random.default_rng([seed, f])
         o = 0
         for (w, h), s in zip(planes, base):
             src = np.roll(s, (f * 2, f * 3), (0, 1))
             pred = synth.pred_from(rng, src, 8)
-            out[f, o:o + w * h] = (src.astype(np.int16) - pred.astype(np.int16)).reshape(-1)
+            out[i, o:o + w * h] = (src.astype(np.int16) - pred.astype(np.int16)).reshape(-1)
             o += w * h
     return out, planes
 
@@ -219,6 +220,96 @@ def cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed, n_threads, sizes=r
     return total_t, total_samples, outs
 
 
+# ------------------------------------------------------------------ ME workload ----
+ME_BORDER = 160  # AOM_ENC_NO_SCALE_BORDER, aom_scale/yv12config.h:28-32
+
+
+def bench_me(ctx, dev, stream, steps, warmup, seed, frame_id):
+    """BASELINE configs[2]: full-pel (NSTEP + mesh {64,8},{28,4},{15,1}) and sub-pel (8-tap
+    tree) search of every 64x64 superblock of a 1080p 8-bit frame against 2 references,
+    +-64 range, L1 (HD) mv cost.  Returns device-timed ms per frame for both kernels."""
+    import torch
+    import b200av1
+    import synth
+    rng = np.random.default_rng([seed, frame_id, 77])
+    w, h = 1920, 1080
+    cur = synth.smooth_frame(rng, w, h, 8)
+    refs = []
+    for r in range(2):
+        dy, dx = int(rng.integers(-20, 21)), int(rng.integers(-20, 21))
+        ref = np.roll(cur, (dy, dx), (0, 1)).astype(np.int32) + np.rint(rng.normal(0, 2, cur.shape)).astype(np.int32)
+        refs.append(np.pad(np.clip(ref, 0, 255).astype(np.uint8), ME_BORDER, mode="edge"))
+    rstride = w + 2 * ME_BORDER
+    sbs = [(bx, by) for by in range(0, h - 63, 64) for bx in range(0, w - 63, 64)]
+    n = len(sbs)
+    blocks = np.zeros(n, b200av1.MEBLOCK_DTYPE)
+    for i, (bx, by) in enumerate(sbs):
+        b = blocks[i]
+        b["src_offset"], b["ref_offset"] = by * w + bx, (by + ME_BORDER) * rstride + bx + ME_BORDER
+        b["col_min"], b["col_max"], b["row_min"], b["row_max"] = -64, 64, -64, 64
+        b["bw"], b["bh"] = 64, 64
+        b["search_method"] = 0  # B200_ME_NSTEP
+        b["flags"] = b200av1.ME_RUN_MESH
+        b["mv_cost_type"] = 3  # MV_COST_L1_HDRES
+        b["sad_per_bit"], b["error_per_bit"] = 40, 90
+    blocks["step_param"] = b200av1.lib().b200_me_init_search_range(64)
+    d_cur = torch.from_numpy(cur.reshape(-1)).to(dev)
+    d_refs = [torch.from_numpy(r.reshape(-1)).to(dev) for r in refs]
+    d_blk = torch.from_numpy(blocks.view(np.uint8)).to(dev)
+    d_res = [torch.zeros(n * 40, dtype=torch.uint8, device=dev) for _ in range(2)]
+
+    def launch(kind, ref_id, d_blocks):
+        l = b200av1.MeLaunch()
+        l.highbd, l.bd, l.n_blocks = 0, 8, n
+        l.blocks, l.cur, l.ref = d_blocks.data_ptr(), d_cur.data_ptr(), d_refs[ref_id].data_ptr()
+        l.cur_stride, l.ref_stride = w, rstride
+        for i, (r, it) in enumerate(((64, 8), (28, 4), (15, 1), (7, 1))):
+            l.mesh_range[i], l.mesh_interval[i] = r, it
+        l.results = d_res[ref_id].data_ptr()
+        l.window_bytes, l.max_bw, l.max_bh = 196 * 192 + 1024, 64, 64
+        fn = b200av1.lib().b200_me_fullpel_launch if kind == 0 else b200av1.lib().b200_me_subpel_launch
+        b200av1.check(fn(ctx.h, C.byref(l), C.c_void_p(stream.cuda_stream)))
+
+    # full-pel once (untimed) to build the sub-pel descriptors from its results
+    for r in range(2):
+        launch(0, r, d_blk)
+    torch.cuda.synchronize(dev)
+    d_sub = []
+    for r in range(2):
+        res = d_res[r].cpu().numpy().view(b200av1.MERESULT_DTYPE)
+        sb = blocks.copy()
+        sb["start_row"], sb["start_col"] = res["best_row"] * 8, res["best_col"] * 8
+        sb["col_min"], sb["col_max"], sb["row_min"], sb["row_max"] = -512, 512, -512, 512
+        sb["flags"] = b200av1.ME_ALLOW_HP
+        sb["subpel"] = 0 | (2 << 2) | (3 << 4)  # EIGHTH_PEL, 2 iters/step, USE_8_TAPS
+        d_sub.append(torch.from_numpy(sb.view(np.uint8)).to(dev))
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    t_full = t_sub = 0.0
+    for it in range(warmup + steps):
+        ev[0].record(stream)
+        for r in range(2):
+            launch(0, r, d_blk)
+        ev[1].record(stream)
+        for r in range(2):
+            launch(1, r, d_sub[r])
+        ev[2].record(stream)
+        torch.cuda.synchronize(dev)
+        if it >= warmup:
+            t_full += ev[0].elapsed_time(ev[1])
+            t_sub += ev[1].elapsed_time(ev[2])
+    # mesh candidates per search (lower bound of the SAD work; diamond steps come on top):
+    # 17x17 @8, 15x15 @4, 31 rows x 30 cols @1 (the reference's tail-loop quirk)
+    cands = 17 * 17 + 15 * 15 + 31 * 30
+    return {"workload": "config[2]: 1080p 8-bit, %d 64x64 SBs x 2 refs, +-64, NSTEP+mesh, 8-tap sub-pel" % n,
+            "fullpel_ms_per_frame": t_full / steps, "subpel_ms_per_frame": t_sub / steps,
+            "frames_per_s": 1e3 * steps / (t_full + t_sub),
+            "mesh_gabsdiff_per_s": 2 * n * cands * 4096 / (t_full / steps * 1e-3) / 1e9,
+            "unique_bytes_per_frame": 2 * n * (4096 + 192 * 192 + 64),
+            "unique_GBps": 2 * n * (4096 + 192 * 192 + 64) / (t_full / steps * 1e-3) / 1e9,
+            "launches_per_frame": 4}
+
+
+
 def build_qrows_product():
     """3 planes x 5 qindexes, all delta_q = 0 (av1_build_quantizer, av1_quantize.c:602)"""
     import b200av1
@@ -240,6 +331,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--force-exact", action="store_true", help="always take the 64-bit half_btf path")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-me", action="store_true", help="skip the motion-search section")
     ap.add_argument("--sizes", default="", help="comma list of tx sizes (debug)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -300,7 +392,9 @@ def main():
     ctx = b200av1.Context(local_rank)
     stream = torch.cuda.Stream(device=dev)
 
-    frames, planes = make_residual_frames(args.frames, seed + rank)
+    from b200av1 import shard
+    frame_ids = shard.frames_of_rank(args.frames * world, rank, world)
+    frames, planes = make_residual_frames(frame_ids, seed)
     frame_elems = frames.shape[1]
     d_src = torch.from_numpy(frames.reshape(-1)).to(dev)
     qrows = build_qrows_product()
@@ -427,6 +521,15 @@ def main():
         for p in (p1, p2, p3, p4):
             pass  # pinned buffers live until process exit
 
+    me = None
+    if not args.no_me:
+        me = bench_me(ctx, dev, stream, max(2, args.steps // 2), 2, seed, frame_ids[0])
+        t_me = torch.tensor([me["fullpel_ms_per_frame"] + me["subpel_ms_per_frame"]],
+                            dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t_me, op=dist.ReduceOp.MAX)
+        me["frames_per_s_all_gpus"] = world * 1e3 / float(t_me.item())
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -462,7 +565,7 @@ def main():
                          "kernel": "txq_kernel<W,H> (19 instances, one launch each per step); "
                                    "algorithmic bytes = 2 B/sample in + 12 B/kept coeff out + 2 B/block",
                          "bytes_per_step": int(total_bytes)},
-            "kernels": kernels, "e2e": e2e,
+            "kernels": kernels, "e2e": e2e, "me": me,
             "step_ms_min_max": [float(min(step_ms)), float(max(step_ms))]}
 
     # ---- cpu_baseline (rank 0, N = 1 only) + full-size parity of frame 0

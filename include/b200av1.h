@@ -346,6 +346,8 @@ typedef struct {
   int max_bw, max_bh;            /* largest block of the batch (sizes the per-search shared
                                     memory); 0 = assume 128 */
 } B200MeLaunch;
+/* av1_init_search_range (mcomp.c:239): step_param for a search of +-size pixels */
+int b200_me_init_search_range(int size);
 int b200_me_fullpel_launch(b200_ctx *ctx, const B200MeLaunch *launch, void *stream);
 int b200_me_subpel_launch(b200_ctx *ctx, const B200MeLaunch *launch, void *stream);
 
