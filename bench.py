@@ -551,8 +551,10 @@ def main():
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
         try:
-            traffic = json.load(open(tp)).get("txq_kernel_dram_bytes_per_launch")
-        except (OSError, ValueError):
+            tj = json.load(open(tp))
+            # ncu capture was taken at tj["frames_per_launch"] frames; DRAM bytes scale with frames
+            traffic = tj["txq_kernel_dram_bytes_per_step_at_8_frames"] * args.frames / tj["frames_per_launch"]
+        except (OSError, ValueError, KeyError):
             traffic = None
     line = {"metric": metric, "value": value, "unit": "1080p frame-equiv/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms_max / args.steps,
