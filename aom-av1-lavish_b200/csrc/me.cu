@@ -50,10 +50,13 @@ struct Ctx {
   const unsigned char *src;  // shared, dense pitch = bw pixels
   const unsigned char *ref0; // reference pixel at mv (0,0): shared window or global plane
   int ref_pitch;             // pixels
+  int src_pitch_w;           // source row pitch in 32-bit words (shared copy)
+  bool fast;                 // staged window with 16-byte aligned rows: vector-load SAD path
   int px;                    // bytes per pixel
   int sad_shift;             // 0 / 2 / 4: encoder_utils.h:153-208
   unsigned *cand;            // shared: kMaxCand totals
   int *bcast;                // shared scratch for broadcasts
+  long long *red;            // shared: 2 * kWarps partial sums (CTA-wide variance)
 };
 
 // ------------------------------------------------------------------- mv cost -----
@@ -124,27 +127,145 @@ __device__ __forceinline__ long long warp_sum_ll(long long v) {
   return v;
 }
 
+// One segment of SEGW consecutive 32-bit words of a row: SEGW aligned source words against
+// SEGW + 1 aligned reference words funnel-shifted to the candidate's byte alignment.
+// PX = 1: four pixels per word (VABSDIFF4 with accumulate); PX = 2: two 16-bit pixels.
+template <int SEGW, int PX>
+__device__ __forceinline__ unsigned seg_sad(const unsigned *sp, const unsigned char *rbytes) {
+  const unsigned long long a = reinterpret_cast<unsigned long long>(rbytes);
+  const unsigned *rw = reinterpret_cast<const unsigned *>(a & ~3ull);
+  const unsigned sh = (unsigned)(a & 3) * 8;
+  unsigned r[SEGW + 1];
+#pragma unroll
+  for (int i = 0; i <= SEGW; ++i) r[i] = rw[i];
+  unsigned acc = 0;
+#pragma unroll
+  for (int i = 0; i < SEGW; ++i) {
+    const unsigned rv = __funnelshift_r(r[i], r[i + 1], sh);
+    if (PX == 1) {
+      acc = __vsadu4(sp[i], rv) + acc;
+    } else {
+      const unsigned d = __vabsdiffu2(sp[i], rv);
+      acc += (d & 0xffffu) + (d >> 16);
+    }
+  }
+  return acc;
+}
+
+template <int SEGW, int PX>
+__device__ __forceinline__ unsigned warp_sad_t(const Ctx &k, const unsigned char *rp, int bh,
+                                               int rmul, int lane) {
+  const int row_words = k.d.bw * PX / 4, spr = row_words / SEGW, nseg = spr * bh;
+  const long long pitch_b = (long long)k.ref_pitch * PX;
+  unsigned acc = 0;
+  for (int s = lane; s < nseg; s += 32) {
+    const int y = (s / spr) * rmul, w0 = (s % spr) * SEGW;
+    acc += seg_sad<SEGW, PX>(reinterpret_cast<const unsigned *>(k.src) + y * k.src_pitch_w + w0,
+                             rp + y * pitch_b + w0 * 4);
+  }
+  return acc;
+}
+
+// ---- staged fast path --------------------------------------------------------------
+// Source rows and window rows both have a pitch of 4 (mod 8) words and 16-byte aligned row
+// starts, so a quarter-warp reading one uint4 from each of 8 consecutive rows touches all
+// 32 banks exactly once.  A lane owns one segment of SEGW words of one row: SEGW/4 vector
+// loads of source, SEGW/4 + 1 of reference (16-byte aligned superset of the candidate's
+// bytes; WO = warp-uniform word offset of the candidate inside it), then one funnel shift
+// + one VABSDIFF4.ACC per 4 pixels.
+template <int SEGW, int PX, int WO>
+__device__ __forceinline__ unsigned seg_sad_vec(const uint4 *sp, const uint4 *rp, unsigned sh) {
+  constexpr int NV = SEGW / 4;
+  unsigned sv[SEGW], r[SEGW + 4];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) {
+    const uint4 t = sp[v];
+    sv[4 * v] = t.x, sv[4 * v + 1] = t.y, sv[4 * v + 2] = t.z, sv[4 * v + 3] = t.w;
+  }
+#pragma unroll
+  for (int v = 0; v <= NV; ++v) {
+    const uint4 t = rp[v];
+    r[4 * v] = t.x, r[4 * v + 1] = t.y, r[4 * v + 2] = t.z, r[4 * v + 3] = t.w;
+  }
+  unsigned acc = 0;
+#pragma unroll
+  for (int i = 0; i < SEGW; ++i) {
+    // WO + i + 1 <= SEGW + 3: always inside r[]
+    const unsigned rv = __funnelshift_r(r[WO + i], r[(WO + i + 1) < SEGW + 4 ? WO + i + 1 : WO + i], sh);
+    if (PX == 1) {
+      acc = __vsadu4(sv[i], rv) + acc;
+    } else {
+      const unsigned d = __vabsdiffu2(sv[i], rv);
+      acc += (d & 0xffffu) + (d >> 16);
+    }
+  }
+  return acc;
+}
+
+template <int SEGW, int PX, int WO>
+__device__ __forceinline__ unsigned warp_sad_vec(const Ctx &k, const unsigned char *rp, int bh,
+                                                 int rmul, int lane, unsigned sh) {
+  const int row_words = k.d.bw * PX / 4, spr = row_words / SEGW;  // 1, 2, 4 or 8
+  const int spp = spr < 4 ? spr : 4;                              // segment columns per pass
+  const int rows_per_it = 32 / spp;
+  // lane -> (segment, row): 8 consecutive lanes = 8 consecutive rows of one segment column
+  const int q = lane >> 3, r8 = lane & 7;
+  const int seg0 = q % spp, yl = (q / spp) * 8 + r8;
+  const int pitch_w = k.ref_pitch * PX / 4;
+  unsigned acc = 0;
+  for (int sb = 0; sb < spr; sb += spp) {
+    const int seg = sb + seg0;
+#pragma unroll 2
+    for (int y0 = 0; y0 < bh; y0 += rows_per_it) {
+      const int y = y0 + yl;
+      if (y < bh) {
+        const int yy = y * rmul;
+        const uint4 *sp = reinterpret_cast<const uint4 *>(reinterpret_cast<const unsigned *>(k.src) +
+                                                          yy * k.src_pitch_w + seg * SEGW);
+        const uint4 *rv = reinterpret_cast<const uint4 *>(reinterpret_cast<const unsigned *>(rp) +
+                                                          (long long)yy * pitch_w + seg * SEGW);
+        acc += seg_sad_vec<SEGW, PX, WO>(sp, rv, sh);
+      }
+    }
+  }
+  return acc;
+}
+
+template <int SEGW, int PX>
+__device__ __forceinline__ unsigned warp_sad_fast(const Ctx &k, const unsigned char *cand, int bh,
+                                                  int rmul, int lane) {
+  const unsigned long long a = reinterpret_cast<unsigned long long>(cand);
+  const unsigned char *rp = reinterpret_cast<const unsigned char *>(a & ~15ull);
+  const unsigned sh = (unsigned)(a & 3) * 8;
+  switch ((a >> 2) & 3) {
+    case 0: return warp_sad_vec<SEGW, PX, 0>(k, rp, bh, rmul, lane, sh);
+    case 1: return warp_sad_vec<SEGW, PX, 1>(k, rp, bh, rmul, lane, sh);
+    case 2: return warp_sad_vec<SEGW, PX, 2>(k, rp, bh, rmul, lane, sh);
+    default: return warp_sad_vec<SEGW, PX, 3>(k, rp, bh, rmul, lane, sh);
+  }
+}
+
 // SAD of the source block against the reference block at full-pel mv (row, col), computed
 // by ONE warp; every lane returns the total.  skip = rows 0,2,4.. only, doubled.
 __device__ __forceinline__ unsigned warp_sad(const Ctx &k, int row, int col, bool skip, int lane) {
-  const int bw = k.d.bw, bh = skip ? k.d.bh >> 1 : k.d.bh, rmul = skip ? 2 : 1;
+  const int bh = skip ? k.d.bh >> 1 : k.d.bh, rmul = skip ? 2 : 1;
   const unsigned char *rp = k.ref0 + ((long long)row * k.ref_pitch + col) * k.px;
-  unsigned acc = 0;
-  if (k.px == 1) {
-    const int gpr = bw >> 2, n = gpr * bh;  // groups of 4 pixels
-    for (int i = lane; i < n; i += 32) {
-      const int y = (i / gpr) * rmul, x = (i % gpr) << 2;
-      const unsigned s = *reinterpret_cast<const unsigned *>(k.src + y * bw + x);
-      acc = __vsadu4(s, load4(rp + (long long)y * k.ref_pitch + x)) + acc;
-    }
+  const int row_words = k.d.bw * k.px / 4;
+  unsigned acc;
+  if (k.fast && row_words >= 4) {
+    if (k.px == 1) acc = row_words >= 8 ? warp_sad_fast<8, 1>(k, rp, bh, rmul, lane)
+                                        : warp_sad_fast<4, 1>(k, rp, bh, rmul, lane);
+    else acc = row_words >= 8 ? warp_sad_fast<8, 2>(k, rp, bh, rmul, lane)
+                              : warp_sad_fast<4, 2>(k, rp, bh, rmul, lane);
+  } else if (k.px == 1) {
+    if (row_words >= 8) acc = warp_sad_t<8, 1>(k, rp, bh, rmul, lane);
+    else if (row_words == 4) acc = warp_sad_t<4, 1>(k, rp, bh, rmul, lane);
+    else if (row_words == 2) acc = warp_sad_t<2, 1>(k, rp, bh, rmul, lane);
+    else acc = warp_sad_t<1, 1>(k, rp, bh, rmul, lane);
   } else {
-    const int gpr = bw >> 1, n = gpr * bh;  // groups of 2 pixels
-    for (int i = lane; i < n; i += 32) {
-      const int y = (i / gpr) * rmul, x = (i % gpr) << 1;
-      const unsigned s = *reinterpret_cast<const unsigned *>(k.src + (y * bw + x) * 2);
-      const unsigned short *r = reinterpret_cast<const unsigned short *>(rp) + (long long)y * k.ref_pitch + x;
-      acc += (unsigned)abs((int)(s & 0xffff) - (int)r[0]) + (unsigned)abs((int)(s >> 16) - (int)r[1]);
-    }
+    if (row_words >= 8) acc = warp_sad_t<8, 2>(k, rp, bh, rmul, lane);
+    else if (row_words == 4) acc = warp_sad_t<4, 2>(k, rp, bh, rmul, lane);
+    else acc = warp_sad_t<2, 2>(k, rp, bh, rmul, lane);
   }
   acc = warp_sum_u(acc);
   if (skip) acc *= 2;
@@ -186,10 +307,10 @@ __device__ __forceinline__ unsigned warp_var(const Ctx &k, int row, int col, boo
     const int y = i / bw, x = i - y * bw;
     int s, r;
     if (k.px == 1) {
-      s = k.src[i];
+      s = k.src[y * k.src_pitch_w * 4 + x];
       r = rp[(long long)y * k.ref_pitch + x];
     } else {
-      s = reinterpret_cast<const unsigned short *>(k.src)[i];
+      s = reinterpret_cast<const unsigned short *>(k.src)[y * k.src_pitch_w * 2 + x];
       r = reinterpret_cast<const unsigned short *>(rp)[(long long)y * k.ref_pitch + x];
     }
     const int df = ref_first ? r - s : s - r;

@@ -202,6 +202,7 @@ __global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) 
   s.k.sad_shift = 0;
   s.k.cand = nullptr;
   s.k.bcast = s_bcast;
+  s.k.red = s_red;
   s.red = s_red;
   s.search_type = (s.k.d.subpel >> 4) & 3;
   // the limits are sub-pel here: no window staging (window_budget 0), reference via L1/L2
@@ -214,6 +215,8 @@ __global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) 
       me_smem[i] = g_src[(size_t)y * l.cur_stride * px + x];
     }
     s.k.src = me_smem;
+    s.k.src_pitch_w = row_bytes / 4;  // dense
+    s.k.fast = false;
     s.k.ref0 = static_cast<const unsigned char *>(l.ref) + (size_t)s.k.d.ref_offset * px;
     s.k.ref_pitch = l.ref_stride;
     s.tmp = reinterpret_cast<unsigned short *>(me_smem + ((bh * row_bytes + 15) & ~15));

@@ -10,7 +10,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 PKG_DIR = os.path.dirname(os.path.dirname(_HERE))
-LIB_PATH = os.path.join(PKG_DIR, "libb200av1.so")
+LIB_PATH = os.environ.get("B200AV1_LIB", os.path.join(PKG_DIR, "libb200av1.so"))
 
 OK = 0
 IN_RESIDUAL, IN_PIXELS8, IN_PIXELS16 = 0, 1, 2

@@ -266,7 +266,7 @@ def bench_me(ctx, dev, stream, steps, warmup, seed, frame_id):
         for i, (r, it) in enumerate(((64, 8), (28, 4), (15, 1), (7, 1))):
             l.mesh_range[i], l.mesh_interval[i] = r, it
         l.results = d_res[ref_id].data_ptr()
-        l.window_bytes, l.max_bw, l.max_bh = 196 * 192 + 1024, 64, 64
+        l.window_bytes, l.max_bw, l.max_bh = 48 * 1024, 64, 64
         fn = b200av1.lib().b200_me_fullpel_launch if kind == 0 else b200av1.lib().b200_me_subpel_launch
         b200av1.check(fn(ctx.h, C.byref(l), C.c_void_p(stream.cuda_stream)))
 
@@ -277,6 +277,10 @@ def bench_me(ctx, dev, stream, steps, warmup, seed, frame_id):
     d_sub = []
     for r in range(2):
         res = d_res[r].cpu().numpy().view(b200av1.MERESULT_DTYPE)
+        if os.environ.get("B200_ME_DEBUG"):  # library built with -DB200_ME_TIMING (dev only)
+            print("ME timing (cycles): staging %.0f diamond %.0f total %.0f" % (
+                16 * res["cost_list"][:, 4].mean(), 16.0 * res["distortion"].mean(),
+                16.0 * res["sse"].mean()), file=sys.stderr)
         sb = blocks.copy()
         sb["start_row"], sb["start_col"] = res["best_row"] * 8, res["best_col"] * 8
         sb["col_min"], sb["col_max"], sb["row_min"], sb["row_max"] = -512, 512, -512, 512
