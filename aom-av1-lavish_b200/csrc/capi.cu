@@ -77,6 +77,7 @@ extern "C" void b200_ctx_destroy(b200_ctx *ctx) {
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   if (ctx->d_iscan) cudaFree(ctx->d_iscan);
+  if (ctx->d_pmask) cudaFree(ctx->d_pmask);
   if (ctx->d_scratch) cudaFree(ctx->d_scratch);
   if (ctx->d_me_sites) cudaFree(ctx->d_me_sites);
   if (ctx->h_scratch) cudaFreeHost(ctx->h_scratch);

@@ -36,6 +36,7 @@ struct b200_ctx {
   int sm_count;
   cudaStream_t stream;
   int16_t *d_iscan;   // all inverse scan tables, see txq.cu
+  unsigned long long *d_pmask;  // scan prefix masks of the <= 64-sample sizes, see txq.cu
   // scratch for the host-buffer (drop-in) tier
   void *d_scratch;
   size_t scratch_bytes;

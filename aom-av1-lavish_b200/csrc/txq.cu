@@ -30,9 +30,13 @@ int txq_group_c(TxqKernelInfo (*table)[3], bool upload);
 int txq_group_d(TxqKernelInfo (*table)[3], bool upload);
 int txq_group_e(TxqKernelInfo (*table)[3], bool upload);
 int txq_group_f(TxqKernelInfo (*table)[3], bool upload);
+int txq_group_g(TxqKernelInfo (*table)[3], bool upload);
+int txq_group_h(TxqKernelInfo (*table)[3], bool upload);
+int txq_group_i(TxqKernelInfo (*table)[3], bool upload);
 typedef int (*GroupFn)(TxqKernelInfo (*)[3], bool);
 static const GroupFn kGroups[] = { txq_group_a, txq_group_b, txq_group_c,
-                                   txq_group_d, txq_group_e, txq_group_f };
+                                   txq_group_d, txq_group_e, txq_group_f,
+                                   txq_group_g, txq_group_h, txq_group_i };
 
 static TxqKernelInfo g_kernels[B200_TX_SIZES_ALL][3];
 static int g_ctas_per_sm[B200_TX_SIZES_ALL][3];
@@ -49,6 +53,10 @@ static void init_entries() {
 static std::vector<int16_t> g_scan[B200_TX_SIZES_ALL][3], g_iscan[B200_TX_SIZES_ALL][3];
 static size_t g_iscan_dev_offset[B200_TX_SIZES_ALL];
 static size_t g_iscan_total;
+// prefix masks for txq_small.cuh: entry [cls][k] has bit p set for each storage position p
+// among the first k scan entries (k = 0..N), sizes with N <= 64 only
+static std::vector<unsigned long long> g_pmask;
+static size_t g_pmask_offset[B200_TX_SIZES_ALL];
 static std::once_flag g_scan_once;
 
 static void build_scans() {
@@ -79,6 +87,17 @@ static void build_scans() {
     }
     g_iscan_dev_offset[ts] = off;
     off += 3 * (size_t)n;
+    g_pmask_offset[ts] = g_pmask.size();
+    if (n <= 64) {
+      for (int cls = 0; cls < 3; ++cls) {
+        unsigned long long m = 0;
+        g_pmask.push_back(0);
+        for (int k = 0; k < n; ++k) {
+          m |= 1ull << g_scan[ts][cls][k];
+          g_pmask.push_back(m);
+        }
+      }
+    }
   }
   g_iscan_total = off;
 }
@@ -99,6 +118,9 @@ int txq_init_device(b200_ctx *ctx) {
              g_iscan[ts][cls].data(), g_iscan[ts][cls].size() * sizeof(int16_t));
   B200_CUDA_TRY(cudaMalloc(&ctx->d_iscan, all.size() * sizeof(int16_t)));
   B200_CUDA_TRY(cudaMemcpy(ctx->d_iscan, all.data(), all.size() * sizeof(int16_t),
+                           cudaMemcpyHostToDevice));
+  B200_CUDA_TRY(cudaMalloc(&ctx->d_pmask, g_pmask.size() * sizeof(unsigned long long)));
+  B200_CUDA_TRY(cudaMemcpy(ctx->d_pmask, g_pmask.data(), g_pmask.size() * sizeof(unsigned long long),
                            cudaMemcpyHostToDevice));
   for (int ts = 0; ts < B200_TX_SIZES_ALL; ++ts)
     for (int k = 0; k < 3; ++k) {
@@ -143,6 +165,7 @@ int txq_launch(b200_ctx *ctx, const B200TxqLaunch &l, cudaStream_t s) {
   a.pred = l.pred;
   a.qrows = l.qrows;
   a.iscan3 = ctx->d_iscan + g_iscan_dev_offset[l.tx_size];
+  a.pmask3 = ctx->d_pmask + g_pmask_offset[l.tx_size];
   a.coeff = l.coeff;
   a.qcoeff = l.qcoeff;
   a.dqcoeff = l.dqcoeff;

@@ -5,6 +5,7 @@
 #include <math.h>
 
 #include "txq_kernel.cuh"
+#include "txq_small.cuh"
 
 namespace b200 {
 
@@ -36,6 +37,13 @@ static void fill_entries(TxqKernelInfo *e) {
   e[B200_IN_PIXELS16] = txq_kernel_info<W, H, B200_IN_PIXELS16>();
 }
 
+template <int W, int H>
+static void fill_entries_small(TxqKernelInfo *e) {
+  e[B200_IN_RESIDUAL] = txq_small_kernel_info<W, H, B200_IN_RESIDUAL>();
+  e[B200_IN_PIXELS8] = txq_small_kernel_info<W, H, B200_IN_PIXELS8>();
+  e[B200_IN_PIXELS16] = txq_small_kernel_info<W, H, B200_IN_PIXELS16>();
+}
+
 }  // namespace b200
 
 #define B200_TXQ_GROUP_BEGIN(NAME)                                   \
@@ -43,6 +51,7 @@ static void fill_entries(TxqKernelInfo *e) {
   int txq_group_##NAME(TxqKernelInfo (*table)[3], bool upload) {     \
     if (upload) return upload_txfm_constants();
 #define B200_TXQ_SIZE(ENUM, W, H) fill_entries<W, H>(table[ENUM]);
+#define B200_TXQ_SIZE_SMALL(ENUM, W, H) fill_entries_small<W, H>(table[ENUM]);
 #define B200_TXQ_GROUP_END \
   return B200_OK;          \
   }                        \

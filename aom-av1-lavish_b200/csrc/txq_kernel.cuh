@@ -132,6 +132,7 @@ struct TxqArgs {
   const void *pred;
   const B200QRow *qrows;
   const int16_t *iscan3;  // default, mrow, mcol inverse scans of this tx size
+  const unsigned long long *pmask3;  // small sizes: scan prefix masks, 3 x (N + 1), see txq.cu
   int32_t *coeff, *qcoeff, *dqcoeff;
   uint16_t *eob;
   int64_t *dist;
