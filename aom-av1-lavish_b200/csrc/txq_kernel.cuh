@@ -120,8 +120,24 @@ struct SmemCfg {
   static constexpr int kStageBytes = cx_round_up(kOperands * S::kPlaneBytes, 16);
   // deeper prefetch for small tiles (bytes in flight per warp)
   static constexpr int kStages = S::kPlaneBytes >= 2048 ? 2 : (S::kPlaneBytes >= 1024 ? 3 : 4);
-  static constexpr int kXposeBytes = C::BPW * C::XS * 4;
-  static constexpr int kWarpBytes = cx_round_up(kStages * kStageBytes + kXposeBytes, 16);
+  static constexpr int kXposeBytes = cx_round_up(C::BPW * C::XS * 4, 16);
+  // Output tiles (optional bulk-store path, -DB200_TXQ_BULK_OUT): the tile's coeff / qcoeff /
+  // dqcoeff blocks are assembled in shared memory in the codec's storage order and leave
+  // through the bulk-copy engine instead of costing one L1 store wavefront per 32..64 bytes
+  // (short storage columns, Hk <= 16).  Measured on B200 (round 1): one 256..2048-byte bulk
+  // copy per block and array is slower than the direct stores for every size (8x8 0.67 ->
+  // 0.52 of the HBM roofline, 16x16 0.75 -> 0.61), so the path is off by default.
+#ifdef B200_TXQ_BULK_OUT
+  static constexpr bool kBulkOut = C::Hk <= 16;
+#else
+  static constexpr bool kBulkOut = false;
+#endif
+  static constexpr int kOutBlockBytes = C::Wk * C::Hk * 4;
+  static constexpr int kOutPitchWords = C::Wk * C::Hk + C::Hk;  // + Hk: the slots of a round hit distinct banks
+  static constexpr int kOutArrayBytes = C::BPW * kOutPitchWords * 4;
+  static constexpr int kOutBytes = kBulkOut ? 3 * kOutArrayBytes : 0;
+  static constexpr int kOutOff = cx_round_up(kStages * kStageBytes + kXposeBytes, 128);
+  static constexpr int kWarpBytes = cx_round_up(kOutOff + kOutBytes, 128);
   static constexpr int kCtaBytes = kWarpsPerCta * kWarpBytes;
 };
 
@@ -170,6 +186,17 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
+
+// shared -> global bulk copy (TMA engine, no L1 store wavefronts); 16-byte aligned, n % 16 == 0
+__device__ __forceinline__ void bulk_store(void *gdst, const void *ssrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
+               "r"(smem_u32(ssrc)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 __device__ __forceinline__ B200TxBlock load_desc(const B200TxBlock *p) {
   const uint4 raw = __ldg(reinterpret_cast<const uint4 *>(p));
@@ -465,6 +492,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) txq_kernel(const TxqArgs a)
         else column_pass<W, H, true>(vt, ht, x, xpose + slot * C::XS, c);
       }
     }
+    if constexpr (M::kBulkOut) {
+      if (lane < C::TB) bulk_wait_read();  // the previous tile's output blocks have left shared memory
+    }
     __syncwarp();
 
     // ------------------------------------------------------------------- row rounds
@@ -486,12 +516,18 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) txq_kernel(const TxqArgs a)
         if (tile_fast) row_pass<W, H, false>(ht, xrow, y);
         else row_pass<W, H, true>(ht, xrow, y);
         const size_t obase = (size_t)d.out_offset + t;
+        int32_t *oc, *qc, *dqc;
+        if constexpr (M::kBulkOut) {  // assemble the blocks in shared memory, stored below
+          int32_t *ot = reinterpret_cast<int32_t *>(wbase + M::kOutOff) + slot * M::kOutPitchWords + t;
+          oc = ot, qc = ot + M::kOutArrayBytes / 4, dqc = ot + 2 * (M::kOutArrayBytes / 4);
+        } else {
+          oc = a.coeff + obase, qc = a.qcoeff + obase, dqc = a.dqcoeff + obase;
+        }
         if (a.flags & B200_TXQ_STORE_COEFF) {
 #pragma unroll
-          for (int c = 0; c < C::Wk; ++c) a.coeff[obase + c * C::Hk] = y[c];
+          for (int c = 0; c < C::Wk; ++c) oc[c * C::Hk] = y[c];
         }
         if (a.q_kind != B200_Q_NONE) {
-          int32_t *qc = a.qcoeff + obase, *dqc = a.dqcoeff + obase;
           const bool we = (a.flags & B200_TXQ_BLOCK_ERROR) != 0;
           switch (a.q_kind) {
             case B200_Q_FP:
@@ -547,9 +583,51 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) txq_kernel(const TxqArgs a)
         }
       }
     }
+    if constexpr (M::kBulkOut) {
+      fence_async_smem();  // generic-proxy writes above -> visible to the bulk-copy engine
+      __syncwarp();
+      const int bi = wt * C::TB + lane;
+      const bool mine = lane < C::TB && bi < a.n_blocks;
+      const bool want_c = (a.flags & B200_TXQ_STORE_COEFF) != 0, want_q = a.q_kind != B200_Q_NONE;
+      uint32_t ob = 0;
+      bool aligned = true;
+      if (mine) {
+        ob = a.blocks[bi].out_offset;
+        uintptr_t al = 0;
+        if (want_c) al |= reinterpret_cast<uintptr_t>(a.coeff + ob);
+        if (want_q) al |= reinterpret_cast<uintptr_t>(a.qcoeff + ob) | reinterpret_cast<uintptr_t>(a.dqcoeff + ob);
+        aligned = (al & 15) == 0;
+      }
+      const int32_t *ot = reinterpret_cast<const int32_t *>(wbase + M::kOutOff);
+      if (mine && aligned) {
+        const int32_t *src = ot + lane * M::kOutPitchWords;
+        if (want_c) bulk_store(a.coeff + ob, src, M::kOutBlockBytes);
+        if (want_q) {
+          bulk_store(a.qcoeff + ob, src + M::kOutArrayBytes / 4, M::kOutBlockBytes);
+          bulk_store(a.dqcoeff + ob, src + 2 * (M::kOutArrayBytes / 4), M::kOutBlockBytes);
+        }
+        bulk_commit();
+      }
+      // output blocks that are not 16-byte aligned: plain cooperative copy (rare)
+      unsigned bad = __ballot_sync(0xffffffffu, mine && !aligned);
+      while (bad) {
+        const int b = __ffs(bad) - 1;
+        bad &= bad - 1;
+        const uint32_t obb = __shfl_sync(0xffffffffu, ob, b);
+        const int32_t *src = ot + b * M::kOutPitchWords;
+        for (int i = lane; i < C::Wk * C::Hk; i += 32) {
+          if (want_c) a.coeff[(size_t)obb + i] = src[i];
+          if (want_q) {
+            a.qcoeff[(size_t)obb + i] = src[M::kOutArrayBytes / 4 + i];
+            a.dqcoeff[(size_t)obb + i] = src[2 * (M::kOutArrayBytes / 4) + i];
+          }
+        }
+      }
+    }
     __syncwarp();  // stage and transpose tile are reused by the next round
   }
   cp_async_wait<0>();
+  if constexpr (M::kBulkOut) bulk_wait_all();  // shared memory must outlive the last bulk reads
 }
 
 // one launcher per (size, input kind); defined in txq_inst_*.cu
