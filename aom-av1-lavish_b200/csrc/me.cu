@@ -52,12 +52,23 @@ struct Ctx {
   int ref_pitch;             // pixels
   int src_pitch_w;           // source row pitch in 32-bit words (shared copy)
   bool fast;                 // staged window with 16-byte aligned rows: vector-load SAD path
+  bool staged;               // reference window is in shared memory (word-aligned rows at least)
+  int win0_off;              // staged: byte offset inside me_smem of the reference pixel at mv (0,0)
   int px;                    // bytes per pixel
   int sad_shift;             // 0 / 2 / 4: encoder_utils.h:153-208
   unsigned *cand;            // shared: kMaxCand totals
   int *bcast;                // shared scratch for broadcasts
   long long *red;            // shared: 2 * kWarps partial sums (CTA-wide variance)
 };
+
+// Dynamic shared memory of both kernels: source block at offset 0, then the staged reference
+// window.  The hot SAD loops address it through this array (not through the generic
+// pointers of Ctx) so that the compiler emits LDS with 32-bit addresses instead of generic
+// loads with 64-bit address arithmetic.
+extern __shared__ __align__(16) unsigned char me_smem[];
+__device__ __forceinline__ const unsigned *smem_words(int byte_off) {
+  return reinterpret_cast<const unsigned *>(me_smem + byte_off);
+}
 
 // ------------------------------------------------------------------- mv cost -----
 __device__ __forceinline__ int mv_joint(int r, int c) { return (r != 0) * 2 + (c != 0); }
@@ -245,10 +256,146 @@ __device__ __forceinline__ unsigned warp_sad_fast(const Ctx &k, const unsigned c
   }
 }
 
-// SAD of the source block against the reference block at full-pel mv (row, col), computed
-// by ONE warp; every lane returns the total.  skip = rows 0,2,4.. only, doubled.
-__device__ __forceinline__ unsigned warp_sad(const Ctx &k, int row, int col, bool skip, int lane) {
-  const int bh = skip ? k.d.bh >> 1 : k.d.bh, rmul = skip ? 2 : 1;
+// ---- staged 8-bit path, shared-memory addressing ------------------------------------
+// Same lane mapping as warp_sad_vec (8 consecutive lanes = 8 consecutive rows of one
+// 32-pixel segment column: conflict-free uint4 reads), but every address is a 32-bit offset
+// into me_smem and the per-lane offsets are formed once, so that one 32-pixel row segment
+// costs 5 LDS.128 + 8 SHF + 8 VABSDIFF4 and two adds.
+template <int SEGW, int WO>
+__device__ __forceinline__ unsigned sad8_lane(int s_off, int r_off, int n_it, int s_step, int r_step,
+                                              unsigned sh) {
+  constexpr int NV = SEGW / 4;
+  unsigned acc = 0;
+#pragma unroll 2
+  for (int it = 0; it < n_it; ++it) {
+    unsigned sv[SEGW], r[SEGW + 4];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      const uint4 t = reinterpret_cast<const uint4 *>(me_smem + s_off)[v];
+      sv[4 * v] = t.x, sv[4 * v + 1] = t.y, sv[4 * v + 2] = t.z, sv[4 * v + 3] = t.w;
+    }
+#pragma unroll
+    for (int v = 0; v <= NV; ++v) {
+      const uint4 t = reinterpret_cast<const uint4 *>(me_smem + r_off)[v];
+      r[4 * v] = t.x, r[4 * v + 1] = t.y, r[4 * v + 2] = t.z, r[4 * v + 3] = t.w;
+    }
+#pragma unroll
+    for (int i = 0; i < SEGW; ++i)
+      acc = __vsadu4(sv[i], __funnelshift_r(r[WO + i], r[(WO + i + 1) < SEGW + 4 ? WO + i + 1 : WO + i], sh)) + acc;
+    s_off += s_step;
+    r_off += r_step;
+  }
+  return acc;
+}
+
+template <int SEGW>
+__device__ __forceinline__ unsigned sad8_wo(int wo, int s_off, int r_off, int n_it, int s_step,
+                                            int r_step, unsigned sh) {
+  switch (wo) {  // warp-uniform
+    case 0: return sad8_lane<SEGW, 0>(s_off, r_off, n_it, s_step, r_step, sh);
+    case 1: return sad8_lane<SEGW, 1>(s_off, r_off, n_it, s_step, r_step, sh);
+    case 2: return sad8_lane<SEGW, 2>(s_off, r_off, n_it, s_step, r_step, sh);
+    default: return sad8_lane<SEGW, 3>(s_off, r_off, n_it, s_step, r_step, sh);
+  }
+}
+
+// cand_off = byte offset in me_smem of the candidate's top-left reference pixel; the source
+// block sits at offset 0.  bw in {16, 32, 64, 128}.  Returns the warp total in every lane.
+__device__ __noinline__ unsigned sad8_staged(int cand_off, int src_pitch_b, int win_pitch_b, int bw,
+                                             int bh, int rmul) {
+  const int lane = threadIdx.x & 31;
+  const unsigned sh = (unsigned)(cand_off & 3) * 8;
+  const int wo = (cand_off >> 2) & 3, base = cand_off & ~15;
+  unsigned acc;
+  if (bw >= 32) {
+    const int lspr = 31 - __clz(bw >> 5);         // log2(segments per row): 0, 1, 2
+    const int q = lane >> 3;
+    const int seg0 = q & ((1 << lspr) - 1), yl = ((q >> lspr) << 3) + (lane & 7);
+    const int lrpi = 5 - lspr;                    // log2(rows per iteration)
+    const int n_it = yl < bh ? ((bh - 1 - yl) >> lrpi) + 1 : 0;
+    const int ys = yl * rmul, rs = rmul << lrpi;
+    acc = sad8_wo<8>(wo, ys * src_pitch_b + seg0 * 32, base + ys * win_pitch_b + seg0 * 32, n_it,
+                     rs * src_pitch_b, rs * win_pitch_b, sh);
+  } else {
+    const int n_it = lane < bh ? ((bh - 1 - lane) >> 5) + 1 : 0;
+    const int ys = lane * rmul, rs = rmul << 5;
+    acc = sad8_wo<4>(wo, ys * src_pitch_b, base + ys * win_pitch_b, n_it, rs * src_pitch_b,
+                     rs * win_pitch_b, sh);
+  }
+  return warp_sum_u(acc);
+}
+
+// Variance sums on the same layout: |s - r| per byte (VABSDIFF4), then dot products --
+// sse += d.d, sum_s += s.1, sum_r += r.1 (DP4A) -- instead of one scalar lane per pixel.
+template <int SEGW, int WO>
+__device__ __forceinline__ void var8_lane(int s_off, int r_off, int it0, int n_it, int it_step,
+                                          int s_step, int r_step, unsigned sh, unsigned &ss,
+                                          unsigned &sr, unsigned &sse) {
+  constexpr int NV = SEGW / 4;
+  for (int it = it0; it < n_it; it += it_step) {
+    unsigned sv[SEGW], r[SEGW + 4];
+    const int so = s_off + it * s_step, ro = r_off + it * r_step;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      const uint4 t = reinterpret_cast<const uint4 *>(me_smem + so)[v];
+      sv[4 * v] = t.x, sv[4 * v + 1] = t.y, sv[4 * v + 2] = t.z, sv[4 * v + 3] = t.w;
+    }
+#pragma unroll
+    for (int v = 0; v <= NV; ++v) {
+      const uint4 t = reinterpret_cast<const uint4 *>(me_smem + ro)[v];
+      r[4 * v] = t.x, r[4 * v + 1] = t.y, r[4 * v + 2] = t.z, r[4 * v + 3] = t.w;
+    }
+#pragma unroll
+    for (int i = 0; i < SEGW; ++i) {
+      const unsigned rv = __funnelshift_r(r[WO + i], r[(WO + i + 1) < SEGW + 4 ? WO + i + 1 : WO + i], sh);
+      const unsigned d = __vabsdiffu4(sv[i], rv);
+      sse = __dp4a(d, d, sse);
+      ss = __dp4a(sv[i], 0x01010101u, ss);
+      sr = __dp4a(rv, 0x01010101u, sr);
+    }
+  }
+}
+
+template <int SEGW>
+__device__ __forceinline__ void var8_wo(int wo, int s_off, int r_off, int it0, int n_it, int it_step,
+                                        int s_step, int r_step, unsigned sh, unsigned &ss,
+                                        unsigned &sr, unsigned &sse) {
+  switch (wo) {
+    case 0: var8_lane<SEGW, 0>(s_off, r_off, it0, n_it, it_step, s_step, r_step, sh, ss, sr, sse); break;
+    case 1: var8_lane<SEGW, 1>(s_off, r_off, it0, n_it, it_step, s_step, r_step, sh, ss, sr, sse); break;
+    case 2: var8_lane<SEGW, 2>(s_off, r_off, it0, n_it, it_step, s_step, r_step, sh, ss, sr, sse); break;
+    default: var8_lane<SEGW, 3>(s_off, r_off, it0, n_it, it_step, s_step, r_step, sh, ss, sr, sse); break;
+  }
+}
+
+// Per-lane partial sums of (src - ref) and (src - ref)^2 over the whole block, the rows
+// dealt out to all `n_warps` warps of the CTA (iteration `it` goes to warp it % n_warps).
+__device__ __noinline__ void var8_staged(int cand_off, int src_pitch_b, int win_pitch_b, int bw, int bh,
+                                         int n_warps, int *sum_out, unsigned *sse_out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned sh = (unsigned)(cand_off & 3) * 8;
+  const int wo = (cand_off >> 2) & 3, base = cand_off & ~15;
+  unsigned ss = 0, sr = 0, sse = 0;
+  if (bw >= 32) {
+    const int lspr = 31 - __clz(bw >> 5);
+    const int q = lane >> 3;
+    const int seg0 = q & ((1 << lspr) - 1), yl = ((q >> lspr) << 3) + (lane & 7);
+    const int lrpi = 5 - lspr;
+    const int n_it = yl < bh ? ((bh - 1 - yl) >> lrpi) + 1 : 0;
+    var8_wo<8>(wo, yl * src_pitch_b + seg0 * 32, base + yl * win_pitch_b + seg0 * 32, warp, n_it,
+               n_warps, src_pitch_b << lrpi, win_pitch_b << lrpi, sh, ss, sr, sse);
+  } else {
+    const int n_it = lane < bh ? ((bh - 1 - lane) >> 5) + 1 : 0;
+    var8_wo<4>(wo, lane * src_pitch_b, base + lane * win_pitch_b, warp, n_it, n_warps,
+               src_pitch_b << 5, win_pitch_b << 5, sh, ss, sr, sse);
+  }
+  *sum_out = (int)ss - (int)sr;
+  *sse_out = sse;
+}
+
+// Everything else (window not staged, high bit depth, 4- and 8-pixel wide blocks).
+__device__ __noinline__ unsigned warp_sad_slow(const Ctx &k, int row, int col, int bh, int rmul) {
+  const int lane = threadIdx.x & 31;
   const unsigned char *rp = k.ref0 + ((long long)row * k.ref_pitch + col) * k.px;
   const int row_words = k.d.bw * k.px / 4;
   unsigned acc;
@@ -267,7 +414,19 @@ __device__ __forceinline__ unsigned warp_sad(const Ctx &k, int row, int col, boo
     else if (row_words == 4) acc = warp_sad_t<4, 2>(k, rp, bh, rmul, lane);
     else acc = warp_sad_t<2, 2>(k, rp, bh, rmul, lane);
   }
-  acc = warp_sum_u(acc);
+  return warp_sum_u(acc);
+}
+
+// SAD of the source block against the reference block at full-pel mv (row, col), computed
+// by ONE warp; every lane returns the total.  skip = rows 0,2,4.. only, doubled.
+__device__ __forceinline__ unsigned warp_sad(const Ctx &k, int row, int col, bool skip, int lane) {
+  const int bh = skip ? k.d.bh >> 1 : k.d.bh, rmul = skip ? 2 : 1;
+  unsigned acc;
+  if (k.fast && k.px == 1 && k.d.bw >= 16)
+    acc = sad8_staged(k.win0_off + row * k.ref_pitch + col, k.src_pitch_w * 4, k.ref_pitch, k.d.bw, bh,
+                      rmul);
+  else
+    acc = warp_sad_slow(k, row, col, bh, rmul);
   if (skip) acc *= 2;
   return acc >> k.sad_shift;
 }

@@ -24,6 +24,14 @@ __device__ int var_cost(const Ctx &k, Mv m) {
   const unsigned char *rp = k.ref0 + ((long long)m.row * k.ref_pitch + m.col) * k.px;
   long long sum = 0;
   unsigned long long sse = 0;
+  if (k.fast && k.px == 1 && bw >= 16) {
+    int lsum;
+    unsigned lsse;
+    var8_staged(k.win0_off + m.row * k.ref_pitch + m.col, k.src_pitch_w * 4, k.ref_pitch, bw, k.d.bh,
+                kWarps, &lsum, &lsse);
+    sum = lsum;
+    sse = lsse;
+  } else
   for (int i = threadIdx.x; i < n; i += kThreads) {
     const int y = i / bw, x = i - y * bw;
     int sv, rv;
@@ -150,6 +158,199 @@ __device__ int full_pixel_diamond(const Ctx &k, bool skip, Mv start, int step_pa
   return bestsme;
 }
 
+// ---- register-blocked SAD maps for the mesh stages -----------------------------------
+// The generic path above spends one warp per candidate and re-reads source and reference
+// from shared memory for every candidate (5 LDS.128 per 8 VABSDIFF4).  A mesh stage is a
+// regular grid of candidates, so neighbouring candidates can share loaded words:
+//   * step 1 (`mesh1_band`): a lane owns RB vertically adjacent candidates of one column
+//     offset; it walks the reference rows once, funnel-shifts each loaded row once, and
+//     compares it against a rotating window of RB source rows held in registers
+//     (SEGW shifts + RB * SEGW VABSDIFF4.ACC per SEGW + 1 reference words loaded);
+//   * step 4 / 8 / 16 (`mesh_strided_band`): candidates of one grid row are whole words
+//     apart, so a lane loads one long aligned strip of a reference row, shifts it once and
+//     slides the source row over it for JB horizontally adjacent candidates.
+// Both write `SAD + mv cost` of every candidate of a band of grid rows into k.cand[] in
+// scan order (shared-memory atomics join the 32-pixel column segments of a block).
+// Preconditions (checked by the caller): 8-bit, window staged in shared memory, no row
+// skipping, bw >= 4 * SEGW, bh a multiple of 4.
+template <int N>
+__device__ __forceinline__ void load_words(const unsigned *p, unsigned (&o)[N]) {
+  if constexpr (N >= 4) {
+#pragma unroll
+    for (int v = 0; v < N / 4; ++v) {
+      const uint4 t = reinterpret_cast<const uint4 *>(p)[v];
+      o[4 * v] = t.x, o[4 * v + 1] = t.y, o[4 * v + 2] = t.z, o[4 * v + 3] = t.w;
+    }
+  } else if constexpr (N == 2) {
+    const uint2 t = *reinterpret_cast<const uint2 *>(p);
+    o[0] = t.x, o[1] = t.y;
+  } else {
+    o[0] = p[0];
+  }
+}
+
+constexpr int kRB = 4;  // vertically adjacent candidates per lane (step 1)
+constexpr int kJB = 4;  // horizontally adjacent candidates per lane (step 4 / 8 / 16)
+
+// PHASE 0: first RB reference rows (source window filling), 1: steady state, 2: last RB - 1
+// rows (window draining).
+template <int SEGW, int PHASE>
+__device__ __forceinline__ void mesh1_chunk(int s_off, int src_pitch_b, int r_off, int pitch_b,
+                                            unsigned sh, int t0, int tmax,
+                                            unsigned (&sw)[kRB][SEGW], unsigned (&acc)[kRB]) {
+#pragma unroll
+  for (int u = 0; u < kRB; ++u) {
+    if (PHASE == 2 && u == kRB - 1) break;
+    const int t = t0 + u;
+    if (PHASE == 2 && t >= tmax) break;  // warp-uniform
+    if (PHASE != 2) load_words<SEGW>(smem_words(s_off + t * src_pitch_b), sw[u]);
+    unsigned r[SEGW + 1], rv[SEGW];
+    const unsigned *rp = smem_words(r_off + t * pitch_b);
+#pragma unroll
+    for (int i = 0; i <= SEGW; ++i) r[i] = rp[i];
+#pragma unroll
+    for (int i = 0; i < SEGW; ++i) rv[i] = __funnelshift_r(r[i], r[i + 1], sh);
+#pragma unroll
+    for (int c = 0; c < kRB; ++c) {
+      if (PHASE == 0 && c > u) continue;
+      if (PHASE == 2 && c <= u) continue;
+#pragma unroll
+      for (int i = 0; i < SEGW; ++i) acc[c] = __vsadu4(sw[(u - c) & (kRB - 1)][i], rv[i]) + acc[c];
+    }
+  }
+}
+
+template <int SEGW>
+__device__ void mesh1_band(const Ctx &k, int row0, int nrows, int col0, int nc) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int bh = k.d.bh, nseg = k.d.bw / (4 * SEGW);
+  const int nrg = (nrows + kRB - 1) / kRB, ncc = (nc + 31) >> 5;
+  const int ntask = nrg * nseg * ncc;
+  const int pitch_b = k.ref_pitch, src_pitch_b = k.src_pitch_w * 4;
+  for (int task = warp; task < ntask; task += kWarps) {
+    const int cc = task % ncc, seg = (task / ncc) % nseg, rg = task / (ncc * nseg);
+    const int nk = min(kRB, nrows - rg * kRB);
+    const int ci = cc * 32 + lane, cia = min(ci, nc - 1);
+    const int row = row0 + rg * kRB, col = col0 + cia;
+    const int a = k.win0_off + row * pitch_b + col + seg * SEGW * 4;
+    const int r_off = a & ~3, s_off = seg * SEGW * 4;
+    const unsigned sh = (unsigned)(a & 3) * 8;
+    unsigned sw[kRB][SEGW], acc[kRB];
+#pragma unroll
+    for (int c = 0; c < kRB; ++c) acc[c] = 0;
+    const int tmax = bh + nk - 1;
+    mesh1_chunk<SEGW, 0>(s_off, src_pitch_b, r_off, pitch_b, sh, 0, tmax, sw, acc);
+    for (int t0 = kRB; t0 < bh; t0 += kRB)
+      mesh1_chunk<SEGW, 1>(s_off, src_pitch_b, r_off, pitch_b, sh, t0, tmax, sw, acc);
+    mesh1_chunk<SEGW, 2>(s_off, src_pitch_b, r_off, pitch_b, sh, bh, tmax, sw, acc);
+    if (ci < nc) {
+#pragma unroll
+      for (int c = 0; c < kRB; ++c)
+        if (c < nk) {
+          unsigned v = acc[c];
+          if (seg == 0) v += (unsigned)sad_cost(k, row + c, col);
+          atomicAdd(&k.cand[(rg * kRB + c) * nc + ci], v);
+        }
+    }
+  }
+}
+
+template <int SEGW, int STEPW, int WO>
+__device__ void mesh_strided_band_t(const Ctx &k, int row0, int nrows, int col0, int nc, int step,
+                                    unsigned sh) {
+  constexpr int NSH = SEGW + (kJB - 1) * STEPW;  // shifted words needed
+  constexpr int NV = (WO + NSH + 1 + 3) / 4;     // aligned uint4 loads covering them (+1 for the funnel)
+  const int lane = threadIdx.x & 31, ylane = threadIdx.x & 7;
+  const unsigned gmask = 0xffu << (lane & 24);
+  const int bh = k.d.bh, nseg = k.d.bw / (4 * SEGW);
+  const int ncg = (nc + kJB - 1) / kJB;
+  const int ntask = nrows * ncg * nseg;
+  const int pitch_b = k.ref_pitch, src_pitch_b = k.src_pitch_w * 4;
+  for (int task = threadIdx.x >> 3; task < ntask; task += kThreads / 8) {
+    const int seg = task % nseg, cg = (task / nseg) % ncg, ri = task / (nseg * ncg);
+    const int row = row0 + ri * step, col = col0 + cg * kJB * step;
+    const int r_off = (k.win0_off + row * pitch_b + col + seg * SEGW * 4) & ~15;
+    const int s_off = seg * SEGW * 4;
+    unsigned acc[kJB];
+#pragma unroll
+    for (int j = 0; j < kJB; ++j) acc[j] = 0;
+    for (int y = ylane; y < bh; y += 8) {
+      unsigned s[SEGW], r[4 * NV], v[NSH];
+      load_words<SEGW>(smem_words(s_off + y * src_pitch_b), s);
+      load_words<4 * NV>(smem_words(r_off + y * pitch_b), r);
+#pragma unroll
+      for (int i = 0; i < NSH; ++i) v[i] = __funnelshift_r(r[WO + i], r[WO + i + 1], sh);
+#pragma unroll
+      for (int j = 0; j < kJB; ++j)
+#pragma unroll
+        for (int i = 0; i < SEGW; ++i) acc[j] = __vsadu4(s[i], v[j * STEPW + i]) + acc[j];
+    }
+#pragma unroll
+    for (int j = 0; j < kJB; ++j) {
+      acc[j] += __shfl_xor_sync(gmask, acc[j], 1);
+      acc[j] += __shfl_xor_sync(gmask, acc[j], 2);
+      acc[j] += __shfl_xor_sync(gmask, acc[j], 4);
+    }
+    if (ylane == 0) {
+#pragma unroll
+      for (int j = 0; j < kJB; ++j) {
+        const int ci = cg * kJB + j;
+        if (ci < nc) {
+          unsigned t = acc[j];
+          if (seg == 0) t += (unsigned)sad_cost(k, row, col + j * step);
+          atomicAdd(&k.cand[ri * nc + ci], t);
+        }
+      }
+    }
+  }
+}
+
+template <int SEGW, int STEPW>
+__device__ __forceinline__ void mesh_strided_band(const Ctx &k, int row0, int nrows, int col0, int nc,
+                                                  int step) {
+  // all candidates of a stage share the byte alignment (their columns differ by whole
+  // multiples of 16 pixels within a lane group and of 4 pixels overall)
+  const int a = k.win0_off + col0;
+  const unsigned sh = (unsigned)(a & 3) * 8;
+  // word offset inside the 16-byte chunk: candidates of one lane group start kJB * step
+  // pixels apart (a multiple of 16), grid rows start step * pitch apart (pitch % 16 == 0)
+  switch ((a >> 2) & 3) {
+    case 0: mesh_strided_band_t<SEGW, STEPW, 0>(k, row0, nrows, col0, nc, step, sh); break;
+    case 1: mesh_strided_band_t<SEGW, STEPW, 1>(k, row0, nrows, col0, nc, step, sh); break;
+    case 2: mesh_strided_band_t<SEGW, STEPW, 2>(k, row0, nrows, col0, nc, step, sh); break;
+    default: mesh_strided_band_t<SEGW, STEPW, 3>(k, row0, nrows, col0, nc, step, sh); break;
+  }
+}
+
+// 0: no fast path for this stage; otherwise fills k.cand[0..nrows*nc) (must be zeroed)
+__device__ __forceinline__ bool mesh_band_fast(const Ctx &k, int row0, int nrows, int col0, int nc,
+                                               int step) {
+  const int bw = k.d.bw;
+  if (step == 1) {
+    if (bw >= 32) mesh1_band<8>(k, row0, nrows, col0, nc);
+    else if (bw == 16) mesh1_band<4>(k, row0, nrows, col0, nc);
+    else mesh1_band<2>(k, row0, nrows, col0, nc);
+    return true;
+  }
+  if (bw >= 32) {
+    if (step == 4) mesh_strided_band<8, 1>(k, row0, nrows, col0, nc, step);
+    else if (step == 8) mesh_strided_band<8, 2>(k, row0, nrows, col0, nc, step);
+    else mesh_strided_band<8, 4>(k, row0, nrows, col0, nc, step);
+  } else {
+    if (step == 4) mesh_strided_band<4, 1>(k, row0, nrows, col0, nc, step);
+    else if (step == 8) mesh_strided_band<4, 2>(k, row0, nrows, col0, nc, step);
+    else mesh_strided_band<4, 4>(k, row0, nrows, col0, nc, step);
+  }
+  return true;
+}
+
+__device__ __forceinline__ bool mesh_fast_ok(const Ctx &k, bool skip, int step, int nc) {
+  if (skip || k.px != 1 || !k.staged || (k.d.bh & 3) || nc > kMaxCand) return false;
+  if (step == 1) return k.d.bw >= 8;
+  // strided: 16-byte aligned window rows (vector loads), whole-word candidate spacing
+  return k.fast && k.d.bw >= 16 && (step == 4 || step == 8 || step == 16);
+}
+
 // exhaustive_mesh_search (mcomp.c:1530-1599).  Candidates are visited row-major; at
 // step 1 the reference works in groups of four columns and its tail loop stops one short
 // of the last column (`i < end_col - c`, :1586) -- reproduced.
@@ -172,14 +373,30 @@ __device__ int mesh_search(const Ctx &k, bool skip, Mv start, int range, int ste
     nc = (full & 3) ? full - 1 : full;
   }
   const int total = nr * nc;
-  for (int base = 0; base < total; base += kMaxCand) {
-    const int cnt = min(kMaxCand, total - base);
-    for (int j = warp; j < cnt; j += kWarps) {
-      const int idx = base + j;
-      const int ri = idx / nc, ci = idx - ri * nc;
-      const int r = start.row + r0 + ri * step, c = start.col + c0 + ci * step;
-      const unsigned t = warp_sad(k, r, c, skip, lane) + (unsigned)sad_cost(k, r, c);
-      if (lane == 0) k.cand[j] = t;
+  // chunks of the scan: whole grid rows ("bands") for the register-blocked SAD maps,
+  // kMaxCand candidates otherwise.  Chunk boundaries do not influence the decisions.
+  const bool fast = mesh_fast_ok(k, skip, step, nc);
+  int band_rows = 0;
+  if (fast) {
+    band_rows = min(nr, kMaxCand / nc);
+    if (band_rows > kRB) band_rows &= ~(kRB - 1);
+  }
+  const int chunk = fast ? band_rows * nc : kMaxCand;
+  for (int base = 0; base < total; base += chunk) {
+    const int cnt = min(chunk, total - base);
+    if (fast) {
+      for (int j = threadIdx.x; j < cnt; j += kThreads) k.cand[j] = 0;
+      __syncthreads();
+      const int ri0 = base / nc;
+      mesh_band_fast(k, start.row + r0 + ri0 * step, cnt / nc, start.col + c0, nc, step);
+    } else {
+      for (int j = warp; j < cnt; j += kWarps) {
+        const int idx = base + j;
+        const int ri = idx / nc, ci = idx - ri * nc;
+        const int r = start.row + r0 + ri * step, c = start.col + c0 + ci * step;
+        const unsigned t = warp_sad(k, r, c, skip, lane) + (unsigned)sad_cost(k, r, c);
+        if (lane == 0) k.cand[j] = t;
+      }
     }
     __syncthreads();
     // Replay update_mvs_and_sad (:858) over the chunk without walking it serially: the
@@ -342,6 +559,7 @@ __device__ void stage_inputs(Ctx &k, unsigned char *smem, int window_budget, int
   k.ref0 = g_ref0;
   k.ref_pitch = l.ref_stride;
   k.fast = false;
+  k.staged = false;
   // window = limits box (+ `extra` pixels on every side) + block
   const int wr0 = k.d.row_min - extra, wc0 = k.d.col_min - extra;
   const int wh = k.d.row_max - k.d.row_min + 2 * extra + bh;
@@ -365,13 +583,14 @@ __device__ void stage_inputs(Ctx &k, unsigned char *smem, int window_budget, int
     k.ref0 = reinterpret_cast<unsigned char *>(s_win) + lead +
              ((long long)(-wr0) * k.ref_pitch + (-wc0)) * px;
     k.fast = vec;
+    k.staged = true;
+    k.win0_off = src_bytes + lead + ((-wr0) * k.ref_pitch + (-wc0)) * px;
   }
   __syncthreads();
 }
 
 __global__ void __launch_bounds__(kThreads, 3) fullpel_kernel(const B200MeLaunch l, const Sites *sites4,
                                                            int window_budget) {
-  extern __shared__ __align__(16) unsigned char me_smem[];
   __shared__ unsigned s_cand[kMaxCand + 16];
   __shared__ int s_bcast[16];
   __shared__ long long s_red[2 * kWarps];

@@ -95,7 +95,8 @@ extern "C" int b200_me_fullpel_launch(b200_ctx *ctx, const B200MeLaunch *l, void
   if (budget > b200::me::kWindowBudget) budget = b200::me::kWindowBudget;
   const int mbw = l->max_bw > 0 ? l->max_bw : 128, mbh = l->max_bh > 0 ? l->max_bh : 128;
   // source block with padded row pitch (<= row words + 11) + window
-  const size_t smem = (size_t)(mbw * (l->highbd ? 2 : 1) + 44) * mbh + 16 + (size_t)budget;
+  // + 128: the strip loads of the strided mesh path may run a few words past the window
+  const size_t smem = (size_t)(mbw * (l->highbd ? 2 : 1) + 44) * mbh + 16 + (size_t)budget + 128;
   b200::me::fullpel_kernel<<<l->n_blocks, b200::me::kThreads, smem, s>>>(
       *l, static_cast<const b200::me::Sites *>(ctx->d_me_sites), budget);
   B200_CUDA_TRY(cudaGetLastError());

@@ -190,7 +190,6 @@ __device__ void subpel_search(const SubCtx &s, SubState &st) {
 }
 
 __global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) {
-  extern __shared__ __align__(16) unsigned char me_smem[];
   __shared__ long long s_red[2 * kWarps];
   __shared__ int s_bcast[16];
   const int bi = blockIdx.x;

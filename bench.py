@@ -224,93 +224,104 @@ def cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed, n_threads, sizes=r
 ME_BORDER = 160  # AOM_ENC_NO_SCALE_BORDER, aom_scale/yv12config.h:28-32
 
 
-def bench_me(ctx, dev, stream, steps, warmup, seed, frame_id):
+def bench_me(ctx, dev, stream, steps, warmup, seed, frame_id, n_frames=8):
     """BASELINE configs[2]: full-pel (NSTEP + mesh {64,8},{28,4},{15,1}) and sub-pel (8-tap
-    tree) search of every 64x64 superblock of a 1080p 8-bit frame against 2 references,
-    +-64 range, L1 (HD) mv cost.  Returns device-timed ms per frame for both kernels."""
+    tree) search of every 64x64 superblock of `n_frames` 1080p 8-bit frames against 2
+    references each, +-64 range, L1 (HD) mv cost.  All frames and references live in one
+    plane pool (stacked vertically), so ONE launch per kernel covers the whole batch.
+    Returns device-timed ms per frame for both kernels."""
     import torch
     import b200av1
     import synth
     rng = np.random.default_rng([seed, frame_id, 77])
     w, h = 1920, 1080
-    cur = synth.smooth_frame(rng, w, h, 8)
-    refs = []
-    for r in range(2):
-        dy, dx = int(rng.integers(-20, 21)), int(rng.integers(-20, 21))
-        ref = np.roll(cur, (dy, dx), (0, 1)).astype(np.int32) + np.rint(rng.normal(0, 2, cur.shape)).astype(np.int32)
-        refs.append(np.pad(np.clip(ref, 0, 255).astype(np.uint8), ME_BORDER, mode="edge"))
-    rstride = w + 2 * ME_BORDER
+    base = synth.smooth_frame(rng, w, h, 8)
+    rstride, rh = w + 2 * ME_BORDER, h + 2 * ME_BORDER
+    curs = np.zeros((n_frames, h, w), np.uint8)
+    refs = np.zeros((n_frames * 2, rh, rstride), np.uint8)
+    for f in range(n_frames):
+        curs[f] = np.roll(base, (f * 2, f * 3), (0, 1))
+        for r in range(2):
+            dy, dx = int(rng.integers(-20, 21)), int(rng.integers(-20, 21))
+            ref = np.roll(curs[f], (dy, dx), (0, 1)).astype(np.int16) + \
+                np.rint(rng.normal(0, 2, (h, w))).astype(np.int16)
+            refs[f * 2 + r] = np.pad(np.clip(ref, 0, 255).astype(np.uint8), ME_BORDER, mode="edge")
     sbs = [(bx, by) for by in range(0, h - 63, 64) for bx in range(0, w - 63, 64)]
-    n = len(sbs)
+    n_sb = len(sbs)
+    n = n_sb * 2 * n_frames
     blocks = np.zeros(n, b200av1.MEBLOCK_DTYPE)
-    for i, (bx, by) in enumerate(sbs):
-        b = blocks[i]
-        b["src_offset"], b["ref_offset"] = by * w + bx, (by + ME_BORDER) * rstride + bx + ME_BORDER
-        b["col_min"], b["col_max"], b["row_min"], b["row_max"] = -64, 64, -64, 64
-        b["bw"], b["bh"] = 64, 64
-        b["search_method"] = 0  # B200_ME_NSTEP
-        b["flags"] = b200av1.ME_RUN_MESH
-        b["mv_cost_type"] = 3  # MV_COST_L1_HDRES
-        b["sad_per_bit"], b["error_per_bit"] = 40, 90
+    i = 0
+    for f in range(n_frames):
+        for r in range(2):
+            for (bx, by) in sbs:
+                b = blocks[i]
+                b["src_offset"] = (f * h + by) * w + bx
+                b["ref_offset"] = ((f * 2 + r) * rh + by + ME_BORDER) * rstride + bx + ME_BORDER
+                i += 1
+    blocks["col_min"], blocks["col_max"], blocks["row_min"], blocks["row_max"] = -64, 64, -64, 64
+    blocks["bw"], blocks["bh"] = 64, 64
+    blocks["search_method"] = 0  # B200_ME_NSTEP
+    blocks["flags"] = b200av1.ME_RUN_MESH
+    blocks["mv_cost_type"] = 3  # MV_COST_L1_HDRES
+    blocks["sad_per_bit"], blocks["error_per_bit"] = 40, 90
     blocks["step_param"] = b200av1.lib().b200_me_init_search_range(64)
-    d_cur = torch.from_numpy(cur.reshape(-1)).to(dev)
-    d_refs = [torch.from_numpy(r.reshape(-1)).to(dev) for r in refs]
+    d_cur = torch.from_numpy(curs.reshape(-1)).to(dev)
+    d_ref = torch.from_numpy(refs.reshape(-1)).to(dev)
     d_blk = torch.from_numpy(blocks.view(np.uint8)).to(dev)
-    d_res = [torch.zeros(n * 40, dtype=torch.uint8, device=dev) for _ in range(2)]
+    d_res = torch.zeros(n * 40, dtype=torch.uint8, device=dev)
 
-    def launch(kind, ref_id, d_blocks):
+    def launch(kind, d_blocks):
         l = b200av1.MeLaunch()
         l.highbd, l.bd, l.n_blocks = 0, 8, n
-        l.blocks, l.cur, l.ref = d_blocks.data_ptr(), d_cur.data_ptr(), d_refs[ref_id].data_ptr()
+        l.blocks, l.cur, l.ref = d_blocks.data_ptr(), d_cur.data_ptr(), d_ref.data_ptr()
         l.cur_stride, l.ref_stride = w, rstride
         for i, (r, it) in enumerate(((64, 8), (28, 4), (15, 1), (7, 1))):
             l.mesh_range[i], l.mesh_interval[i] = r, it
-        l.results = d_res[ref_id].data_ptr()
+        l.results = d_res.data_ptr()
         l.window_bytes, l.max_bw, l.max_bh = 48 * 1024, 64, 64
         fn = b200av1.lib().b200_me_fullpel_launch if kind == 0 else b200av1.lib().b200_me_subpel_launch
         b200av1.check(fn(ctx.h, C.byref(l), C.c_void_p(stream.cuda_stream)))
 
     # full-pel once (untimed) to build the sub-pel descriptors from its results
-    for r in range(2):
-        launch(0, r, d_blk)
+    launch(0, d_blk)
     torch.cuda.synchronize(dev)
-    d_sub = []
-    for r in range(2):
-        res = d_res[r].cpu().numpy().view(b200av1.MERESULT_DTYPE)
-        if os.environ.get("B200_ME_DEBUG"):  # library built with -DB200_ME_TIMING (dev only)
-            print("ME timing (cycles): staging %.0f diamond %.0f total %.0f" % (
-                16 * res["cost_list"][:, 4].mean(), 16.0 * res["distortion"].mean(),
-                16.0 * res["sse"].mean()), file=sys.stderr)
-        sb = blocks.copy()
-        sb["start_row"], sb["start_col"] = res["best_row"] * 8, res["best_col"] * 8
-        sb["col_min"], sb["col_max"], sb["row_min"], sb["row_max"] = -512, 512, -512, 512
-        sb["flags"] = b200av1.ME_ALLOW_HP
-        sb["subpel"] = 0 | (2 << 2) | (3 << 4)  # EIGHTH_PEL, 2 iters/step, USE_8_TAPS
-        d_sub.append(torch.from_numpy(sb.view(np.uint8)).to(dev))
+    res = d_res.cpu().numpy().view(b200av1.MERESULT_DTYPE)
+    if os.environ.get("B200_ME_DEBUG"):  # library built with -DB200_ME_TIMING (dev only)
+        print("ME timing (cycles): staging %.0f diamond %.0f total %.0f" % (
+            16 * res["cost_list"][:, 4].mean(), 16.0 * res["distortion"].mean(),
+            16.0 * res["sse"].mean()), file=sys.stderr)
+    sb = blocks.copy()
+    sb["start_row"], sb["start_col"] = res["best_row"] * 8, res["best_col"] * 8
+    sb["col_min"], sb["col_max"], sb["row_min"], sb["row_max"] = -512, 512, -512, 512
+    sb["flags"] = b200av1.ME_ALLOW_HP
+    sb["subpel"] = 0 | (2 << 2) | (3 << 4)  # EIGHTH_PEL, 2 iters/step, USE_8_TAPS
+    d_sub = torch.from_numpy(sb.view(np.uint8)).to(dev)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
     t_full = t_sub = 0.0
     for it in range(warmup + steps):
         ev[0].record(stream)
-        for r in range(2):
-            launch(0, r, d_blk)
+        launch(0, d_blk)
         ev[1].record(stream)
-        for r in range(2):
-            launch(1, r, d_sub[r])
+        launch(1, d_sub)
         ev[2].record(stream)
         torch.cuda.synchronize(dev)
         if it >= warmup:
             t_full += ev[0].elapsed_time(ev[1])
             t_sub += ev[1].elapsed_time(ev[2])
+    t_full /= steps * n_frames  # ms per frame
+    t_sub /= steps * n_frames
     # mesh candidates per search (lower bound of the SAD work; diamond steps come on top):
     # 17x17 @8, 15x15 @4, 31 rows x 30 cols @1 (the reference's tail-loop quirk)
     cands = 17 * 17 + 15 * 15 + 31 * 30
-    return {"workload": "config[2]: 1080p 8-bit, %d 64x64 SBs x 2 refs, +-64, NSTEP+mesh, 8-tap sub-pel" % n,
-            "fullpel_ms_per_frame": t_full / steps, "subpel_ms_per_frame": t_sub / steps,
-            "frames_per_s": 1e3 * steps / (t_full + t_sub),
-            "mesh_gabsdiff_per_s": 2 * n * cands * 4096 / (t_full / steps * 1e-3) / 1e9,
-            "unique_bytes_per_frame": 2 * n * (4096 + 192 * 192 + 64),
-            "unique_GBps": 2 * n * (4096 + 192 * 192 + 64) / (t_full / steps * 1e-3) / 1e9,
-            "launches_per_frame": 4}
+    per_frame = 2 * n_sb
+    return {"workload": "config[2]: %d frames x 1080p 8-bit, %d 64x64 SBs x 2 refs per frame, +-64, "
+                        "NSTEP+mesh, 8-tap sub-pel; one launch per kernel" % (n_frames, n_sb),
+            "fullpel_ms_per_frame": t_full, "subpel_ms_per_frame": t_sub,
+            "frames_per_s": 1e3 / (t_full + t_sub),
+            "mesh_gabsdiff_per_s": per_frame * cands * 4096 / (t_full * 1e-3) / 1e9,
+            "unique_bytes_per_frame": per_frame * (4096 + 192 * 192 + 64),
+            "unique_GBps": per_frame * (4096 + 192 * 192 + 64) / (t_full * 1e-3) / 1e9,
+            "launches_per_step": 2, "frames_per_launch": n_frames}
 
 
 
