@@ -54,6 +54,8 @@ struct Ctx {
   bool fast;                 // staged window with 16-byte aligned rows: vector-load SAD path
   bool staged;               // reference window is in shared memory (word-aligned rows at least)
   int win0_off;              // staged: byte offset inside me_smem of the reference pixel at mv (0,0)
+  int cost_fr, cost_fc;      // full-pel reference mv of the sad-domain mv cost
+  int l1_mul;                // 32 / 15 / 8 for the L1 cost types, 0 otherwise
   int px;                    // bytes per pixel
   int sad_shift;             // 0 / 2 / 4: encoder_utils.h:153-208
   unsigned *cand;            // shared: kMaxCand totals
@@ -77,21 +79,22 @@ __device__ __forceinline__ int mv_cost_tab(const Ctx &k, int dr, int dc) {
   return k.l->mvjcost[mv_joint(dr, dc)] + k.l->mvcost[0][dr] + k.l->mvcost[1][dc];
 }
 
-// mvsad_err_cost (mcomp.c:329)
-__device__ __forceinline__ int sad_cost(const Ctx &k, int row, int col) {
+// mvsad_err_cost (mcomp.c:329).  The full-pel reference mv (GET_MV_RAWPEL of ref_mv) and the
+// L1 weight of the cost type are per-search constants kept in Ctx (init_costs).
+__device__ __forceinline__ void init_costs(Ctx &k) {
   const int rr = k.d.ref_mv_row, rc = k.d.ref_mv_col;
-  const int fr = (rr + 3 + (rr >= 0)) >> 3, fc = (rc + 3 + (rc >= 0)) >> 3;  // GET_MV_RAWPEL
-  const int dr = (short)((row - fr) * 8), dc = (short)((col - fc) * 8);
-  switch (k.d.mv_cost_type) {
-    case B200_MV_COST_ENTROPY: {
-      const unsigned c = (unsigned)mv_cost_tab(k, dr, dc) * (unsigned)k.d.sad_per_bit;
-      return (int)((c + 256u) >> 9);
-    }
-    case B200_MV_COST_L1_LOWRES: return (32 * (abs(dr) + abs(dc))) >> 3;
-    case B200_MV_COST_L1_MIDRES: return (15 * (abs(dr) + abs(dc))) >> 3;
-    case B200_MV_COST_L1_HDRES: return (8 * (abs(dr) + abs(dc))) >> 3;
-    default: return 0;
+  k.cost_fr = (rr + 3 + (rr >= 0)) >> 3;
+  k.cost_fc = (rc + 3 + (rc >= 0)) >> 3;
+  const int t = k.d.mv_cost_type;
+  k.l1_mul = t == B200_MV_COST_L1_LOWRES ? 32 : (t == B200_MV_COST_L1_MIDRES ? 15 : (t == B200_MV_COST_L1_HDRES ? 8 : 0));
+}
+__device__ __forceinline__ int sad_cost(const Ctx &k, int row, int col) {
+  const int dr = (short)((row - k.cost_fr) * 8), dc = (short)((col - k.cost_fc) * 8);
+  if (k.d.mv_cost_type == B200_MV_COST_ENTROPY) {
+    const unsigned c = (unsigned)mv_cost_tab(k, dr, dc) * (unsigned)k.d.sad_per_bit;
+    return (int)((c + 256u) >> 9);
   }
+  return (k.l1_mul * (abs(dr) + abs(dc))) >> 3;
 }
 
 // mv_err_cost (mcomp.c:290), 1/8-pel mv
@@ -117,6 +120,15 @@ __device__ __forceinline__ Mv clamp_mv(const Ctx &k, Mv m) {
 }
 
 // ----------------------------------------------------------------- pixel sums -----
+// acc + sum of |a.b[i] - b.b[i]| over the four bytes: ONE VABSDIFF4.U8.ACC.  (__vsadu4(a, b)
+// + acc compiles to the instruction with a zero accumulator plus an IADD3 tree, i.e. 1.5
+// ALU-pipe slots per word.)
+__device__ __forceinline__ unsigned sad4_acc(unsigned a, unsigned b, unsigned acc) {
+  unsigned d;
+  asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(acc));
+  return d;
+}
+
 // 4 consecutive bytes at an arbitrary address: two aligned word loads + funnel shift.
 __device__ __forceinline__ unsigned load4(const unsigned char *p) {
   const unsigned long long a = reinterpret_cast<unsigned long long>(p);
@@ -128,9 +140,7 @@ __device__ __forceinline__ unsigned load4(const unsigned char *p) {
 }
 
 __device__ __forceinline__ unsigned warp_sum_u(unsigned v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
+  return __reduce_add_sync(0xffffffffu, v);  // REDUX.SUM: one instruction instead of 5 shuffles
 }
 __device__ __forceinline__ long long warp_sum_ll(long long v) {
 #pragma unroll
@@ -265,7 +275,7 @@ template <int SEGW, int WO>
 __device__ __forceinline__ unsigned sad8_lane(int s_off, int r_off, int n_it, int s_step, int r_step,
                                               unsigned sh) {
   constexpr int NV = SEGW / 4;
-  unsigned acc = 0;
+  unsigned acc = 0, acc2 = 0;  // two chains: the accumulate form is a dependent sequence
 #pragma unroll 2
   for (int it = 0; it < n_it; ++it) {
     unsigned sv[SEGW], r[SEGW + 4];
@@ -280,12 +290,15 @@ __device__ __forceinline__ unsigned sad8_lane(int s_off, int r_off, int n_it, in
       r[4 * v] = t.x, r[4 * v + 1] = t.y, r[4 * v + 2] = t.z, r[4 * v + 3] = t.w;
     }
 #pragma unroll
-    for (int i = 0; i < SEGW; ++i)
-      acc = __vsadu4(sv[i], __funnelshift_r(r[WO + i], r[(WO + i + 1) < SEGW + 4 ? WO + i + 1 : WO + i], sh)) + acc;
+    for (int i = 0; i < SEGW; i += 2) {
+      acc = sad4_acc(sv[i], __funnelshift_r(r[WO + i], r[WO + i + 1], sh), acc);
+      acc2 = sad4_acc(sv[i + 1],
+                      __funnelshift_r(r[WO + i + 1], r[(WO + i + 2) < SEGW + 4 ? WO + i + 2 : WO + i + 1], sh), acc2);
+    }
     s_off += s_step;
     r_off += r_step;
   }
-  return acc;
+  return acc + acc2;
 }
 
 template <int SEGW>

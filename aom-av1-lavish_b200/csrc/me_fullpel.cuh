@@ -67,8 +67,10 @@ __device__ int var_cost(const Ctx &k, Mv m) {
 }
 
 // diamond_search_sad (mcomp.c:1318-1477)
-__device__ int diamond_search(const Ctx &k, bool skip, Mv start, int search_step, int *num00,
-                              Mv *best, Mv *second, bool has_second) {
+// `start_sad`: SAD + cost of the clamped start mv (the same for every run of
+// full_pixel_diamond, so it is computed once there).
+__device__ int diamond_search(const Ctx &k, bool skip, Mv start, unsigned start_sad, int search_step,
+                              int *num00, Mv *best, Mv *second, bool has_second) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const Sites &cfg = *k.sites;
   int off_center = 0, center_steps = 0;
@@ -76,26 +78,30 @@ __device__ int diamond_search(const Ctx &k, bool skip, Mv start, int search_step
   const int tot = cfg.n_steps - search_step;
   Mv tmp_second = has_second ? *second : start;
   *best = start;
-  unsigned bestsad = cta_value(k, [&](int ln) { return warp_sad(k, start.row, start.col, skip, ln); }) +
-                     (unsigned)sad_cost(k, start.row, start.col);
+  unsigned bestsad = start_sad;
+  __syncthreads();  // k.cand may still be read by the previous stage
+  // candidate totals ping-pong between two halves of k.cand, so one barrier per step is
+  // enough: a step's writers can never overtake the readers of two steps ago
+  int pp = 0;
   for (int step = tot - 1; step >= 0; --step) {
     const int n = cfg.per_step[step];
+    unsigned *cand = k.cand + pp;
+    pp ^= 32;
     for (int i = 1 + warp; i <= n; i += kWarps) {
       const int r = best->row + cfg.site[step][i][0], c = best->col + cfg.site[step][i][1];
       unsigned t = 0xffffffffu;
       if (in_range(k, r, c)) t = warp_sad(k, r, c, skip, lane) + (unsigned)sad_cost(k, r, c);
-      if (lane == 0) k.cand[i] = t;
+      if (lane == 0) cand[i] = t;
     }
     __syncthreads();
     int best_site = 0;
     for (int i = 1; i <= n; ++i) {
-      const unsigned t = k.cand[i];
+      const unsigned t = cand[i];
       if (t < bestsad) {
         bestsad = t;
         best_site = i;
       }
     }
-    __syncthreads();
     if (best_site) {
       tmp_second = *best;
       best->row += cfg.site[step][best_site][0];
@@ -137,13 +143,16 @@ __device__ void sad_list(const Ctx &k, bool skip, Mv best, int *cl) {
 __device__ int full_pixel_diamond(const Ctx &k, bool skip, Mv start, int step_param, int *cl,
                                   Mv *best, Mv *second, bool has_second) {
   int n, num00 = 0;
-  diamond_search(k, skip, start, step_param, &n, best, second, has_second);
+  const Mv cs = clamp_mv(k, start);
+  const unsigned start_sad = cta_value(k, [&](int ln) { return warp_sad(k, cs.row, cs.col, skip, ln); }) +
+                             (unsigned)sad_cost(k, cs.row, cs.col);
+  diamond_search(k, skip, start, start_sad, step_param, &n, best, second, has_second);
   int bestsme = var_cost(k, *best);
   const int further = k.sites->n_steps - 1 - step_param;
   while (n < further) {
     ++n;
     Mv tmp;
-    diamond_search(k, skip, start, step_param + n, &num00, &tmp, second, has_second);
+    diamond_search(k, skip, start, start_sad, step_param + n, &num00, &tmp, second, has_second);
     const int sme = var_cost(k, tmp);
     if (sme < bestsme) {
       bestsme = sme;
@@ -215,7 +224,7 @@ __device__ __forceinline__ void mesh1_chunk(int s_off, int src_pitch_b, int r_of
       if (PHASE == 0 && c > u) continue;
       if (PHASE == 2 && c <= u) continue;
 #pragma unroll
-      for (int i = 0; i < SEGW; ++i) acc[c] = __vsadu4(sw[(u - c) & (kRB - 1)][i], rv[i]) + acc[c];
+      for (int i = 0; i < SEGW; ++i) acc[c] = sad4_acc(sw[(u - c) & (kRB - 1)][i], rv[i], acc[c]);
     }
   }
 }
@@ -283,7 +292,7 @@ __device__ void mesh_strided_band_t(const Ctx &k, int row0, int nrows, int col0,
 #pragma unroll
       for (int j = 0; j < kJB; ++j)
 #pragma unroll
-        for (int i = 0; i < SEGW; ++i) acc[j] = __vsadu4(s[i], v[j * STEPW + i]) + acc[j];
+        for (int i = 0; i < SEGW; ++i) acc[j] = sad4_acc(s[i], v[j * STEPW + i], acc[j]);
     }
 #pragma unroll
     for (int j = 0; j < kJB; ++j) {
@@ -327,8 +336,7 @@ __device__ __forceinline__ bool mesh_band_fast(const Ctx &k, int row0, int nrows
                                                int step) {
   const int bw = k.d.bw;
   if (step == 1) {
-    if (bw >= 32) mesh1_band<8>(k, row0, nrows, col0, nc);
-    else if (bw == 16) mesh1_band<4>(k, row0, nrows, col0, nc);
+    if (bw >= 16) mesh1_band<4>(k, row0, nrows, col0, nc);  // 16-pixel segments: 64 registers suffice
     else mesh1_band<2>(k, row0, nrows, col0, nc);
     return true;
   }
@@ -403,38 +411,49 @@ __device__ int mesh_search(const Ctx &k, bool skip, Mv start, int range, int ste
     // last improvement of the sequential scan is the FIRST occurrence of the chunk minimum
     // (if it beats the running best), and second_best is whatever was best just before it,
     // i.e. the first minimum of the prefix in front of the winner (or the old best).
-    if (warp == 0) {
-      const int lo = lane * (kMaxCand / 32), hi = min(cnt, lo + kMaxCand / 32);
-      unsigned bv = best_sad;
-      int bi = INT_MAX;
-      for (int j = lo; j < hi; ++j) {
-        const unsigned t = k.cand[j];
-        if (t < bv) bv = t, bi = j;
-      }
+    // Every thread owns kMaxCand / kThreads consecutive candidates; (value, index) pairs
+    // are reduced lexicographically per warp (REDUX) and then over the warps' slots.
+    {
+      constexpr int PER = kMaxCand / kThreads;
+      const int lo = threadIdx.x * PER;
+      unsigned cv[PER];
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const unsigned ov = __shfl_xor_sync(0xffffffffu, bv, o);
-        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        if (ov < bv || (ov == bv && oi < bi)) bv = ov, bi = oi;
-      }
-      const int win = bi;  // INT_MAX: nothing in the chunk beats the running best
-      unsigned pv = best_sad;
-      int pi = INT_MAX;
-      if (win != INT_MAX) {
-        for (int j = lo; j < min(hi, win); ++j) {
-          const unsigned t = k.cand[j];
-          if (t < pv) pv = t, pi = j;
-        }
+      for (int j = 0; j < PER; ++j) cv[j] = lo + j < cnt ? k.cand[lo + j] : 0xffffffffu;
+      int win = INT_MAX, pi = INT_MAX;
+      unsigned wv = best_sad;
+      for (int pass = 0; pass < 2; ++pass) {
+        // pass 0: whole chunk; pass 1: the prefix in front of the winner
+        const int lim = pass == 0 ? cnt : win;
+        unsigned bv = best_sad;
+        int bi = INT_MAX;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-          const unsigned ov = __shfl_xor_sync(0xffffffffu, pv, o);
-          const int oi = __shfl_xor_sync(0xffffffffu, pi, o);
-          if (ov < pv || (ov == pv && oi < pi)) pv = ov, pi = oi;
+        for (int j = 0; j < PER; ++j)
+          if (lo + j < lim && cv[j] < bv) bv = cv[j], bi = lo + j;
+        const unsigned mv = __reduce_min_sync(0xffffffffu, bv);
+        const int mi = (int)__reduce_min_sync(0xffffffffu, bv == mv ? (unsigned)bi : 0x7fffffffu);
+        if (lane == 0) {
+          k.red[warp] = (long long)(((unsigned long long)mv << 32) | (unsigned)mi);
+        }
+        __syncthreads();
+        unsigned long long m = ~0ull;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) {
+          const unsigned long long t = (unsigned long long)k.red[w];
+          m = t < m ? t : m;
+        }
+        const int idx = (int)(unsigned)m;
+        if (pass == 0) {
+          win = idx;
+          wv = (unsigned)(m >> 32);
+          if (win == INT_MAX || !has_second) break;  // CTA-uniform
+          __syncthreads();  // k.red is reused by the second pass
+        } else {
+          pi = idx;
         }
       }
-      if (lane == 0) {
+      if (threadIdx.x == 0) {
         k.bcast[8] = win;
-        k.bcast[9] = (int)bv;
+        k.bcast[9] = (int)wv;
         k.bcast[10] = pi;
       }
     }
@@ -599,6 +618,7 @@ __global__ void __launch_bounds__(kThreads, 3) fullpel_kernel(const B200MeLaunch
   k.red = s_red;
   k.l = &l;
   k.d = l.blocks[bi];
+  init_costs(k);
   k.sites = sites4 + (k.d.search_method & 3);
   k.px = l.highbd ? 2 : 1;
   k.sad_shift = l.highbd ? (l.bd == 10 ? 2 : (l.bd == 12 ? 4 : 0)) : 0;

@@ -196,6 +196,7 @@ __global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) 
   SubCtx s;
   s.k.l = &l;
   s.k.d = l.blocks[bi];
+  init_costs(s.k);
   s.k.sites = nullptr;
   s.k.px = l.highbd ? 2 : 1;
   s.k.sad_shift = 0;
