@@ -68,6 +68,8 @@ struct Ctx {
 // pointers of Ctx) so that the compiler emits LDS with 32-bit addresses instead of generic
 // loads with 64-bit address arithmetic.
 extern __shared__ __align__(16) unsigned char me_smem[];
+// The search-site table of the CTA's method (copied from global memory at kernel start).
+__shared__ Sites g_sites;
 __device__ __forceinline__ const unsigned *smem_words(int byte_off) {
   return reinterpret_cast<const unsigned *>(me_smem + byte_off);
 }
@@ -271,7 +273,7 @@ __device__ __forceinline__ unsigned warp_sad_fast(const Ctx &k, const unsigned c
 // 32-pixel segment column: conflict-free uint4 reads), but every address is a 32-bit offset
 // into me_smem and the per-lane offsets are formed once, so that one 32-pixel row segment
 // costs 5 LDS.128 + 8 SHF + 8 VABSDIFF4 and two adds.
-template <int SEGW, int WO>
+template <int SEGW, int WO, bool ALIGNED = false>
 __device__ __forceinline__ unsigned sad8_lane(int s_off, int r_off, int n_it, int s_step, int r_step,
                                               unsigned sh) {
   constexpr int NV = SEGW / 4;
@@ -291,9 +293,14 @@ __device__ __forceinline__ unsigned sad8_lane(int s_off, int r_off, int n_it, in
     }
 #pragma unroll
     for (int i = 0; i < SEGW; i += 2) {
-      acc = sad4_acc(sv[i], __funnelshift_r(r[WO + i], r[WO + i + 1], sh), acc);
-      acc2 = sad4_acc(sv[i + 1],
-                      __funnelshift_r(r[WO + i + 1], r[(WO + i + 2) < SEGW + 4 ? WO + i + 2 : WO + i + 1], sh), acc2);
+      if (ALIGNED) {  // candidate column is a multiple of 4 pixels: no funnel shifts
+        acc = sad4_acc(sv[i], r[WO + i], acc);
+        acc2 = sad4_acc(sv[i + 1], r[WO + i + 1], acc2);
+      } else {
+        acc = sad4_acc(sv[i], __funnelshift_r(r[WO + i], r[WO + i + 1], sh), acc);
+        acc2 = sad4_acc(sv[i + 1],
+                        __funnelshift_r(r[WO + i + 1], r[(WO + i + 2) < SEGW + 4 ? WO + i + 2 : WO + i + 1], sh), acc2);
+      }
     }
     s_off += s_step;
     r_off += r_step;
@@ -314,8 +321,10 @@ __device__ __forceinline__ unsigned sad8_wo(int wo, int s_off, int r_off, int n_
 
 // cand_off = byte offset in me_smem of the candidate's top-left reference pixel; the source
 // block sits at offset 0.  bw in {16, 32, 64, 128}.  Returns the warp total in every lane.
+// `part` of `parts`: the lane's row iterations are cut into `parts` contiguous pieces so that
+// several warps can share one candidate (the pieces' totals add up to the SAD).
 __device__ __noinline__ unsigned sad8_staged(int cand_off, int src_pitch_b, int win_pitch_b, int bw,
-                                             int bh, int rmul) {
+                                             int bh, int rmul, int part, int parts) {
   const int lane = threadIdx.x & 31;
   const unsigned sh = (unsigned)(cand_off & 3) * 8;
   const int wo = (cand_off >> 2) & 3, base = cand_off & ~15;
@@ -326,13 +335,15 @@ __device__ __noinline__ unsigned sad8_staged(int cand_off, int src_pitch_b, int 
     const int seg0 = q & ((1 << lspr) - 1), yl = ((q >> lspr) << 3) + (lane & 7);
     const int lrpi = 5 - lspr;                    // log2(rows per iteration)
     const int n_it = yl < bh ? ((bh - 1 - yl) >> lrpi) + 1 : 0;
-    const int ys = yl * rmul, rs = rmul << lrpi;
-    acc = sad8_wo<8>(wo, ys * src_pitch_b + seg0 * 32, base + ys * win_pitch_b + seg0 * 32, n_it,
+    const int i0 = (n_it * part) / parts, i1 = (n_it * (part + 1)) / parts;
+    const int ys = (yl + (i0 << lrpi)) * rmul, rs = rmul << lrpi;
+    acc = sad8_wo<8>(wo, ys * src_pitch_b + seg0 * 32, base + ys * win_pitch_b + seg0 * 32, i1 - i0,
                      rs * src_pitch_b, rs * win_pitch_b, sh);
   } else {
     const int n_it = lane < bh ? ((bh - 1 - lane) >> 5) + 1 : 0;
-    const int ys = lane * rmul, rs = rmul << 5;
-    acc = sad8_wo<4>(wo, ys * src_pitch_b, base + ys * win_pitch_b, n_it, rs * src_pitch_b,
+    const int i0 = (n_it * part) / parts, i1 = (n_it * (part + 1)) / parts;
+    const int ys = (lane + (i0 << 5)) * rmul, rs = rmul << 5;
+    acc = sad8_wo<4>(wo, ys * src_pitch_b, base + ys * win_pitch_b, i1 - i0, rs * src_pitch_b,
                      rs * win_pitch_b, sh);
   }
   return warp_sum_u(acc);
@@ -432,16 +443,23 @@ __device__ __noinline__ unsigned warp_sad_slow(const Ctx &k, int row, int col, i
 
 // SAD of the source block against the reference block at full-pel mv (row, col), computed
 // by ONE warp; every lane returns the total.  skip = rows 0,2,4.. only, doubled.
-__device__ __forceinline__ unsigned warp_sad(const Ctx &k, int row, int col, bool skip, int lane) {
+// warp_sad_part: piece `part` of `parts` of that sum (before doubling / shifting); only the
+// staged 8-bit path splits, elsewhere piece 0 is the whole sum and the others are 0.
+__device__ __forceinline__ bool sad_splits(const Ctx &k) { return k.fast && k.px == 1 && k.d.bw >= 16; }
+__device__ __forceinline__ unsigned warp_sad_part(const Ctx &k, int row, int col, bool skip, int part,
+                                                  int parts) {
   const int bh = skip ? k.d.bh >> 1 : k.d.bh, rmul = skip ? 2 : 1;
-  unsigned acc;
-  if (k.fast && k.px == 1 && k.d.bw >= 16)
-    acc = sad8_staged(k.win0_off + row * k.ref_pitch + col, k.src_pitch_w * 4, k.ref_pitch, k.d.bw, bh,
-                      rmul);
-  else
-    acc = warp_sad_slow(k, row, col, bh, rmul);
+  if (sad_splits(k))
+    return sad8_staged(k.win0_off + row * k.ref_pitch + col, k.src_pitch_w * 4, k.ref_pitch, k.d.bw, bh,
+                       rmul, part, parts);
+  return part == 0 ? warp_sad_slow(k, row, col, bh, rmul) : 0u;
+}
+__device__ __forceinline__ unsigned sad_finish(const Ctx &k, unsigned acc, bool skip) {
   if (skip) acc *= 2;
   return acc >> k.sad_shift;
+}
+__device__ __forceinline__ unsigned warp_sad(const Ctx &k, int row, int col, bool skip, int lane) {
+  return sad_finish(k, warp_sad_part(k, row, col, skip, 0, 1), skip);
 }
 
 // variance family result of (a - b) sums -> (var, sse) exactly as aom_varianceWxH_c /

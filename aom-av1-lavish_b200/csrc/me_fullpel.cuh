@@ -72,7 +72,7 @@ __device__ int var_cost(const Ctx &k, Mv m) {
 __device__ int diamond_search(const Ctx &k, bool skip, Mv start, unsigned start_sad, int search_step,
                               int *num00, Mv *best, Mv *second, bool has_second) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const Sites &cfg = *k.sites;
+  const Sites &cfg = g_sites;  // file-scope shared: LDS, not generic loads
   int off_center = 0, center_steps = 0;
   start = clamp_mv(k, start);
   const int tot = cfg.n_steps - search_step;
@@ -80,23 +80,41 @@ __device__ int diamond_search(const Ctx &k, bool skip, Mv start, unsigned start_
   *best = start;
   unsigned bestsad = start_sad;
   __syncthreads();  // k.cand may still be read by the previous stage
-  // candidate totals ping-pong between two halves of k.cand, so one barrier per step is
-  // enough: a step's writers can never overtake the readers of two steps ago
+  // Each candidate of a step is evaluated in two pieces (upper / lower rows) by two
+  // different warps: 2n half-tasks spread evenly over the warps instead of n whole ones
+  // in ceil(n / 8) rounds.  Piece totals land in k.cand[2i], k.cand[2i + 1] and are summed by
+  // the scan.  The slots ping-pong between two halves of k.cand, so one barrier per step
+  // is enough: a step's writers can never overtake the readers of two steps ago.
   int pp = 0;
   for (int step = tot - 1; step >= 0; --step) {
     const int n = cfg.per_step[step];
     unsigned *cand = k.cand + pp;
-    pp ^= 32;
+    pp ^= 64;
+#if B200_ME_SPLIT_DIAMOND
+    for (int t = warp; t < 2 * n; t += kWarps) {
+      const int i = 1 + (t >> 1), part = t & 1;
+      const int r = best->row + cfg.site[step][i][0], c = best->col + cfg.site[step][i][1];
+      // outside the limits: the two slots add up to UINT_MAX, which never wins.  Only the
+      // 8-bit path splits (sad_shift == 0), so finishing the pieces separately is exact.
+      unsigned v = part ? 0u : 0xffffffffu;
+      if (in_range(k, r, c)) {
+        v = sad_finish(k, warp_sad_part(k, r, c, skip, part, 2), skip);
+        if (part == 0) v += (unsigned)sad_cost(k, r, c);
+      }
+      if (lane == 0) cand[t] = v;
+    }
+#else
     for (int i = 1 + warp; i <= n; i += kWarps) {
       const int r = best->row + cfg.site[step][i][0], c = best->col + cfg.site[step][i][1];
-      unsigned t = 0xffffffffu;
-      if (in_range(k, r, c)) t = warp_sad(k, r, c, skip, lane) + (unsigned)sad_cost(k, r, c);
-      if (lane == 0) cand[i] = t;
+      unsigned v = 0xffffffffu;
+      if (in_range(k, r, c)) v = warp_sad(k, r, c, skip, lane) + (unsigned)sad_cost(k, r, c);
+      if (lane == 0) cand[2 * i - 2] = v, cand[2 * i - 1] = 0;
     }
+#endif
     __syncthreads();
     int best_site = 0;
     for (int i = 1; i <= n; ++i) {
-      const unsigned t = cand[i];
+      const unsigned t = cand[2 * i - 2] + cand[2 * i - 1];
       if (t < bestsad) {
         bestsad = t;
         best_site = i;
@@ -619,7 +637,12 @@ __global__ void __launch_bounds__(kThreads, 3) fullpel_kernel(const B200MeLaunch
   k.l = &l;
   k.d = l.blocks[bi];
   init_costs(k);
-  k.sites = sites4 + (k.d.search_method & 3);
+  {  // the method's site table: read at every step of the search, keep it on chip
+    const int *g = reinterpret_cast<const int *>(sites4 + (k.d.search_method & 3));
+    int *d = reinterpret_cast<int *>(&g_sites);
+    for (int i = threadIdx.x; i < (int)(sizeof(Sites) / 4); i += kThreads) d[i] = g[i];
+  }
+  k.sites = &g_sites;
   k.px = l.highbd ? 2 : 1;
   k.sad_shift = l.highbd ? (l.bd == 10 ? 2 : (l.bd == 12 ? 4 : 0)) : 0;
   k.cand = s_cand;
