@@ -61,6 +61,10 @@ extern "C" int b200_ctx_create(int device, b200_ctx **out) {
   ctx->device = device;
   ctx->sm_count = prop.multiProcessorCount;
   B200_CUDA_TRY(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  B200_CUDA_TRY(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+  for (int i = 0; i < B200_TX_SIZES_ALL; ++i)
+    B200_CUDA_TRY(cudaEventCreateWithFlags(&ctx->group_done[i], cudaEventDisableTiming));
+  B200_CUDA_TRY(cudaEventCreateWithFlags(&ctx->copy_done, cudaEventDisableTiming));
   int rc = txq_init_device(ctx);
   if (rc == B200_OK) rc = blockops_init_device(ctx);
   if (rc == B200_OK) rc = me_init_device(ctx);
@@ -81,6 +85,10 @@ extern "C" void b200_ctx_destroy(b200_ctx *ctx) {
   if (ctx->d_scratch) cudaFree(ctx->d_scratch);
   if (ctx->d_me_sites) cudaFree(ctx->d_me_sites);
   if (ctx->h_scratch) cudaFreeHost(ctx->h_scratch);
+  cudaStreamSynchronize(ctx->copy_stream);
+  for (int i = 0; i < B200_TX_SIZES_ALL; ++i) cudaEventDestroy(ctx->group_done[i]);
+  cudaEventDestroy(ctx->copy_done);
+  cudaStreamDestroy(ctx->copy_stream);
   cudaStreamDestroy(ctx->stream);
   free(ctx);
 }
@@ -153,6 +161,22 @@ int scratch_reserve(b200_ctx *ctx, size_t bytes) {
 }
 }  // namespace b200
 
+namespace b200 {
+// Grow-only pinned host staging.
+static int host_scratch_reserve(b200_ctx *ctx, size_t bytes) {
+  if (bytes <= ctx->h_scratch_bytes) return B200_OK;
+  B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+  B200_CUDA_TRY(cudaStreamSynchronize(ctx->copy_stream));
+  if (ctx->h_scratch) B200_CUDA_TRY(cudaFreeHost(ctx->h_scratch));
+  ctx->h_scratch = nullptr;
+  ctx->h_scratch_bytes = 0;
+  const size_t want = bytes + bytes / 2 + (1 << 16);
+  B200_CUDA_TRY(cudaMallocHost(&ctx->h_scratch, want));
+  ctx->h_scratch_bytes = want;
+  return B200_OK;
+}
+}  // namespace b200
+
 extern "C" int b200_txq_launch(b200_ctx *ctx, const B200TxqLaunch *launch, void *stream) {
   if (!ctx || !launch) return B200_EINVAL;
   B200_CUDA_TRY(cudaSetDevice(ctx->device));
@@ -161,6 +185,18 @@ extern "C" int b200_txq_launch(b200_ctx *ctx, const B200TxqLaunch *launch, void 
 
 static size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
 
+// Host-buffer wrapper of the fused kernel -- the reference-facing call of the frame tier
+// (what `e2e` in bench.py times).  Pipeline per call:
+//   host   counting sort of the descriptors by (tx_size, tx_type) -- skipped when the queue
+//          already arrives in that order -- and a pass that finds, per tx-size group, the
+//          range of the output arrays its blocks write
+//   stream   H2D of planes / tables / descriptors, one kernel launch per tx-size group
+//   copy_stream   as each group's kernel finishes, D2H of exactly that group's output range,
+//          so the PCIe read-back (12 of the 14 bytes per sample) overlaps the remaining
+//          uploads and kernels instead of following them
+// When the groups' output ranges are not dense and disjoint (a caller that interleaves
+// sizes inside the arrays) the function falls back to zero-filled device arrays and one
+// whole-array read-back at the end.
 extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int bd, unsigned flags,
                                    const B200TxBlock *blocks, const B200TxPred *preds,
                                    int n_blocks, const void *src, size_t src_elems,
@@ -176,107 +212,215 @@ extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int b
   const bool want_coeff = (flags & B200_TXQ_STORE_COEFF) != 0;
   const bool want_err = (flags & B200_TXQ_BLOCK_ERROR) != 0 && dist;
   if (has_pred && (!preds || !pred)) return B200_EINVAL;
+  const size_t n = (size_t)n_blocks;
 
-  // group the blocks by tx_size (stable), remembering each block's original index
-  std::vector<int> order(n_blocks);
-  for (int i = 0; i < n_blocks; ++i) order[i] = i;
-  std::stable_sort(order.begin(), order.end(), [&](int x, int y) {
-    if (blocks[x].tx_size != blocks[y].tx_size) return blocks[x].tx_size < blocks[y].tx_size;
-    return blocks[x].tx_type < blocks[y].tx_type;  // keep warps on one code path
+  // ---- one pass over the queue: validate, bucket by (tx_size, tx_type) so that warps stay
+  // on one code path, and find the range of the output arrays each tx size writes
+  constexpr int kKeys = B200_TX_SIZES_ALL * 16;
+  static bool s_valid[kKeys];
+  static size_t s_max_eob[B200_TX_SIZES_ALL];
+  static std::once_flag s_once;
+  std::call_once(s_once, [] {
+    for (int ts = 0; ts < B200_TX_SIZES_ALL; ++ts) {
+      s_max_eob[ts] = (size_t)b200_tx_max_eob(ts);
+      for (int tt = 0; tt < 16; ++tt) s_valid[ts * 16 + tt] = b200_tx_valid(ts, tt) != 0;
+    }
   });
-  std::vector<B200TxBlock> sorted(n_blocks);
-  std::vector<B200TxPred> sorted_p(has_pred ? n_blocks : 0);
-  for (int i = 0; i < n_blocks; ++i) {
-    sorted[i] = blocks[order[i]];
-    if (sorted[i].tx_size >= B200_TX_SIZES_ALL || !b200_tx_valid(sorted[i].tx_size, sorted[i].tx_type)) {
-      set_error("b200_txq_batch_host: block %d has invalid tx_size/tx_type %d/%d", order[i],
-                sorted[i].tx_size, sorted[i].tx_type);
+  std::vector<uint32_t> bucket(kKeys + 1, 0);
+  size_t g_lo[B200_TX_SIZES_ALL], g_hi[B200_TX_SIZES_ALL];
+  for (int ts = 0; ts < B200_TX_SIZES_ALL; ++ts) g_lo[ts] = (size_t)-1, g_hi[ts] = 0;
+  bool in_order = true;
+  unsigned prev_key = 0;
+  for (size_t i = 0; i < n; ++i) {
+    const unsigned ts = blocks[i].tx_size, key = ts * 16u + blocks[i].tx_type;
+    if (ts >= B200_TX_SIZES_ALL || blocks[i].tx_type >= 16 || !s_valid[key]) {
+      set_error("b200_txq_batch_host: block %zu has invalid tx_size/tx_type %d/%d", i, (int)ts,
+                (int)blocks[i].tx_type);
       return B200_EINVAL;
     }
-    if (has_pred) sorted_p[i] = preds[order[i]];
+    in_order = in_order && key >= prev_key;
+    prev_key = key;
+    ++bucket[key + 1];
+    const size_t o = blocks[i].out_offset;
+    g_lo[ts] = o < g_lo[ts] ? o : g_lo[ts];
+    g_hi[ts] = o > g_hi[ts] ? o : g_hi[ts];
+  }
+  for (int k = 0; k < kKeys; ++k) bucket[k + 1] += bucket[k];
+
+  // pinned staging: [sorted blocks][sorted preds][eob][dist]
+  size_t hoff = 0;
+  auto hcarve = [&](size_t bytes) {
+    const size_t o = hoff;
+    hoff += (bytes + 255) & ~(size_t)255;
+    return o;
+  };
+  const size_t ho_blocks = hcarve(in_order ? 0 : sizeof(B200TxBlock) * n);
+  const size_t ho_preds = hcarve(!in_order && has_pred ? sizeof(B200TxPred) * n : 0);
+  const size_t ho_eob = hcarve(has_q ? n * 2 : 0);
+  const size_t ho_dist = hcarve(want_err ? n * 16 : 0);
+  int rc = host_scratch_reserve(ctx, hoff);
+  if (rc != B200_OK) return rc;
+  char *hbase = (char *)ctx->h_scratch;
+  std::vector<uint32_t> order;  // sorted position -> caller's index
+  const B200TxBlock *sblocks = blocks;
+  const B200TxPred *spreds = preds;
+  if (!in_order) {
+    order.resize(n);
+    std::vector<uint32_t> cursor(bucket.begin(), bucket.end() - 1);
+    B200TxBlock *sb = (B200TxBlock *)(hbase + ho_blocks);
+    B200TxPred *sp = (B200TxPred *)(hbase + ho_preds);
+    for (size_t i = 0; i < n; ++i) {
+      const uint32_t pos = cursor[blocks[i].tx_size * 16 + blocks[i].tx_type]++;
+      order[pos] = (uint32_t)i;
+      sb[pos] = blocks[i];
+      if (has_pred) sp[pos] = preds[i];
+    }
+    sblocks = sb;
+    spreds = sp;
   }
 
+  // ---- tx-size groups and the output range each one writes
+  struct Group {
+    int ts;
+    size_t first, count, lo, hi, elems;
+  };
+  std::vector<Group> groups;
+  for (int ts = 0; ts < B200_TX_SIZES_ALL; ++ts) {
+    const size_t first = bucket[ts * 16], last = bucket[ts * 16 + 16];
+    if (last == first) continue;
+    const size_t me = s_max_eob[ts];
+    Group g = { ts, first, last - first, g_lo[ts], g_hi[ts] + me, (last - first) * me };
+    if (g.hi > out_elems) {
+      set_error("b200_txq_batch_host: a %s block writes past out_elems", "queued");
+      return B200_EINVAL;
+    }
+    groups.push_back(g);
+  }
+  bool dense = true;
+  std::vector<const Group *> by_lo;
+  for (const Group &g : groups) {
+    dense = dense && g.hi - g.lo == g.elems;
+    by_lo.push_back(&g);
+  }
+  std::sort(by_lo.begin(), by_lo.end(), [](const Group *a, const Group *b) { return a->lo < b->lo; });
+  for (size_t i = 0; i + 1 < by_lo.size(); ++i) dense = dense && by_lo[i]->hi <= by_lo[i + 1]->lo;
+
+  // ---- device carve-out
   size_t off = 0;
   auto carve = [&](size_t bytes) {
     size_t o = off;
     off += align_up(bytes);
     return o;
   };
-  const size_t o_blocks = carve(sizeof(B200TxBlock) * n_blocks);
-  const size_t o_preds = carve(has_pred ? sizeof(B200TxPred) * n_blocks : 0);
+  const size_t o_blocks = carve(sizeof(B200TxBlock) * n);
+  const size_t o_preds = carve(has_pred ? sizeof(B200TxPred) * n : 0);
   const size_t o_src = carve(src_elems * px);
   const size_t o_pred = carve(has_pred ? pred_elems * px : 0);
   const size_t o_q = carve(has_q ? sizeof(B200QRow) * n_qrows : 0);
   const size_t o_coeff = carve(want_coeff ? out_elems * 4 : 0);
   const size_t o_qc = carve(has_q ? out_elems * 4 : 0);
   const size_t o_dq = carve(has_q ? out_elems * 4 : 0);
-  const size_t o_eob = carve(has_q ? n_blocks * 2 : 0);
-  const size_t o_dist = carve(want_err ? n_blocks * 16 : 0);
-  int rc = scratch_reserve(ctx, off);
+  const size_t o_eob = carve(has_q ? n * 2 : 0);
+  const size_t o_dist = carve(want_err ? n * 16 : 0);
+  rc = scratch_reserve(ctx, off);
   if (rc != B200_OK) return rc;
   char *base = (char *)ctx->d_scratch;
-  cudaStream_t s = ctx->stream;
-  B200_CUDA_TRY(cudaMemcpyAsync(base + o_blocks, sorted.data(), sizeof(B200TxBlock) * n_blocks,
-                                cudaMemcpyHostToDevice, s));
-  if (has_pred) {
-    B200_CUDA_TRY(cudaMemcpyAsync(base + o_preds, sorted_p.data(), sizeof(B200TxPred) * n_blocks,
-                                  cudaMemcpyHostToDevice, s));
-    B200_CUDA_TRY(cudaMemcpyAsync(base + o_pred, pred, pred_elems * px, cudaMemcpyHostToDevice, s));
-  }
+  cudaStream_t s = ctx->stream, cs = ctx->copy_stream;
+
   B200_CUDA_TRY(cudaMemcpyAsync(base + o_src, src, src_elems * px, cudaMemcpyHostToDevice, s));
+  if (has_pred)
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_pred, pred, pred_elems * px, cudaMemcpyHostToDevice, s));
   if (has_q)
     B200_CUDA_TRY(cudaMemcpyAsync(base + o_q, qrows, sizeof(B200QRow) * n_qrows,
                                   cudaMemcpyHostToDevice, s));
-  // regions of the output buffers that no block covers read back as zero
-  if (want_coeff) B200_CUDA_TRY(cudaMemsetAsync(base + o_coeff, 0, out_elems * 4, s));
-  if (has_q) {
-    B200_CUDA_TRY(cudaMemsetAsync(base + o_qc, 0, out_elems * 4, s));
-    B200_CUDA_TRY(cudaMemsetAsync(base + o_dq, 0, out_elems * 4, s));
+  if (!dense) {
+    // regions of the output arrays that no block covers read back as zero
+    if (want_coeff) B200_CUDA_TRY(cudaMemsetAsync(base + o_coeff, 0, out_elems * 4, s));
+    if (has_q) {
+      B200_CUDA_TRY(cudaMemsetAsync(base + o_qc, 0, out_elems * 4, s));
+      B200_CUDA_TRY(cudaMemsetAsync(base + o_dq, 0, out_elems * 4, s));
+    }
   }
-  for (int i = 0; i < n_blocks;) {
-    int j = i;
-    while (j < n_blocks && sorted[j].tx_size == sorted[i].tx_size) ++j;
+  for (size_t gi = 0; gi < groups.size(); ++gi) {
+    const Group &g = groups[gi];
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_blocks + g.first * sizeof(B200TxBlock), sblocks + g.first,
+                                  g.count * sizeof(B200TxBlock), cudaMemcpyHostToDevice, s));
+    if (has_pred)
+      B200_CUDA_TRY(cudaMemcpyAsync(base + o_preds + g.first * sizeof(B200TxPred), spreds + g.first,
+                                    g.count * sizeof(B200TxPred), cudaMemcpyHostToDevice, s));
     B200TxqLaunch l;
     memset(&l, 0, sizeof(l));
-    l.tx_size = sorted[i].tx_size;
+    l.tx_size = g.ts;
     l.in_kind = in_kind;
     l.q_kind = q_kind;
     l.bd = bd;
     l.flags = flags & ~(want_err ? 0u : B200_TXQ_BLOCK_ERROR);
-    l.n_blocks = j - i;
-    l.blocks = (const B200TxBlock *)(base + o_blocks) + i;
-    l.preds = has_pred ? (const B200TxPred *)(base + o_preds) + i : nullptr;
+    l.n_blocks = (int)g.count;
+    l.blocks = (const B200TxBlock *)(base + o_blocks) + g.first;
+    l.preds = has_pred ? (const B200TxPred *)(base + o_preds) + g.first : nullptr;
     l.src = base + o_src;
     l.pred = has_pred ? base + o_pred : nullptr;
     l.qrows = has_q ? (const B200QRow *)(base + o_q) : nullptr;
     l.coeff = want_coeff ? (int32_t *)(base + o_coeff) : nullptr;
     l.qcoeff = has_q ? (int32_t *)(base + o_qc) : nullptr;
     l.dqcoeff = has_q ? (int32_t *)(base + o_dq) : nullptr;
-    l.eob = has_q ? (uint16_t *)(base + o_eob) + i : nullptr;
-    l.dist = want_err ? (int64_t *)(base + o_dist) + 2 * (size_t)i : nullptr;
+    l.eob = has_q ? (uint16_t *)(base + o_eob) + g.first : nullptr;
+    l.dist = want_err ? (int64_t *)(base + o_dist) + 2 * g.first : nullptr;
     rc = txq_launch(ctx, l, s);
     if (rc != B200_OK) return rc;
-    i = j;
+    B200_CUDA_TRY(cudaEventRecord(ctx->group_done[gi], s));
+    B200_CUDA_TRY(cudaStreamWaitEvent(cs, ctx->group_done[gi], 0));
+    if (dense) {
+      const size_t b0 = g.lo * 4, nb = g.elems * 4;
+      if (want_coeff)
+        B200_CUDA_TRY(cudaMemcpyAsync((char *)coeff + b0, base + o_coeff + b0, nb, cudaMemcpyDeviceToHost, cs));
+      if (has_q) {
+        B200_CUDA_TRY(cudaMemcpyAsync((char *)qcoeff + b0, base + o_qc + b0, nb, cudaMemcpyDeviceToHost, cs));
+        B200_CUDA_TRY(cudaMemcpyAsync((char *)dqcoeff + b0, base + o_dq + b0, nb, cudaMemcpyDeviceToHost, cs));
+      }
+    }
   }
-  std::vector<uint16_t> eob_sorted(has_q ? n_blocks : 0);
-  std::vector<int64_t> dist_sorted(want_err ? 2 * (size_t)n_blocks : 0);
-  if (want_coeff)
-    B200_CUDA_TRY(cudaMemcpyAsync(coeff, base + o_coeff, out_elems * 4, cudaMemcpyDeviceToHost, s));
-  if (has_q) {
-    B200_CUDA_TRY(cudaMemcpyAsync(qcoeff, base + o_qc, out_elems * 4, cudaMemcpyDeviceToHost, s));
-    B200_CUDA_TRY(cudaMemcpyAsync(dqcoeff, base + o_dq, out_elems * 4, cudaMemcpyDeviceToHost, s));
-    B200_CUDA_TRY(cudaMemcpyAsync(eob_sorted.data(), base + o_eob, n_blocks * 2,
-                                  cudaMemcpyDeviceToHost, s));
+  if (!dense) {
+    if (want_coeff)
+      B200_CUDA_TRY(cudaMemcpyAsync(coeff, base + o_coeff, out_elems * 4, cudaMemcpyDeviceToHost, cs));
+    if (has_q) {
+      B200_CUDA_TRY(cudaMemcpyAsync(qcoeff, base + o_qc, out_elems * 4, cudaMemcpyDeviceToHost, cs));
+      B200_CUDA_TRY(cudaMemcpyAsync(dqcoeff, base + o_dq, out_elems * 4, cudaMemcpyDeviceToHost, cs));
+    }
   }
+  if (has_q)
+    B200_CUDA_TRY(cudaMemcpyAsync(hbase + ho_eob, base + o_eob, n * 2, cudaMemcpyDeviceToHost, cs));
   if (want_err)
-    B200_CUDA_TRY(cudaMemcpyAsync(dist_sorted.data(), base + o_dist, n_blocks * 16,
-                                  cudaMemcpyDeviceToHost, s));
+    B200_CUDA_TRY(cudaMemcpyAsync(hbase + ho_dist, base + o_dist, n * 16, cudaMemcpyDeviceToHost, cs));
+  if (dense) {
+    // zero what no group covers, on the host, while the copies run
+    size_t at = 0;
+    for (const Group *g : by_lo) {
+      if (g->lo > at) {
+        if (want_coeff) memset(coeff + at, 0, (g->lo - at) * 4);
+        if (has_q) memset(qcoeff + at, 0, (g->lo - at) * 4), memset(dqcoeff + at, 0, (g->lo - at) * 4);
+      }
+      at = g->hi;
+    }
+    if (out_elems > at) {
+      if (want_coeff) memset(coeff + at, 0, (out_elems - at) * 4);
+      if (has_q) memset(qcoeff + at, 0, (out_elems - at) * 4), memset(dqcoeff + at, 0, (out_elems - at) * 4);
+    }
+  }
+  B200_CUDA_TRY(cudaStreamSynchronize(cs));
   B200_CUDA_TRY(cudaStreamSynchronize(s));
-  for (int i = 0; i < n_blocks; ++i) {
-    if (has_q && eob) eob[order[i]] = eob_sorted[i];
-    if (want_err) {
-      dist[2 * (size_t)order[i]] = dist_sorted[2 * (size_t)i];
-      dist[2 * (size_t)order[i] + 1] = dist_sorted[2 * (size_t)i + 1];
+  const uint16_t *eob_s = (const uint16_t *)(hbase + ho_eob);
+  const int64_t *dist_s = (const int64_t *)(hbase + ho_dist);
+  if (in_order) {
+    if (has_q && eob) memcpy(eob, eob_s, n * 2);
+    if (want_err) memcpy(dist, dist_s, n * 16);
+  } else {
+    for (size_t i = 0; i < n; ++i) {
+      if (has_q && eob) eob[order[i]] = eob_s[i];
+      if (want_err) {
+        dist[2 * (size_t)order[i]] = dist_s[2 * i];
+        dist[2 * (size_t)order[i] + 1] = dist_s[2 * i + 1];
+      }
     }
   }
   return B200_OK;

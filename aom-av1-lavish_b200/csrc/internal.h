@@ -40,8 +40,11 @@ struct b200_ctx {
   // scratch for the host-buffer (drop-in) tier
   void *d_scratch;
   size_t scratch_bytes;
-  void *h_scratch;
+  void *h_scratch;      // pinned staging of the host-buffer tier (sorted descriptors, eob, dist)
   size_t h_scratch_bytes;
+  cudaStream_t copy_stream;            // device->host leg of the host-buffer tier
+  cudaEvent_t group_done[B200_TX_SIZES_ALL];  // one per tx-size group of a batch
+  cudaEvent_t copy_done;
   void *d_me_sites;   // search-site tables of the four served methods, see me_host.cuh
 };
 

@@ -62,8 +62,8 @@ def me_launch(ctx, cur, refb, params, tables_dev, subpel, window_bytes):
     l.highbd, l.bd, l.n_blocks = int(cur.itemsize == 2), params[0].bd, n
     l.blocks, l.cur, l.ref = d_blk.ptr, d_cur.ptr, d_ref.ptr
     l.cur_stride, l.ref_stride = cur.shape[1], refb.shape[1]
-    for i, (r, it) in enumerate(M.MESH):
-        l.mesh_range[i], l.mesh_interval[i] = r, it
+    for i in range(4):  # one mesh pattern per launch (MV_SPEED_FEATURES::mesh_patterns)
+        l.mesh_range[i], l.mesh_interval[i] = params[0].mesh_range[i], params[0].mesh_interval[i]
     l.mvjcost, l.mvcost[0], l.mvcost[1] = tables_dev
     l.results = d_res.ptr
     l.window_bytes = window_bytes
@@ -164,3 +164,45 @@ def test_config3_shape_64x64_pm64_two_refs(ctx):
             g = got2[i]
             assert (int(g["best_row"]), int(g["best_col"]), int(g["ret"]), int(g["distortion"]),
                     int(g["sse"])) == e.key(True), (ref_id, i)
+
+
+MESH_PATTERNS = [  # speed_features.c:25-44
+    ((64, 16), (24, 8), (12, 4), (7, 1)),   # good quality, mesh speed >= 3: 16-pixel stage
+    ((64, 8), (14, 2), (7, 1), (7, 1)),     # mesh speed 2: 2-pixel stage (no strip path)
+    ((64, 4), (16, 1), (0, 0), (0, 0)),     # intrabc
+    ((24, 1), (24, 1), (0, 0), (0, 0)),     # dense first stage: several bands of rows
+]
+
+
+@pytest.mark.parametrize("pattern", range(len(MESH_PATTERNS)))
+def test_fullpel_mesh_patterns(ctx, pattern):
+    """Every mesh stage shape of the reference's tables through the register-blocked SAD
+    maps (step 1: column lanes; step 4/8/16: strips) and the generic path (step 2, row
+    skipping, 4/8-pixel blocks), forced mesh, limits clipped at the frame edge."""
+    O = H.oracle()
+    rng = np.random.default_rng(900 + pattern)
+    tables = H.make_mv_cost_tables(4)
+    keep, tdev = upload_tables(ctx, tables)
+    mesh = MESH_PATTERNS[pattern]
+    for trial in range(2):
+        cur, refb = M.make_frames(rng, 320, 256, 8, flat=(trial == 1))
+        params = []
+        for (bw, bh) in [(64, 64), (32, 32), (16, 16), (128, 128), (8, 8), (16, 8), (64, 32), (32, 8),
+                         (128, 64), (16, 64)]:
+            for rep in range(3):
+                p = M.random_fullpel_params(rng, cur, refb, bw, bh, 8, tables)
+                for i, (r, it) in enumerate(mesh):
+                    p.mesh_range[i], p.mesh_interval[i] = r, it
+                p.run_mesh_search, p.prune_mesh_search = 1, 0
+                p.search_method = 0
+                p.use_skip_sad = int(rep == 2 and bh >= 8)
+                p.want_cost_list = p.want_second_best = 1
+                params.append(p)
+        got = me_launch(ctx, cur, refb, params, tdev, False, 150 * 1024)
+        for i, p in enumerate(params):
+            e = H.MeResult()
+            O.av1o_full_pixel_search(C.byref(p), C.byref(e))
+            g = got[i]
+            assert (int(g["best_row"]), int(g["best_col"]), int(g["second_row"]), int(g["second_col"]),
+                    tuple(int(v) for v in g["cost_list"]), int(g["ret"])) == e.key(), \
+                (pattern, trial, i, p.bw, p.bh, p.use_skip_sad, p.fine_search_interval)
