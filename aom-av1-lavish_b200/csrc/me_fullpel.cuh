@@ -185,6 +185,172 @@ __device__ int full_pixel_diamond(const Ctx &k, bool skip, Mv start, int step_pa
   return bestsme;
 }
 
+// ---- pattern_search family (mcomp.c:1017-1316) --------------------------------------
+// Candidate j of scale s, generated by rule from the reference's tables (:498-660): scale s
+// reaches 2^s pixels.  kind 0: hex (8-point ring at scale 0, then 6-point hexagons), 1:
+// bigdia (4 nearest points at scale 0, then 8-point diamonds), 2: square.
+__device__ __forceinline__ int pat_count(int kind, int s) {
+  return kind == 2 ? 8 : (kind == 0 ? (s == 0 ? 8 : 6) : (s == 0 ? 4 : 8));
+}
+__constant__ signed char c_pat_ring[2][8] = { { -1, 0, 1, 1, 1, 0, -1, -1 }, { -1, -1, -1, 0, 1, 1, 1, 0 } };
+__constant__ signed char c_pat_hex[2][6] = { { -1, 1, 2, 1, -1, -2 }, { -2, -2, 0, 2, 2, 0 } };
+__constant__ signed char c_pat_dia[2][8] = { { -1, 0, 1, 2, 1, 0, -1, -2 }, { -1, -2, -1, 0, 1, 2, 1, 0 } };
+__constant__ signed char c_pat_near[2][4] = { { 0, 1, 0, -1 }, { -1, 0, 1, 0 } };
+__device__ __forceinline__ Mv pat_site(int kind, int s, int j) {
+  const int d = 1 << s, h = d >> 1;
+  if (kind == 2 || (kind == 0 && s == 0)) return Mv{ c_pat_ring[0][j] * d, c_pat_ring[1][j] * d };
+  if (kind == 0) return Mv{ c_pat_hex[0][j] * h, c_pat_hex[1][j] * h };
+  if (s == 0) return Mv{ c_pat_near[0][j], c_pat_near[1][j] };
+  return Mv{ c_pat_dia[0][j] * h, c_pat_dia[1][j] * h };
+}
+
+struct PatState {
+  int kind, br, bc, pp;
+  unsigned bestsad, raw_bestsad;
+};
+
+// One round: candidates idx0, idx0 + 1, ... (n of them, or the three check points when
+// chk != nullptr) of scale s around (br, bc), one warp each; then every thread replays
+// the reference's in-order update (update_mvs_and_sad :858).  Returns the position of the
+// last improvement or -1.  cl (optional): raw SADs at cl[index + 1]; `marks`: INT_MAX for
+// points outside the limits (calc_sad_update_bestmv_with_indices :983).
+__device__ int pat_round(const Ctx &k, PatState &st, bool skip, int s, const int *chk, int n, int *cl,
+                         bool marks) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned *cand = k.cand + st.pp;
+  st.pp ^= 32;
+  if (warp < n) {
+    const Mv o = pat_site(st.kind, s, chk ? chk[warp] : warp);
+    const int r = st.br + o.row, c = st.bc + o.col;
+    unsigned v = 0xffffffffu;
+    if (in_range(k, r, c)) v = warp_sad(k, r, c, skip, lane);
+    if (lane == 0) cand[warp] = v;
+  }
+  __syncthreads();
+  int best = -1;
+  for (int i = 0; i < n; ++i) {
+    const int index = chk ? chk[i] : i;
+    const unsigned v = cand[i];
+    if (v == 0xffffffffu) {
+      if (cl && marks) cl[index + 1] = INT_MAX;
+      continue;
+    }
+    if (cl) cl[index + 1] = (int)v;
+    if (v >= st.bestsad) continue;
+    const Mv o = pat_site(st.kind, s, index);
+    const unsigned t = v + (unsigned)sad_cost(k, st.br + o.row, st.bc + o.col);
+    if (t < st.bestsad) {
+      st.raw_bestsad = v;
+      st.bestsad = t;
+      best = i;
+    }
+  }
+  return best;
+}
+
+// All candidates of a scale; inside the limits the reference only reaches the first
+// n & ~3 of them (its scalar tail loop never runs, :1065-1078) -- kept.
+__device__ __forceinline__ int pat_round_all(const Ctx &k, PatState &st, bool skip, int s) {
+  const int range = 1 << s, n = pat_count(st.kind, s);
+  const bool inside = st.br - range >= k.d.row_min && st.br + range <= k.d.row_max &&
+                      st.bc - range >= k.d.col_min && st.bc + range <= k.d.col_max;
+  return pat_round(k, st, skip, s, nullptr, inside ? n & ~3 : n, nullptr, false);
+}
+
+__device__ __forceinline__ void pat_move(PatState &st, int s, int j) {
+  const Mv o = pat_site(st.kind, s, j);
+  st.br += o.row;
+  st.bc += o.col;
+}
+
+__device__ __noinline__ int pattern_search(const Ctx &k, bool skip, Mv start, int search_step, bool do_init, int *cl,
+                              Mv *best_mv) {
+  PatState st;
+  const int m = k.d.search_method;
+  st.kind = (m == B200_ME_HEX || m == B200_ME_FAST_HEX) ? 0 : (m == B200_ME_SQUARE ? 2 : 1);
+  st.pp = 0;
+  const bool last_is_4 = st.kind == 1;
+  search_step = min(search_step, kMaxSteps - 1);
+  int best_init_s = kMaxSteps - 1 - search_step, s, kk = -1;
+  start = clamp_mv(k, start);
+  st.br = start.row;
+  st.bc = start.col;
+  if (cl)
+    for (int i = 0; i < 5; ++i) cl[i] = INT_MAX;
+  bool has_sad = false;
+  st.raw_bestsad = cta_value(k, [&](int ln) { return warp_sad(k, start.row, start.col, skip, ln); });
+  st.bestsad = st.raw_bestsad + (unsigned)sad_cost(k, start.row, start.col);
+  if (do_init) {
+    s = best_init_s;
+    best_init_s = -1;
+    for (int t = 0; t <= s; ++t) {
+      const int bs = pat_round_all(k, st, skip, t);
+      if (bs != -1) {
+        best_init_s = t;
+        kk = bs;
+      }
+    }
+    if (best_init_s != -1) pat_move(st, best_init_s, kk);
+  }
+  if (best_init_s != -1) {
+    const int last_s = last_is_4 && cl != nullptr;
+    int best_site = -1;
+    for (s = best_init_s; s >= last_s; s--) {
+      const int n = pat_count(st.kind, s);
+      if (!do_init || s != best_init_s) {
+        best_site = pat_round_all(k, st, skip, s);
+        if (best_site == -1) continue;
+        pat_move(st, s, best_site);
+        kk = best_site;
+      }
+      do {
+        const int chk[3] = { kk == 0 ? n - 1 : kk - 1, kk, kk == n - 1 ? 0 : kk + 1 };
+        best_site = pat_round(k, st, skip, s, chk, 3, nullptr, false);
+        if (best_site != -1) {
+          kk = chk[best_site];
+          pat_move(st, s, kk);
+        }
+      } while (best_site != -1);
+    }
+    if (s == 0) {  // only with a cost list: the 4-point scale fills it on the way
+      cl[0] = (int)st.raw_bestsad;
+      has_sad = true;
+      if (!do_init || s != best_init_s) {
+        best_site = pat_round(k, st, skip, 0, nullptr, 4, cl, false);
+        if (best_site != -1) {
+          pat_move(st, 0, best_site);
+          kk = best_site;
+        }
+      }
+      while (best_site != -1) {
+        const int chk[3] = { kk == 0 ? 3 : kk - 1, kk, kk == 3 ? 0 : kk + 1 };
+        cl[1] = cl[2] = cl[3] = cl[4] = INT_MAX;
+        cl[((kk + 2) & 3) + 1] = cl[0];
+        cl[0] = (int)st.raw_bestsad;
+        best_site = pat_round(k, st, skip, 0, chk, 3, cl, true);
+        if (best_site != -1) {
+          kk = chk[best_site];
+          pat_move(st, 0, kk);
+        }
+      }
+    }
+  }
+  best_mv->row = st.br;
+  best_mv->col = st.bc;
+  if (cl) {
+    if (!has_sad) {
+      sad_list(k, skip, *best_mv, cl);
+    } else {  // calc_int_sad_list with costlist_has_sad: only the mv costs are added
+      cl[0] += sad_cost(k, st.br, st.bc);
+      if (cl[1] != INT_MAX) cl[1] += sad_cost(k, st.br, st.bc - 1);
+      if (cl[2] != INT_MAX) cl[2] += sad_cost(k, st.br + 1, st.bc);
+      if (cl[3] != INT_MAX) cl[3] += sad_cost(k, st.br, st.bc + 1);
+      if (cl[4] != INT_MAX) cl[4] += sad_cost(k, st.br - 1, st.bc);
+    }
+  }
+  return var_cost(k, *best_mv);
+}
+
 // ---- register-blocked SAD maps for the mesh stages -----------------------------------
 // The generic path above spends one warp per candidate and re-reads source and reference
 // from shared memory for every candidate (5 LDS.128 per 8 VABSDIFF4).  A mesh stage is a
@@ -538,7 +704,20 @@ __device__ int full_pixel_search(const Ctx &k, bool skip, int *cl, Mv *best, Mv 
 #ifdef B200_ME_TIMING
     const long long tq0 = clock64();
 #endif
-    var = full_pixel_diamond(k, skip, start, k.d.step_param, cl, best, second, true);
+    {
+      const int m = k.d.search_method, sp = k.d.step_param;
+      int *pcl = (k.d.flags & B200_ME_COST_LIST) ? cl : nullptr;  // changes the BIGDIA family's last scale
+      if (m == B200_ME_HEX || m == B200_ME_BIGDIA || m == B200_ME_SQUARE)
+        var = pattern_search(k, skip, start, sp, true, pcl, best);
+      else if (m == B200_ME_FAST_HEX || m == B200_ME_FAST_DIAMOND)
+        var = pattern_search(k, skip, start, max(kMaxSteps - 2, sp), false, pcl, best);
+      else if (m == B200_ME_FAST_BIGDIA)
+        var = pattern_search(k, skip, start, max(kMaxSteps - 3, sp), false, pcl, best);
+      else if (m == B200_ME_VFAST_DIAMOND)
+        var = pattern_search(k, skip, start, max(kMaxSteps - 1, sp), false, pcl, best);
+      else
+        var = full_pixel_diamond(k, skip, start, sp, cl, best, second, true);
+    }
 #ifdef B200_ME_TIMING
     k.bcast[12] = (int)((clock64() - tq0) >> 4);
 #endif

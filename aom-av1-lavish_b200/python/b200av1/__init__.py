@@ -209,6 +209,7 @@ MERESULT_DTYPE = np.dtype([("best_row", "<i2"), ("best_col", "<i2"), ("second_ro
                            ("distortion", "<i4"), ("sse", "<u4")])
 assert MEBLOCK_DTYPE.itemsize == 44 and MERESULT_DTYPE.itemsize == 40
 ME_RUN_MESH, ME_PRUNE_MESH, ME_FINE_INTERVAL, ME_SKIP_SAD, ME_ALLOW_HP = 1, 2, 4, 8, 16
+ME_COST_LIST = 32
 
 
 class MeLaunch(C.Structure):

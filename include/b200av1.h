@@ -295,7 +295,10 @@ int b200_upsampled_pred_launch(b200_ctx *ctx, const B200UpsampleLaunch *launch, 
  * candidates of every search step are evaluated in parallel (SAD / variance per warp),
  * the decision rule is the reference's "first candidate in scan order with the strictly
  * smallest sad + mv cost", second_best_mv and the 5-point cost list included. */
-enum { B200_ME_NSTEP = 0, B200_ME_NSTEP_8PT = 1, B200_ME_DIAMOND = 2, B200_ME_CLAMPED_DIAMOND = 3 };
+enum { B200_ME_NSTEP = 0, B200_ME_NSTEP_8PT = 1, B200_ME_DIAMOND = 2, B200_ME_CLAMPED_DIAMOND = 3,
+       /* pattern_search family (mcomp.c:1017-1316); values of the reference's SEARCH_METHODS */
+       B200_ME_HEX = 4, B200_ME_BIGDIA = 5, B200_ME_SQUARE = 6, B200_ME_FAST_HEX = 7,
+       B200_ME_FAST_DIAMOND = 8, B200_ME_FAST_BIGDIA = 9, B200_ME_VFAST_DIAMOND = 10 };
 enum { B200_MV_COST_ENTROPY = 0, B200_MV_COST_L1_LOWRES, B200_MV_COST_L1_MIDRES,
        B200_MV_COST_L1_HDRES, B200_MV_COST_NONE };           /* MV_COST_TYPE, mcomp.h:32-38 */
 enum { B200_USE_2_TAPS_ORIG = 0, B200_USE_2_TAPS, B200_USE_4_TAPS, B200_USE_8_TAPS };
@@ -305,6 +308,8 @@ enum { B200_EIGHTH_PEL = 0, B200_QUARTER_PEL, B200_HALF_PEL, B200_FULL_PEL };
 #define B200_ME_FINE_INTERVAL 4u /* fine_search_interval */
 #define B200_ME_SKIP_SAD 8u      /* ms_params->sdf = vfp->sdsf (row-skipping SAD) */
 #define B200_ME_ALLOW_HP 16u     /* sub-pel: allow_hp */
+#define B200_ME_COST_LIST 32u    /* the caller passes cost_list != NULL (pattern_search takes a
+                                    different path through its last scale when it does) */
 typedef struct {
   uint32_t src_offset; /* pixels from the current-frame base to the block */
   uint32_t ref_offset; /* pixels from the reference-frame base to the co-located block */

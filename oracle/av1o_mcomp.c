@@ -6,6 +6,7 @@
  *   diamond_search_sad           :1318-1477     full_pixel_diamond      :1479-1526
  *   exhaustive_mesh_search       :1530-1599     full_pixel_exhaustive   :1603-1679
  *   calc_int_sad_list            :791-841       av1_full_pixel_search   :1755-1895
+ *   pattern_search (hex / bigdia / square and their fast_* variants) :498-660,:883-1316
  *   sub-pel tree                 :2371-2551,2566-2779,2781-2868,3128-3196
  * The reference walks candidates one at a time updating a running best with strict '<';
  * this restatement evaluates the candidates of a step as a list and takes the first
@@ -251,6 +252,179 @@ static int full_pixel_diamond(const Av1oMeParams *p, const Sites *cfg, int skip,
   return bestsme;
 }
 
+/* ------------------------------------------------------------- pattern search --- */
+/* Site tables of av1_init_motion_compensation_{hex,bigdia,square} (mcomp.c:498-660), built
+ * by rule: scale i reaches 2^i pixels.  hex: 8-point ring at scale 0, then 6-point hexagons;
+ * bigdia: 4 nearest points at scale 0, then 8-point diamonds; square: 8-point squares. */
+#define PAT_SCALES 11 /* MAX_PATTERN_SCALES */
+typedef struct {
+  Mv site[PAT_SCALES][8];
+  int n[PAT_SCALES];
+} PatSites;
+
+static void init_pattern_sites(PatSites *s, int method) {
+  static const Mv ring[8] = { { -1, -1 }, { 0, -1 }, { 1, -1 }, { 1, 0 }, { 1, 1 }, { 0, 1 },
+                              { -1, 1 }, { -1, 0 } };
+  memset(s, 0, sizeof(*s));
+  const int hex = method == AV1O_HEX || method == AV1O_FAST_HEX;
+  const int square = method == AV1O_SQUARE;
+  for (int i = 0; i < PAT_SCALES; ++i) {
+    const int d = 1 << i, h = d >> 1;
+    if (square || (hex && i == 0)) {
+      s->n[i] = 8;
+      for (int j = 0; j < 8; ++j) s->site[i][j] = (Mv){ ring[j].row * d, ring[j].col * d };
+    } else if (hex) {
+      const Mv m[6] = { { -h, -d }, { h, -d }, { d, 0 }, { h, d }, { -h, d }, { -d, 0 } };
+      s->n[i] = 6;
+      for (int j = 0; j < 6; ++j) s->site[i][j] = m[j];
+    } else if (i == 0) {
+      const Mv m[4] = { { 0, -1 }, { 1, 0 }, { 0, 1 }, { -1, 0 } };
+      s->n[i] = 4;
+      for (int j = 0; j < 4; ++j) s->site[i][j] = m[j];
+    } else {
+      const Mv m[8] = { { -h, -h }, { 0, -d }, { h, -h }, { d, 0 }, { h, h }, { 0, d }, { -h, h },
+                        { -d, 0 } };
+      s->n[i] = 8;
+      for (int j = 0; j < 8; ++j) s->site[i][j] = m[j];
+    }
+  }
+}
+
+typedef struct {
+  const Av1oMeParams *p;
+  const PatSites *cfg;
+  int skip, br, bc;
+  unsigned bestsad, raw_bestsad;
+} PatState;
+
+/* One round of candidates idx[0..n) of scale s around the centre (calc_sad4/3/_update_bestmv
+ * and their bounds-checking twins, :883-1011): candidates outside the limits are skipped,
+ * the others update the running best in order.  Returns the position in idx[] of the last
+ * improvement or -1; cl (optional) receives the raw SADs at cl[idx + 1]. */
+static int pat_round(PatState *st, int s, const int *idx, int n, int *cl, int cl_oob_marks) {
+  int best = -1;
+  for (int i = 0; i < n; ++i) {
+    const Mv m = { st->br + st->cfg->site[s][idx[i]].row, st->bc + st->cfg->site[s][idx[i]].col };
+    if (!in_range(st->p, m.row, m.col)) {
+      if (cl && cl_oob_marks) cl[idx[i] + 1] = INT_MAX;
+      continue;
+    }
+    const unsigned sad = me_sad(st->p, m.row, m.col, st->skip);
+    if (cl) cl[idx[i] + 1] = (int)sad;
+    if (sad >= st->bestsad) continue; /* update_mvs_and_sad :858 */
+    const unsigned t = sad + (unsigned)sad_cost(st->p, m.row, m.col);
+    if (t < st->bestsad) {
+      st->raw_bestsad = sad;
+      st->bestsad = t;
+      best = i;
+    }
+  }
+  return best;
+}
+
+/* All candidates of a scale.  Quirk kept from the reference (:1065-1078): when the whole
+ * scale is inside the limits (check_bounds) it evaluates groups of four and then calls the
+ * scalar routine with (num_candidates = n % 4, cand_start = 4 * (n / 4)), whose loop runs
+ * from cand_start up to n % 4 -- i.e. never: the last two points of a 6-point hexagon are
+ * only looked at near the limits. */
+static int pat_round_all(PatState *st, int s) {
+  static const int all[8] = { 0, 1, 2, 3, 4, 5, 6, 7 };
+  const Av1oMeParams *p = st->p;
+  const int range = 1 << s;
+  const int inside = st->br - range >= p->row_min && st->br + range <= p->row_max &&
+                     st->bc - range >= p->col_min && st->bc + range <= p->col_max;
+  return pat_round(st, s, all, inside ? st->cfg->n[s] & ~3 : st->cfg->n[s], NULL, 0);
+}
+
+static void pat_move(PatState *st, int s, int k) {
+  st->br += st->cfg->site[s][k].row;
+  st->bc += st->cfg->site[s][k].col;
+}
+
+/* pattern_search (mcomp.c:1017-1243) */
+static int pattern_search(const Av1oMeParams *p, int skip, Mv start, int search_step, int do_init,
+                          int *cl, Mv *best_mv) {
+  static const int all[8] = { 0, 1, 2, 3, 4, 5, 6, 7 };
+  PatSites cfg;
+  init_pattern_sites(&cfg, p->search_method);
+  const int last_is_4 = cfg.n[0] == 4;
+  if (search_step > MAX_STEPS - 1) search_step = MAX_STEPS - 1;
+  int best_init_s = MAX_STEPS - 1 - search_step, s, k = -1;
+  start = clamp_mv(p, start);
+  PatState st = { p, &cfg, skip, start.row, start.col, 0, 0 };
+  if (cl) for (int i = 0; i < 5; ++i) cl[i] = INT_MAX;
+  int has_sad = 0;
+  st.raw_bestsad = me_sad(p, start.row, start.col, skip);
+  st.bestsad = st.raw_bestsad + (unsigned)sad_cost(p, start.row, start.col);
+  if (do_init) {
+    s = best_init_s;
+    best_init_s = -1;
+    for (int t = 0; t <= s; ++t) {
+      const int bs = pat_round_all(&st, t);
+      if (bs != -1) {
+        best_init_s = t;
+        k = bs;
+      }
+    }
+    if (best_init_s != -1) pat_move(&st, best_init_s, k);
+  }
+  if (best_init_s != -1) {
+    const int last_s = last_is_4 && cl != NULL;
+    int best_site = -1;
+    for (s = best_init_s; s >= last_s; s--) {
+      if (!do_init || s != best_init_s) {
+        best_site = pat_round_all(&st, s);
+        if (best_site == -1) continue;
+        pat_move(&st, s, best_site);
+        k = best_site;
+      }
+      do {
+        const int chk[3] = { k == 0 ? cfg.n[s] - 1 : k - 1, k, k == cfg.n[s] - 1 ? 0 : k + 1 };
+        best_site = pat_round(&st, s, chk, 3, NULL, 0);
+        if (best_site != -1) {
+          k = chk[best_site];
+          pat_move(&st, s, k);
+        }
+      } while (best_site != -1);
+    }
+    if (s == 0) { /* only reachable with a cost list: the 4-point scale fills it on the way */
+      cl[0] = (int)st.raw_bestsad;
+      has_sad = 1;
+      if (!do_init || s != best_init_s) {
+        best_site = pat_round(&st, 0, all, 4, cl, 0);
+        if (best_site != -1) {
+          pat_move(&st, 0, best_site);
+          k = best_site;
+        }
+      }
+      while (best_site != -1) {
+        const int chk[3] = { k == 0 ? 3 : k - 1, k, k == 3 ? 0 : k + 1 };
+        cl[1] = cl[2] = cl[3] = cl[4] = INT_MAX;
+        cl[((k + 2) % 4) + 1] = cl[0];
+        cl[0] = (int)st.raw_bestsad;
+        best_site = pat_round(&st, 0, chk, 3, cl, 1);
+        if (best_site != -1) {
+          k = chk[best_site];
+          pat_move(&st, 0, k);
+        }
+      }
+    }
+  }
+  best_mv->row = st.br;
+  best_mv->col = st.bc;
+  if (cl) {
+    if (!has_sad) {
+      sad_list(p, skip, *best_mv, cl);
+    } else { /* calc_int_sad_list :791 with costlist_has_sad: only the mv costs are added */
+      static const Mv nb[4] = { { 0, -1 }, { 1, 0 }, { 0, 1 }, { -1, 0 } };
+      cl[0] += sad_cost(p, st.br, st.bc);
+      for (int i = 0; i < 4; ++i)
+        if (cl[i + 1] != INT_MAX) cl[i + 1] += sad_cost(p, st.br + nb[i].row, st.bc + nb[i].col);
+    }
+  }
+  return var_cost(p, *best_mv);
+}
+
 /* ---------------------------------------------------------------- mesh search --- */
 static void try_mv(const Av1oMeParams *p, unsigned sad, Mv m, unsigned *best_sad, Mv *best,
                    Mv *second) {
@@ -328,7 +502,24 @@ static int full_pixel_search_impl(const Av1oMeParams *p, const Sites *cfg, int s
   best->row = best->col = -32768; /* MARK_MV_INVALID */
   if (second) second->row = second->col = -32768;
   if (cl) for (int i = 0; i < 5; ++i) cl[i] = INT_MAX;
-  int var = full_pixel_diamond(p, cfg, skip, start, p->step_param, cl, best, second);
+  int var;
+  const int big = MAX_STEPS; /* fast_* wrappers clamp the step from below, :1278-1316 */
+  switch (p->search_method) {
+    case AV1O_HEX: case AV1O_BIGDIA: case AV1O_SQUARE:
+      var = pattern_search(p, skip, start, p->step_param, 1, cl, best);
+      break;
+    case AV1O_FAST_HEX: case AV1O_FAST_DIAMOND:
+      var = pattern_search(p, skip, start, p->step_param > big - 2 ? p->step_param : big - 2, 0, cl, best);
+      break;
+    case AV1O_FAST_BIGDIA:
+      var = pattern_search(p, skip, start, p->step_param > big - 3 ? p->step_param : big - 3, 0, cl, best);
+      break;
+    case AV1O_VFAST_DIAMOND:
+      var = pattern_search(p, skip, start, p->step_param > big - 1 ? p->step_param : big - 1, 0, cl, best);
+      break;
+    default:
+      var = full_pixel_diamond(p, cfg, skip, start, p->step_param, cl, best, second);
+  }
   const int mi_log2 = ilog2i(p->bw / 4) + ilog2i(p->bh / 4);
   if (!run_mesh && (p->search_method == AV1O_NSTEP || p->search_method == AV1O_NSTEP_8PT)) {
     const int thr = p->force_mesh_thresh >> (10 - mi_log2);

@@ -21,7 +21,10 @@ extern "C" {
 #endif
 
 /* search methods served (SEARCH_METHODS, av1/encoder/speed_features.h) */
-enum { AV1O_NSTEP = 0, AV1O_NSTEP_8PT = 1, AV1O_DIAMOND = 2, AV1O_CLAMPED_DIAMOND = 3 };
+enum { AV1O_NSTEP = 0, AV1O_NSTEP_8PT = 1, AV1O_DIAMOND = 2, AV1O_CLAMPED_DIAMOND = 3,
+       /* pattern_search family; values as in the reference's enum (mcomp_structs.h:56-85) */
+       AV1O_HEX = 4, AV1O_BIGDIA = 5, AV1O_SQUARE = 6, AV1O_FAST_HEX = 7, AV1O_FAST_DIAMOND = 8,
+       AV1O_FAST_BIGDIA = 9, AV1O_VFAST_DIAMOND = 10 };
 /* MV_COST_TYPE, mcomp.h:32-38 */
 enum { AV1O_COST_ENTROPY = 0, AV1O_COST_L1_LOWRES, AV1O_COST_L1_MIDRES, AV1O_COST_L1_HDRES,
        AV1O_COST_NONE };

@@ -149,9 +149,25 @@ void refshim_full_pixel_search(const Av1oMeParams *p, Av1oMeResult *r) {
       ms.search_method = DIAMOND;
       av1_init_dsmotion_compensation(cfg, p->ref_stride, 0);
       break;
-    default:
+    case AV1O_CLAMPED_DIAMOND:
       ms.search_method = CLAMPED_DIAMOND;
       av1_init_dsmotion_compensation(cfg, p->ref_stride, 1);
+      break;
+    case AV1O_HEX:
+    case AV1O_FAST_HEX:
+      ms.search_method = p->search_method == AV1O_HEX ? HEX : FAST_HEX;
+      av1_init_motion_compensation_hex(cfg, p->ref_stride, 0);
+      break;
+    case AV1O_SQUARE:
+      ms.search_method = SQUARE;
+      av1_init_motion_compensation_square(cfg, p->ref_stride, 0);
+      break;
+    default:
+      ms.search_method = p->search_method == AV1O_BIGDIA        ? BIGDIA
+                         : p->search_method == AV1O_FAST_DIAMOND ? FAST_DIAMOND
+                         : p->search_method == AV1O_FAST_BIGDIA  ? FAST_BIGDIA
+                                                                 : VFAST_DIAMOND;
+      av1_init_motion_compensation_bigdia(cfg, p->ref_stride, 0);
       break;
   }
   ms.search_sites = cfg;

@@ -49,7 +49,8 @@ def me_launch(ctx, cur, refb, params, tables_dev, subpel, window_bytes):
         b["search_method"], b["step_param"] = p.search_method, p.step_param
         b["flags"] = (p.run_mesh_search * b200av1.ME_RUN_MESH | p.prune_mesh_search * b200av1.ME_PRUNE_MESH |
                       p.fine_search_interval * b200av1.ME_FINE_INTERVAL |
-                      p.use_skip_sad * b200av1.ME_SKIP_SAD | p.allow_hp * b200av1.ME_ALLOW_HP)
+                      p.use_skip_sad * b200av1.ME_SKIP_SAD | p.allow_hp * b200av1.ME_ALLOW_HP |
+                      p.want_cost_list * b200av1.ME_COST_LIST)
         b["mv_cost_type"] = p.mv_cost_type
         b["mesh_mv_diff_threshold"] = p.mesh_search_mv_diff_threshold
         b["subpel"] = p.forced_stop | (p.iters_per_step << 2) | (p.subpel_search_type << 4)
@@ -206,3 +207,41 @@ def test_fullpel_mesh_patterns(ctx, pattern):
             assert (int(g["best_row"]), int(g["best_col"]), int(g["second_row"]), int(g["second_col"]),
                     tuple(int(v) for v in g["cost_list"]), int(g["ret"])) == e.key(), \
                 (pattern, trial, i, p.bw, p.bh, p.use_skip_sad, p.fine_search_interval)
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+def test_pattern_search_methods(ctx, bd):
+    """HEX / BIGDIA / SQUARE / FAST_HEX / FAST_DIAMOND / FAST_BIGDIA / VFAST_DIAMOND
+    (pattern_search, mcomp.c:1017-1316) with and without a cost list, staged window and
+    global-memory path."""
+    O = H.oracle()
+    rng = np.random.default_rng(950 + bd)
+    tables = H.make_mv_cost_tables(6)
+    keep, tdev = upload_tables(ctx, tables)
+    for trial in range(3):
+        cur, refb = M.make_frames(rng, 256, 192, bd, flat=(trial == 2))
+        params = []
+        for (bw, bh) in M.FULLPEL_SIZES:
+            for method in range(4, 11):
+                p = M.random_fullpel_params(rng, cur, refb, bw, bh, bd, tables)
+                p.search_method = method
+                p.step_param = int(rng.integers(0, 12))
+                p.run_mesh_search = int(rng.integers(0, 4) == 0)
+                params.append(p)
+        exp = []
+        for p in params:
+            e = H.MeResult()
+            O.av1o_full_pixel_search(C.byref(p), C.byref(e))
+            exp.append(e)
+        for window in (150 * 1024, 0):
+            got = me_launch(ctx, cur, refb, params, tdev, False, window)
+            for i, (p, e) in enumerate(zip(params, exp)):
+                g = got[i]
+                tag = (trial, i, p.bw, p.bh, p.search_method, p.step_param, p.want_cost_list,
+                       p.use_skip_sad, p.run_mesh_search, window)
+                assert (int(g["best_row"]), int(g["best_col"]), int(g["ret"])) == \
+                    (e.best_row, e.best_col, e.ret), tag
+                if p.want_cost_list:
+                    assert tuple(int(v) for v in g["cost_list"]) == tuple(e.cost_list), tag
+                if p.want_second_best:
+                    assert (int(g["second_row"]), int(g["second_col"])) == (e.second_row, e.second_col), tag

@@ -57,3 +57,30 @@ def test_sub_pixel_tree_vs_reference(bd):
                 a, b = run_both(O.av1o_find_best_sub_pixel_tree, R.refshim_find_best_sub_pixel_tree,
                                 p, subpel=True)
                 assert a == b, (trial, bw, bh, st, p.allow_hp, p.forced_stop, p.iters_per_step, a, b)
+
+
+PATTERN_METHODS = [4, 5, 6, 7, 8, 9, 10]  # HEX, BIGDIA, SQUARE, FAST_HEX, FAST_DIAMOND, FAST_BIGDIA, VFAST_DIAMOND
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+def test_pattern_search_vs_reference(bd):
+    """pattern_search family (mcomp.c:1017-1316): with and without a cost list (the cost
+    list changes the last scale of the BIGDIA family), limits clipped at the frame edge,
+    flat regions for ties, row-skipping SAD with its redo rule, optional mesh follow-up."""
+    O, R = H.oracle(), H.ref()
+    rng = np.random.default_rng(500 + bd)
+    tables = H.make_mv_cost_tables(5)
+    n = 0
+    for trial in range(6):
+        cur, refb = M.make_frames(rng, 256, 192, bd, flat=(trial % 3 == 2))
+        for (bw, bh) in M.FULLPEL_SIZES:
+            for method in PATTERN_METHODS:
+                p = M.random_fullpel_params(rng, cur, refb, bw, bh, bd, tables)
+                p.search_method = method
+                p.step_param = int(rng.integers(0, 12))
+                p.run_mesh_search = int(rng.integers(0, 4) == 0)
+                a, b = run_both(O.av1o_full_pixel_search, R.refshim_full_pixel_search, p)
+                assert a == b, (trial, bw, bh, method, p.step_param, p.want_cost_list, p.use_skip_sad,
+                                p.mv_cost_type, a, b)
+                n += 1
+    assert n == 6 * len(M.FULLPEL_SIZES) * len(PATTERN_METHODS)
