@@ -752,6 +752,52 @@ __device__ int full_pixel_search(const Ctx &k, bool skip, int *cl, Mv *best, Mv 
   return var;
 }
 
+// av1_refining_search_8p_c (mcomp.c:1683-1753), single reference: up to SEARCH_RANGE_8P = 3
+// rounds over the 8 neighbours of the running best, each grid position evaluated once.
+// One warp per neighbour; every thread replays the reference's in-order double test
+// (raw SAD first, then SAD + cost).
+__device__ int refine_8p(const Ctx &k, bool skip, Mv *bestp) {
+  constexpr int kRange = 3, kStride = 2 * kRange + 1;
+  const int nb[8][2] = { { -1, 0 }, { 0, -1 }, { 0, 1 }, { 1, 0 }, { -1, -1 }, { 1, -1 }, { -1, 1 }, { 1, 1 } };
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const Mv start = { k.d.start_row, k.d.start_col };
+  Mv best = clamp_mv(k, start);
+  unsigned best_sad = cta_value(k, [&](int ln) { return warp_sad(k, best.row, best.col, skip, ln); });
+  best_sad += (unsigned)sad_cost(k, best.row, best.col);
+  int centre = kRange * kStride + kRange;
+  unsigned long long visited = 1ull << centre;
+  for (int i = 0; i < kRange; ++i) {
+    __syncthreads();
+    if (warp < 8) {
+      const int g = centre + nb[warp][0] * kStride + nb[warp][1];
+      const int r = best.row + nb[warp][0], c = best.col + nb[warp][1];
+      unsigned v = 0xffffffffu;
+      if (!((visited >> g) & 1) && in_range(k, r, c)) v = warp_sad(k, r, c, skip, lane);
+      if (lane == 0) k.cand[warp] = v;
+    }
+    __syncthreads();
+    int best_site = -1;
+    for (int j = 0; j < 8; ++j) {
+      const int g = centre + nb[j][0] * kStride + nb[j][1];
+      if ((visited >> g) & 1) continue;
+      visited |= 1ull << g;
+      const unsigned v = k.cand[j];
+      if (v == 0xffffffffu || v >= best_sad) continue;
+      const unsigned t = v + (unsigned)sad_cost(k, best.row + nb[j][0], best.col + nb[j][1]);
+      if (t < best_sad) {
+        best_sad = t;
+        best_site = j;
+      }
+    }
+    if (best_site < 0) break;
+    best.row += nb[best_site][0];
+    best.col += nb[best_site][1];
+    centre += nb[best_site][0] * kStride + nb[best_site][1];
+  }
+  *bestp = best;
+  return (int)best_sad;
+}
+
 // pitch in words that is 4 (mod 8): conflict-free uint4 access by 8 consecutive rows
 __host__ __device__ __forceinline__ int vec_pitch(int words) { return ((words + 3) & ~7) + 4 >= words ? ((words + 3) & ~7) + 4 : ((words + 11) & ~7) + 4; }
 
@@ -835,7 +881,14 @@ __global__ void __launch_bounds__(kThreads, 3) fullpel_kernel(const B200MeLaunch
 #endif
   Mv best, second;
   int cl[5];
-  const int var = full_pixel_search(k, (k.d.flags & B200_ME_SKIP_SAD) != 0, cl, &best, &second);
+  int var;
+  if (k.d.search_method == B200_ME_REFINE_8P) {
+    second.row = second.col = -32768;
+    for (int i = 0; i < 5; ++i) cl[i] = 0;
+    var = refine_8p(k, (k.d.flags & B200_ME_SKIP_SAD) != 0, &best);
+  } else {
+    var = full_pixel_search(k, (k.d.flags & B200_ME_SKIP_SAD) != 0, cl, &best, &second);
+  }
   if (threadIdx.x == 0) {
     B200MeResult r;
     r.best_row = (short)best.row;

@@ -1,4 +1,5 @@
-// me_subpel.cuh -- av1_find_best_sub_pixel_tree on one CTA (included by me.cu).
+// me_subpel.cuh -- av1_find_best_sub_pixel_tree and its _pruned / _pruned_more variants
+// (mcomp.c:2907-3126) on one CTA (included by me.cu).
 // mcomp.c:2371-2551 (error functions, check_better), :2566-2779 (level checks),
 // :2781-2868 (centre error), :3128-3196 (the tree).  Unscaled references,
 // last_mv_search_list == NULL.
@@ -189,6 +190,100 @@ __device__ void subpel_search(const SubCtx &s, SubState &st) {
   }
 }
 
+// first_level_check(_fast) (mcomp.c:2566,2689): four cardinals, then the diagonal of the
+// better halves.  Returns the diagonal step.
+__device__ Mv first_level(const SubCtx &s, SubState &st, Mv c, int hstep, int mode) {
+  const Mv l = { c.row, c.col - hstep }, r = { c.row, c.col + hstep };
+  const Mv t = { c.row - hstep, c.col }, b = { c.row + hstep, c.col };
+  const unsigned left = check_better(s, st, l, mode, nullptr);
+  const unsigned right = check_better(s, st, r, mode, nullptr);
+  const unsigned up = check_better(s, st, t, mode, nullptr);
+  const unsigned down = check_better(s, st, b, mode, nullptr);
+  const Mv diag = { up <= down ? -hstep : hstep, left <= right ? -hstep : hstep };
+  const Mv dm = { c.row + diag.row, c.col + diag.col };
+  check_better(s, st, dm, mode, nullptr);
+  return diag;
+}
+
+// two_level_checks_fast (mcomp.c:2675): first_level_check_fast + second_level_check_fast
+// (:2610), every probe through the bilinear estimate (mode 1).
+__device__ void two_level_fast(const SubCtx &s, SubState &st, Mv c, int hstep, int iters) {
+  const Mv diag = first_level(s, st, c, hstep, 1);
+  if (iters <= 1) return;
+  const int tr = c.row, tc = c.col, br = st.best.row, bc = st.best.col;
+  if (tr != br && tc != bc) {
+    const Mv c1 = { br, bc + diag.col }, c2 = { br + diag.row, bc };
+    check_better(s, st, c1, 1, nullptr);
+    check_better(s, st, c2, 1, nullptr);
+  } else if (tr == br && tc != bc) {
+    const Mv bl = { br + hstep, bc + diag.col }, tl = { br - hstep, bc + diag.col };
+    const Mv rev = { br - diag.row, bc };
+    check_better(s, st, bl, 1, nullptr);
+    check_better(s, st, tl, 1, nullptr);
+    check_better(s, st, rev, 1, nullptr);
+  } else if (tr != br && tc == bc) {
+    const Mv rl = { br + diag.row, bc + hstep }, ll = { br + diag.row, bc - hstep };
+    const Mv rev = { br, bc - diag.col };
+    check_better(s, st, rl, 1, nullptr);
+    check_better(s, st, ll, 1, nullptr);
+    check_better(s, st, rev, 1, nullptr);
+  }
+}
+
+// divide_and_round (mcomp.c:2853)
+__device__ __forceinline__ int div_round(int n, int d) {
+  return ((n < 0) ^ (d < 0)) ? ((n - d / 2) / d) : ((n + d / 2) / d);
+}
+
+// av1_find_best_sub_pixel_tree_pruned (mcomp.c:2992, tree == 1) and _pruned_more (:2907,
+// tree == 2); last_mv_search_list == NULL, unscaled reference.  cl = ms_params->cost_list or
+// nullptr.  All control flow is CTA-uniform (every thread holds the same SubState).
+__device__ void subpel_search_pruned(const SubCtx &s, SubState &st, int tree, const int *cl) {
+  const Ctx &k = s.k;
+  const int forced_stop = k.d.subpel & 3, iters_per_step = (k.d.subpel >> 2) & 3;
+  const int allow_hp = (k.d.flags & B200_ME_ALLOW_HP) != 0;
+  int hstep = 4;
+  st.best.row = k.d.start_row;
+  st.best.col = k.d.start_col;
+  const Mv start = st.best;
+  unsigned sse;
+  const unsigned e = cta_pref_error(s, st.best, 0, &sse);  // setup_center_error :2781
+  st.distortion = (int)e;
+  st.sse = sse;
+  st.besterr = e + (unsigned)err_cost(k, st.best.row, st.best.col);
+  if (forced_stop == B200_FULL_PEL) return;
+  const bool usable = cl && cl[0] != INT_MAX && cl[1] != INT_MAX && cl[2] != INT_MAX &&
+                      cl[3] != INT_MAX && cl[4] != INT_MAX;
+  if (tree == B200_SUBPEL_TREE_PRUNED_MORE && usable && cl[0] < cl[1] && cl[0] < cl[2] &&
+      cl[0] < cl[3] && cl[0] < cl[4]) {
+    // get_cost_surf_min (:2870), bits = 1
+    const int ic = div_round(cl[1] - cl[3], cl[1] - 2 * cl[0] + cl[3]);
+    const int ir = div_round(cl[4] - cl[2], cl[4] - 2 * cl[0] + cl[2]);
+    if (ir != 0 || ic != 0) {
+      const Mv m = { start.row + ir * hstep, start.col + ic * hstep };
+      check_better(s, st, m, 1, nullptr);
+    }
+  } else if (tree == B200_SUBPEL_TREE_PRUNED && usable) {
+    // the quadrant of the two cheaper full-pel neighbours: horizontal, vertical, diagonal
+    const Mv h = { start.row, start.col + (cl[1] < cl[3] ? -hstep : hstep) };
+    const Mv v = { start.row + (cl[2] < cl[4] ? hstep : -hstep), start.col };
+    const Mv d = { v.row, h.col };
+    check_better(s, st, h, 1, nullptr);
+    check_better(s, st, v, 1, nullptr);
+    check_better(s, st, d, 1, nullptr);
+  } else {
+    two_level_fast(s, st, start, hstep, iters_per_step);
+  }
+  if (forced_stop < B200_HALF_PEL) {
+    hstep >>= 1;
+    two_level_fast(s, st, st.best, hstep, iters_per_step);
+  }
+  if (allow_hp && forced_stop == B200_EIGHTH_PEL) {
+    hstep >>= 1;
+    two_level_fast(s, st, st.best, hstep, iters_per_step);
+  }
+}
+
 __global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) {
   __shared__ long long s_red[2 * kWarps];
   __shared__ int s_bcast[16];
@@ -223,7 +318,18 @@ __global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) 
     __syncthreads();
   }
   SubState st;
-  subpel_search(s, st);
+  const int tree = s.k.d.search_method;
+  if (tree == B200_SUBPEL_TREE) {
+    subpel_search(s, st);
+  } else {
+    int cl[5];
+    const bool have = (s.k.d.flags & B200_ME_COST_LIST) && l.cost_lists;
+    if (have) {
+      const int *g = l.cost_lists + (size_t)bi * (l.cost_list_stride > 0 ? l.cost_list_stride : 5);
+      for (int i = 0; i < 5; ++i) cl[i] = g[i];
+    }
+    subpel_search_pruned(s, st, tree, have ? cl : nullptr);
+  }
   if (threadIdx.x == 0) {
     B200MeResult r;
     memset(&r, 0, sizeof(r));

@@ -210,6 +210,8 @@ MERESULT_DTYPE = np.dtype([("best_row", "<i2"), ("best_col", "<i2"), ("second_ro
 assert MEBLOCK_DTYPE.itemsize == 44 and MERESULT_DTYPE.itemsize == 40
 ME_RUN_MESH, ME_PRUNE_MESH, ME_FINE_INTERVAL, ME_SKIP_SAD, ME_ALLOW_HP = 1, 2, 4, 8, 16
 ME_COST_LIST = 32
+ME_REFINE_8P = 11
+SUBPEL_TREE, SUBPEL_TREE_PRUNED, SUBPEL_TREE_PRUNED_MORE = 0, 1, 2
 
 
 class MeLaunch(C.Structure):
@@ -217,4 +219,5 @@ class MeLaunch(C.Structure):
                 ("cur", C.c_void_p), ("ref", C.c_void_p), ("cur_stride", C.c_int),
                 ("ref_stride", C.c_int), ("mesh_range", C.c_int * 4), ("mesh_interval", C.c_int * 4),
                 ("mvjcost", C.c_void_p), ("mvcost", C.c_void_p * 2), ("results", C.c_void_p),
-                ("window_bytes", C.c_int), ("max_bw", C.c_int), ("max_bh", C.c_int)]
+                ("window_bytes", C.c_int), ("max_bw", C.c_int), ("max_bh", C.c_int),
+                ("cost_lists", C.c_void_p), ("cost_list_stride", C.c_int)]

@@ -298,7 +298,13 @@ int b200_upsampled_pred_launch(b200_ctx *ctx, const B200UpsampleLaunch *launch, 
 enum { B200_ME_NSTEP = 0, B200_ME_NSTEP_8PT = 1, B200_ME_DIAMOND = 2, B200_ME_CLAMPED_DIAMOND = 3,
        /* pattern_search family (mcomp.c:1017-1316); values of the reference's SEARCH_METHODS */
        B200_ME_HEX = 4, B200_ME_BIGDIA = 5, B200_ME_SQUARE = 6, B200_ME_FAST_HEX = 7,
-       B200_ME_FAST_DIAMOND = 8, B200_ME_FAST_BIGDIA = 9, B200_ME_VFAST_DIAMOND = 10 };
+       B200_ME_FAST_DIAMOND = 8, B200_ME_FAST_BIGDIA = 9, B200_ME_VFAST_DIAMOND = 10,
+       /* not a SEARCH_METHODS value: av1_refining_search_8p_c (mcomp.c:1683, single reference)
+        * instead of av1_full_pixel_search; result = best mv + returned sad-with-cost */
+       B200_ME_REFINE_8P = 11 };
+/* b200_me_subpel_launch reads search_method as the sub-pel function: av1_find_best_sub_pixel_tree
+ * (mcomp.c:3128), _pruned (:2992), _pruned_more (:2907) */
+enum { B200_SUBPEL_TREE = 0, B200_SUBPEL_TREE_PRUNED = 1, B200_SUBPEL_TREE_PRUNED_MORE = 2 };
 enum { B200_MV_COST_ENTROPY = 0, B200_MV_COST_L1_LOWRES, B200_MV_COST_L1_MIDRES,
        B200_MV_COST_L1_HDRES, B200_MV_COST_NONE };           /* MV_COST_TYPE, mcomp.h:32-38 */
 enum { B200_USE_2_TAPS_ORIG = 0, B200_USE_2_TAPS, B200_USE_4_TAPS, B200_USE_8_TAPS };
@@ -309,7 +315,8 @@ enum { B200_EIGHTH_PEL = 0, B200_QUARTER_PEL, B200_HALF_PEL, B200_FULL_PEL };
 #define B200_ME_SKIP_SAD 8u      /* ms_params->sdf = vfp->sdsf (row-skipping SAD) */
 #define B200_ME_ALLOW_HP 16u     /* sub-pel: allow_hp */
 #define B200_ME_COST_LIST 32u    /* the caller passes cost_list != NULL (pattern_search takes a
-                                    different path through its last scale when it does) */
+                                    different path through its last scale when it does; the pruned
+                                    sub-pel trees read it from B200MeLaunch.cost_lists) */
 typedef struct {
   uint32_t src_offset; /* pixels from the current-frame base to the block */
   uint32_t ref_offset; /* pixels from the reference-frame base to the co-located block */
@@ -350,6 +357,11 @@ typedef struct {
                                     reference through L1/L2 instead.  0 = never stage. */
   int max_bw, max_bh;            /* largest block of the batch (sizes the per-search shared
                                     memory); 0 = assume 128 */
+  const int32_t *cost_lists;     /* device; sub-pel pruned trees: ms_params->cost_list of block i at
+                                    cost_lists[i * cost_list_stride .. +5], read when the block has
+                                    B200_ME_COST_LIST.  Pointing it at the full-pel launch's
+                                    results[0].cost_list with stride 10 chains the two launches. */
+  int cost_list_stride;          /* in int32 units; 0 = 5 */
 } B200MeLaunch;
 /* av1_init_search_range (mcomp.c:239): step_param for a search of +-size pixels */
 int b200_me_init_search_range(int size);

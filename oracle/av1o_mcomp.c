@@ -694,3 +694,143 @@ void av1o_find_best_sub_pixel_tree(const Av1oMeParams *p, Av1oMeResult *r) {
   r->distortion = s.distortion;
   r->sse = s.sse;
 }
+
+/* ============================================== pruned sub-pel trees (a24) ===== */
+/* second_level_check_fast (:2610): two or three more bilinear probes in the best quadrant */
+static void second_level_fast(SubpelState *s, Mv c, Mv diag, int hstep) {
+  const int tr = c.row, tc = c.col, br = s->best.row, bc = s->best.col;
+  if (tr != br && tc != bc) {
+    const Mv c1 = { br, bc + diag.col }, c2 = { br + diag.row, bc };
+    check_better(s, c1, 0, NULL);
+    check_better(s, c2, 0, NULL);
+  } else if (tr == br && tc != bc) {
+    const Mv bl = { br + hstep, bc + diag.col }, tl = { br - hstep, bc + diag.col };
+    const Mv rev = { br - diag.row, bc };
+    check_better(s, bl, 0, NULL);
+    check_better(s, tl, 0, NULL);
+    check_better(s, rev, 0, NULL);
+  } else if (tr != br && tc == bc) {
+    const Mv rl = { br + diag.row, bc + hstep }, ll = { br + diag.row, bc - hstep };
+    const Mv rev = { br, bc - diag.col };
+    check_better(s, rl, 0, NULL);
+    check_better(s, ll, 0, NULL);
+    check_better(s, rev, 0, NULL);
+  }
+}
+
+/* two_level_checks_fast (:2675) */
+static void two_level_fast(SubpelState *s, Mv c, int hstep, int iters) {
+  const Mv diag = first_level(s, c, hstep, 0);
+  if (iters > 1) second_level_fast(s, c, diag, hstep);
+}
+
+/* divide_and_round (:2853) */
+static int div_round(int n, int d) { return ((n < 0) ^ (d < 0)) ? ((n - d / 2) / d) : ((n + d / 2) / d); }
+
+/* av1_find_best_sub_pixel_tree_pruned (:2992) for sp_tree == 1, _pruned_more (:2907) for
+ * sp_tree == 2; last_mv_search_list == NULL, unscaled references: the centre error is
+ * setup_center_error (vf on the full-pel block) and every probe is the bilinear svf. */
+void av1o_find_best_sub_pixel_tree_pruned(const Av1oMeParams *p, Av1oMeResult *r) {
+  SubpelState s;
+  memset(r, 0, sizeof(*r));
+  s.p = p;
+  s.best.row = p->sp_start_row;
+  s.best.col = p->sp_start_col;
+  const Mv start = s.best;
+  int hstep = 4;
+  unsigned sse, e;
+  {
+    const int fr = s.best.row >> 3, fc = s.best.col >> 3;
+    if (p->highbd)
+      e = av1o_highbd_variance((const uint16_t *)p->ref + fr * p->ref_stride + fc, p->ref_stride,
+                               (const uint16_t *)p->src, p->src_stride, p->bw, p->bh, p->bd, &sse);
+    else
+      e = av1o_variance((const uint8_t *)p->ref + fr * p->ref_stride + fc, p->ref_stride,
+                        (const uint8_t *)p->src, p->src_stride, p->bw, p->bh, &sse);
+  }
+  s.distortion = (int)e;
+  s.sse = sse;
+  s.besterr = e + (unsigned)err_cost(p, s.best.row, s.best.col);
+  if (p->forced_stop != AV1O_FULL_PEL) {
+    const int *cl = p->sp_cost_list;
+    const int usable = p->sp_have_cost_list && cl[0] != INT_MAX && cl[1] != INT_MAX &&
+                       cl[2] != INT_MAX && cl[3] != INT_MAX && cl[4] != INT_MAX;
+    if (p->sp_tree == 2 && usable && cl[0] < cl[1] && cl[0] < cl[2] && cl[0] < cl[3] &&
+        cl[0] < cl[4]) {
+      /* get_cost_surf_min (:2870) with bits = 1 */
+      const int ic = div_round((cl[1] - cl[3]) * 1, cl[1] - 2 * cl[0] + cl[3]);
+      const int ir = div_round((cl[4] - cl[2]) * 1, cl[4] - 2 * cl[0] + cl[2]);
+      if (ir != 0 || ic != 0) {
+        const Mv m = { start.row + ir * hstep, start.col + ic * hstep };
+        check_better(&s, m, 0, NULL);
+      }
+    } else if (p->sp_tree == 1 && usable) {
+      const int right = !(cl[1] < cl[3]), top = !(cl[2] < cl[4]);
+      const Mv h = { start.row, start.col + (right ? hstep : -hstep) };
+      const Mv v = { start.row + (top ? -hstep : hstep), start.col };
+      const Mv d = { v.row, h.col };
+      check_better(&s, h, 0, NULL);
+      check_better(&s, v, 0, NULL);
+      check_better(&s, d, 0, NULL);
+    } else {
+      two_level_fast(&s, start, hstep, p->iters_per_step);
+    }
+    if (p->forced_stop < AV1O_HALF_PEL) {
+      hstep >>= 1;
+      two_level_fast(&s, s.best, hstep, p->iters_per_step);
+    }
+    if (p->allow_hp && p->forced_stop == AV1O_EIGHTH_PEL) {
+      hstep >>= 1;
+      two_level_fast(&s, s.best, hstep, p->iters_per_step);
+    }
+  }
+  r->best_row = s.best.row;
+  r->best_col = s.best.col;
+  r->ret = (int)s.besterr;
+  r->distortion = s.distortion;
+  r->sse = s.sse;
+}
+
+/* ===================================== av1_refining_search_8p_c (:1683) ===== */
+/* single reference (second_pred == NULL, no mask): get_mvpred_compound_sad is sdf */
+void av1o_refining_search_8p(const Av1oMeParams *p, Av1oMeResult *r) {
+  static const int nb[8][2] = { { -1, 0 }, { 0, -1 }, { 0, 1 }, { 1, 0 },
+                                { -1, -1 }, { 1, -1 }, { -1, 1 }, { 1, 1 } };
+  enum { RANGE = 3, STRIDE = 7 };
+  unsigned char grid[STRIDE * STRIDE];
+  memset(grid, 0, sizeof(grid));
+  memset(r, 0, sizeof(*r));
+  int centre = RANGE * STRIDE + RANGE;
+  Mv start = { p->start_row, p->start_col };
+  Mv best = clamp_mv(p, start);
+  unsigned best_sad = me_sad(p, best.row, best.col, p->use_skip_sad);
+  best_sad += (unsigned)sad_cost(p, best.row, best.col);
+  grid[centre] = 1;
+  for (int i = 0; i < RANGE; ++i) {
+    int best_site = -1;
+    for (int j = 0; j < 8; ++j) {
+      const int g = centre + nb[j][0] * STRIDE + nb[j][1];
+      if (grid[g]) continue;
+      grid[g] = 1;
+      const Mv m = { best.row + nb[j][0], best.col + nb[j][1] };
+      if (m.col < p->col_min || m.col > p->col_max || m.row < p->row_min || m.row > p->row_max)
+        continue;
+      unsigned sad = me_sad(p, m.row, m.col, p->use_skip_sad);
+      if (sad < best_sad) {
+        sad += (unsigned)sad_cost(p, m.row, m.col);
+        if (sad < best_sad) {
+          best_sad = sad;
+          best_site = j;
+        }
+      }
+    }
+    if (best_site < 0) break;
+    best.row += nb[best_site][0];
+    best.col += nb[best_site][1];
+    centre += nb[best_site][0] * STRIDE + nb[best_site][1];
+  }
+  r->best_row = best.row;
+  r->best_col = best.col;
+  r->second_row = r->second_col = -32768;
+  r->ret = (int)best_sad;
+}

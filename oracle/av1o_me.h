@@ -64,6 +64,10 @@ typedef struct {
   int allow_hp, forced_stop, iters_per_step, subpel_search_type;
   int sp_col_min, sp_col_max, sp_row_min, sp_row_max; /* SubpelMvLimits, 1/8 pel */
   int sp_start_row, sp_start_col;                     /* 1/8 pel start mv */
+  /* which sub-pel function: 0 av1_find_best_sub_pixel_tree (mcomp.c:3128), 1 _pruned (:2992),
+   * 2 _pruned_more (:2907); sp_have_cost_list = (ms_params->cost_list != NULL) */
+  int sp_tree, sp_have_cost_list;
+  int sp_cost_list[5];
 } Av1oMeParams;
 
 typedef struct {
@@ -77,6 +81,10 @@ typedef struct {
 
 void av1o_full_pixel_search(const Av1oMeParams *p, Av1oMeResult *r);
 void av1o_find_best_sub_pixel_tree(const Av1oMeParams *p, Av1oMeResult *r);
+/* av1_find_best_sub_pixel_tree_pruned / _pruned_more, selected by p->sp_tree (1 / 2) */
+void av1o_find_best_sub_pixel_tree_pruned(const Av1oMeParams *p, Av1oMeResult *r);
+/* av1_refining_search_8p_c (mcomp.c:1683): full-pel 8-point refinement around start */
+void av1o_refining_search_8p(const Av1oMeParams *p, Av1oMeResult *r);
 /* av1_init_search_range (mcomp.c:239) */
 int av1o_init_search_range(int size);
 

@@ -118,7 +118,7 @@ static void fill_cost(MV_COST_PARAMS *c, const Av1oMeParams *p, MV *ref_mv_store
   c->sad_per_bit = p->sad_per_bit;
 }
 
-void refshim_full_pixel_search(const Av1oMeParams *p, Av1oMeResult *r) {
+static void fullpel_common(const Av1oMeParams *p, Av1oMeResult *r, int refine8p) {
   FULLPEL_MOTION_SEARCH_PARAMS ms;
   memset(&ms, 0, sizeof(ms));
   aom_variance_fn_ptr_t vfp;
@@ -202,6 +202,15 @@ void refshim_full_pixel_search(const Av1oMeParams *p, Av1oMeResult *r) {
   const FULLPEL_MV start = { (int16_t)p->start_row, (int16_t)p->start_col };
   FULLPEL_MV best, second;
   int cost_list[5];
+  if (refine8p) {
+    memset(r, 0, sizeof(*r));
+    r->ret = av1_refining_search_8p_c(&ms, start, &best);
+    r->best_row = best.row;
+    r->best_col = best.col;
+    r->second_row = r->second_col = -32768;
+    free(cfg);
+    return;
+  }
   r->ret = av1_full_pixel_search(start, &ms, p->step_param, p->want_cost_list ? cost_list : NULL,
                                  &best, p->want_second_best ? &second : NULL);
   r->best_row = best.row;
@@ -212,7 +221,7 @@ void refshim_full_pixel_search(const Av1oMeParams *p, Av1oMeResult *r) {
   free(cfg);
 }
 
-void refshim_find_best_sub_pixel_tree(const Av1oMeParams *p, Av1oMeResult *r) {
+static void subpel_common(const Av1oMeParams *p, Av1oMeResult *r, int tree) {
   SUBPEL_MOTION_SEARCH_PARAMS ms;
   memset(&ms, 0, sizeof(ms));
   aom_variance_fn_ptr_t vfp;
@@ -225,7 +234,9 @@ void refshim_find_best_sub_pixel_tree(const Av1oMeParams *p, Av1oMeResult *r) {
   ref.buf = (uint8_t *)as_ref_ptr(p->ref, p->highbd);
   ref.stride = p->ref_stride;
   ms.allow_hp = p->allow_hp;
-  ms.cost_list = NULL;
+  int cl[5];
+  for (int i = 0; i < 5; ++i) cl[i] = p->sp_cost_list[i];
+  ms.cost_list = (tree && p->sp_have_cost_list) ? cl : NULL;
   ms.forced_stop = (SUBPEL_FORCE_STOP)p->forced_stop;
   ms.iters_per_step = p->iters_per_step;
   ms.mv_limits.col_min = p->sp_col_min;
@@ -264,7 +275,13 @@ void refshim_find_best_sub_pixel_tree(const Av1oMeParams *p, Av1oMeResult *r) {
   MV best;
   int distortion = 0;
   unsigned sse = 0;
-  r->ret = av1_find_best_sub_pixel_tree(xd, cm, &ms, start, &best, &distortion, &sse, NULL);
+  if (tree == 0)
+    r->ret = av1_find_best_sub_pixel_tree(xd, cm, &ms, start, &best, &distortion, &sse, NULL);
+  else if (tree == 1)
+    r->ret = av1_find_best_sub_pixel_tree_pruned(xd, cm, &ms, start, &best, &distortion, &sse, NULL);
+  else
+    r->ret = av1_find_best_sub_pixel_tree_pruned_more(xd, cm, &ms, start, &best, &distortion, &sse,
+                                                      NULL);
   r->best_row = best.row;
   r->best_col = best.col;
   r->distortion = distortion;
@@ -274,3 +291,17 @@ void refshim_find_best_sub_pixel_tree(const Av1oMeParams *p, Av1oMeResult *r) {
   free(mbmi);
   free(cur);
 }
+
+void refshim_find_best_sub_pixel_tree(const Av1oMeParams *p, Av1oMeResult *r) {
+  subpel_common(p, r, 0);
+}
+
+/* av1_find_best_sub_pixel_tree_pruned (sp_tree 1) / _pruned_more (sp_tree 2), unmodified */
+void refshim_find_best_sub_pixel_tree_pruned(const Av1oMeParams *p, Av1oMeResult *r) {
+  subpel_common(p, r, p->sp_tree == 2 ? 2 : 1);
+}
+
+void refshim_full_pixel_search(const Av1oMeParams *p, Av1oMeResult *r) { fullpel_common(p, r, 0); }
+
+/* av1_refining_search_8p_c (mcomp.c:1683), single reference */
+void refshim_refining_search_8p(const Av1oMeParams *p, Av1oMeResult *r) { fullpel_common(p, r, 1); }

@@ -192,7 +192,8 @@ class MeParams(C.Structure):
                 ("allow_hp", C.c_int), ("forced_stop", C.c_int), ("iters_per_step", C.c_int),
                 ("subpel_search_type", C.c_int), ("sp_col_min", C.c_int), ("sp_col_max", C.c_int),
                 ("sp_row_min", C.c_int), ("sp_row_max", C.c_int), ("sp_start_row", C.c_int),
-                ("sp_start_col", C.c_int)]
+                ("sp_start_col", C.c_int), ("sp_tree", C.c_int), ("sp_have_cost_list", C.c_int),
+                ("sp_cost_list", C.c_int * 5)]
 
 
 class MeResult(C.Structure):

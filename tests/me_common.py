@@ -89,3 +89,18 @@ def random_subpel_params(rng, cur, refb, bw, bh, bd, tables, search_type):
     p.sp_row_min, p.sp_row_max = fr * 8 - lim, fr * 8 + lim
     p.sp_col_min, p.sp_col_max = fc * 8 - lim, fc * 8 + lim
     return p
+
+
+def random_cost_list(rng, p):
+    """fill p.sp_cost_list / sp_have_cost_list: absent, holding an INT_MAX entry, a
+    well-behaved bowl (centre strictly smallest) or an arbitrary list"""
+    mode = int(rng.integers(0, 5))
+    p.sp_have_cost_list = int(mode != 0)
+    vals = [int(v) for v in rng.integers(200, 6000, 5)]
+    if mode == 2:
+        vals[int(rng.integers(0, 5))] = 2 ** 31 - 1
+    elif mode >= 3:
+        vals[0] = min(vals) - int(rng.integers(1, 150))
+    for i in range(5):
+        p.sp_cost_list[i] = vals[i]
+    return p

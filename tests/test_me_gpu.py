@@ -40,17 +40,19 @@ def me_launch(ctx, cur, refb, params, tables_dev, subpel, window_bytes):
             b["col_min"], b["col_max"], b["row_min"], b["row_max"] = (p.sp_col_min, p.sp_col_max,
                                                                       p.sp_row_min, p.sp_row_max)
             b["start_row"], b["start_col"] = p.sp_start_row, p.sp_start_col
+            want_cl = p.sp_have_cost_list
         else:
+            want_cl = p.want_cost_list
             b["col_min"], b["col_max"], b["row_min"], b["row_max"] = (p.col_min, p.col_max,
                                                                       p.row_min, p.row_max)
             b["start_row"], b["start_col"] = p.start_row, p.start_col
         b["ref_mv_row"], b["ref_mv_col"] = p.ref_mv_row, p.ref_mv_col
         b["bw"], b["bh"] = p.bw, p.bh
-        b["search_method"], b["step_param"] = p.search_method, p.step_param
+        b["search_method"], b["step_param"] = (p.sp_tree if subpel else p.search_method), p.step_param
         b["flags"] = (p.run_mesh_search * b200av1.ME_RUN_MESH | p.prune_mesh_search * b200av1.ME_PRUNE_MESH |
                       p.fine_search_interval * b200av1.ME_FINE_INTERVAL |
                       p.use_skip_sad * b200av1.ME_SKIP_SAD | p.allow_hp * b200av1.ME_ALLOW_HP |
-                      p.want_cost_list * b200av1.ME_COST_LIST)
+                      want_cl * b200av1.ME_COST_LIST)
         b["mv_cost_type"] = p.mv_cost_type
         b["mesh_mv_diff_threshold"] = p.mesh_search_mv_diff_threshold
         b["subpel"] = p.forced_stop | (p.iters_per_step << 2) | (p.subpel_search_type << 4)
@@ -68,6 +70,10 @@ def me_launch(ctx, cur, refb, params, tables_dev, subpel, window_bytes):
     l.mvjcost, l.mvcost[0], l.mvcost[1] = tables_dev
     l.results = d_res.ptr
     l.window_bytes = window_bytes
+    if subpel and any(p.sp_have_cost_list for p in params):
+        cls = np.array([list(p.sp_cost_list) for p in params], np.int32)
+        d_cls = b200av1.to_device(ctx, cls)
+        l.cost_lists, l.cost_list_stride = d_cls.ptr, 5
     fn = b200av1.lib().b200_me_subpel_launch if subpel else b200av1.lib().b200_me_fullpel_launch
     b200av1.check(fn(ctx.h, C.byref(l), None))
     return b200av1.to_host(ctx, d_res, b200av1.MERESULT_DTYPE, n)
@@ -245,3 +251,97 @@ def test_pattern_search_methods(ctx, bd):
                     assert tuple(int(v) for v in g["cost_list"]) == tuple(e.cost_list), tag
                 if p.want_second_best:
                     assert (int(g["second_row"]), int(g["second_col"])) == (e.second_row, e.second_col), tag
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+@pytest.mark.parametrize("tree", [1, 2])
+def test_subpel_pruned_batch_vs_oracle(ctx, bd, tree):
+    """av1_find_best_sub_pixel_tree_pruned / _pruned_more through b200_me_subpel_launch
+    (search_method = B200_SUBPEL_TREE_PRUNED / _PRUNED_MORE, cost lists in device memory)."""
+    O = H.oracle()
+    rng = np.random.default_rng(900 + bd + 7 * tree)
+    tables = H.make_mv_cost_tables(2)
+    keep, tdev = upload_tables(ctx, tables)
+    for trial in range(3):
+        cur, refb = M.make_frames(rng, 256, 192, bd, flat=(trial % 3 == 2))
+        params = []
+        for (bw, bh) in M.SUBPEL_SIZES:
+            for rep in range(8):
+                p = M.random_subpel_params(rng, cur, refb, bw, bh, bd, tables, rep % 4)
+                p.sp_tree = tree
+                params.append(M.random_cost_list(rng, p))
+        got = me_launch(ctx, cur, refb, params, tdev, True, 0)
+        for i, p in enumerate(params):
+            e = H.MeResult()
+            O.av1o_find_best_sub_pixel_tree_pruned(C.byref(p), C.byref(e))
+            g = got[i]
+            assert (int(g["best_row"]), int(g["best_col"]), int(g["ret"]), int(g["distortion"]),
+                    int(g["sse"])) == e.key(True), (trial, i, p.bw, p.bh, tree, p.forced_stop,
+                                                    p.iters_per_step, p.sp_have_cost_list,
+                                                    list(p.sp_cost_list))
+
+
+def test_fullpel_cost_list_chains_into_pruned_subpel(ctx):
+    """the full-pel launch's results[].cost_list feeds the pruned sub-pel launch in place
+    (cost_lists = &results[0].cost_list, stride 10 ints), like av1_single_motion_search does
+    with its cost_list array (motion_search_facade.c:120-494)."""
+    import b200av1
+    O = H.oracle()
+    rng = np.random.default_rng(951)
+    tables = H.make_mv_cost_tables(3)
+    keep, tdev = upload_tables(ctx, tables)
+    cur, refb = M.make_frames(rng, 256, 192, 8)
+    params = []
+    for (bw, bh) in ((32, 32), (16, 16), (64, 64)):
+        for _ in range(10):
+            p = M.random_fullpel_params(rng, cur, refb, bw, bh, 8, tables)
+            p.search_method, p.run_mesh_search, p.use_skip_sad = 0, 0, 0
+            p.want_cost_list = 1
+            params.append(p)
+    got = me_launch(ctx, cur, refb, params, tdev, False, 150 * 1024)
+    sub = []
+    for i, p in enumerate(params):
+        e = H.MeResult()
+        O.av1o_full_pixel_search(C.byref(p), C.byref(e))
+        assert tuple(int(v) for v in got[i]["cost_list"]) == tuple(e.cost_list)
+        p.sp_tree, p.sp_have_cost_list = 1 + i % 2, 1
+        for j in range(5):
+            p.sp_cost_list[j] = e.cost_list[j]
+        p.subpel_search_type, p.allow_hp, p.forced_stop, p.iters_per_step = 0, 1, 0, 2
+        p.sp_start_row, p.sp_start_col = e.best_row * 8, e.best_col * 8
+        p.sp_row_min, p.sp_row_max = p.row_min * 8, p.row_max * 8
+        p.sp_col_min, p.sp_col_max = p.col_min * 8, p.col_max * 8
+        sub.append(p)
+    got2 = me_launch(ctx, cur, refb, sub, tdev, True, 0)
+    for i, p in enumerate(sub):
+        e = H.MeResult()
+        O.av1o_find_best_sub_pixel_tree_pruned(C.byref(p), C.byref(e))
+        g = got2[i]
+        assert (int(g["best_row"]), int(g["best_col"]), int(g["ret"]), int(g["distortion"]),
+                int(g["sse"])) == e.key(True), (i, p.bw, p.sp_tree)
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+def test_refining_search_8p_batch_vs_oracle(ctx, bd):
+    """av1_refining_search_8p_c through b200_me_fullpel_launch (search_method = B200_ME_REFINE_8P)"""
+    import b200av1
+    O = H.oracle()
+    rng = np.random.default_rng(970 + bd)
+    tables = H.make_mv_cost_tables(4)
+    keep, tdev = upload_tables(ctx, tables)
+    for trial in range(3):
+        cur, refb = M.make_frames(rng, 256, 192, bd, flat=(trial % 3 == 2))
+        params = [M.random_fullpel_params(rng, cur, refb, bw, bh, bd, tables)
+                  for (bw, bh) in M.FULLPEL_SIZES for _ in range(5)]
+        exp = []
+        for p in params:
+            e = H.MeResult()
+            O.av1o_refining_search_8p(C.byref(p), C.byref(e))
+            exp.append(e)
+            p.search_method = b200av1.ME_REFINE_8P
+        for window in (150 * 1024, 0):
+            got = me_launch(ctx, cur, refb, params, tdev, False, window)
+            for i, (p, e) in enumerate(zip(params, exp)):
+                g = got[i]
+                assert (int(g["best_row"]), int(g["best_col"]), int(g["ret"])) == \
+                    (e.best_row, e.best_col, e.ret), (trial, i, p.bw, p.bh, p.use_skip_sad, window)

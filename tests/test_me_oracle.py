@@ -84,3 +84,39 @@ def test_pattern_search_vs_reference(bd):
                                 p.mv_cost_type, a, b)
                 n += 1
     assert n == 6 * len(M.FULLPEL_SIZES) * len(PATTERN_METHODS)
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+@pytest.mark.parametrize("tree", [1, 2])
+def test_sub_pixel_tree_pruned_vs_reference(bd, tree):
+    """av1_find_best_sub_pixel_tree_pruned (mcomp.c:2992) / _pruned_more (:2907): with no
+    cost list, an unusable one (INT_MAX entry), a well-behaved bowl and an arbitrary one."""
+    O, R = H.oracle(), H.ref()
+    rng = np.random.default_rng(600 + bd + 7 * tree)
+    tables = H.make_mv_cost_tables(3)
+    for trial in range(6):
+        cur, refb = M.make_frames(rng, 256, 192, bd, flat=(trial % 3 == 2))
+        for (bw, bh) in M.SUBPEL_SIZES:
+            for rep in range(4):
+                p = M.random_subpel_params(rng, cur, refb, bw, bh, bd, tables, rep)
+                p.sp_tree = tree
+                M.random_cost_list(rng, p)
+                a, b = run_both(O.av1o_find_best_sub_pixel_tree_pruned,
+                                R.refshim_find_best_sub_pixel_tree_pruned, p, subpel=True)
+                assert a == b, (trial, bw, bh, tree, p.allow_hp, p.forced_stop, p.iters_per_step,
+                                p.sp_have_cost_list, list(p.sp_cost_list), a, b)
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+def test_refining_search_8p_vs_reference(bd):
+    """av1_refining_search_8p_c (mcomp.c:1683), single reference"""
+    O, R = H.oracle(), H.ref()
+    rng = np.random.default_rng(700 + bd)
+    tables = H.make_mv_cost_tables(4)
+    for trial in range(6):
+        cur, refb = M.make_frames(rng, 256, 192, bd, flat=(trial % 3 == 2))
+        for (bw, bh) in M.FULLPEL_SIZES:
+            for rep in range(3):
+                p = M.random_fullpel_params(rng, cur, refb, bw, bh, bd, tables)
+                a, b = run_both(O.av1o_refining_search_8p, R.refshim_refining_search_8p, p)
+                assert a == b, (trial, bw, bh, p.use_skip_sad, p.mv_cost_type, a, b)
