@@ -55,4 +55,9 @@ int txq_launch(b200_ctx *ctx, const B200TxqLaunch &l, cudaStream_t s);
 int blockops_init_device(b200_ctx *ctx);
 int me_init_device(b200_ctx *ctx);
 int scratch_reserve(b200_ctx *ctx, size_t bytes);
+// hadamard.cu: single-call helpers behind the drop-in tier
+int int_pro_launch(b200_ctx *ctx, short *out, const unsigned char *ref, int ref_stride, int width,
+                   int height, int norm, int col, cudaStream_t s);
+int vector_var_launch(b200_ctx *ctx, const short *ref, const short *src, int bwl, int *out, cudaStream_t s);
+int satd_launch(b200_ctx *ctx, const void *coeff, int lp, int length, int *out, cudaStream_t s);
 }  // namespace b200

@@ -595,3 +595,184 @@ void aom_highbd_upsampled_pred_b200(void *xd, const void *cm, int mi_row, int mi
 }
 
 }  // extern "C"
+
+
+// ------------------------------------------- Hadamard / SATD / averages (avg.c) ----
+namespace {
+
+// one n x n Hadamard (or `count` side-by-side 8x8 LP blocks) of a host residual
+void hadamard_one(int n, int kind, const int16_t *src_diff, ptrdiff_t stride, void *coeff, int count = 1) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  b200_ctx *c = ctx0();
+  const size_t esz = kind == B200_HAD_LP ? 2 : 4, nn = (size_t)n * n;
+  Arena a(c, nn * count * (2 + esz) + 4096);
+  int16_t *d_src = a.take<int16_t>(nn * count);
+  char *d_out = a.take<char>(nn * count * esz);
+  B200HadBlock *d_blk = a.take<B200HadBlock>(count);
+  B200HadBlock blk[2];
+  cudaStream_t s = c->stream;
+  const int w = n * count;  // the blocks sit side by side in the caller's buffer
+  CKCUDA(cudaMemcpy2DAsync(d_src, (size_t)w * 2, src_diff, (size_t)stride * 2, (size_t)w * 2, n,
+                           cudaMemcpyHostToDevice, s));
+  for (int i = 0; i < count; ++i) {
+    blk[i].src_offset = (uint32_t)(i * n);
+    blk[i].out_offset = (uint32_t)(i * nn);
+    blk[i].stride = w;
+  }
+  CKCUDA(cudaMemcpyAsync(d_blk, blk, sizeof(B200HadBlock) * count, cudaMemcpyHostToDevice, s));
+  B200HadamardLaunch l;
+  memset(&l, 0, sizeof(l));
+  l.n = n;
+  l.kind = kind;
+  l.n_blocks = count;
+  l.blocks = d_blk;
+  l.src = d_src;
+  l.coeff = d_out;
+  CK(b200_hadamard_launch(c, &l, s));
+  CKCUDA(cudaMemcpyAsync(coeff, d_out, nn * count * esz, cudaMemcpyDeviceToHost, s));
+  CKCUDA(cudaStreamSynchronize(s));
+}
+
+int satd_one(const void *coeff, int lp, int length) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  b200_ctx *c = ctx0();
+  const size_t esz = lp ? 2 : 4;
+  Arena a(c, (size_t)length * esz + 1024);
+  char *d_c = a.take<char>((size_t)length * esz);
+  int *d_o = a.take<int>(1);
+  cudaStream_t s = c->stream;
+  CKCUDA(cudaMemcpyAsync(d_c, coeff, (size_t)length * esz, cudaMemcpyHostToDevice, s));
+  CK(satd_launch(c, d_c, lp, length, d_o, s));
+  int r = 0;
+  CKCUDA(cudaMemcpyAsync(&r, d_o, sizeof(r), cudaMemcpyDeviceToHost, s));
+  CKCUDA(cudaStreamSynchronize(s));
+  return r;
+}
+
+// `count` n x n blocks at (x, y) pixel offsets inside one w x h host window
+void avg_run(int op, int highbd, const uint8_t *a8, int a_stride, const uint8_t *b8, int b_stride,
+             int w, int h, int count, const int (*xy)[2], int (*out)[2]) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  b200_ctx *c = ctx0();
+  const size_t px = highbd ? 2 : 1;
+  Arena ar(c, (size_t)w * h * px * 2 + 4096);
+  char *d_a = ar.take<char>((size_t)w * h * px);
+  char *d_b = b8 ? ar.take<char>((size_t)w * h * px) : nullptr;
+  B200AvgBlock *d_blk = ar.take<B200AvgBlock>(count);
+  int32_t *d_out = ar.take<int32_t>(2 * count);
+  cudaStream_t s = c->stream;
+  CKCUDA(cudaMemcpy2DAsync(d_a, w * px, unbyte(a8, highbd), a_stride * px, w * px, h,
+                           cudaMemcpyHostToDevice, s));
+  if (b8)
+    CKCUDA(cudaMemcpy2DAsync(d_b, w * px, unbyte(b8, highbd), b_stride * px, w * px, h,
+                             cudaMemcpyHostToDevice, s));
+  B200AvgBlock blk[4];
+  for (int i = 0; i < count; ++i) {
+    blk[i].a_offset = blk[i].b_offset = (uint32_t)(xy[i][1] * w + xy[i][0]);
+    blk[i].a_stride = blk[i].b_stride = w;
+  }
+  CKCUDA(cudaMemcpyAsync(d_blk, blk, sizeof(B200AvgBlock) * count, cudaMemcpyHostToDevice, s));
+  B200AvgLaunch l;
+  memset(&l, 0, sizeof(l));
+  l.op = op;
+  l.highbd = highbd;
+  l.n_blocks = count;
+  l.blocks = d_blk;
+  l.a = d_a;
+  l.b = d_b;
+  l.out = d_out;
+  CK(b200_avg_launch(c, &l, s));
+  CKCUDA(cudaMemcpyAsync(out, d_out, sizeof(int32_t) * 2 * count, cudaMemcpyDeviceToHost, s));
+  CKCUDA(cudaStreamSynchronize(s));
+}
+
+unsigned avg_single(int op, int highbd, const uint8_t *s8, int p) {
+  const int n = op == B200_AVG_4X4 ? 4 : 8;
+  const int xy[1][2] = { { 0, 0 } };
+  int out[1][2];
+  avg_run(op, highbd, s8, p, nullptr, 0, n, n, 1, xy, out);
+  return (unsigned)out[0][0];
+}
+
+void int_pro_one(int16_t *buf, const uint8_t *ref, int ref_stride, int width, int height, int norm,
+                 int col) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  b200_ctx *c = ctx0();
+  const int n = col ? height : width;
+  Arena a(c, (size_t)width * height + (size_t)n * 2 + 1024);
+  unsigned char *d_ref = a.take<unsigned char>((size_t)width * height);
+  short *d_out = a.take<short>(n);
+  cudaStream_t s = c->stream;
+  CKCUDA(cudaMemcpy2DAsync(d_ref, width, ref, ref_stride, width, height, cudaMemcpyHostToDevice, s));
+  CK(int_pro_launch(c, d_out, d_ref, width, width, height, norm, col, s));
+  CKCUDA(cudaMemcpyAsync(buf, d_out, (size_t)n * 2, cudaMemcpyDeviceToHost, s));
+  CKCUDA(cudaStreamSynchronize(s));
+}
+
+}  // namespace
+
+extern "C" {
+void aom_hadamard_4x4_b200(const int16_t *s, ptrdiff_t st, b200_tran_low_t *c) { hadamard_one(4, B200_HAD_LOWBD, s, st, c); }
+void aom_hadamard_8x8_b200(const int16_t *s, ptrdiff_t st, b200_tran_low_t *c) { hadamard_one(8, B200_HAD_LOWBD, s, st, c); }
+void aom_hadamard_16x16_b200(const int16_t *s, ptrdiff_t st, b200_tran_low_t *c) { hadamard_one(16, B200_HAD_LOWBD, s, st, c); }
+void aom_hadamard_32x32_b200(const int16_t *s, ptrdiff_t st, b200_tran_low_t *c) { hadamard_one(32, B200_HAD_LOWBD, s, st, c); }
+void aom_hadamard_lp_8x8_b200(const int16_t *s, ptrdiff_t st, int16_t *c) { hadamard_one(8, B200_HAD_LP, s, st, c); }
+void aom_hadamard_lp_16x16_b200(const int16_t *s, ptrdiff_t st, int16_t *c) { hadamard_one(16, B200_HAD_LP, s, st, c); }
+void aom_hadamard_lp_8x8_dual_b200(const int16_t *s, ptrdiff_t st, int16_t *c) { hadamard_one(8, B200_HAD_LP, s, st, c, 2); }
+void aom_highbd_hadamard_8x8_b200(const int16_t *s, ptrdiff_t st, b200_tran_low_t *c) { hadamard_one(8, B200_HAD_HIGHBD, s, st, c); }
+void aom_highbd_hadamard_16x16_b200(const int16_t *s, ptrdiff_t st, b200_tran_low_t *c) { hadamard_one(16, B200_HAD_HIGHBD, s, st, c); }
+void aom_highbd_hadamard_32x32_b200(const int16_t *s, ptrdiff_t st, b200_tran_low_t *c) { hadamard_one(32, B200_HAD_HIGHBD, s, st, c); }
+int aom_satd_b200(const b200_tran_low_t *coeff, int length) { return satd_one(coeff, 0, length); }
+int aom_satd_lp_b200(const int16_t *coeff, int length) { return satd_one(coeff, 1, length); }
+void av1_fwht4x4_b200(const int16_t *input, b200_tran_low_t *output, int stride) {
+  hadamard_one(4, B200_HAD_WHT, input, stride, output);
+}
+unsigned int aom_avg_4x4_b200(const uint8_t *s, int p) { return avg_single(B200_AVG_4X4, 0, s, p); }
+unsigned int aom_avg_8x8_b200(const uint8_t *s, int p) { return avg_single(B200_AVG_8X8, 0, s, p); }
+unsigned int aom_highbd_avg_4x4_b200(const uint8_t *s8, int p) { return avg_single(B200_AVG_4X4, 1, s8, p); }
+unsigned int aom_highbd_avg_8x8_b200(const uint8_t *s8, int p) { return avg_single(B200_AVG_8X8, 1, s8, p); }
+void aom_avg_8x8_quad_b200(const uint8_t *s, int p, int x16_idx, int y16_idx, int *avg) {
+  const int xy[4][2] = { { 0, 0 }, { 8, 0 }, { 0, 8 }, { 8, 8 } };
+  int out[4][2];
+  avg_run(B200_AVG_8X8, 0, s + (size_t)y16_idx * p + x16_idx, p, nullptr, 0, 16, 16, 4, xy, out);
+  for (int k = 0; k < 4; ++k) avg[k] = out[k][0];
+}
+void aom_minmax_8x8_b200(const uint8_t *s, int p, const uint8_t *d, int dp, int *min, int *max) {
+  const int xy[1][2] = { { 0, 0 } };
+  int out[1][2];
+  avg_run(B200_MINMAX_8X8, 0, s, p, d, dp, 8, 8, 1, xy, out);
+  *min = out[0][0];
+  *max = out[0][1];
+}
+void aom_highbd_minmax_8x8_b200(const uint8_t *s8, int p, const uint8_t *d8, int dp, int *min, int *max) {
+  const int xy[1][2] = { { 0, 0 } };
+  int out[1][2];
+  avg_run(B200_MINMAX_8X8, 1, s8, p, d8, dp, 8, 8, 1, xy, out);
+  *min = out[0][0];
+  *max = out[0][1];
+}
+void aom_int_pro_row_b200(int16_t *hbuf, const uint8_t *ref, const int ref_stride, const int width,
+                          const int height, int norm_factor) {
+  int_pro_one(hbuf, ref, ref_stride, width, height, norm_factor, 0);
+}
+void aom_int_pro_col_b200(int16_t *vbuf, const uint8_t *ref, const int ref_stride, const int width,
+                          const int height, int norm_factor) {
+  int_pro_one(vbuf, ref, ref_stride, width, height, norm_factor, 1);
+}
+int aom_vector_var_b200(const int16_t *ref, const int16_t *src, int bwl) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  b200_ctx *c = ctx0();
+  const int width = 4 << bwl;
+  Arena a(c, (size_t)width * 4 + 1024);
+  short *d_r = a.take<short>(width), *d_s = a.take<short>(width);
+  int *d_o = a.take<int>(1);
+  cudaStream_t s = c->stream;
+  CKCUDA(cudaMemcpyAsync(d_r, ref, (size_t)width * 2, cudaMemcpyHostToDevice, s));
+  CKCUDA(cudaMemcpyAsync(d_s, src, (size_t)width * 2, cudaMemcpyHostToDevice, s));
+  CK(vector_var_launch(c, d_r, d_s, bwl, d_o, s));
+  int r = 0;
+  CKCUDA(cudaMemcpyAsync(&r, d_o, sizeof(r), cudaMemcpyDeviceToHost, s));
+  CKCUDA(cudaStreamSynchronize(s));
+  return r;
+}
+}  // extern "C"

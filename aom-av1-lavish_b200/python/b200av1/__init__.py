@@ -221,3 +221,22 @@ class MeLaunch(C.Structure):
                 ("mvjcost", C.c_void_p), ("mvcost", C.c_void_p * 2), ("results", C.c_void_p),
                 ("window_bytes", C.c_int), ("max_bw", C.c_int), ("max_bh", C.c_int),
                 ("cost_lists", C.c_void_p), ("cost_list_stride", C.c_int)]
+
+
+# ---- Hadamard / SATD / averages (include/b200av1.h) ----
+HAD_LOWBD, HAD_LP, HAD_HIGHBD, HAD_WHT = 0, 1, 2, 3
+AVG_4X4, AVG_8X8, MINMAX_8X8 = 0, 1, 2
+HADBLOCK_DTYPE = np.dtype([("src_offset", "<u4"), ("out_offset", "<u4"), ("stride", "<i4")])
+AVGBLOCK_DTYPE = np.dtype([("a_offset", "<u4"), ("b_offset", "<u4"), ("a_stride", "<i4"),
+                           ("b_stride", "<i4")])
+assert HADBLOCK_DTYPE.itemsize == 12 and AVGBLOCK_DTYPE.itemsize == 16
+
+
+class HadamardLaunch(C.Structure):
+    _fields_ = [("n", C.c_int), ("kind", C.c_int), ("n_blocks", C.c_int), ("blocks", C.c_void_p),
+                ("src", C.c_void_p), ("coeff", C.c_void_p), ("satd", C.c_void_p)]
+
+
+class AvgLaunch(C.Structure):
+    _fields_ = [("op", C.c_int), ("highbd", C.c_int), ("n_blocks", C.c_int), ("blocks", C.c_void_p),
+                ("a", C.c_void_p), ("b", C.c_void_p), ("out", C.c_void_p)]

@@ -287,6 +287,51 @@ typedef struct {
 int b200_upsampled_pred_launch(b200_ctx *ctx, const B200UpsampleLaunch *launch, void *stream);
 
 
+/* ------------------------------------------- Hadamard / SATD / block averages ------ */
+/* aom_dsp/avg.c: the Hadamard transforms tx-search pruning and TPL use for their SATD cost
+ * (tpl_model.c:97-130, tx_search.c prune paths), plus the lossless WHT (hybrid_fwd_txfm.c:24).
+ * One warp per block (a lane per block at 4x4); coeff and satd are both optional so that the
+ * SATD-only use (aom_hadamard_NxN followed by aom_satd, the common case) writes 4 bytes per
+ * block instead of 4 bytes per sample. */
+enum {
+  B200_HAD_LOWBD = 0,  /* aom_hadamard_{4x4,8x8,16x16,32x32}_c (avg.c:115,177,247,318): int32 out */
+  B200_HAD_LP = 1,     /* aom_hadamard_lp_{8x8,16x16}_c (avg.c:207,289): int16 out */
+  B200_HAD_HIGHBD = 2, /* aom_highbd_hadamard_{8x8,16x16,32x32}_c (avg.c:416,442,474): int32 out */
+  B200_HAD_WHT = 3     /* av1_fwht4x4_c (hybrid_fwd_txfm.c:24), n = 4: int32 out */
+};
+typedef struct {
+  uint32_t src_offset; /* int16 elements from `src` to the block's first residual */
+  uint32_t out_offset; /* elements from `coeff` to the block's n*n coefficients */
+  int32_t stride;      /* residual row stride, elements */
+} B200HadBlock; /* 12 bytes */
+typedef struct {
+  int n;    /* 4, 8, 16 or 32 */
+  int kind; /* B200_HAD_* */
+  int n_blocks;
+  const B200HadBlock *blocks; /* device */
+  const int16_t *src;         /* device */
+  void *coeff;                /* device, int32 (int16 for B200_HAD_LP), or NULL */
+  int32_t *satd;              /* device, aom_satd / aom_satd_lp of block i, or NULL */
+} B200HadamardLaunch;
+int b200_hadamard_launch(b200_ctx *ctx, const B200HadamardLaunch *launch, void *stream);
+
+enum {
+  B200_AVG_4X4 = 0,    /* aom_avg_4x4 / aom_highbd_avg_4x4 (avg.c:32,74)        out0 = average */
+  B200_AVG_8X8 = 1,    /* aom_avg_8x8 / aom_highbd_avg_8x8 (avg.c:42,63)        out0 = average */
+  B200_MINMAX_8X8 = 2  /* aom_minmax_8x8 / highbd (avg.c:18,85), b = second plane   out0 = min, out1 = max */
+};
+typedef struct {
+  uint32_t a_offset, b_offset; /* pixels from the plane bases */
+  int32_t a_stride, b_stride;  /* pixels */
+} B200AvgBlock; /* 16 bytes */
+typedef struct {
+  int op, highbd, n_blocks;
+  const B200AvgBlock *blocks; /* device */
+  const void *a, *b;          /* device planes (b only for B200_MINMAX_8X8) */
+  int32_t *out;               /* device, 2 ints per block */
+} B200AvgLaunch;
+int b200_avg_launch(b200_ctx *ctx, const B200AvgLaunch *launch, void *stream);
+
 /* ------------------------------------------------------ motion search batch ------ */
 /* One descriptor = one single-reference translational search of one block: the fields
  * of FULLPEL_MOTION_SEARCH_PARAMS / SUBPEL_MOTION_SEARCH_PARAMS (av1/encoder/mcomp.h:

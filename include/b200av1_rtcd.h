@@ -213,6 +213,34 @@ void aom_highbd_upsampled_pred_b200(void *xd, const void *cm, int mi_row, int mi
                                     const void *mv, uint8_t *comp_pred8, int width, int height,
                                     int subpel_x_q3, int subpel_y_q3, const uint8_t *ref8,
                                     int ref_stride, int bd, int subpel_search);
+/* ---- Hadamard / SATD / averages: aom_dsp_rtcd_defs.pl:1209-1279 (aom_dsp/avg.c), and the
+ * lossless WHT av1_rtcd_defs.pl:351 (hybrid_fwd_txfm.c:24) ---- */
+void aom_hadamard_4x4_b200(const int16_t *src_diff, ptrdiff_t src_stride, b200_tran_low_t *coeff);
+void aom_hadamard_8x8_b200(const int16_t *src_diff, ptrdiff_t src_stride, b200_tran_low_t *coeff);
+void aom_hadamard_16x16_b200(const int16_t *src_diff, ptrdiff_t src_stride, b200_tran_low_t *coeff);
+void aom_hadamard_32x32_b200(const int16_t *src_diff, ptrdiff_t src_stride, b200_tran_low_t *coeff);
+void aom_hadamard_lp_8x8_b200(const int16_t *src_diff, ptrdiff_t src_stride, int16_t *coeff);
+void aom_hadamard_lp_16x16_b200(const int16_t *src_diff, ptrdiff_t src_stride, int16_t *coeff);
+void aom_hadamard_lp_8x8_dual_b200(const int16_t *src_diff, ptrdiff_t src_stride, int16_t *coeff);
+void aom_highbd_hadamard_8x8_b200(const int16_t *src_diff, ptrdiff_t src_stride, b200_tran_low_t *coeff);
+void aom_highbd_hadamard_16x16_b200(const int16_t *src_diff, ptrdiff_t src_stride, b200_tran_low_t *coeff);
+void aom_highbd_hadamard_32x32_b200(const int16_t *src_diff, ptrdiff_t src_stride, b200_tran_low_t *coeff);
+int aom_satd_b200(const b200_tran_low_t *coeff, int length);
+int aom_satd_lp_b200(const int16_t *coeff, int length);
+void av1_fwht4x4_b200(const int16_t *input, b200_tran_low_t *output, int stride);
+unsigned int aom_avg_4x4_b200(const uint8_t *s, int p);
+unsigned int aom_avg_8x8_b200(const uint8_t *s, int p);
+void aom_avg_8x8_quad_b200(const uint8_t *s, int p, int x16_idx, int y16_idx, int *avg);
+void aom_minmax_8x8_b200(const uint8_t *s, int p, const uint8_t *d, int dp, int *min, int *max);
+unsigned int aom_highbd_avg_4x4_b200(const uint8_t *s8, int p);
+unsigned int aom_highbd_avg_8x8_b200(const uint8_t *s8, int p);
+void aom_highbd_minmax_8x8_b200(const uint8_t *s8, int p, const uint8_t *d8, int dp, int *min,
+                                int *max);
+void aom_int_pro_row_b200(int16_t *hbuf, const uint8_t *ref, const int ref_stride, const int width,
+                          const int height, int norm_factor);
+void aom_int_pro_col_b200(int16_t *vbuf, const uint8_t *ref, const int ref_stride, const int width,
+                          const int height, int norm_factor);
+int aom_vector_var_b200(const int16_t *ref, const int16_t *src, int bwl);
 
 #ifdef __cplusplus
 }

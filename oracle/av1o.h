@@ -53,6 +53,20 @@ void av1o_fwd_txfm2d(const int16_t *input, int32_t *output, int stride, int tx_s
 void av1o_fwht4x4(const int16_t *input, int32_t *output, int stride);
 void av1o_round_shift_array(int32_t *arr, int size, int bit);
 
+/* ---- Hadamard / SATD / averages (av1o_avg.c; aom_dsp/avg.c) -------------------- */
+/* n x n Hadamard; kind 0 aom_hadamard_NxN_c (n 4..32), 1 aom_hadamard_lp_NxN_c (n 8, 16; int16
+ * values widened), 2 aom_highbd_hadamard_NxN_c (n 8..32) */
+void av1o_hadamard(const int16_t *src, ptrdiff_t stride, int32_t *coeff, int n, int kind);
+void av1o_hadamard_4x4(const int16_t *src, ptrdiff_t stride, int32_t *coeff);
+int av1o_satd(const int32_t *coeff, int length);
+unsigned av1o_avg(const void *s, int stride, int n, int highbd);
+void av1o_minmax_8x8(const void *s, int p, const void *d, int dp, int highbd, int *mn, int *mx);
+void av1o_int_pro_row(int16_t *hbuf, const uint8_t *ref, int ref_stride, int width, int height,
+                      int norm_factor);
+void av1o_int_pro_col(int16_t *vbuf, const uint8_t *ref, int ref_stride, int width, int height,
+                      int norm_factor);
+int av1o_vector_var(const int16_t *ref, const int16_t *src, int bwl);
+
 /* ---- scan tables (av1o_scan.c) ----------------------------------------------- */
 /* scan / iscan of av1_scan_orders[tx_size][tx_type] (scan.c:1666); n = max_eob */
 const int16_t *av1o_scan(int tx_size, int tx_type);
