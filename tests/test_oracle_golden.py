@@ -47,3 +47,67 @@ def test_pixel_golden():
                O.av1o_sub_pixel_variance(ptr(a, u8p), 144, 3, 5, ptr(b, u8p), 144, w, h, C.byref(sse2)), 0]
         got[2], got[4] = sse.value, sse2.value
         assert got == [int(v) for v in exp], (w, h)
+
+
+# ---- motion search + Hadamard golden vectors (tests/golden/gen_golden_me.py) ----
+GM = np.load(os.path.join(H.ROOT, "tests", "golden", "me_avg_golden.npz"))
+ME_FIELDS = [n for n, _ in H.MeParams._fields_ if n not in ("src", "ref", "mvjcost", "mvcost0", "mvcost1")]
+
+
+def _unpack(row, cur, refb, tables, border):
+    p = H.MeParams()
+    it = iter(int(v) for v in row)
+    for n in ME_FIELDS:
+        cur_v = getattr(p, n)
+        if hasattr(cur_v, "__len__"):
+            for i in range(len(cur_v)):
+                cur_v[i] = next(it)
+        else:
+            setattr(p, n, next(it))
+    bx, by = next(it), next(it)
+    esz = cur.itemsize
+    p.src = cur.ctypes.data + (by * cur.shape[1] + bx) * esz
+    p.ref = refb.ctypes.data + ((by + border) * refb.shape[1] + bx + border) * esz
+    p.mvjcost, p.mvcost0, p.mvcost1 = H.mv_cost_ptrs(*tables)
+    return p
+
+
+def test_motion_search_golden():
+    """full-pel (11 methods), 8-point refinement, sub-pel tree / pruned / pruned_more: the
+    oracle reproduces the results the reference build produced for the committed frames"""
+    import me_common as M
+    O = H.oracle()
+    tables = tuple(np.ascontiguousarray(GM[k]) for k in ("mv_joint", "mv_t0", "mv_t1"))
+    fns = [O.av1o_full_pixel_search, O.av1o_refining_search_8p, O.av1o_find_best_sub_pixel_tree,
+           O.av1o_find_best_sub_pixel_tree_pruned, O.av1o_find_best_sub_pixel_tree_pruned]
+    n = 0
+    for bd in (8, 10):
+        cur, refb = np.ascontiguousarray(GM["cur_%d" % bd]), np.ascontiguousarray(GM["ref_%d" % bd])
+        for row, exp, kind in zip(GM["me_params_%d" % bd], GM["me_results_%d" % bd], GM["me_kinds_%d" % bd]):
+            p = _unpack(row, cur, refb, tables, M.BORDER)
+            r = H.MeResult()
+            fns[int(kind)](C.byref(p), C.byref(r))
+            exp = [int(v) for v in exp]
+            if kind >= 2:
+                got = [r.best_row, r.best_col, r.ret, r.distortion, r.sse]
+                assert got == [exp[0], exp[1], exp[9], exp[10], exp[11]], (bd, n, int(kind))
+            else:
+                got = [r.best_row, r.best_col, r.ret]
+                assert got == [exp[0], exp[1], exp[9]], (bd, n, int(kind))
+                if kind == 0 and p.want_second_best:
+                    assert [r.second_row, r.second_col] == exp[2:4], (bd, n)
+                if kind == 0 and p.want_cost_list:
+                    assert list(r.cost_list) == exp[4:9], (bd, n)
+            n += 1
+    assert n == 2 * 6 * (11 + 1 + 12)
+
+
+def test_hadamard_golden():
+    O = H.oracle()
+    for (n, kind) in ((4, 0), (8, 0), (16, 0), (32, 0), (8, 1), (16, 1), (8, 2), (16, 2), (32, 2)):
+        src, exp = GM["had_in_%d_%d" % (n, kind)], GM["had_out_%d_%d" % (n, kind)]
+        for i in range(2):
+            s = np.ascontiguousarray(src[i])
+            got = np.zeros(n * n, np.int32)
+            O.av1o_hadamard(ptr(s, i16p), C.c_ssize_t(n), ptr(got, i32p), n, kind)
+            assert np.array_equal(got, exp[i]), (n, kind, i)
