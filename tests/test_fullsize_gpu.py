@@ -154,3 +154,58 @@ def test_config2_1080p_8bit_full_plane_properties(ctx, ts):
     blocks, preds, outs, kinds = run_plane(ctx, src, pred, stride, pstride, w, h, ts, bd, rows, qrows, 2100)
     check_properties(ts, bd, blocks, outs, rows)
     compare_with_oracle(ts, bd, blocks, preds, outs, rows, kinds, src, pred, 1500, 2200 + ts)
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+def test_config3_1080p_motion_search_full_frame(ctx, bd):
+    """BASELINE config[2] at full size: every 64x64 superblock of a 1080p frame (480) against
+    two references, +-64, NSTEP + the 4-stage good-quality mesh, L1 (HD) cost, then the 8-tap
+    sub-pel tree started from the full-pel winner.  8-bit: all 960 searches against the oracle;
+    10-bit (the config[4] variant, highbd SAD >> 2): every third one."""
+    import ctypes as C
+    import b200av1
+    import me_common as M
+    from test_me_gpu import me_launch, upload_tables
+    O = H.oracle()
+    rng = np.random.default_rng(3000 + bd)
+    tables = H.make_mv_cost_tables(3)
+    keep, tdev = upload_tables(ctx, tables)
+    w, h = 1920, 1080
+    cur = synth.smooth_frame(rng, w, h, bd)
+    step = 1 if bd == 8 else 3
+    for ref_id in range(2):
+        dy, dx = int(rng.integers(-20, 21)), int(rng.integers(-20, 21))
+        ref = np.roll(cur, (dy, dx), (0, 1)).astype(np.int32) + np.rint(rng.normal(0, 2, cur.shape)).astype(np.int32)
+        refb = H.bordered(np.clip(ref, 0, (1 << bd) - 1).astype(cur.dtype), M.BORDER)
+        params = []
+        for by in range(0, h - 63, 64):
+            for bx in range(0, w - 63, 64):
+                p = M.base_params(cur, refb, bx, by, 64, 64, bd, tables)
+                p.col_min, p.col_max, p.row_min, p.row_max = -64, 64, -64, 64
+                p.search_method, p.step_param = 0, O.av1o_init_search_range(64)
+                p.run_mesh_search, p.mv_cost_type = 1, 3
+                p.want_cost_list = p.want_second_best = 1
+                params.append(p)
+        assert len(params) == 480
+        got = me_launch(ctx, cur, refb, params, tdev, False, 48 * 1024)
+        sub, exp_full = [], {}
+        for i, p in enumerate(params):
+            if i % step == 0:
+                e = H.MeResult()
+                O.av1o_full_pixel_search(C.byref(p), C.byref(e))
+                g = got[i]
+                assert (int(g["best_row"]), int(g["best_col"]), int(g["second_row"]), int(g["second_col"]),
+                        tuple(int(v) for v in g["cost_list"]), int(g["ret"])) == e.key(), (bd, ref_id, i)
+            p.subpel_search_type, p.allow_hp, p.forced_stop, p.iters_per_step = 3, 1, 0, 2
+            p.sp_start_row, p.sp_start_col = int(got[i]["best_row"]) * 8, int(got[i]["best_col"]) * 8
+            p.sp_row_min, p.sp_row_max, p.sp_col_min, p.sp_col_max = -512, 512, -512, 512
+            sub.append(p)
+        got2 = me_launch(ctx, cur, refb, sub, tdev, True, 0)
+        for i, p in enumerate(sub):
+            if i % step:
+                continue
+            e = H.MeResult()
+            O.av1o_find_best_sub_pixel_tree(C.byref(p), C.byref(e))
+            g = got2[i]
+            assert (int(g["best_row"]), int(g["best_col"]), int(g["ret"]), int(g["distortion"]),
+                    int(g["sse"])) == e.key(True), (bd, ref_id, i)
