@@ -325,15 +325,130 @@ def bench_me(ctx, dev, stream, steps, warmup, seed, frame_id, n_frames=8):
 
 
 
+def bench_hbd4k(ctx, dev, stream, steps, warmup, seed, n_frames=3):
+    """BASELINE configs[3]: 10-bit fused subtract + fwd txfm + av1_highbd_quantize_fp +
+    av1_highbd_block_error over all 19 TX sizes of `n_frames` synthetic 4K 4:2:0 frames
+    (uint16 source and prediction planes resident in HBM, 150 MB > L2)."""
+    import torch
+    import b200av1
+    planes = [(3840, 2160), (1920, 1080), (1920, 1080)]
+    frame_elems = sum(w * h for w, h in planes)
+    rng = np.random.default_rng([seed, 4001])
+    src = np.zeros((n_frames, frame_elems), np.uint16)
+    pred = np.zeros((n_frames, frame_elems), np.uint16)
+    for f in range(n_frames):
+        o = 0
+        for (w, h) in planes:
+            low = rng.integers(100, 900, (h // 8 + 1, w // 8 + 1))
+            img = np.kron(low, np.ones((8, 8), np.int64))[:h, :w] + rng.integers(-8, 9, (h, w))
+            pr = np.roll(img, (1, 1), (0, 1)) + rng.integers(-12, 13, (h, w))
+            src[f, o:o + w * h] = np.clip(img, 0, 1023).reshape(-1)
+            pred[f, o:o + w * h] = np.clip(pr, 0, 1023).reshape(-1)
+            o += w * h
+    d_src = torch.from_numpy(src.reshape(-1).view(np.int16)).to(dev)
+    d_pred = torch.from_numpy(pred.reshape(-1).view(np.int16)).to(dev)
+    qrows = build_qrows(10)
+    d_qrows = torch.from_numpy(qrows.view(np.uint8)).to(dev)
+    n_out = n_frames * frame_elems
+    d_coeff, d_qc, d_dq = (torch.empty(n_out, dtype=torch.int32, device=dev) for _ in range(3))
+    launches, keep, tot_bytes, tot_samples = [], [], 0, 0
+    for ts in range(19):
+        blocks, samples = make_descriptors(ts, n_frames, planes, frame_elems, seed + 4)
+        preds = np.zeros(blocks.size, b200av1.TXPRED_DTYPE)
+        preds["pred_offset"], preds["pred_stride"] = blocks["src_offset"], blocks["src_stride"]
+        d_blocks = torch.from_numpy(blocks.view(np.uint8)).to(dev)
+        d_preds = torch.from_numpy(preds.view(np.uint8)).to(dev)
+        d_eob = torch.zeros(blocks.size, dtype=torch.int16, device=dev)
+        d_dist = torch.zeros(blocks.size * 2, dtype=torch.int64, device=dev)
+        keep += [d_blocks, d_preds, d_eob, d_dist]
+        l = b200av1.TxqLaunch()
+        l.tx_size, l.in_kind, l.q_kind, l.bd = ts, b200av1.IN_PIXELS16, b200av1.Q_FP_HBD, 10
+        l.flags = b200av1.TXQ_STORE_COEFF | b200av1.TXQ_BLOCK_ERROR
+        l.n_blocks = int(blocks.size)
+        l.blocks, l.preds = d_blocks.data_ptr(), d_preds.data_ptr()
+        l.src, l.pred, l.qrows = d_src.data_ptr(), d_pred.data_ptr(), d_qrows.data_ptr()
+        l.coeff, l.qcoeff, l.dqcoeff = d_coeff.data_ptr(), d_qc.data_ptr(), d_dq.data_ptr()
+        l.eob, l.dist = d_eob.data_ptr(), d_dist.data_ptr()
+        launches.append(l)
+        # SURVEY 8d: 2 + 2 B/sample in, 12 B/kept coeff out, 2 B eob + 16 B dist per block
+        tot_bytes += blocks.size * (TX_W[ts] * TX_H[ts] * 4 + max_eob(ts) * 12 + 18)
+        tot_samples += samples
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ms = 0.0
+    for it in range(warmup + steps):
+        ev[0].record(stream)
+        for l in launches:
+            ctx.txq_launch(l, stream.cuda_stream)
+        ev[1].record(stream)
+        torch.cuda.synchronize(dev)
+        if it >= warmup:
+            ms += ev[0].elapsed_time(ev[1])
+    ms /= steps
+    fe4k = 3840 * 2160 * 3 // 2
+    return {"workload": "config[3]: %d synthetic 4K 10-bit 4:2:0 frames, fused subtract + txfm + "
+                        "av1_highbd_quantize_fp + av1_highbd_block_error, all 19 TX sizes" % n_frames,
+            "ms_per_sweep": ms, "fe4k_per_s": tot_samples / fe4k / (ms * 1e-3),
+            "fe1080p_per_s": tot_samples / FE_SAMPLES / (ms * 1e-3),
+            "GBps": tot_bytes / (ms * 1e-3) / 1e9, "bytes_per_sweep": int(tot_bytes),
+            "launches_per_step": 19}
+
+
+def bench_hadamard(ctx, dev, stream, steps, warmup, d_src, n_frames):
+    """Hadamard + SATD over the luma residual of the resident 1080p frames (the TPL /
+    tx-prune cost, aom_dsp/avg.c): coefficient + SATD output, and SATD only."""
+    import torch
+    import b200av1
+    w, h = 1920, 1080
+    frame_elems = FE_SAMPLES
+    out = {}
+    for n in (8, 16, 32):
+        xs, ys = np.arange(w // n) * n, np.arange(h // n) * n
+        offs = (ys[:, None] * w + xs[None, :]).reshape(-1)
+        nb = offs.size * n_frames
+        blocks = np.zeros(nb, b200av1.HADBLOCK_DTYPE)
+        blocks["src_offset"] = (offs[None, :] + (np.arange(n_frames) * frame_elems)[:, None]).reshape(-1)
+        blocks["out_offset"] = np.arange(nb, dtype=np.uint64) * n * n
+        blocks["stride"] = w
+        d_blk = torch.from_numpy(blocks.view(np.uint8)).to(dev)
+        d_coeff = torch.empty(nb * n * n, dtype=torch.int32, device=dev)
+        d_satd = torch.empty(nb, dtype=torch.int32, device=dev)
+        for mode in ("coeff+satd", "satd"):
+            l = b200av1.HadamardLaunch()
+            l.n, l.kind, l.n_blocks = n, b200av1.HAD_LOWBD, nb
+            l.blocks, l.src = d_blk.data_ptr(), d_src.data_ptr()
+            l.coeff = d_coeff.data_ptr() if mode != "satd" else None
+            l.satd = d_satd.data_ptr()
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+            ms = 0.0
+            for it in range(warmup + steps):
+                ev[0].record(stream)
+                b200av1.check(b200av1.lib().b200_hadamard_launch(ctx.h, C.byref(l), C.c_void_p(stream.cuda_stream)))
+                ev[1].record(stream)
+                torch.cuda.synchronize(dev)
+                if it >= warmup:
+                    ms += ev[0].elapsed_time(ev[1])
+            ms /= steps
+            nbytes = nb * (n * n * (6 if mode != "satd" else 2) + 4)
+            out["%dx%d %s" % (n, n, mode)] = {"ms": round(ms, 4), "GBps": round(nbytes / (ms * 1e-3) / 1e9, 1),
+                                              "luma_frames_per_s": round(n_frames / (ms * 1e-3), 1)}
+    return out
+
+
 def build_qrows_product():
     """3 planes x 5 qindexes, all delta_q = 0 (av1_build_quantizer, av1_quantize.c:602)"""
+    return build_qrows(8)
+
+
+def build_qrows(bd):
+    """the product's own b200_build_quantizer_row (no oracle on the b200 arm)"""
     import b200av1
-    import harness as H
-    rows = []
+    rows = np.zeros(3 * len(QINDEXES), b200av1.QROW_DTYPE)
+    row = b200av1.QRow()
     for pl in range(3):
-        for q in QINDEXES:
-            rows.append(b200av1.qrow_from_oracle(H.oracle_qrow(8, q, pl)))
-    return np.array(rows, b200av1.QROW_DTYPE)
+        for j, q in enumerate(QINDEXES):
+            b200av1.check(b200av1.lib().b200_build_quantizer_row(bd, q, 0, 0, 0, C.byref(row)))
+            rows[pl * len(QINDEXES) + j] = np.frombuffer(bytes(row), b200av1.QROW_DTYPE)[0]
+    return rows
 
 
 def main():
@@ -347,6 +462,7 @@ def main():
     ap.add_argument("--force-exact", action="store_true", help="always take the 64-bit half_btf path")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-me", action="store_true", help="skip the motion-search section")
+    ap.add_argument("--no-extras", action="store_true", help="skip the config[3] 4K 10-bit and Hadamard sections")
     ap.add_argument("--sizes", default="", help="comma list of tx sizes (debug)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -549,6 +665,11 @@ def main():
             dist.all_reduce(t_me, op=dist.ReduceOp.MAX)
         me["frames_per_s_all_gpus"] = world * 1e3 / float(t_me.item())
 
+    extras = None
+    if not args.no_extras and world == 1:
+        extras = {"hadamard": bench_hadamard(ctx, dev, stream, max(2, args.steps // 2), 2, d_src, args.frames),
+                  "hbd4k": bench_hbd4k(ctx, dev, stream, max(2, args.steps // 2), 2, seed)}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -586,7 +707,7 @@ def main():
                          "kernel": "txq_kernel<W,H> (19 instances, one launch each per step); "
                                    "algorithmic bytes = 2 B/sample in + 12 B/kept coeff out + 2 B/block",
                          "bytes_per_step": int(total_bytes)},
-            "kernels": kernels, "e2e": e2e, "me": me,
+            "kernels": kernels, "e2e": e2e, "me": me, "extras": extras,
             "step_ms_min_max": [float(min(step_ms)), float(max(step_ms))]}
 
     # ---- cpu_baseline (rank 0, N = 1 only) + full-size parity of frame 0

@@ -90,14 +90,22 @@ const int16_t *b200_iscan(int tx_size, int tx_type);
 
 /* One quantiser row: the [0]=DC / [1]=AC entries of the reference's per-qindex
  * tables (QUANTS / Dequants, av1/encoder/av1_quantize.h:45-84), as the encoder
- * keeps them in MACROBLOCK_PLANE (av1/encoder/block.h:129-167).  The encoder builds
- * them (av1_build_quantizer, av1_quantize.c:602); this library only consumes them. */
+ * keeps them in MACROBLOCK_PLANE (av1/encoder/block.h:129-167).  The encoder may pass its
+ * own (av1_build_quantizer, av1_quantize.c:602) or have b200_build_quantizer_row make them. */
 typedef struct {
   int16_t zbin[2], round[2], quant[2], quant_shift[2]; /* "B" quantiser */
   int16_t round_fp[2], quant_fp[2];                    /* "FP" quantiser */
   int16_t dequant[2];
   int16_t reserved[2];
 } B200QRow; /* 32 bytes */
+/* One row of av1_build_quantizer (av1_quantize.c:602-686): plane deltas as in
+ * av1_dc_quant_QTX(qindex, dc_delta_q, bd) / av1_ac_quant_QTX(qindex, ac_delta_q, bd)
+ * (quant_common.c:193-215; y: (y_dc_delta_q, 0), u: (u_dc_delta_q, u_ac_delta_q), ...);
+ * quant_sharpness is this fork's extra argument.  Host only, no GPU needed. */
+int b200_build_quantizer_row(int bd, int qindex, int dc_delta_q, int ac_delta_q,
+                             int quant_sharpness, B200QRow *row);
+int b200_dc_quant(int qindex, int delta, int bd); /* av1_dc_quant_QTX */
+int b200_ac_quant(int qindex, int delta, int bd); /* av1_ac_quant_QTX */
 
 /* One transform block of a batch. */
 typedef struct {

@@ -62,3 +62,46 @@ def test_no_gpu_fails_loudly():
     with pytest.raises(b200av1.B200Error) as e:
         b200av1.Context(0)
     assert "no CPU fallback" in str(e.value)
+
+
+def test_build_quantizer_row_matches_oracle_and_reference():
+    """b200_build_quantizer_row (host) against the oracle's row for every qindex / bit depth /
+    sharpness, and -- where the reference build is present -- against av1_build_quantizer with
+    non-zero plane deltas (u/v rows)."""
+    import b200av1
+    L, O = b200av1.lib(), H.oracle()
+    row = b200av1.QRow()
+    for bd in (8, 10, 12):
+        for sharp in (0, 3, -2, 7, -7):
+            for q in range(256):
+                assert L.b200_build_quantizer_row(bd, q, 0, 0, sharp, C.byref(row)) == 0
+                o = H.oracle_qrow(bd, q, 0, sharp)
+                for name in ("zbin", "round", "quant", "quant_shift", "round_fp", "quant_fp", "dequant"):
+                    assert list(getattr(row, name)) == list(getattr(o, name))[:2], (bd, sharp, q, name)
+    assert L.b200_build_quantizer_row(9, 0, 0, 0, 0, C.byref(row)) != 0
+    R = H.ref() if H.have_ref() else None
+    if R is None:
+        return
+
+    class Quants(C.Structure):
+        _fields_ = [(n, C.c_int16 * 8 * 256) for n in
+                    ("y_quant", "y_quant_shift", "y_zbin", "y_round", "y_quant_fp",
+                     "u_quant_fp", "v_quant_fp", "y_round_fp", "u_round_fp", "v_round_fp",
+                     "u_quant", "v_quant", "u_quant_shift", "v_quant_shift", "u_zbin",
+                     "v_zbin", "u_round", "v_round")]
+
+    class Dequants(C.Structure):
+        _fields_ = [(n, C.c_int16 * 8 * 256) for n in ("y", "u", "v")]
+
+    for bd in (8, 10):
+        for sharp in (0, 2, -3):
+            qs, dq = Quants(), Dequants()
+            ydc, udc, uac, vdc, vac = -7, 5, -12, 20, 63
+            R.av1_build_quantizer(bd, ydc, udc, uac, vdc, vac, C.byref(qs), C.byref(dq), sharp)
+            for q in range(0, 256, 3):
+                for pl, (dcd, acd) in zip("yuv", ((ydc, 0), (udc, uac), (vdc, vac))):
+                    assert L.b200_build_quantizer_row(bd, q, dcd, acd, sharp, C.byref(row)) == 0
+                    for name in ("zbin", "round", "quant", "quant_shift", "round_fp", "quant_fp"):
+                        theirs = getattr(qs, "%s_%s" % (pl, name))[q]
+                        assert list(getattr(row, name)) == list(theirs)[:2], (bd, sharp, q, pl, name)
+                    assert list(row.dequant) == list(getattr(dq, pl)[q])[:2], (bd, sharp, q, pl)
