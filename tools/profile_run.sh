@@ -7,11 +7,16 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
   --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 --no-cpu --e2e-steps 0 \
   > gpurun_out/ncu_launches.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:txq --launch-skip 19 -c 19 \
-  -o gpurun_out/txq_full python bench.py --steps 1 --warmup 1 --no-cpu --no-me --e2e-steps 0 \
+  -o gpurun_out/txq_full python bench.py --steps 1 --warmup 1 --no-cpu --no-me --no-extras --e2e-steps 0 \
   > gpurun_out/ncu_txq.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:pel_kernel --launch-skip 2 -c 2 \
-  -o gpurun_out/me_full python bench.py --sizes 0 --steps 2 --warmup 1 --no-cpu --e2e-steps 0 \
+  -o gpurun_out/me_full python bench.py --sizes 0 --steps 2 --warmup 1 --no-cpu --no-extras --e2e-steps 0 \
   > gpurun_out/ncu_me.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:hadamard_kernel --launch-skip 6 -c 6 \
+  -o gpurun_out/had_full python bench.py --sizes 0 --steps 2 --warmup 1 --no-cpu --no-me --e2e-steps 0 \
+  > gpurun_out/ncu_had.log 2>&1
+ncu -i gpurun_out/had_full.ncu-rep --page raw --csv > gpurun_out/had_raw.csv
+rm -f gpurun_out/had_full.ncu-rep
 # the reports are too big to travel back (64 MiB cap): export what profiles/ needs here
 ncu -i gpurun_out/txq_full.ncu-rep --page raw --csv > gpurun_out/txq_raw.csv
 ncu -i gpurun_out/me_full.ncu-rep --page raw --csv > gpurun_out/me_raw.csv
