@@ -72,15 +72,43 @@ __global__ void __launch_bounds__(kThreads) hadamard_kernel(const B200HadamardLa
   for (int tile = blockIdx.x * kWarps + warp; tile < tiles; tile += gridDim.x * kWarps) {
     const int blk0 = tile * kPerWarp;
     __syncwarp();
-    // stage the residual(s): tile layout = block-major, row-major inside a block
-    for (int i = lane; i < kElems; i += 32) {
-      const int b = i / (N * N), e = i - b * (N * N), y = e / N, x = e - y * N;
-      int v = 0;
-      if (blk0 + b < l.n_blocks) {
-        const B200HadBlock d = l.blocks[blk0 + b];
-        v = l.src[(size_t)d.src_offset + (size_t)y * d.stride + x];
+    // stage the residual(s): tile layout = block-major, row-major inside a block.  Each lane
+    // moves 8-sample row pieces: one 16-byte load when the piece is aligned, 8 independent
+    // 2-byte loads otherwise (all issued before the first use: the kernel is latency-bound).
+    {
+      constexpr int kPieces = kElems / 8 / 32;  // 16-byte pieces per lane: 1 (8x8 x4, 16x16) or 4
+      constexpr int kPiecesPerRow = N / 8;
+      short v[kPieces][8];
+#pragma unroll
+      for (int j = 0; j < kPieces; ++j) {
+        const int piece = j * 32 + lane;                 // piece index inside the warp tile
+        const int b = piece / (N * kPiecesPerRow), pr = piece - b * (N * kPiecesPerRow);
+        const int y = pr / kPiecesPerRow, x = (pr - y * kPiecesPerRow) * 8;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[j][k] = 0;
+        if (blk0 + b < l.n_blocks) {
+          const B200HadBlock d = l.blocks[blk0 + b];
+          const short *p = l.src + (size_t)d.src_offset + (size_t)y * d.stride + x;
+          if ((reinterpret_cast<size_t>(p) & 15) == 0) {
+            const int4 w = *reinterpret_cast<const int4 *>(p);
+            const int ww[4] = { w.x, w.y, w.z, w.w };
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              v[j][2 * k] = (short)(ww[k] & 0xffff);
+              v[j][2 * k + 1] = (short)(ww[k] >> 16);
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[j][k] = p[k];
+          }
+        }
       }
-      buf[i] = v;
+#pragma unroll
+      for (int j = 0; j < kPieces; ++j) {
+        const int piece = j * 32 + lane;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) buf[piece * 8 + k] = v[j][k];
+      }
     }
     __syncwarp();
     // first pass: 8-point transform down each column of each 8x8 sub-block (int16 stores)
@@ -327,7 +355,7 @@ __global__ void __launch_bounds__(kThreads) satd_kernel(const void *coeff, int l
 
 int grid_for(const b200_ctx *ctx, long long units, int per_cta) {
   long long g = (units + per_cta - 1) / per_cta;
-  const long long cap = (long long)ctx->sm_count * 8;  // multiple of the SM count; grid-stride beyond
+  const long long cap = (long long)ctx->sm_count * 16;  // multiple of the SM count; grid-stride beyond
   if (g > cap) g = cap;
   return g < 1 ? 1 : (int)g;
 }
