@@ -119,7 +119,13 @@ struct SmemCfg {
   static constexpr int kOperands = IN == B200_IN_RESIDUAL ? 1 : 2;  // src (+ pred)
   static constexpr int kStageBytes = cx_round_up(kOperands * S::kPlaneBytes, 16);
   // deeper prefetch for small tiles (bytes in flight per warp)
-  static constexpr int kStages = S::kPlaneBytes >= 2048 ? 2 : (S::kPlaneBytes >= 1024 ? 3 : 4);
+#ifdef B200_TXQ_STAGES_BY_TOTAL
+  // experiment: count BOTH operand planes of the pixel-input kinds as bytes in flight
+  static constexpr int kFlight = kOperands * S::kPlaneBytes;
+#else
+  static constexpr int kFlight = S::kPlaneBytes;
+#endif
+  static constexpr int kStages = kFlight >= 2048 ? 2 : (kFlight >= 1024 ? 3 : 4);
   static constexpr int kXposeBytes = cx_round_up(C::BPW * C::XS * 4, 16);
   // Output tiles (optional bulk-store path, -DB200_TXQ_BULK_OUT): the tile's coeff / qcoeff /
   // dqcoeff blocks are assembled in shared memory in the codec's storage order and leave
