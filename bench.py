@@ -715,12 +715,17 @@ def main():
         H, O, R = load_cpu_libs()
         n_threads = os.cpu_count() or 1
         t, s, outs = cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed + rank, n_threads,
-                                   sizes, keep_outputs=True)
+                                   sizes, keep_outputs=True)  # warm-up pass; its outputs feed the parity check
+        reps, t, s = 8, 0.0, 0
+        for _ in range(reps):  # a bounded sample, long enough to average the thread start-up noise out
+            ti, si, _o = cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed + rank, n_threads, sizes)
+            t += ti
+            s += si
         line["cpu_baseline"] = {"value": s / FE_SAMPLES / t, "unit": "1080p frame-equiv/s",
                                 "cores": n_threads, "kind": "reference" if R is not None else "port",
-                                "sample": "1 frame x %d TX sizes (%.1f FE), av1_fwd_txfm2d_*_c + "
-                                          "av1_quantize_fp*_c on %d host threads"
-                                          % (len(sizes), s / FE_SAMPLES, n_threads)}
+                                "sample": "%d x (1 frame x %d TX sizes) = %.1f FE after one warm-up pass, "
+                                          "av1_fwd_txfm2d_*_c + av1_quantize_fp*_c on %d host threads"
+                                          % (reps, len(sizes), s / FE_SAMPLES, n_threads)}
         # parity at full size: GPU (host-buffer call, frame 0) vs CPU outputs, bit-exact
         ok = True
         for ts in sizes:
