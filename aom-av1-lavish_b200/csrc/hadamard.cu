@@ -137,12 +137,45 @@ __global__ void __launch_bounds__(kThreads) hadamard_kernel(const B200HadamardLa
 #pragma unroll
       for (int r = 0; r < 8; ++r) x[r] = tmp[sub * kTmpPitch + r * 9 + c];
       net8<KIND != B200_HAD_HIGHBD>(x, o);
+      if constexpr (N == 8) {
+        // 8x8 is finished here: coefficients leave straight from the registers (for every k
+        // the 8 lanes of a block write one 32-byte sector; highbd: 32 contiguous bytes per
+        // lane) and the SATD is an 8-lane reduction -- no second trip through shared memory.
+        const bool live = blk0 + sub < l.n_blocks;
+        if (l.coeff && live) {
+          const size_t ob = l.blocks[blk0 + sub].out_offset;
+          if constexpr (KIND == B200_HAD_LP) {
+            short *op = static_cast<short *>(l.coeff) + ob;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        if (KIND == B200_HAD_HIGHBD) buf[sub * 64 + 8 * c + k] = o[k];
-        else buf[sub * 64 + k * 8 + c] = o[k];
+            for (int k = 0; k < 8; ++k) op[k * 8 + c] = (short)o[k];
+          } else if constexpr (KIND == B200_HAD_HIGHBD) {
+            int *op = static_cast<int *>(l.coeff) + ob + 8 * c;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) op[k] = o[k];
+          } else {
+            int *op = static_cast<int *>(l.coeff) + ob;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) op[k * 8 + c] = o[k];
+          }
+        }
+        if (l.satd) {
+          int sacc = 0;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) sacc += abs(o[k]);
+          sacc += __shfl_xor_sync(0xffffffffu, sacc, 4);
+          sacc += __shfl_xor_sync(0xffffffffu, sacc, 2);
+          sacc += __shfl_xor_sync(0xffffffffu, sacc, 1);
+          if (c == 0 && live) l.satd[blk0 + sub] = sacc;
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          if (KIND == B200_HAD_HIGHBD) buf[sub * 64 + 8 * c + k] = o[k];
+          else buf[sub * 64 + k * 8 + c] = o[k];
+        }
       }
     }
+    if constexpr (N == 8) continue;
     __syncwarp();
     if (N >= 16) {
       // 16x16: combine the four 8x8 transforms of each 16x16 (>> 1)
