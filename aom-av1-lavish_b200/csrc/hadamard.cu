@@ -129,105 +129,93 @@ __global__ void __launch_bounds__(kThreads) hadamard_kernel(const B200HadamardLa
     }
     __syncwarp();
     // second pass down the columns of the intermediate (tmp[c * 8 + k] of the reference is
-    // tmp[c * 9 + k] here); low bit depth stores transposed (avg.c:198-203)
+    // tmp[c * 9 + k] here).  Everything after it stays in registers: lane (s = lane >> 3, c)
+    // holds, for task t and k = 0..7, the coefficient of 8x8 sub-block t * 4 + s at storage
+    // position k * 8 + c (low bit depth: transposed, avg.c:198-203) or 8 * c + k (highbd).
+    int o[kTasks][8];
 #pragma unroll
     for (int t = 0; t < kTasks; ++t) {
-      const int task = t * 32 + lane, sub = task >> 3, c = task & 7;
-      int x[8], o[8];
+      const int sub = (t * 32 + lane) >> 3, c = lane & 7;
+      int x[8];
 #pragma unroll
       for (int r = 0; r < 8; ++r) x[r] = tmp[sub * kTmpPitch + r * 9 + c];
-      net8<KIND != B200_HAD_HIGHBD>(x, o);
-      if constexpr (N == 8) {
-        // 8x8 is finished here: coefficients leave straight from the registers (for every k
-        // the 8 lanes of a block write one 32-byte sector; highbd: 32 contiguous bytes per
-        // lane) and the SATD is an 8-lane reduction -- no second trip through shared memory.
-        const bool live = blk0 + sub < l.n_blocks;
-        if (l.coeff && live) {
-          const size_t ob = l.blocks[blk0 + sub].out_offset;
-          if constexpr (KIND == B200_HAD_LP) {
-            short *op = static_cast<short *>(l.coeff) + ob;
+      net8<KIND != B200_HAD_HIGHBD>(x, o[t]);
+    }
+    const int s4 = lane >> 3, c = lane & 7;
+    if constexpr (N >= 16) {
+      // 16x16 stage (avg.c:258-276, :298-315, :455-472): the four 8x8 transforms of a 16x16
+      // sit in the lanes s4 = 0..3 of the same (t, k, c) -> two butterfly rounds over
+      // lane ^ 8 and lane ^ 16
 #pragma unroll
-            for (int k = 0; k < 8; ++k) op[k * 8 + c] = (short)o[k];
-          } else if constexpr (KIND == B200_HAD_HIGHBD) {
-            int *op = static_cast<int *>(l.coeff) + ob + 8 * c;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) op[k] = o[k];
-          } else {
-            int *op = static_cast<int *>(l.coeff) + ob;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) op[k * 8 + c] = o[k];
-          }
-        }
-        if (l.satd) {
-          int sacc = 0;
-#pragma unroll
-          for (int k = 0; k < 8; ++k) sacc += abs(o[k]);
-          sacc += __shfl_xor_sync(0xffffffffu, sacc, 4);
-          sacc += __shfl_xor_sync(0xffffffffu, sacc, 2);
-          sacc += __shfl_xor_sync(0xffffffffu, sacc, 1);
-          if (c == 0 && live) l.satd[blk0 + sub] = sacc;
-        }
-      } else {
+      for (int t = 0; t < kTasks; ++t)
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          if (KIND == B200_HAD_HIGHBD) buf[sub * 64 + 8 * c + k] = o[k];
-          else buf[sub * 64 + k * 8 + c] = o[k];
+          int v = o[t][k];
+          int p1 = __shfl_xor_sync(0xffffffffu, v, 8);
+          v = (s4 & 1) ? (p1 - v) >> 1 : (v + p1) >> 1;
+          if (KIND == B200_HAD_LP) v = w16(v);
+          p1 = __shfl_xor_sync(0xffffffffu, v, 16);
+          v = (s4 & 2) ? p1 - v : v + p1;
+          if (KIND == B200_HAD_LP) v = w16(v);
+          o[t][k] = v;
         }
+    }
+    if constexpr (N == 32) {
+      // 32x32 stage (avg.c:329-347, :485-503): the four 16x16 quadrants are the four tasks of
+      // the same lane -> plain register arithmetic (>> 2)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int a0 = o[0][k], a1 = o[1][k], a2 = o[2][k], a3 = o[3][k];
+        const int b0 = (a0 + a1) >> 2, b1 = (a0 - a1) >> 2, b2 = (a2 + a3) >> 2, b3 = (a2 - a3) >> 2;
+        o[0][k] = b0 + b2;
+        o[1][k] = b1 + b3;
+        o[2][k] = b0 - b2;
+        o[3][k] = b1 - b3;
       }
     }
-    if constexpr (N == 8) continue;
-    __syncwarp();
-    if (N >= 16) {
-      // 16x16: combine the four 8x8 transforms of each 16x16 (>> 1)
-      for (int i = lane; i < kElems / 4; i += 32) {
-        const int s16 = i >> 6, e = i & 63;
-        combine<KIND == B200_HAD_LP>(buf + s16 * 256 + e, 64, 1);
-      }
-      __syncwarp();
-      if (KIND == B200_HAD_LOWBD) {
-        // the column swap that matches the AVX2 output order (avg.c:279-286)
-        for (int i = lane; i < kElems / 4; i += 32) {
-          const int s16 = i >> 6, row = (i >> 2) & 15, j = i & 3;
-          int *p = buf + s16 * 256 + row * 16 + 4 + j;
-          const int t = p[0];
-          p[0] = p[4];
-          p[4] = t;
+    // outputs.  8x8: lane group s4 is block blk0 + s4; larger: one block per warp, 8x8
+    // sub-block t * 4 + s4 at offset (t * 4 + s4) * 64.
+    const int blk = N == 8 ? blk0 + s4 : blk0;
+    const bool live = blk < l.n_blocks;
+    int sacc = 0;
+#pragma unroll
+    for (int t = 0; t < kTasks; ++t)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) sacc += abs(o[t][k]);
+    if (l.coeff && live) {
+      const size_t ob = l.blocks[blk].out_offset;
+#pragma unroll
+      for (int t = 0; t < kTasks; ++t) {
+        const int base = N == 8 ? 0 : (t * 4 + s4) * 64;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          int pos;
+          if (KIND == B200_HAD_HIGHBD) {
+            pos = 8 * c + k;
+          } else if (KIND == B200_HAD_LOWBD && N >= 16) {
+            // the column swap that matches the AVX2 output order (avg.c:279-286): in a row of
+            // 16, columns 4..7 <-> 8..11, i.e. (k even, c >= 4) <-> (k odd, c < 4)
+            const bool lo = (k & 1) == 0;
+            if (lo && c >= 4) pos = (k + 1) * 8 + c - 4;
+            else if (!lo && c < 4) pos = (k - 1) * 8 + c + 4;
+            else pos = k * 8 + c;
+          } else {
+            pos = k * 8 + c;
+          }
+          if (KIND == B200_HAD_LP) static_cast<short *>(l.coeff)[ob + base + pos] = (short)o[t][k];
+          else static_cast<int *>(l.coeff)[ob + base + pos] = o[t][k];
         }
-        __syncwarp();
-      }
-    }
-    if (N == 32) {
-      for (int i = lane; i < 256; i += 32) combine<false>(buf + i, 256, 2);
-      __syncwarp();
-    }
-    // outputs
-    int acc = 0;
-    for (int i = lane; i < kElems; i += 32) {
-      const int b = i / (N * N), e = i - b * (N * N);
-      const int v = buf[i];
-      acc += abs(v);
-      if (l.coeff && blk0 + b < l.n_blocks) {
-        const size_t o = (size_t)l.blocks[blk0 + b].out_offset + e;
-        if (KIND == B200_HAD_LP) static_cast<short *>(l.coeff)[o] = (short)v;
-        else static_cast<int *>(l.coeff)[o] = v;
       }
     }
     if (l.satd) {
-      if (kPerWarp == 1) {
-#pragma unroll
-        for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        if (lane == 0) l.satd[blk0] = acc;
-      } else {
-        // N == 8, four blocks per warp: per-block sums, 8 lanes per block, 8 elements each
-        const int b = lane >> 3, q = lane & 7;
-        int s = 0;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) s += abs(buf[b * 64 + k * 8 + q]);
-        s += __shfl_xor_sync(0xffffffffu, s, 4);
-        s += __shfl_xor_sync(0xffffffffu, s, 2);
-        s += __shfl_xor_sync(0xffffffffu, s, 1);
-        if (q == 0 && blk0 + b < l.n_blocks) l.satd[blk0 + b] = s;
+      sacc += __shfl_xor_sync(0xffffffffu, sacc, 4);
+      sacc += __shfl_xor_sync(0xffffffffu, sacc, 2);
+      sacc += __shfl_xor_sync(0xffffffffu, sacc, 1);
+      if (N > 8) {
+        sacc += __shfl_xor_sync(0xffffffffu, sacc, 8);
+        sacc += __shfl_xor_sync(0xffffffffu, sacc, 16);
       }
+      if ((N == 8 ? c == 0 : lane == 0) && live) l.satd[blk] = sacc;
     }
   }
 }
