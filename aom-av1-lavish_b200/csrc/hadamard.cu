@@ -2,16 +2,19 @@
 // (av1/encoder/hybrid_fwd_txfm.c:24) and the small block statistics of avg.c (averages,
 // min/max, integer projections, vector variance).
 //
-// Mapping.  8x8 and larger: ONE warp per block.  The residual is staged once into a per-warp
-// shared tile; both 8-point passes run one (8x8 sub-block, column) task per lane -- 4 tasks
-// per lane at 32x32, so no lane idles for n >= 16 -- with `__syncwarp` between passes (no CTA
-// barrier), then the 16x16 / 32x32 combination stages run element-parallel in place.  The
-// int16 stores of the reference (every intermediate of hadamard_col8 is an int16_t) are
-// reproduced by sign-extending after each add; the highbd second pass and the combination
-// stages stay 32-bit like the reference's.  Coefficients leave as lane-contiguous coalesced
-// stores; the SATD is a warp reduction of the same registers, so the SATD-only use writes
-// 4 bytes per block.  4x4 (Hadamard and WHT): a lane owns a block (8 blocks would otherwise
-// share a warp with 3/4 of the lanes idle).  Bound: HBM (2 B/sample in, 4 B/sample out).
+// Mapping.  8x8 and larger: ONE warp per block (four 8x8 blocks share a warp).  Lane
+// (s = lane >> 3, c = lane & 7) owns column c of 8x8 sub-block s (4 tasks per lane at 32x32):
+// pass 1 reads its 8 samples straight from global memory (8 independent loads; the 8 lanes of
+// a sub-block cover 16 contiguous bytes per row, neighbouring sub-blocks complete the
+// sectors), pass 2 reads the transposed intermediate through a pitch-9 shared tile
+// (conflict-free, `__syncwarp` only), and everything after that stays in registers: the
+// 16x16 stage is two butterfly rounds over lane ^ 8 / lane ^ 16, the 32x32 stage is plain
+// arithmetic on the lane's four tasks, the AVX2-order column swap of aom_hadamard_16x16_c is
+// folded into the store address, the SATD is a shuffle reduction.  The int16 stores of the
+// reference (every intermediate of hadamard_col8 is an int16_t) are reproduced by
+// sign-extending after each add; the highbd second pass and the combination stages stay
+// 32-bit like the reference's.  4x4 (Hadamard and WHT): a lane owns a block.
+// Bound: HBM (2 B/sample in, 4 B/sample out); measured 3.0-4.2 TB/s with coefficient output.
 #include <string.h>
 
 #include <type_traits>
@@ -63,55 +66,17 @@ __global__ void __launch_bounds__(kThreads) hadamard_kernel(const B200HadamardLa
   constexpr int kTasks = kSub * 8 / 32;              // column tasks per lane (1 or 4)
   constexpr int kSubPerRow = N / 8;
   constexpr int kTmpPitch = 72;                       // 8x8 intermediate at row pitch 9 (+8): conflict-free
-  __shared__ int s_buf[kWarps][kElems];
   __shared__ int s_tmp[kWarps][kSub * kTmpPitch];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  int *buf = s_buf[warp];
   int *tmp = s_tmp[warp];
   const int tiles = (l.n_blocks + kPerWarp - 1) / kPerWarp;
   for (int tile = blockIdx.x * kWarps + warp; tile < tiles; tile += gridDim.x * kWarps) {
     const int blk0 = tile * kPerWarp;
     __syncwarp();
-    // stage the residual(s): tile layout = block-major, row-major inside a block.  Each lane
-    // moves 8-sample row pieces: one 16-byte load when the piece is aligned, 8 independent
-    // 2-byte loads otherwise (all issued before the first use: the kernel is latency-bound).
-    {
-      constexpr int kPieces = kElems / 8 / 32;  // 16-byte pieces per lane: 1 (8x8 x4, 16x16) or 4
-      constexpr int kPiecesPerRow = N / 8;
-      short v[kPieces][8];
-#pragma unroll
-      for (int j = 0; j < kPieces; ++j) {
-        const int piece = j * 32 + lane;                 // piece index inside the warp tile
-        const int b = piece / (N * kPiecesPerRow), pr = piece - b * (N * kPiecesPerRow);
-        const int y = pr / kPiecesPerRow, x = (pr - y * kPiecesPerRow) * 8;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) v[j][k] = 0;
-        if (blk0 + b < l.n_blocks) {
-          const B200HadBlock d = l.blocks[blk0 + b];
-          const short *p = l.src + (size_t)d.src_offset + (size_t)y * d.stride + x;
-          if ((reinterpret_cast<size_t>(p) & 15) == 0) {
-            const int4 w = *reinterpret_cast<const int4 *>(p);
-            const int ww[4] = { w.x, w.y, w.z, w.w };
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              v[j][2 * k] = (short)(ww[k] & 0xffff);
-              v[j][2 * k + 1] = (short)(ww[k] >> 16);
-            }
-          } else {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) v[j][k] = p[k];
-          }
-        }
-      }
-#pragma unroll
-      for (int j = 0; j < kPieces; ++j) {
-        const int piece = j * 32 + lane;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) buf[piece * 8 + k] = v[j][k];
-      }
-    }
-    __syncwarp();
-    // first pass: 8-point transform down each column of each 8x8 sub-block (int16 stores)
+    // first pass: 8-point transform down each column of each 8x8 sub-block (int16 stores),
+    // read straight from global memory: the 8 lanes of a sub-block read 16 contiguous bytes per
+    // row and horizontally adjacent sub-blocks complete the 32-byte sectors in the same
+    // request; all 8 loads of a task are independent (the kernel is latency-bound).
 #pragma unroll
     for (int t = 0; t < kTasks; ++t) {
       const int task = t * 32 + lane, sub = task >> 3, c = task & 7;
@@ -119,10 +84,15 @@ __global__ void __launch_bounds__(kThreads) hadamard_kernel(const B200HadamardLa
       // sub-block order of the reference's recursion: quadrant q of a 32x32, then 8x8 i inside it
       const int q = sb >> 2, qi = sb & 3;
       const int sy = ((q >> 1) << 1) + (qi >> 1), sx = ((q & 1) << 1) + (qi & 1);
-      const int *p = buf + b * N * N + (sy * 8) * N + sx * 8 + c;
       int x[8], o[8];
 #pragma unroll
-      for (int r = 0; r < 8; ++r) x[r] = p[r * N];
+      for (int r = 0; r < 8; ++r) x[r] = 0;
+      if (blk0 + b < l.n_blocks) {
+        const B200HadBlock d = l.blocks[blk0 + b];
+        const short *p = l.src + (size_t)d.src_offset + (size_t)(sy * 8) * d.stride + sx * 8 + c;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) x[r] = p[(size_t)r * d.stride];
+      }
       net8<true>(x, o);
 #pragma unroll
       for (int k = 0; k < 8; ++k) tmp[sub * kTmpPitch + c * 9 + k] = o[k];
