@@ -43,19 +43,6 @@ __device__ __forceinline__ void net8(const int (&x)[8], int (&o)[8]) {
 #undef B200_W
 }
 
-// combination of four quarter transforms, in place (avg.c:258-276 and friends); LP narrows
-// every store to int16 like aom_hadamard_lp_16x16_c (:298-315)
-template <bool LP>
-__device__ __forceinline__ void combine(int *c, int q, int shift) {
-  const int a0 = c[0], a1 = c[q], a2 = c[2 * q], a3 = c[3 * q];
-  int b0 = (a0 + a1) >> shift, b1 = (a0 - a1) >> shift, b2 = (a2 + a3) >> shift, b3 = (a2 - a3) >> shift;
-  if (LP) { b0 = w16(b0); b1 = w16(b1); b2 = w16(b2); b3 = w16(b3); }
-  c[0] = LP ? w16(b0 + b2) : b0 + b2;
-  c[q] = LP ? w16(b1 + b3) : b1 + b3;
-  c[2 * q] = LP ? w16(b0 - b2) : b0 - b2;
-  c[3 * q] = LP ? w16(b1 - b3) : b1 - b3;
-}
-
 // N in {8, 16, 32}; KIND = B200_HAD_LOWBD / _LP / _HIGHBD.  Blocks per warp: 4 at 8x8 (so
 // that all 32 lanes carry a column task), 1 otherwise.
 template <int N, int KIND>
