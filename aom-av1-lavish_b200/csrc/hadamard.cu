@@ -130,6 +130,20 @@ __global__ void __launch_bounds__(kThreads) hadamard_kernel(const B200HadamardLa
         o[3][k] = b1 - b3;
       }
     }
+    if constexpr (KIND == B200_HAD_LOWBD && N >= 16) {
+      // the column swap that matches the AVX2 output order (avg.c:279-286): in a row of 16,
+      // columns 4..7 <-> 8..11, i.e. (k even, c >= 4) <-> (k odd, c < 4) of the same 8x8.
+      // Done as one lane ^ 4 exchange per row pair so that the stores stay 32-byte runs.
+#pragma unroll
+      for (int t = 0; t < kTasks; ++t)
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          const int send = c >= 4 ? o[t][2 * m] : o[t][2 * m + 1];
+          const int recv = __shfl_xor_sync(0xffffffffu, send, 4);
+          if (c >= 4) o[t][2 * m] = recv;
+          else o[t][2 * m + 1] = recv;
+        }
+    }
     // outputs.  8x8: lane group s4 is block blk0 + s4; larger: one block per warp, 8x8
     // sub-block t * 4 + s4 at offset (t * 4 + s4) * 64.
     const int blk = N == 8 ? blk0 + s4 : blk0;
@@ -149,13 +163,6 @@ __global__ void __launch_bounds__(kThreads) hadamard_kernel(const B200HadamardLa
           int pos;
           if (KIND == B200_HAD_HIGHBD) {
             pos = 8 * c + k;
-          } else if (KIND == B200_HAD_LOWBD && N >= 16) {
-            // the column swap that matches the AVX2 output order (avg.c:279-286): in a row of
-            // 16, columns 4..7 <-> 8..11, i.e. (k even, c >= 4) <-> (k odd, c < 4)
-            const bool lo = (k & 1) == 0;
-            if (lo && c >= 4) pos = (k + 1) * 8 + c - 4;
-            else if (!lo && c < 4) pos = (k - 1) * 8 + c + 4;
-            else pos = k * 8 + c;
           } else {
             pos = k * 8 + c;
           }
