@@ -80,9 +80,14 @@ __global__ void __launch_bounds__(kThreads) hadamard_kernel(const B200HadamardLa
 #pragma unroll
         for (int r = 0; r < 8; ++r) x[r] = p[(size_t)r * d.stride];
       }
-      net8<true>(x, o);
+      // The reference narrows every intermediate to int16.  Only additions and subtractions
+      // are involved up to the end of the second pass, and wrapping is a ring homomorphism
+      // (mod 2^16), so narrowing ONCE where the value is next used as a number gives the
+      // same bits: low bit depth after pass 2, highbd (32-bit second pass) after pass 1.
+      net8<false>(x, o);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) tmp[sub * kTmpPitch + c * 9 + k] = o[k];
+      for (int k = 0; k < 8; ++k)
+        tmp[sub * kTmpPitch + c * 9 + k] = KIND == B200_HAD_HIGHBD ? w16(o[k]) : o[k];
     }
     __syncwarp();
     // second pass down the columns of the intermediate (tmp[c * 8 + k] of the reference is
@@ -96,7 +101,11 @@ __global__ void __launch_bounds__(kThreads) hadamard_kernel(const B200HadamardLa
       int x[8];
 #pragma unroll
       for (int r = 0; r < 8; ++r) x[r] = tmp[sub * kTmpPitch + r * 9 + c];
-      net8<KIND != B200_HAD_HIGHBD>(x, o[t]);
+      net8<false>(x, o[t]);
+      if (KIND != B200_HAD_HIGHBD) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[t][k] = w16(o[t][k]);
+      }
     }
     const int s4 = lane >> 3, c = lane & 7;
     if constexpr (N >= 16) {
