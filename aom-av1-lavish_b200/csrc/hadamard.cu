@@ -10,10 +10,10 @@
 // (conflict-free, `__syncwarp` only), and everything after that stays in registers: the
 // 16x16 stage is two butterfly rounds over lane ^ 8 / lane ^ 16, the 32x32 stage is plain
 // arithmetic on the lane's four tasks, the AVX2-order column swap of aom_hadamard_16x16_c is
-// folded into the store address, the SATD is a shuffle reduction.  The int16 stores of the
-// reference (every intermediate of hadamard_col8 is an int16_t) are reproduced by
-// sign-extending after each add; the highbd second pass and the combination stages stay
-// 32-bit like the reference's.  4x4 (Hadamard and WHT): a lane owns a block.
+// a lane ^ 4 exchange, the SATD is a shuffle reduction.  The reference keeps every
+// intermediate of hadamard_col8 in an int16_t; wrapping commutes with the add/sub network, so
+// the kernel narrows once per pass boundary (see pass 1); the highbd second pass and the
+// combination stages stay 32-bit like the reference's.  4x4 (Hadamard and WHT): a lane owns a block.
 // Bound: HBM (2 B/sample in, 4 B/sample out); measured 3.0-4.2 TB/s with coefficient output.
 #include <string.h>
 
