@@ -455,6 +455,10 @@ extern "C" int b200_block_error_launch(b200_ctx *ctx, const B200ErrLaunch *l, vo
     set_error("b200_block_error_launch: missing buffer or bad kind");
     return B200_EINVAL;
   }
+  if (l->kind == B200_ERR_HBD && l->bd != 8 && l->bd != 10 && l->bd != 12) {
+    set_error("b200_block_error_launch: bd must be 8, 10 or 12 (got %d)", l->bd);
+    return B200_EINVAL;
+  }
   block_error_kernel<<<grid_for(l->n_blocks), kWarps * 32, 0, s_>>>(*l);
   B200_CUDA_TRY(cudaGetLastError());
   return B200_OK;

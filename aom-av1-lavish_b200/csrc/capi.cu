@@ -39,6 +39,21 @@ extern "C" int b200_device_count(void) {
   return n;
 }
 
+static int ctx_init(b200_ctx *ctx) {
+  B200_CUDA_TRY(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  B200_CUDA_TRY(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+  for (int i = 0; i < B200_TX_SIZES_ALL; ++i)
+    B200_CUDA_TRY(cudaEventCreateWithFlags(&ctx->group_done[i], cudaEventDisableTiming));
+  B200_CUDA_TRY(cudaEventCreateWithFlags(&ctx->copy_done, cudaEventDisableTiming));
+  int rc = txq_init_device(ctx);
+  if (rc == B200_OK) rc = blockops_init_device(ctx);
+  if (rc == B200_OK) rc = me_init_device(ctx);
+  if (rc == B200_OK) rc = compact_init_device(ctx);
+  return rc;
+}
+
+extern "C" void b200_ctx_destroy(b200_ctx *ctx);
+
 extern "C" int b200_ctx_create(int device, b200_ctx **out) {
   if (!out) return B200_EINVAL;
   *out = nullptr;
@@ -58,18 +73,15 @@ extern "C" int b200_ctx_create(int device, b200_ctx **out) {
   }
   B200_CUDA_TRY(cudaSetDevice(device));
   b200_ctx *ctx = (b200_ctx *)calloc(1, sizeof(b200_ctx));
+  if (!ctx) {
+    set_error("b200_ctx_create: out of host memory");
+    return B200_EINVAL;
+  }
   ctx->device = device;
   ctx->sm_count = prop.multiProcessorCount;
-  B200_CUDA_TRY(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-  B200_CUDA_TRY(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
-  for (int i = 0; i < B200_TX_SIZES_ALL; ++i)
-    B200_CUDA_TRY(cudaEventCreateWithFlags(&ctx->group_done[i], cudaEventDisableTiming));
-  B200_CUDA_TRY(cudaEventCreateWithFlags(&ctx->copy_done, cudaEventDisableTiming));
-  int rc = txq_init_device(ctx);
-  if (rc == B200_OK) rc = blockops_init_device(ctx);
-  if (rc == B200_OK) rc = me_init_device(ctx);
+  int rc = ctx_init(ctx);
   if (rc != B200_OK) {
-    free(ctx);
+    b200_ctx_destroy(ctx);  // releases whatever was created so far
     return rc;
   }
   *out = ctx;
@@ -79,17 +91,21 @@ extern "C" int b200_ctx_create(int device, b200_ctx **out) {
 extern "C" void b200_ctx_destroy(b200_ctx *ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
-  cudaStreamSynchronize(ctx->stream);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
   if (ctx->d_iscan) cudaFree(ctx->d_iscan);
+  if (ctx->d_scan) cudaFree(ctx->d_scan);
   if (ctx->d_pmask) cudaFree(ctx->d_pmask);
   if (ctx->d_scratch) cudaFree(ctx->d_scratch);
   if (ctx->d_me_sites) cudaFree(ctx->d_me_sites);
+  if (ctx->d_partials) cudaFree(ctx->d_partials);
   if (ctx->h_scratch) cudaFreeHost(ctx->h_scratch);
-  cudaStreamSynchronize(ctx->copy_stream);
-  for (int i = 0; i < B200_TX_SIZES_ALL; ++i) cudaEventDestroy(ctx->group_done[i]);
-  cudaEventDestroy(ctx->copy_done);
-  cudaStreamDestroy(ctx->copy_stream);
-  cudaStreamDestroy(ctx->stream);
+  for (int i = 0; i < B200_TX_SIZES_ALL; ++i)
+    if (ctx->group_done[i]) cudaEventDestroy(ctx->group_done[i]);
+  if (ctx->copy_done) cudaEventDestroy(ctx->copy_done);
+  if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  cudaGetLastError();
   free(ctx);
 }
 
@@ -188,30 +204,55 @@ static size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
 // Host-buffer wrapper of the fused kernel -- the reference-facing call of the frame tier
 // (what `e2e` in bench.py times).  Pipeline per call:
 //   host   counting sort of the descriptors by (tx_size, tx_type) -- skipped when the queue
-//          already arrives in that order -- and a pass that finds, per tx-size group, the
-//          range of the output arrays its blocks write
+//          already arrives in that order -- with bounds checks of every descriptor, and a pass
+//          that finds, per tx-size group, the range of the output arrays its blocks write
 //   stream   H2D of planes / tables / descriptors, one kernel launch per tx-size group
-//   copy_stream   as each group's kernel finishes, D2H of exactly that group's output range,
-//          so the PCIe read-back (12 of the 14 bytes per sample) overlaps the remaining
-//          uploads and kernels instead of following them
+//   copy_stream   dense mode: as each group's kernel finishes, D2H of exactly that group's
+//          output range, so the PCIe read-back (12 of the 14 bytes per sample) overlaps the
+//          remaining uploads and kernels instead of following them;
+//          compact mode: the dense qcoeff / dqcoeff never leave the device -- one compaction
+//          pass (compact.cu) packs the levels, the host reads eob + offsets + total, then
+//          exactly `total` levels
 // When the groups' output ranges are not dense and disjoint (a caller that interleaves
-// sizes inside the arrays) the function falls back to zero-filled device arrays and one
-// whole-array read-back at the end.
-extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int bd, unsigned flags,
-                                   const B200TxBlock *blocks, const B200TxPred *preds,
-                                   int n_blocks, const void *src, size_t src_elems,
-                                   const void *pred, size_t pred_elems, const B200QRow *qrows,
-                                   int n_qrows, int32_t *coeff, int32_t *qcoeff, int32_t *dqcoeff,
-                                   size_t out_elems, uint16_t *eob, int64_t *dist) {
+// sizes inside the arrays, or blocks that overlap) the dense mode falls back to zero-filled
+// device arrays and one whole-array read-back at the end.
+namespace {
+struct CompactOut {
+  void *levels;
+  size_t levels_cap;
+  uint32_t *level_offset;
+  size_t *d2h_bytes;
+};
+}  // namespace
+
+static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, unsigned flags,
+                               const B200TxBlock *blocks, const B200TxPred *preds, int n_blocks,
+                               const void *src, size_t src_elems, const void *pred, size_t pred_elems,
+                               const B200QRow *qrows, int n_qrows, int32_t *coeff, int32_t *qcoeff,
+                               int32_t *dqcoeff, size_t out_elems, uint16_t *eob, int64_t *dist,
+                               const CompactOut *cmp) {
   if (!ctx || !blocks || n_blocks < 0 || !src) return B200_EINVAL;
-  if (n_blocks == 0) return B200_OK;
+  if (cmp && cmp->d2h_bytes) *cmp->d2h_bytes = 0;
+  if (n_blocks == 0) {
+    if (cmp) cmp->level_offset[0] = 0;
+    return B200_OK;
+  }
   B200_CUDA_TRY(cudaSetDevice(ctx->device));
   const size_t px = in_kind == B200_IN_PIXELS8 ? 1 : 2;
   const bool has_pred = in_kind != B200_IN_RESIDUAL;
   const bool has_q = q_kind != B200_Q_NONE;
-  const bool want_coeff = (flags & B200_TXQ_STORE_COEFF) != 0;
+  const bool want_coeff = (flags & B200_TXQ_STORE_COEFF) != 0 && coeff;
   const bool want_err = (flags & B200_TXQ_BLOCK_ERROR) != 0 && dist;
   if (has_pred && (!preds || !pred)) return B200_EINVAL;
+  if (has_q && (!qrows || n_qrows <= 0)) return B200_EINVAL;
+  if (cmp && (!has_q || !cmp->levels || !cmp->level_offset || !eob)) {
+    set_error("b200_txq_batch_host_compact: needs a quantiser, levels, level_offset and eob");
+    return B200_EINVAL;
+  }
+  if (!cmp && ((has_q && (!qcoeff || !dqcoeff)) || ((flags & B200_TXQ_STORE_COEFF) && !coeff))) {
+    set_error("b200_txq_batch_host: missing output buffer");
+    return B200_EINVAL;
+  }
   const size_t n = (size_t)n_blocks;
 
   // ---- one pass over the queue: validate, bucket by (tx_size, tx_type) so that warps stay
@@ -219,10 +260,13 @@ extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int b
   constexpr int kKeys = B200_TX_SIZES_ALL * 16;
   static bool s_valid[kKeys];
   static size_t s_max_eob[B200_TX_SIZES_ALL];
+  static int s_w[B200_TX_SIZES_ALL], s_h[B200_TX_SIZES_ALL];
   static std::once_flag s_once;
   std::call_once(s_once, [] {
     for (int ts = 0; ts < B200_TX_SIZES_ALL; ++ts) {
       s_max_eob[ts] = (size_t)b200_tx_max_eob(ts);
+      s_w[ts] = b200_tx_wide(ts);
+      s_h[ts] = b200_tx_high(ts);
       for (int tt = 0; tt < 16; ++tt) s_valid[ts * 16 + tt] = b200_tx_valid(ts, tt) != 0;
     }
   });
@@ -238,6 +282,15 @@ extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int b
                 (int)blocks[i].tx_type);
       return B200_EINVAL;
     }
+    // the last sample a block reads must lie inside the input buffers
+    const size_t span = (size_t)(s_h[ts] - 1) * blocks[i].src_stride + s_w[ts];
+    if ((size_t)blocks[i].src_offset + span > src_elems ||
+        (has_pred && (size_t)preds[i].pred_offset + (size_t)(s_h[ts] - 1) * preds[i].pred_stride + s_w[ts] >
+                         pred_elems) ||
+        (has_q && blocks[i].qrow >= (unsigned)n_qrows)) {
+      set_error("b200_txq_batch_host: block %zu reads outside src / pred / qrows", i);
+      return B200_EINVAL;
+    }
     in_order = in_order && key >= prev_key;
     prev_key = key;
     ++bucket[key + 1];
@@ -247,7 +300,7 @@ extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int b
   }
   for (int k = 0; k < kKeys; ++k) bucket[k + 1] += bucket[k];
 
-  // pinned staging: [sorted blocks][sorted preds][eob][dist]
+  // pinned staging: [sorted blocks][sorted preds][eob][dist][level offsets]
   size_t hoff = 0;
   auto hcarve = [&](size_t bytes) {
     const size_t o = hoff;
@@ -258,6 +311,7 @@ extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int b
   const size_t ho_preds = hcarve(!in_order && has_pred ? sizeof(B200TxPred) * n : 0);
   const size_t ho_eob = hcarve(has_q ? n * 2 : 0);
   const size_t ho_dist = hcarve(want_err ? n * 16 : 0);
+  const size_t ho_loff = hcarve(cmp ? (n + 1) * 4 : 0);
   int rc = host_scratch_reserve(ctx, hoff);
   if (rc != B200_OK) return rc;
   char *hbase = (char *)ctx->h_scratch;
@@ -296,16 +350,31 @@ extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int b
     }
     groups.push_back(g);
   }
-  bool dense = true;
+  // dense = every group's blocks tile its [lo, hi) range exactly once and the groups' ranges
+  // are disjoint; checked per block (slot bitmap), not only by the range length
+  bool dense = !cmp;
   std::vector<const Group *> by_lo;
-  for (const Group &g : groups) {
-    dense = dense && g.hi - g.lo == g.elems;
-    by_lo.push_back(&g);
+  if (!cmp) {
+    std::vector<uint8_t> seen;
+    for (const Group &g : groups) {
+      dense = dense && g.hi - g.lo == g.elems;
+      by_lo.push_back(&g);
+      if (!dense) break;
+      const size_t me = s_max_eob[g.ts];
+      seen.assign(g.count, 0);
+      for (size_t i = g.first; i < g.first + g.count && dense; ++i) {
+        const size_t rel = sblocks[i].out_offset - g.lo;
+        if (rel % me != 0 || seen[rel / me]) dense = false;
+        else seen[rel / me] = 1;
+      }
+    }
+    std::sort(by_lo.begin(), by_lo.end(), [](const Group *a, const Group *b) { return a->lo < b->lo; });
+    for (size_t i = 0; i + 1 < by_lo.size(); ++i) dense = dense && by_lo[i]->hi <= by_lo[i + 1]->lo;
   }
-  std::sort(by_lo.begin(), by_lo.end(), [](const Group *a, const Group *b) { return a->lo < b->lo; });
-  for (size_t i = 0; i + 1 < by_lo.size(); ++i) dense = dense && by_lo[i]->hi <= by_lo[i + 1]->lo;
 
   // ---- device carve-out
+  const bool wide = q_kind == B200_Q_FP_HBD || q_kind == B200_Q_B_HBD;
+  const size_t lv_bytes = wide ? 4 : 2;
   size_t off = 0;
   auto carve = [&](size_t bytes) {
     size_t o = off;
@@ -322,6 +391,8 @@ extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int b
   const size_t o_dq = carve(has_q ? out_elems * 4 : 0);
   const size_t o_eob = carve(has_q ? n * 2 : 0);
   const size_t o_dist = carve(want_err ? n * 16 : 0);
+  const size_t o_loff = carve(cmp ? (n + 1) * 4 : 0);
+  const size_t o_lv = carve(cmp ? out_elems * lv_bytes : 0);
   rc = scratch_reserve(ctx, off);
   if (rc != B200_OK) return rc;
   char *base = (char *)ctx->d_scratch;
@@ -333,7 +404,7 @@ extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int b
   if (has_q)
     B200_CUDA_TRY(cudaMemcpyAsync(base + o_q, qrows, sizeof(B200QRow) * n_qrows,
                                   cudaMemcpyHostToDevice, s));
-  if (!dense) {
+  if (!dense && !cmp) {
     // regions of the output arrays that no block covers read back as zero
     if (want_coeff) B200_CUDA_TRY(cudaMemsetAsync(base + o_coeff, 0, out_elems * 4, s));
     if (has_q) {
@@ -341,6 +412,7 @@ extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int b
       B200_CUDA_TRY(cudaMemsetAsync(base + o_dq, 0, out_elems * 4, s));
     }
   }
+  if (cmp && want_coeff) B200_CUDA_TRY(cudaMemsetAsync(base + o_coeff, 0, out_elems * 4, s));
   for (size_t gi = 0; gi < groups.size(); ++gi) {
     const Group &g = groups[gi];
     B200_CUDA_TRY(cudaMemcpyAsync(base + o_blocks + g.first * sizeof(B200TxBlock), sblocks + g.first,
@@ -354,7 +426,7 @@ extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int b
     l.in_kind = in_kind;
     l.q_kind = q_kind;
     l.bd = bd;
-    l.flags = flags & ~(want_err ? 0u : B200_TXQ_BLOCK_ERROR);
+    l.flags = flags & ~(want_err ? 0u : B200_TXQ_BLOCK_ERROR) & ~(want_coeff ? 0u : B200_TXQ_STORE_COEFF);
     l.n_blocks = (int)g.count;
     l.blocks = (const B200TxBlock *)(base + o_blocks) + g.first;
     l.preds = has_pred ? (const B200TxPred *)(base + o_preds) + g.first : nullptr;
@@ -368,6 +440,7 @@ extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int b
     l.dist = want_err ? (int64_t *)(base + o_dist) + 2 * g.first : nullptr;
     rc = txq_launch(ctx, l, s);
     if (rc != B200_OK) return rc;
+    if (cmp) continue;
     B200_CUDA_TRY(cudaEventRecord(ctx->group_done[gi], s));
     B200_CUDA_TRY(cudaStreamWaitEvent(cs, ctx->group_done[gi], 0));
     if (dense) {
@@ -380,31 +453,66 @@ extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int b
       }
     }
   }
-  if (!dense) {
+  size_t d2h = 0;
+  if (cmp) {
+    // pack the levels on the device; the host learns the total before it sizes the read-back
+    B200CompactLaunch cl;
+    cl.n_blocks = n_blocks;
+    cl.blocks = (const B200TxBlock *)(base + o_blocks);
+    cl.qcoeff = (const int32_t *)(base + o_qc);
+    cl.eob = (const uint16_t *)(base + o_eob);
+    cl.wide = wide;
+    cl.levels = base + o_lv;
+    cl.level_offset = (uint32_t *)(base + o_loff);
+    rc = b200_txq_compact_launch(ctx, &cl, s);
+    if (rc != B200_OK) return rc;
+    uint32_t *h_loff = (uint32_t *)(hbase + ho_loff);
+    B200_CUDA_TRY(cudaMemcpyAsync(h_loff, base + o_loff, (n + 1) * 4, cudaMemcpyDeviceToHost, s));
+    B200_CUDA_TRY(cudaMemcpyAsync(hbase + ho_eob, base + o_eob, n * 2, cudaMemcpyDeviceToHost, s));
+    B200_CUDA_TRY(cudaEventRecord(ctx->group_done[0], s));
+    B200_CUDA_TRY(cudaStreamWaitEvent(cs, ctx->group_done[0], 0));
+    // meanwhile the second stream brings the per-block distortion and the dense coeff back
+    if (want_err)
+      B200_CUDA_TRY(cudaMemcpyAsync(hbase + ho_dist, base + o_dist, n * 16, cudaMemcpyDeviceToHost, cs));
     if (want_coeff)
       B200_CUDA_TRY(cudaMemcpyAsync(coeff, base + o_coeff, out_elems * 4, cudaMemcpyDeviceToHost, cs));
-    if (has_q) {
-      B200_CUDA_TRY(cudaMemcpyAsync(qcoeff, base + o_qc, out_elems * 4, cudaMemcpyDeviceToHost, cs));
-      B200_CUDA_TRY(cudaMemcpyAsync(dqcoeff, base + o_dq, out_elems * 4, cudaMemcpyDeviceToHost, cs));
+    B200_CUDA_TRY(cudaStreamSynchronize(s));
+    const size_t total = h_loff[n];
+    if (total > cmp->levels_cap) {
+      cudaStreamSynchronize(cs);
+      set_error("b200_txq_batch_host_compact: %zu levels do not fit levels_cap %zu", total, cmp->levels_cap);
+      return B200_EINVAL;
     }
-  }
-  if (has_q)
-    B200_CUDA_TRY(cudaMemcpyAsync(hbase + ho_eob, base + o_eob, n * 2, cudaMemcpyDeviceToHost, cs));
-  if (want_err)
-    B200_CUDA_TRY(cudaMemcpyAsync(hbase + ho_dist, base + o_dist, n * 16, cudaMemcpyDeviceToHost, cs));
-  if (dense) {
-    // zero what no group covers, on the host, while the copies run
-    size_t at = 0;
-    for (const Group *g : by_lo) {
-      if (g->lo > at) {
-        if (want_coeff) memset(coeff + at, 0, (g->lo - at) * 4);
-        if (has_q) memset(qcoeff + at, 0, (g->lo - at) * 4), memset(dqcoeff + at, 0, (g->lo - at) * 4);
+    if (total)
+      B200_CUDA_TRY(cudaMemcpyAsync(cmp->levels, base + o_lv, total * lv_bytes, cudaMemcpyDeviceToHost, s));
+    d2h = (n + 1) * 4 + n * 2 + total * lv_bytes + (want_err ? n * 16 : 0) + (want_coeff ? out_elems * 4 : 0);
+  } else {
+    if (!dense) {
+      if (want_coeff)
+        B200_CUDA_TRY(cudaMemcpyAsync(coeff, base + o_coeff, out_elems * 4, cudaMemcpyDeviceToHost, cs));
+      if (has_q) {
+        B200_CUDA_TRY(cudaMemcpyAsync(qcoeff, base + o_qc, out_elems * 4, cudaMemcpyDeviceToHost, cs));
+        B200_CUDA_TRY(cudaMemcpyAsync(dqcoeff, base + o_dq, out_elems * 4, cudaMemcpyDeviceToHost, cs));
       }
-      at = g->hi;
     }
-    if (out_elems > at) {
-      if (want_coeff) memset(coeff + at, 0, (out_elems - at) * 4);
-      if (has_q) memset(qcoeff + at, 0, (out_elems - at) * 4), memset(dqcoeff + at, 0, (out_elems - at) * 4);
+    if (has_q)
+      B200_CUDA_TRY(cudaMemcpyAsync(hbase + ho_eob, base + o_eob, n * 2, cudaMemcpyDeviceToHost, cs));
+    if (want_err)
+      B200_CUDA_TRY(cudaMemcpyAsync(hbase + ho_dist, base + o_dist, n * 16, cudaMemcpyDeviceToHost, cs));
+    if (dense) {
+      // zero what no group covers, on the host, while the copies run
+      size_t at = 0;
+      for (const Group *g : by_lo) {
+        if (g->lo > at) {
+          if (want_coeff) memset(coeff + at, 0, (g->lo - at) * 4);
+          if (has_q) memset(qcoeff + at, 0, (g->lo - at) * 4), memset(dqcoeff + at, 0, (g->lo - at) * 4);
+        }
+        at = g->hi;
+      }
+      if (out_elems > at) {
+        if (want_coeff) memset(coeff + at, 0, (out_elems - at) * 4);
+        if (has_q) memset(qcoeff + at, 0, (out_elems - at) * 4), memset(dqcoeff + at, 0, (out_elems - at) * 4);
+      }
     }
   }
   B200_CUDA_TRY(cudaStreamSynchronize(cs));
@@ -414,14 +522,44 @@ extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int b
   if (in_order) {
     if (has_q && eob) memcpy(eob, eob_s, n * 2);
     if (want_err) memcpy(dist, dist_s, n * 16);
+    if (cmp) memcpy(cmp->level_offset, hbase + ho_loff, (n + 1) * 4);
   } else {
+    const uint32_t *loff_s = (const uint32_t *)(hbase + ho_loff);
     for (size_t i = 0; i < n; ++i) {
       if (has_q && eob) eob[order[i]] = eob_s[i];
       if (want_err) {
         dist[2 * (size_t)order[i]] = dist_s[2 * i];
         dist[2 * (size_t)order[i] + 1] = dist_s[2 * i + 1];
       }
+      // the levels stay packed in device-queue order; each block keeps its own offset
+      if (cmp) cmp->level_offset[order[i]] = loff_s[i];
     }
+    if (cmp) cmp->level_offset[n] = loff_s[n];
   }
+  if (cmp && cmp->d2h_bytes) *cmp->d2h_bytes = d2h;
   return B200_OK;
+}
+
+extern "C" int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int bd, unsigned flags,
+                                   const B200TxBlock *blocks, const B200TxPred *preds,
+                                   int n_blocks, const void *src, size_t src_elems,
+                                   const void *pred, size_t pred_elems, const B200QRow *qrows,
+                                   int n_qrows, int32_t *coeff, int32_t *qcoeff, int32_t *dqcoeff,
+                                   size_t out_elems, uint16_t *eob, int64_t *dist) {
+  return txq_batch_host_impl(ctx, in_kind, q_kind, bd, flags, blocks, preds, n_blocks, src, src_elems,
+                             pred, pred_elems, qrows, n_qrows, coeff, qcoeff, dqcoeff, out_elems, eob,
+                             dist, nullptr);
+}
+
+extern "C" int b200_txq_batch_host_compact(b200_ctx *ctx, int in_kind, int q_kind, int bd, unsigned flags,
+                                           const B200TxBlock *blocks, const B200TxPred *preds,
+                                           int n_blocks, const void *src, size_t src_elems,
+                                           const void *pred, size_t pred_elems, const B200QRow *qrows,
+                                           int n_qrows, size_t out_elems, void *levels,
+                                           size_t levels_cap, uint32_t *level_offset, uint16_t *eob,
+                                           int64_t *dist, int32_t *coeff, size_t *d2h_bytes) {
+  CompactOut c = { levels, levels_cap, level_offset, d2h_bytes };
+  return txq_batch_host_impl(ctx, in_kind, q_kind, bd, flags, blocks, preds, n_blocks, src, src_elems,
+                             pred, pred_elems, qrows, n_qrows, coeff, nullptr, nullptr, out_elems, eob,
+                             dist, &c);
 }

@@ -1,6 +1,7 @@
 // internal.h -- shared between the translation units of libb200av1.so (not installed).
 #pragma once
 #include <cuda_runtime.h>
+#include <math.h>
 #include <stdint.h>
 #include <stdio.h>
 
@@ -29,6 +30,20 @@ void set_error(const char *fmt, ...);
     }                                                                              \
   } while (0)
 
+// av1_cospi_arr_data (av1_txfm.c:18-60), bits 10..13: round(cos(j*pi/128) * 2^bit).  Returns
+// false when the computed table is not the reference's literal one (FNV-1a over the 256
+// entries, constant taken from the reference table), whatever the host libm does.
+inline bool fill_cospi_tables(int32_t (*cosv)[64]) {
+  const double pi = 3.14159265358979323846;
+  unsigned long long fnv = 0xcbf29ce484222325ull;
+  for (int b = 0; b < 4; ++b)
+    for (int j = 0; j < 64; ++j) {
+      cosv[b][j] = (int32_t)floor(cos(pi * j / 128.0) * (double)(1 << (10 + b)) + 0.5);
+      fnv = (fnv ^ (unsigned)cosv[b][j]) * 0x100000001b3ull;
+    }
+  return fnv == 0x66b250b93dc05948ull;
+}
+
 }  // namespace b200
 
 struct b200_ctx {
@@ -36,6 +51,8 @@ struct b200_ctx {
   int sm_count;
   cudaStream_t stream;
   int16_t *d_iscan;   // all inverse scan tables, see txq.cu
+  int16_t *d_scan;    // all forward scan tables, same layout (compact.cu)
+  uint32_t *d_partials;  // per-chunk sums of the compaction prefix sum (compact.cu)
   unsigned long long *d_pmask;  // scan prefix masks of the <= 64-sample sizes, see txq.cu
   // scratch for the host-buffer (drop-in) tier
   void *d_scratch;
@@ -54,6 +71,11 @@ int txq_init_device(b200_ctx *ctx);
 int txq_launch(b200_ctx *ctx, const B200TxqLaunch &l, cudaStream_t s);
 int blockops_init_device(b200_ctx *ctx);
 int me_init_device(b200_ctx *ctx);
+int compact_init_device(b200_ctx *ctx);
+// element offset of the scan tables of `tx_size` inside d_scan / d_iscan (3 classes of
+// max_eob entries each, see txq.cu) and the scan class of a tx_type
+size_t scan_dev_offset(int tx_size);
+__host__ __device__ inline int scan_class_of(int tx_type) { return tx_type < 10 ? 0 : ((tx_type & 1) ? 2 : 1); }
 int scratch_reserve(b200_ctx *ctx, size_t bytes);
 // hadamard.cu: single-call helpers behind the drop-in tier
 int int_pro_launch(b200_ctx *ctx, short *out, const unsigned char *ref, int ref_stride, int width,

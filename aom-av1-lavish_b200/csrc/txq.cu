@@ -102,6 +102,11 @@ static void build_scans() {
   g_iscan_total = off;
 }
 
+size_t scan_dev_offset(int tx_size) {
+  std::call_once(g_scan_once, build_scans);
+  return g_iscan_dev_offset[tx_size];
+}
+
 static int scan_class(int tx_type) { return tx_type < 10 ? 0 : ((tx_type & 1) ? 2 : 1); }
 
 int txq_init_device(b200_ctx *ctx) {
@@ -118,6 +123,13 @@ int txq_init_device(b200_ctx *ctx) {
              g_iscan[ts][cls].data(), g_iscan[ts][cls].size() * sizeof(int16_t));
   B200_CUDA_TRY(cudaMalloc(&ctx->d_iscan, all.size() * sizeof(int16_t)));
   B200_CUDA_TRY(cudaMemcpy(ctx->d_iscan, all.data(), all.size() * sizeof(int16_t),
+                           cudaMemcpyHostToDevice));
+  for (int ts = 0; ts < B200_TX_SIZES_ALL; ++ts)
+    for (int cls = 0; cls < 3; ++cls)
+      memcpy(all.data() + g_iscan_dev_offset[ts] + cls * g_scan[ts][cls].size(),
+             g_scan[ts][cls].data(), g_scan[ts][cls].size() * sizeof(int16_t));
+  B200_CUDA_TRY(cudaMalloc(&ctx->d_scan, all.size() * sizeof(int16_t)));
+  B200_CUDA_TRY(cudaMemcpy(ctx->d_scan, all.data(), all.size() * sizeof(int16_t),
                            cudaMemcpyHostToDevice));
   B200_CUDA_TRY(cudaMalloc(&ctx->d_pmask, g_pmask.size() * sizeof(unsigned long long)));
   B200_CUDA_TRY(cudaMemcpy(ctx->d_pmask, g_pmask.data(), g_pmask.size() * sizeof(unsigned long long),
@@ -150,6 +162,14 @@ int txq_launch(b200_ctx *ctx, const B200TxqLaunch &l, cudaStream_t s) {
   }
   if ((l.flags & B200_TXQ_STORE_COEFF) && !l.coeff) {
     set_error("b200_txq_launch: STORE_COEFF without coeff buffer");
+    return B200_EINVAL;
+  }
+  if (l.bd != 8 && l.bd != 10 && l.bd != 12) {
+    set_error("b200_txq_launch: bd must be 8, 10 or 12 (got %d)", l.bd);
+    return B200_EINVAL;
+  }
+  if (l.q_kind < B200_Q_NONE || l.q_kind > B200_Q_B_HBD) {
+    set_error("b200_txq_launch: bad q_kind %d", l.q_kind);
     return B200_EINVAL;
   }
   if (l.n_blocks == 0) return B200_OK;
@@ -201,6 +221,11 @@ extern "C" int b200_tx_valid(int tx_size, int tx_type) {
     if (dims[i] == 32 && (kinds[i] == 1 || kinds[i] == 2)) return 0;
   }
   return 1;
+}
+extern "C" const int32_t *b200_cospi(int bit) {
+  static int32_t t[4][64];
+  static const bool ok = b200::fill_cospi_tables(t);
+  return ok && bit >= 10 && bit <= 13 ? t[bit - 10] : nullptr;
 }
 extern "C" const int16_t *b200_scan(int tx_size, int tx_type) {
   std::call_once(b200::g_scan_once, b200::build_scans);

@@ -2,8 +2,6 @@
 // the kernel for a few transform sizes (parallel compilation) and owns a private copy of
 // the cosine tables in constant memory, which it uploads in its init function.
 #pragma once
-#include <math.h>
-
 #include "txq_kernel.cuh"
 #include "txq_small.cuh"
 
@@ -11,13 +9,12 @@ namespace b200 {
 
 static int upload_txfm_constants() {
   int32_t cosv[4][64], ncosv[4][64];
-  const double pi = 3.14159265358979323846;
+  if (!fill_cospi_tables(cosv)) {
+    set_error("cospi table differs from av1_cospi_arr_data (host libm rounding?)");
+    return B200_EINVAL;
+  }
   for (int b = 0; b < 4; ++b)
-    for (int j = 0; j < 64; ++j) {
-      // av1_cospi_arr_data (av1_txfm.c:18-60): round(cos(j*pi/128) * 2^(10+b))
-      cosv[b][j] = (int32_t)floor(cos(pi * j / 128.0) * (double)(1 << (10 + b)) + 0.5);
-      ncosv[b][j] = -cosv[b][j];
-    }
+    for (int j = 0; j < 64; ++j) ncosv[b][j] = -cosv[b][j];
   // av1_sinpi_arr_data (av1_txfm.c:62-69), bits 10..13: round(sqrt2*sin(j*pi/9)*2/3 * 2^bit)
   // with entries 1 and 2 adjusted by the codec so that s1 + s2 == s4
   const int32_t sinv[4][5] = { { 0, 330, 621, 836, 951 },

@@ -43,6 +43,29 @@ class TxqLaunch(C.Structure):
                 ("dqcoeff", C.c_void_p), ("eob", C.c_void_p), ("dist", C.c_void_p)]
 
 
+class CompactLaunch(C.Structure):
+    _fields_ = [("n_blocks", C.c_int), ("blocks", C.c_void_p), ("qcoeff", C.c_void_p),
+                ("eob", C.c_void_p), ("wide", C.c_int), ("levels", C.c_void_p),
+                ("level_offset", C.c_void_p)]
+
+
+def expand_compact(blocks, qrows, levels, level_offset, eob, out_elems, wide=False):
+    """host-side expansion of a compact batch into dense qcoeff / dqcoeff (b200_txq_expand_block
+    per block)"""
+    qc = np.zeros(out_elems, np.int32)
+    dq = np.zeros(out_elems, np.int32)
+    L = lib()
+    isz = levels.itemsize
+    for i, b in enumerate(blocks):
+        oo = int(b["out_offset"])
+        row = qrows[int(b["qrow"]):int(b["qrow"]) + 1]
+        check(L.b200_txq_expand_block(int(b["tx_size"]), int(b["tx_type"]),
+                                      C.c_void_p(levels.ctypes.data + int(level_offset[i]) * isz),
+                                      int(wide), int(eob[i]), vp(row),
+                                      C.c_void_p(qc.ctypes.data + oo * 4), C.c_void_p(dq.ctypes.data + oo * 4)))
+    return qc, dq
+
+
 _lib = None
 
 
@@ -112,6 +135,17 @@ class Context:
             C.c_size_t(src.size), vp(pred), C.c_size_t(0 if pred is None else pred.size),
             vp(qrows), 0 if qrows is None else len(qrows), vp(coeff), vp(qcoeff), vp(dqcoeff),
             C.c_size_t(out_elems), vp(eob), vp(dist)))
+
+    def txq_batch_host_compact(self, in_kind, q_kind, bd, flags, blocks, preds, src, pred, qrows,
+                               out_elems, levels, level_offset, eob, dist=None, coeff=None):
+        """b200_txq_batch_host_compact; returns the bytes that crossed PCIe towards the host"""
+        d2h = C.c_size_t(0)
+        check(lib().b200_txq_batch_host_compact(
+            self.h, in_kind, q_kind, bd, C.c_uint(flags), vp(blocks), vp(preds), len(blocks), vp(src),
+            C.c_size_t(src.size), vp(pred), C.c_size_t(0 if pred is None else pred.size),
+            vp(qrows), 0 if qrows is None else len(qrows), C.c_size_t(out_elems), vp(levels),
+            C.c_size_t(levels.size), vp(level_offset), vp(eob), vp(dist), vp(coeff), C.byref(d2h)))
+        return d2h.value
 
     def txq_launch(self, launch, stream=None):
         check(lib().b200_txq_launch(self.h, C.byref(launch), C.c_void_p(stream)))

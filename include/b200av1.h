@@ -82,6 +82,9 @@ int b200_tx_wide(int tx_size);
 int b200_tx_high(int tx_size);
 int b200_tx_max_eob(int tx_size);
 int b200_tx_valid(int tx_size, int tx_type);
+/* Host copy of the cosine table the kernels use, av1_cospi_arr(bit) (av1/common/av1_txfm.c:18),
+ * bit = 10..13; NULL when the table failed its self-check against the reference's literal. */
+const int32_t *b200_cospi(int bit);
 /* Host copy of scan / iscan of av1_scan_orders[tx_size][tx_type] (scan.c:1666). */
 const int16_t *b200_scan(int tx_size, int tx_type);
 const int16_t *b200_iscan(int tx_size, int tx_type);
@@ -182,6 +185,47 @@ int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int bd, unsigned
                         int32_t *coeff, int32_t *qcoeff, int32_t *dqcoeff,
                         size_t out_elems, uint16_t *eob, int64_t *dist);
 
+
+/* ------------------------------------------------ compact result format ---------- */
+/* What the encoder consumes after the quantiser is the levels in SCAN order up to eob
+ * (av1_write_coeffs_txb / av1_cost_coeffs_txb, av1/encoder/encodetxb.c) and dqcoeff is a
+ * function of the level ((|q| * dequant[rc != 0]) >> log_scale, av1_quantize.c:61-63), so the
+ * dense int32 coeff + qcoeff + dqcoeff arrays (12 bytes per sample) need not cross PCIe.
+ * Compact form of a batch: block i owns eob[i] consecutive levels at level_offset[i]
+ * (exclusive prefix sum of eob in batch order; level_offset[n_blocks] = total), int16 for
+ * the low-bit-depth quantisers (levels are clamped to int16 there, av1_quantize.c:48-52),
+ * int32 (`wide`) for the high-bit-depth ones. */
+typedef struct {
+  int n_blocks;
+  const B200TxBlock *blocks; /* device: tx_size, tx_type and out_offset are read */
+  const int32_t *qcoeff;     /* device: dense qcoeff as b200_txq_launch wrote it */
+  const uint16_t *eob;       /* device, n_blocks */
+  int wide;                  /* 0: int16 levels, 1: int32 levels */
+  void *levels;              /* device out: packed levels (capacity >= sum of eob) */
+  uint32_t *level_offset;    /* device out: n_blocks + 1 entries */
+} B200CompactLaunch;
+int b200_txq_compact_launch(b200_ctx *ctx, const B200CompactLaunch *launch, void *stream);
+
+/* Host-buffer call returning the compact form: like b200_txq_batch_host, but the dense
+ * qcoeff / dqcoeff stay on the device; the host receives eob, level_offset (n_blocks + 1),
+ * the packed levels (at most levels_cap elements of 2 or 4 bytes: `wide` = q_kind is a
+ * high-bit-depth quantiser), optionally {error, ssz} per block (B200_TXQ_BLOCK_ERROR) and
+ * optionally the dense coeff (B200_TXQ_STORE_COEFF; trellis wants it, TPL's
+ * txfm_quant_rdcost, tpl_model.c:228, does not).  *d2h_bytes (optional) receives the bytes
+ * that crossed PCIe towards the host.  Fails with B200_EINVAL when levels_cap is too small. */
+int b200_txq_batch_host_compact(b200_ctx *ctx, int in_kind, int q_kind, int bd, unsigned flags,
+                                const B200TxBlock *blocks, const B200TxPred *preds, int n_blocks,
+                                const void *src, size_t src_elems, const void *pred,
+                                size_t pred_elems, const B200QRow *qrows, int n_qrows,
+                                size_t out_elems, void *levels, size_t levels_cap,
+                                uint32_t *level_offset, uint16_t *eob, int64_t *dist,
+                                int32_t *coeff, size_t *d2h_bytes);
+
+/* Host-side expander of one block of the compact form into the dense arrays the quantisers
+ * (without qmatrix) write: qcoeff[scan[i]] = level i, dqcoeff from the row's dequant.  Either
+ * output may be NULL. */
+int b200_txq_expand_block(int tx_size, int tx_type, const void *levels, int wide, int eob,
+                          const B200QRow *row, int32_t *qcoeff, int32_t *dqcoeff);
 
 /* ------------------------------------------------ stand-alone quantiser batch ---- */
 /* The quantisers as separate launches over coefficient buffers that already sit in

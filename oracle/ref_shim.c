@@ -305,3 +305,33 @@ void refshim_full_pixel_search(const Av1oMeParams *p, Av1oMeResult *r) { fullpel
 
 /* av1_refining_search_8p_c (mcomp.c:1683), single reference */
 void refshim_refining_search_8p(const Av1oMeParams *p, Av1oMeResult *r) { fullpel_common(p, r, 1); }
+
+/* quantize_fp_helper_c / highbd_quantize_fp_helper_c WITH a qmatrix are static
+ * (av1_quantize.c:70,125); the only way in is the facade with a hand-filled
+ * MACROBLOCK_PLANE + QUANT_PARAM (av1_quantize.c:266, :423). */
+void refshim_quantize_fp_qm(const int32_t *coeff, intptr_t n, const int16_t *zbin,
+                            const int16_t *round_fp, const int16_t *quant_fp,
+                            const int16_t *quant_shift, int32_t *qcoeff, int32_t *dqcoeff,
+                            const int16_t *dequant, uint16_t *eob, const int16_t *scan,
+                            const int16_t *iscan, const uint8_t *qm, const uint8_t *iqm,
+                            int log_scale, int highbd) {
+  MACROBLOCK_PLANE p;
+  memset(&p, 0, sizeof(p));
+  p.zbin_QTX = zbin;
+  p.round_fp_QTX = round_fp;
+  p.quant_fp_QTX = quant_fp;
+  p.quant_shift_QTX = quant_shift;
+  p.dequant_QTX = dequant;
+  SCAN_ORDER sc;
+  sc.scan = scan;
+  sc.iscan = iscan;
+  QUANT_PARAM qp;
+  memset(&qp, 0, sizeof(qp));
+  qp.log_scale = log_scale;
+  qp.qmatrix = qm;
+  qp.iqmatrix = iqm;
+  if (highbd)
+    av1_highbd_quantize_fp_facade(coeff, n, &p, qcoeff, dqcoeff, eob, &sc, &qp);
+  else
+    av1_quantize_fp_facade(coeff, n, &p, qcoeff, dqcoeff, eob, &sc, &qp);
+}

@@ -55,6 +55,17 @@ def test_host_tables_match_oracle():
             assert np.array_equal(np.ctypeslib.as_array(L.b200_iscan(ts, tt), shape=(n,)), i)
 
 
+def test_cospi_table_matches_oracle():
+    """the kernels' cosine table is computed with the host libm; it must equal the reference's
+    literal av1_cospi_arr_data (pinned in the oracle) -- the library also self-checks it"""
+    import b200av1
+    L, O = b200av1.lib(), H.oracle()
+    L.b200_cospi.restype = C.POINTER(C.c_int32)
+    for bit in range(10, 14):
+        got = np.ctypeslib.as_array(L.b200_cospi(bit), shape=(64,))
+        assert np.array_equal(got, np.ctypeslib.as_array(O.av1o_cospi(bit), shape=(64,)))
+
+
 def test_no_gpu_fails_loudly():
     import b200av1
     if b200av1.lib().b200_device_count() > 0:

@@ -79,7 +79,7 @@ def me_launch(ctx, cur, refb, params, tables_dev, subpel, window_bytes):
     return b200av1.to_host(ctx, d_res, b200av1.MERESULT_DTYPE, n)
 
 
-@pytest.mark.parametrize("bd", [8, 10])
+@pytest.mark.parametrize("bd", [8, 10, 12])
 def test_fullpel_batch_vs_oracle(ctx, bd):
     O = H.oracle()
     rng = np.random.default_rng(700 + bd)
@@ -109,7 +109,7 @@ def test_fullpel_batch_vs_oracle(ctx, bd):
                     assert tuple(int(v) for v in g["cost_list"]) == tuple(e.cost_list), tag
 
 
-@pytest.mark.parametrize("bd", [8, 10])
+@pytest.mark.parametrize("bd", [8, 10, 12])
 def test_subpel_batch_vs_oracle(ctx, bd):
     O = H.oracle()
     rng = np.random.default_rng(800 + bd)
@@ -215,7 +215,7 @@ def test_fullpel_mesh_patterns(ctx, pattern):
                 (pattern, trial, i, p.bw, p.bh, p.use_skip_sad, p.fine_search_interval)
 
 
-@pytest.mark.parametrize("bd", [8, 10])
+@pytest.mark.parametrize("bd", [8, 10, 12])
 def test_pattern_search_methods(ctx, bd):
     """HEX / BIGDIA / SQUARE / FAST_HEX / FAST_DIAMOND / FAST_BIGDIA / VFAST_DIAMOND
     (pattern_search, mcomp.c:1017-1316) with and without a cost list, staged window and
@@ -253,7 +253,7 @@ def test_pattern_search_methods(ctx, bd):
                     assert (int(g["second_row"]), int(g["second_col"])) == (e.second_row, e.second_col), tag
 
 
-@pytest.mark.parametrize("bd", [8, 10])
+@pytest.mark.parametrize("bd", [8, 10, 12])
 @pytest.mark.parametrize("tree", [1, 2])
 def test_subpel_pruned_batch_vs_oracle(ctx, bd, tree):
     """av1_find_best_sub_pixel_tree_pruned / _pruned_more through b200_me_subpel_launch
@@ -321,7 +321,7 @@ def test_fullpel_cost_list_chains_into_pruned_subpel(ctx):
                 int(g["sse"])) == e.key(True), (i, p.bw, p.sp_tree)
 
 
-@pytest.mark.parametrize("bd", [8, 10])
+@pytest.mark.parametrize("bd", [8, 10, 12])
 def test_refining_search_8p_batch_vs_oracle(ctx, bd):
     """av1_refining_search_8p_c through b200_me_fullpel_launch (search_method = B200_ME_REFINE_8P)"""
     import b200av1

@@ -20,7 +20,7 @@ def run_both(fn_o, fn_r, p, subpel=False):
     return a.key(subpel), b.key(subpel)
 
 
-@pytest.mark.parametrize("bd", [8, 10])
+@pytest.mark.parametrize("bd", [8, 10, 12])
 def test_full_pixel_search_vs_reference(bd):
     O, R = H.oracle(), H.ref()
     rng = np.random.default_rng(300 + bd)
@@ -44,7 +44,7 @@ def test_init_search_range():
         assert O.av1o_init_search_range(size) == R.av1_init_search_range(size)
 
 
-@pytest.mark.parametrize("bd", [8, 10])
+@pytest.mark.parametrize("bd", [8, 10, 12])
 def test_sub_pixel_tree_vs_reference(bd):
     O, R = H.oracle(), H.ref()
     rng = np.random.default_rng(400 + bd)
@@ -62,7 +62,7 @@ def test_sub_pixel_tree_vs_reference(bd):
 PATTERN_METHODS = [4, 5, 6, 7, 8, 9, 10]  # HEX, BIGDIA, SQUARE, FAST_HEX, FAST_DIAMOND, FAST_BIGDIA, VFAST_DIAMOND
 
 
-@pytest.mark.parametrize("bd", [8, 10])
+@pytest.mark.parametrize("bd", [8, 10, 12])
 def test_pattern_search_vs_reference(bd):
     """pattern_search family (mcomp.c:1017-1316): with and without a cost list (the cost
     list changes the last scale of the BIGDIA family), limits clipped at the frame edge,
@@ -86,7 +86,7 @@ def test_pattern_search_vs_reference(bd):
     assert n == 6 * len(M.FULLPEL_SIZES) * len(PATTERN_METHODS)
 
 
-@pytest.mark.parametrize("bd", [8, 10])
+@pytest.mark.parametrize("bd", [8, 10, 12])
 @pytest.mark.parametrize("tree", [1, 2])
 def test_sub_pixel_tree_pruned_vs_reference(bd, tree):
     """av1_find_best_sub_pixel_tree_pruned (mcomp.c:2992) / _pruned_more (:2907): with no
@@ -107,7 +107,7 @@ def test_sub_pixel_tree_pruned_vs_reference(bd, tree):
                                 p.sp_have_cost_list, list(p.sp_cost_list), a, b)
 
 
-@pytest.mark.parametrize("bd", [8, 10])
+@pytest.mark.parametrize("bd", [8, 10, 12])
 def test_refining_search_8p_vs_reference(bd):
     """av1_refining_search_8p_c (mcomp.c:1683), single reference"""
     O, R = H.oracle(), H.ref()

@@ -263,6 +263,40 @@ def test_quantize_b_helper_qmatrix():
                 assert np.array_equal(res[0][1], res[1][1])
 
 
+def test_quantize_fp_qmatrix_via_facade():
+    """quantize_fp_helper_c / highbd_quantize_fp_helper_c with a qmatrix (av1_quantize.c:96-120,
+    :150-169) are static: reached through av1_quantize_fp_facade / av1_highbd_quantize_fp_facade
+    with a hand-filled MACROBLOCK_PLANE + QUANT_PARAM (oracle/ref_shim.c)."""
+    R, O = H.ref(), H.oracle()
+    rng = np.random.default_rng(12)
+    for highbd, oname in ((0, "av1o_quantize_fp"), (1, "av1o_highbd_quantize_fp")):
+        for ts in (0, 1, 2, 3, 4, 9, 13, 18):
+            n, ls = H.max_eob(ts), H.log_scale(ts)
+            for it in range(12):
+                bd = (10, 12)[it % 2] if highbd else 8
+                row = H.oracle_qrow(bd, int(rng.integers(0, 256)))
+                scan, iscan = H.oracle_scan(ts, 0)
+                coeff = _fill_coeff(rng, n, bd, ("rand", "sparse", "neg")[it % 3], highbd)
+                qm = rng.integers(16, 200, n).astype(np.uint8)
+                iqm = rng.integers(16, 200, n).astype(np.uint8)
+                res = []
+                for which in (0, 1):
+                    qc = np.zeros(n, np.int32)
+                    dq = np.zeros(n, np.int32)
+                    eob = C.c_uint16(0)
+                    args = [ptr(coeff, i32p), C.c_ssize_t(n), row.zbin, row.round_fp, row.quant_fp,
+                            row.quant_shift, ptr(qc, i32p), ptr(dq, i32p), row.dequant, C.byref(eob),
+                            ptr(scan, i16p), ptr(iscan, i16p), ptr(qm, u8p), ptr(iqm, u8p), ls]
+                    if which == 0:
+                        R.refshim_quantize_fp_qm(*args, highbd)
+                    else:
+                        getattr(O, oname)(*args)
+                    res.append((qc, dq, eob.value))
+                assert res[0][2] == res[1][2], (oname, ts, bd, it)
+                assert np.array_equal(res[0][0], res[1][0]), (oname, ts, bd, it)
+                assert np.array_equal(res[0][1], res[1][1]), (oname, ts, bd, it)
+
+
 def test_quantize_lp():
     R, O = H.ref(), H.oracle()
     rng = np.random.default_rng(12)

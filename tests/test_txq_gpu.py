@@ -195,3 +195,93 @@ def test_txq_fused_subtract_from_planes(ctx, bd):
         r = H.oracle_txq_batch(src, blocks, rows, q_kind, bd, out_elems, in_kind, pred, preds)
         for a, b in zip((coeff, qc, dq, eob, dist), r):
             assert np.array_equal(a, b), (H.TX_NAMES[ts], bd)
+
+
+@pytest.mark.parametrize("q_kind", [1, 2, 3, 4], ids=["fp", "fp_hbd", "b", "b_hbd"])
+def test_txq_compact_expands_to_dense_oracle(ctx, q_kind):
+    """b200_txq_batch_host_compact: eob + packed levels in scan order (int16, int32 for the
+    high-bit-depth quantisers) + offsets; b200_txq_expand_block(compact) must equal the oracle's
+    dense qcoeff / dqcoeff bit for bit (dqcoeff = (|q| * dequant[rc != 0]) >> log_scale,
+    av1_quantize.c:61-63), shuffled mixed-size queue, with and without the dense coeff."""
+    import b200av1
+    bd = 8 if q_kind in (1, 3) else 12
+    rng = np.random.default_rng(6100 + q_kind)
+    qidx = [0, 40, 128, 255]
+    parts, srcs, off_src, off_out = [], [], 0, 0
+    for ts in range(19):
+        mode = ("rand", "small", "max")[ts % 3]
+        src, blocks, out_elems = _make_batch(rng, ts, 2, bd, mode, qidx)
+        blocks["src_offset"] += off_src
+        blocks["out_offset"] += off_out
+        off_src += len(src)
+        off_out += out_elems
+        parts.append(blocks)
+        srcs.append(src)
+    blocks = np.concatenate(parts)
+    rng.shuffle(blocks)
+    src = np.concatenate(srcs)
+    rows = [H.oracle_qrow(bd, q) for q in qidx]
+    qrows = np.array([b200av1.qrow_from_oracle(r) for r in rows], b200av1.QROW_DTYPE)
+    r = H.oracle_txq_batch(src, blocks, rows, q_kind, bd, off_out)
+    wide = q_kind in (2, 4)
+    for with_coeff in (0, 1):
+        levels = np.full(off_out, 0x5a5a, np.int32 if wide else np.int16)
+        loff = np.zeros(len(blocks) + 1, np.uint32)
+        eob = np.zeros(len(blocks), np.uint16)
+        dist = np.zeros((len(blocks), 2), np.int64)
+        coeff = np.full(off_out, 7, np.int32) if with_coeff else None
+        flags = b200av1.TXQ_BLOCK_ERROR | (b200av1.TXQ_STORE_COEFF if with_coeff else 0)
+        d2h = ctx.txq_batch_host_compact(b200av1.IN_RESIDUAL, q_kind, bd, flags, blocks, None, src,
+                                         None, qrows, off_out, levels, loff, eob, dist, coeff)
+        assert np.array_equal(eob, r[3])
+        assert np.array_equal(dist, r[4])
+        assert int(loff[-1]) == int(eob.astype(np.int64).sum())
+        qc, dq = b200av1.expand_compact(blocks, qrows, levels, loff, eob, off_out, wide)
+        assert np.array_equal(qc, r[1])
+        assert np.array_equal(dq, r[2])
+        if with_coeff:
+            assert np.array_equal(coeff, r[0])
+        dense_bytes = off_out * 12 + len(blocks) * 2
+        assert d2h < dense_bytes
+    # a levels buffer that is too small is refused, not overrun
+    small = np.zeros(max(1, int(loff[-1]) // 2), levels.dtype)
+    with pytest.raises(b200av1.B200Error):
+        ctx.txq_batch_host_compact(b200av1.IN_RESIDUAL, q_kind, bd, 0, blocks, None, src, None, qrows,
+                                   off_out, small, loff, eob)
+
+
+def test_txq_batch_host_rejects_out_of_bounds_descriptors(ctx):
+    """descriptors that read outside src / qrows are refused on the host (never launched)"""
+    import b200av1
+    rng = np.random.default_rng(9)
+    src, blocks, out_elems = _make_batch(rng, 1, 1, 8, "rand", [0])
+    rows = [H.oracle_qrow(8, 50)]
+    qrows = np.array([b200av1.qrow_from_oracle(r) for r in rows], b200av1.QROW_DTYPE)
+    coeff, qc, dq = (np.zeros(out_elems, np.int32) for _ in range(3))
+    eob = np.zeros(len(blocks), np.uint16)
+    for field, val in (("src_offset", len(src)), ("qrow", 3)):
+        bad = blocks.copy()
+        bad[field][0] = val
+        with pytest.raises(b200av1.B200Error):
+            ctx.txq_batch_host(b200av1.IN_RESIDUAL, b200av1.Q_FP, 8, b200av1.TXQ_STORE_COEFF, bad, None,
+                               src, None, qrows, coeff, qc, dq, eob, None)
+
+
+def test_txq_batch_host_overlapping_blocks_take_the_safe_path(ctx):
+    """two blocks sharing an out_offset plus one gap have the 'dense' range length; the slot
+    bitmap must detect it so the gap reads back as zero, not as uninitialised scratch"""
+    import b200av1
+    rng = np.random.default_rng(10)
+    n = H.max_eob(1)
+    src = rng.integers(-255, 256, 8 * 64).astype(np.int16)
+    blocks = np.zeros(3, b200av1.TXBLOCK_DTYPE)
+    for i, oo in enumerate((0, 0, 2 * n)):   # slot 1 is never written
+        blocks[i] = (i * 8, oo, 64, 0, 1, 0, 0)
+    rows = [H.oracle_qrow(8, 50)]
+    qrows = np.array([b200av1.qrow_from_oracle(r) for r in rows], b200av1.QROW_DTYPE)
+    for _ in range(2):  # second call: the device scratch holds the first call's data
+        coeff, qc, dq = (np.full(3 * n, 99, np.int32) for _ in range(3))
+        eob = np.zeros(3, np.uint16)
+        ctx.txq_batch_host(b200av1.IN_RESIDUAL, b200av1.Q_FP, 8, b200av1.TXQ_STORE_COEFF, blocks, None,
+                           src, None, qrows, coeff, qc, dq, eob, None)
+        assert not coeff[n:2 * n].any() and not qc[n:2 * n].any() and not dq[n:2 * n].any()
