@@ -17,6 +17,8 @@
 #include <limits.h>
 #include <string.h>
 
+#include <cuda.h>
+
 #include "internal.h"
 
 namespace b200 {
@@ -44,7 +46,8 @@ struct Sites {
 struct Ctx {
   // per-search constants (CTA-uniform)
   const B200MeLaunch *l;
-  B200MeBlock d;
+  const B200MeBlock &d;  // the search descriptor, copied to shared memory at kernel start (a
+                         // by-value copy lands in local memory: its byte fields defeat SROA)
   const Sites *sites;
   // pixel views
   const unsigned char *src;  // shared, dense pitch = bw pixels
@@ -58,20 +61,84 @@ struct Ctx {
   int l1_mul;                // 32 / 15 / 8 for the L1 cost types, 0 otherwise
   int px;                    // bytes per pixel
   int sad_shift;             // 0 / 2 / 4: encoder_utils.h:153-208
-  unsigned *cand;            // shared: kMaxCand totals
-  int *bcast;                // shared scratch for broadcasts
-  long long *red;            // shared: 2 * kWarps partial sums (CTA-wide variance)
+  int col_min, col_max, row_min, row_max;  // register copies of d's mv limits (tested per candidate)
+  __device__ explicit Ctx(const B200MeBlock &desc) : d(desc) {}
 };
+__shared__ B200MeBlock g_desc;
+// CTA scratch, file scope so that every access is an LDS / STS / ATOMS (through a pointer in
+// Ctx the compiler lost the address space: generic loads and ATOM.E on shared memory)
+__shared__ unsigned g_cand[kMaxCand + 64];  // candidate totals of a step / a mesh chunk
+__shared__ int g_bcast[32];                 // broadcast slots
+__shared__ long long g_red[2 * kWarps];     // partial sums of the CTA-wide variance
+constexpr int kMaxRuns = 16;                // runs of full_pixel_diamond evaluated side by side
+__shared__ int g_cda[kMaxRuns * 16];        // n-step: window byte address of the candidates, or -1
+__shared__ int g_cdp[kMaxRuns * 16];        // n-step: their positions, (row & 0xffff) | col << 16
+__shared__ int g_runn[kMaxRuns];            // n-step: candidates of run r in this round (0 = finished)
+__shared__ int g_runres[kMaxRuns][8];       // n-step: per run {best row, col, second row, col, sad, num00, moved}
+// Copies descriptor `bi` into shared memory (11 words) and synchronises the CTA.
+__device__ __forceinline__ void load_desc(const B200MeLaunch &l, int bi) {
+  static_assert(sizeof(B200MeBlock) == 44, "descriptor is 11 words");
+  if (threadIdx.x < 11)
+    reinterpret_cast<int *>(&g_desc)[threadIdx.x] = reinterpret_cast<const int *>(l.blocks + bi)[threadIdx.x];
+  __syncthreads();
+}
 
 // Dynamic shared memory of both kernels: source block at offset 0, then the staged reference
 // window.  The hot SAD loops address it through this array (not through the generic
 // pointers of Ctx) so that the compiler emits LDS with 32-bit addresses instead of generic
 // loads with 64-bit address arithmetic.
-extern __shared__ __align__(16) unsigned char me_smem[];
+extern __shared__ __align__(128) unsigned char me_smem[];
 // The search-site table of the CTA's method (copied from global memory at kernel start).
 __shared__ Sites g_sites;
 __device__ __forceinline__ const unsigned *smem_words(int byte_off) {
   return reinterpret_cast<const unsigned *>(me_smem + byte_off);
+}
+
+// ---- TMA staging -----------------------------------------------------------------------
+// With plane extents known (B200MeLaunch.cur_rows / ref_rows), 16-byte aligned bases and
+// strides, the source block and the search window are brought into shared memory by the TMA
+// engine: one thread arms an mbarrier with the byte count and issues cp.async.bulk.tensor.2d
+// boxes (tensor of 32-bit words, so a box row may be up to 1 KB), the CTA waits on the
+// barrier's phase.  The boxes have a fixed size per launch (the tensor map holds it): the
+// window box is `win_pitch_w` words x kTmaRows rows and a search issues as many as its own
+// window height needs; out-of-bounds parts of a box are zero-filled by the hardware and are
+// never read.  Destination pitches are 4 (mod 8) words like the cooperative copy's, so the
+// vector SAD paths stay conflict-free.
+constexpr int kTmaRows = 64;
+struct TmaCfg {
+  int use;          // 0: cooperative copy
+  int win_pitch_w;  // words per window row in shared memory (= box width)
+  int src_pitch_w;  // words per source row in shared memory (= box width)
+  int src_rows;     // source box height
+};
+__shared__ __align__(8) unsigned long long g_mbar;
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) {
+  return (unsigned)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned phase) {
+  asm volatile(
+      "{\n\t.reg .pred P1;\n\tLAB_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+      "@P1 bra DONE;\n\tbra LAB_WAIT;\n\tDONE:\n\t}" ::"r"(smem_u32(bar)),
+      "r"(phase)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, int x, int y,
+                                            unsigned long long *bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::
+          "r"(smem_u32(dst)),
+      "l"(reinterpret_cast<unsigned long long>(map)), "r"(smem_u32(bar)), "r"(x), "r"(y)
+      : "memory");
 }
 
 // ------------------------------------------------------------------- mv cost -----
@@ -84,6 +151,7 @@ __device__ __forceinline__ int mv_cost_tab(const Ctx &k, int dr, int dc) {
 // mvsad_err_cost (mcomp.c:329).  The full-pel reference mv (GET_MV_RAWPEL of ref_mv) and the
 // L1 weight of the cost type are per-search constants kept in Ctx (init_costs).
 __device__ __forceinline__ void init_costs(Ctx &k) {
+  k.col_min = k.d.col_min, k.col_max = k.d.col_max, k.row_min = k.d.row_min, k.row_max = k.d.row_max;
   const int rr = k.d.ref_mv_row, rc = k.d.ref_mv_col;
   k.cost_fr = (rr + 3 + (rr >= 0)) >> 3;
   k.cost_fc = (rc + 3 + (rc >= 0)) >> 3;
@@ -93,6 +161,7 @@ __device__ __forceinline__ void init_costs(Ctx &k) {
 __device__ __forceinline__ int sad_cost(const Ctx &k, int row, int col) {
   const int dr = (short)((row - k.cost_fr) * 8), dc = (short)((col - k.cost_fc) * 8);
   if (k.d.mv_cost_type == B200_MV_COST_ENTROPY) {
+    if (!k.l->mvcost[0]) return 0;  // no tables given with the launch (me_check pairs them up)
     const unsigned c = (unsigned)mv_cost_tab(k, dr, dc) * (unsigned)k.d.sad_per_bit;
     return (int)((c + 256u) >> 9);
   }
@@ -113,11 +182,11 @@ __device__ __forceinline__ int err_cost(const Ctx &k, int row, int col) {
 }
 
 __device__ __forceinline__ bool in_range(const Ctx &k, int row, int col) {
-  return col >= k.d.col_min && col <= k.d.col_max && row >= k.d.row_min && row <= k.d.row_max;
+  return col >= k.col_min && col <= k.col_max && row >= k.row_min && row <= k.row_max;
 }
 __device__ __forceinline__ Mv clamp_mv(const Ctx &k, Mv m) {
-  m.col = min(max(m.col, (int)k.d.col_min), (int)k.d.col_max);
-  m.row = min(max(m.row, (int)k.d.row_min), (int)k.d.row_max);
+  m.col = min(max(m.col, k.col_min), k.col_max);
+  m.row = min(max(m.row, k.row_min), k.row_max);
   return m;
 }
 
@@ -460,6 +529,158 @@ __device__ __forceinline__ unsigned sad_finish(const Ctx &k, unsigned acc, bool 
 }
 __device__ __forceinline__ unsigned warp_sad(const Ctx &k, int row, int col, bool skip, int lane) {
   return sad_finish(k, warp_sad_part(k, row, col, skip, 0, 1), skip);
+}
+
+// ---- CTA-cooperative evaluation of a step's candidates (staged 8-bit path) ----------
+// One warp per candidate re-reads the source block from shared memory for every candidate
+// (4 KB + 6 KB per 64x64 candidate) and pays four dependent row passes per warp: the n-step
+// phase was bound by shared-memory bandwidth and latency.  Here a LANE owns one row segment
+// of up to 64 pixels (SEGW words) whose source words stay in registers for the whole step,
+// task = pass * 32 + lane with a quarter warp = 8 consecutive rows of one segment column
+// (pitches of 4 mod 8 words: conflict-free uint4 reads), and a warp walks the step's
+// candidates over its rows: SEGW/4 + 1 LDS.128, SEGW SHF, SEGW VABSDIFF4 per candidate.
+// A 64x64 block is two passes, so the 8 warps form 4 candidate groups.  Warp totals are added
+// into out[i] with shared-memory atomics: out[0 .. n) must be zero on entry.  Candidates
+// outside the mv limits are skipped (their slot stays 0; callers test in_range again).
+// Lane i of every warp derives candidate i's window address once per step; the loop
+// fetches it with a shuffle.  All control flow is warp-uniform.
+template <int N>
+__device__ __forceinline__ void load_words(const unsigned *p, unsigned (&o)[N]) {
+  if constexpr (N >= 4) {
+#pragma unroll
+    for (int v = 0; v < N / 4; ++v) {
+      const uint4 t = reinterpret_cast<const uint4 *>(p)[v];
+      o[4 * v] = t.x, o[4 * v + 1] = t.y, o[4 * v + 2] = t.z, o[4 * v + 3] = t.w;
+    }
+  } else if constexpr (N == 2) {
+    const uint2 t = *reinterpret_cast<const uint2 *>(p);
+    o[0] = t.x, o[1] = t.y;
+  } else {
+    o[0] = p[0];
+  }
+}
+
+template <int SEGW, int WO>
+__device__ __forceinline__ unsigned seg_sad_regs(const unsigned (&sv)[SEGW], int addr, unsigned sh) {
+  constexpr int NV = SEGW / 4 + 1;
+  unsigned r[4 * NV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) {
+    const uint4 t = *reinterpret_cast<const uint4 *>(me_smem + addr + 16 * v);
+    r[4 * v] = t.x, r[4 * v + 1] = t.y, r[4 * v + 2] = t.z, r[4 * v + 3] = t.w;
+  }
+  unsigned a0 = 0, a1 = 0;
+#pragma unroll
+  for (int i = 0; i < SEGW; i += 2) {
+    a0 = sad4_acc(sv[i], __funnelshift_r(r[WO + i], r[WO + i + 1], sh), a0);
+    a1 = sad4_acc(sv[i + 1], __funnelshift_r(r[WO + i + 1], r[WO + i + 2], sh), a1);
+  }
+  return a0 + a1;
+}
+
+__device__ __forceinline__ bool multi_ok(const Ctx &k) { return k.fast && k.px == 1 && k.d.bw >= 16; }
+
+// A lane's share of the block, fixed for one search and skip mode: hoisted out of the step
+// loop (deriving it costs more than evaluating a candidate).  Every block has at most 8
+// passes of 32 lane tasks (128 rows x 2 segments), so a warp owns exactly one pass and
+// kWarps / passes warps share it, each taking every (kWarps / passes)-th candidate.
+template <int SEGW>
+struct LaneShare {
+  unsigned sv[SEGW];  // the lane's source words
+  int l_off;          // byte offset of the lane's segment inside a candidate block
+  int c0, cstep;      // candidate subset of the warp
+  bool act;
+};
+
+template <int SEGW>
+__device__ __forceinline__ void lane_share_init(const Ctx &k, bool skip, LaneShare<SEGW> &ls) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int R = skip ? k.d.bh >> 1 : k.d.bh, rmul = skip ? 2 : 1;
+  const int lS = k.d.bw > 4 * SEGW ? 1 : 0;            // log2(segments per row): 128-wide blocks have two
+  const int np = ((R << lS) + 31) >> 5;                // passes: 1, 2, 4 or 8
+  const int lP = np <= 1 ? 0 : 32 - __clz(np - 1);
+  const int T = ((warp & ((1 << lP) - 1)) << 5) + lane, q = T >> 3;
+  const int seg = q & ((1 << lS) - 1), row = ((q >> lS) << 3) + (T & 7);
+  ls.act = row < R;
+  const int yy = ls.act ? row * rmul : 0;
+  ls.l_off = yy * k.ref_pitch + seg * (4 * SEGW);
+  ls.c0 = warp >> lP;
+  ls.cstep = kWarps >> lP;
+  load_words<SEGW>(smem_words(yy * k.src_pitch_w * 4 + seg * (4 * SEGW)), ls.sv);
+}
+
+// Candidate i of the step lives in g_cda[i] (window byte address, or -1 outside the limits).
+template <int SEGW>
+__device__ __forceinline__ void cta_sad_multi_t(bool skip, int n, const int *cda, unsigned *out,
+                                                const LaneShare<SEGW> &ls) {
+  const int lane = threadIdx.x & 31;
+  for (int i = ls.c0; i < n; i += ls.cstep) {
+    const int a = cda[i];
+    if (a < 0) continue;
+    const int addr = (a & ~15) + ls.l_off;
+    const unsigned sh = (unsigned)(a & 3) * 8;
+    unsigned acc;
+    switch ((a >> 2) & 3) {
+      case 0: acc = seg_sad_regs<SEGW, 0>(ls.sv, addr, sh); break;
+      case 1: acc = seg_sad_regs<SEGW, 1>(ls.sv, addr, sh); break;
+      case 2: acc = seg_sad_regs<SEGW, 2>(ls.sv, addr, sh); break;
+      default: acc = seg_sad_regs<SEGW, 3>(ls.sv, addr, sh); break;
+    }
+#ifdef EXP_NOREDUX
+    if (acc == 0x12345) out[i] = acc;
+#else
+    acc = warp_sum_u(ls.act ? acc : 0u);
+#ifdef EXP_NOATOM
+    if (lane == 0 && acc == 0x12345) out[i] = acc;
+#else
+    if (lane == 0) atomicAdd(&out[i], skip ? 2 * acc : acc);
+#endif
+#endif
+  }
+}
+
+// SEGW = 0: no register-resident share (unstaged window, high bit depth, narrow blocks)
+template <>
+struct LaneShare<0> {};
+__device__ __forceinline__ int multi_segw(const Ctx &k) {
+  if (!multi_ok(k)) return 0;
+  return k.d.bw >= 64 ? 16 : (k.d.bw == 32 ? 8 : 4);
+}
+
+// The step's candidates (g_cda / g_cdp, n of them) -> out[i] = SAD (finished: doubled when rows
+// are skipped, shifted at high bit depth); slots of candidates outside the limits are left
+// untouched.  out[0 .. n) must be zero on entry; the caller synchronises the CTA before reading.
+template <int SEGW>
+__device__ __forceinline__ void eval_candidates(const Ctx &k, bool skip, int n, unsigned *out,
+                                                const LaneShare<SEGW> &ls, int slot0 = 0) {
+  if constexpr (SEGW > 0) {
+    cta_sad_multi_t<SEGW>(skip, n, g_cda + slot0, out, ls);
+  } else {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = warp; i < n; i += kWarps) {
+      if (g_cda[slot0 + i] < 0) continue;
+      const int p = g_cdp[slot0 + i];
+      const unsigned v = warp_sad(k, (short)(p & 0xffff), p >> 16, skip, lane);
+      if (lane == 0) out[i] = v;
+    }
+  }
+}
+
+// Warp 0 publishes a step's candidates: positions pos(0 .. n) -> g_cdp, window addresses (or
+// 0 on the share-less path) / -1 outside the limits -> g_cda.  n <= 16.
+template <int SEGW, class PosF>
+__device__ __forceinline__ void publish_candidates(const Ctx &k, int n, PosF pos, int slot0 = 0) {
+  const int lane = threadIdx.x & 31;
+  if (lane < 16) {
+    int a = -1, p = 0;
+    if (lane < n) {
+      const Mv m = pos(lane);
+      p = (m.row & 0xffff) | (m.col << 16);
+      if (in_range(k, m.row, m.col)) a = SEGW > 0 ? k.win0_off + m.row * k.ref_pitch + m.col : 0;
+    }
+    g_cda[slot0 + lane] = a;
+    g_cdp[slot0 + lane] = p;
+  }
 }
 
 // variance family result of (a - b) sums -> (var, sse) exactly as aom_varianceWxH_c /

@@ -11,10 +11,10 @@ __device__ __forceinline__ unsigned cta_value(const Ctx &k, F f) {
   __syncthreads();
   if (threadIdx.x < 32) {
     const unsigned v = f(lane);
-    if (lane == 0) k.bcast[0] = (int)v;
+    if (lane == 0) g_bcast[0] = (int)v;
   }
   __syncthreads();
-  return (unsigned)k.bcast[0];
+  return (unsigned)g_bcast[0];
 }
 
 // get_mvpred_var_cost (mcomp.c:665): vf(src, ref) + sub-pel-domain mv cost.  The whole CTA
@@ -51,138 +51,219 @@ __device__ int var_cost(const Ctx &k, Mv m) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __syncthreads();
   if (lane == 0) {
-    k.red[warp] = sum;
-    k.red[kWarps + warp] = (long long)sse;
+    g_red[warp] = sum;
+    g_red[kWarps + warp] = (long long)sse;
   }
   __syncthreads();
   long long tsum = 0;
   unsigned long long tsse = 0;
   for (int w = 0; w < kWarps; ++w) {
-    tsum += k.red[w];
-    tsse += (unsigned long long)k.red[kWarps + w];
+    tsum += g_red[w];
+    tsse += (unsigned long long)g_red[kWarps + w];
   }
   unsigned sse32;
   const unsigned v = finish_var(tsum, tsse, n, k.l->highbd != 0, k.l->bd, &sse32);
   return (int)v + err_cost(k, m.row * 8, m.col * 8);
 }
 
-// diamond_search_sad (mcomp.c:1318-1477)
-// `start_sad`: SAD + cost of the clamped start mv (the same for every run of
-// full_pixel_diamond, so it is computed once there).
-__device__ int diamond_search(const Ctx &k, bool skip, Mv start, unsigned start_sad, int search_step,
-                              int *num00, Mv *best, Mv *second, bool has_second) {
+// diamond_search_sad (mcomp.c:1318-1477), ALL runs of full_pixel_diamond side by side.
+// full_pixel_diamond (:1479) restarts the n-step search from the same start with a smaller
+// first radius up to `further` times; run n + 1 does not depend on run n's result, only on
+// whether it is executed at all (num00 skips).  One run per step leaves the CTA waiting on
+// two barriers for ~10 SADs (the phase was latency bound: 54 % of the kernel's time for 24 %
+// of its SAD work), so here every run advances one step per ROUND: run r's candidates are
+// published by warp r % 8 into slots [16 r, 16 r + n), every warp adds its rows of its share
+// of ALL runs' candidates into g_cand (eval_candidates), barrier, the owning warp decides its
+// runs -- lane i owns candidate i; the reference's in-order strict-< scan = the lexicographic
+// minimum of (sad + cost, index) that beats the running best -- moves the centre, picks the
+// run's next step and publishes it, barrier.  Runs the sequential code would have skipped are
+// computed and then ignored by the replay in full_pixel_diamond_t (about a third more SADs,
+// for a quarter of the barriers).  `start_sad`: SAD + cost of the clamped start mv, the same for
+// every run.  Results: g_runres[r].  The slots rotate through three groups, cleared two
+// rounds ahead.
+template <int SEGW>
+__device__ void diamond_runs(const Ctx &k, bool skip, Mv start, unsigned start_sad, int step_param,
+                             int nruns, const LaneShare<SEGW> &ls) {
+  constexpr int kSlots = kMaxRuns / kWarps;  // runs owned by a warp
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const Sites &cfg = g_sites;  // file-scope shared: LDS, not generic loads
-  int off_center = 0, center_steps = 0;
   start = clamp_mv(k, start);
-  const int tot = cfg.n_steps - search_step;
-  Mv tmp_second = has_second ? *second : start;
-  *best = start;
-  unsigned bestsad = start_sad;
-  __syncthreads();  // k.cand may still be read by the previous stage
-  // Each candidate of a step is evaluated in two pieces (upper / lower rows) by two
-  // different warps: 2n half-tasks spread evenly over the warps instead of n whole ones
-  // in ceil(n / 8) rounds.  Piece totals land in k.cand[2i], k.cand[2i + 1] and are summed by
-  // the scan.  The slots ping-pong between two halves of k.cand, so one barrier per step
-  // is enough: a step's writers can never overtake the readers of two steps ago.
-  int pp = 0;
-  for (int step = tot - 1; step >= 0; --step) {
-    const int n = cfg.per_step[step];
-    unsigned *cand = k.cand + pp;
-    pp ^= 64;
-#if B200_ME_SPLIT_DIAMOND
-    for (int t = warp; t < 2 * n; t += kWarps) {
-      const int i = 1 + (t >> 1), part = t & 1;
-      const int r = best->row + cfg.site[step][i][0], c = best->col + cfg.site[step][i][1];
-      // outside the limits: the two slots add up to UINT_MAX, which never wins.  Only the
-      // 8-bit path splits (sad_shift == 0), so finishing the pieces separately is exact.
-      unsigned v = part ? 0u : 0xffffffffu;
-      if (in_range(k, r, c)) {
-        v = sad_finish(k, warp_sad_part(k, r, c, skip, part, 2), skip);
-        if (part == 0) v += (unsigned)sad_cost(k, r, c);
-      }
-      if (lane == 0) cand[t] = v;
-    }
-#else
-    for (int i = 1 + warp; i <= n; i += kWarps) {
-      const int r = best->row + cfg.site[step][i][0], c = best->col + cfg.site[step][i][1];
-      unsigned v = 0xffffffffu;
-      if (in_range(k, r, c)) v = warp_sad(k, r, c, skip, lane) + (unsigned)sad_cost(k, r, c);
-      if (lane == 0) cand[2 * i - 2] = v, cand[2 * i - 1] = 0;
-    }
-#endif
-    __syncthreads();
-    int best_site = 0;
-    for (int i = 1; i <= n; ++i) {
-      const unsigned t = cand[2 * i - 2] + cand[2 * i - 1];
-      if (t < bestsad) {
-        bestsad = t;
-        best_site = i;
-      }
-    }
-    if (best_site) {
-      tmp_second = *best;
-      best->row += cfg.site[step][best_site][0];
-      best->col += cfg.site[step][best_site][1];
-      off_center = 1;
-    }
-    if (!off_center) center_steps++;
-    if (best_site == 0 && step > 2) {
-      int next = cfg.radius[step - 1];
-      while (next == cfg.radius[step] && step > 2) {
-        center_steps++;
-        --step;
-        next = cfg.radius[step - 1];
-      }
-    }
+  // the owning warp's state of its runs
+  Mv cur[kSlots], sec[kSlots];
+  unsigned bestsad[kSlots];
+  int off_center[kSlots], center_steps[kSlots], step[kSlots];
+#pragma unroll
+  for (int s = 0; s < kSlots; ++s) {
+    const int r = warp + s * kWarps;
+    cur[s] = start, sec[s] = start;
+    bestsad[s] = start_sad;
+    off_center[s] = center_steps[s] = 0;
+    step[s] = r < nruns ? cfg.n_steps - (step_param + r) - 1 : -1;
   }
-  *num00 = center_steps;
-  if (has_second) *second = tmp_second;
-  return (int)bestsad;
+  __syncthreads();  // g_cand / g_cda may still be read by the previous stage
+  for (int i = threadIdx.x; i < 3 * kMaxRuns * 16; i += kThreads) g_cand[i] = 0;
+  auto publish = [&](int s) {  // the candidates of run (warp, s)'s step around its centre, or its results
+    const int r = warp + s * kWarps;
+    if (r >= nruns) {
+      if (lane == 0 && r < kMaxRuns) g_runn[r] = 0;
+      return;
+    }
+    if (step[s] >= 0) {
+      const int st = step[s], n = cfg.per_step[st];
+      const Mv c = cur[s];
+      publish_candidates<SEGW>(k, n, [&](int i) {
+        return Mv{ c.row + cfg.site[st][i + 1][0], c.col + cfg.site[st][i + 1][1] };
+      }, r * 16);
+      if (lane == 0) g_runn[r] = n;
+    } else if (lane == 0) {
+      g_runn[r] = 0;
+      g_runres[r][0] = cur[s].row, g_runres[r][1] = cur[s].col;
+      g_runres[r][2] = sec[s].row, g_runres[r][3] = sec[s].col;
+      g_runres[r][4] = (int)bestsad[s], g_runres[r][5] = center_steps[s], g_runres[r][6] = off_center[s];
+    }
+  };
+#pragma unroll
+  for (int s = 0; s < kSlots; ++s) publish(s);
+  __syncthreads();
+  int ring = 0;
+  for (;;) {
+    if (!__any_sync(0xffffffffu, lane < nruns && g_runn[lane] > 0)) break;
+    unsigned *cand = g_cand + ring * (kMaxRuns * 16);
+    for (int r = 0; r < nruns; ++r) {
+      const int n = g_runn[r];
+#ifndef EXP_NOEVAL
+      if (n) eval_candidates<SEGW>(k, skip, n, cand + r * 16, ls, r * 16);
+#endif
+    }
+    __syncthreads();
+#pragma unroll
+    for (int s = 0; s < kSlots; ++s) {
+      const int r = warp + s * kWarps;
+      if (r >= nruns || step[s] < 0) continue;  // warp-uniform
+      const int st = step[s], n = cfg.per_step[st];
+#ifdef B200_ME_TIMING
+      if (lane == 0) atomicAdd(&g_bcast[11], 1 + (n << 8));  // steps | candidates << 8
+#endif
+      unsigned t = 0xffffffffu;
+      if (lane < n && g_cda[r * 16 + lane] >= 0) {
+        const int p = g_cdp[r * 16 + lane];
+        t = cand[r * 16 + lane] + (unsigned)sad_cost(k, (short)(p & 0xffff), p >> 16);
+      }
+      const unsigned tmin = __reduce_min_sync(0xffffffffu, t);
+      const bool moved = tmin < bestsad[s];
+      if (moved) {
+        const int site = 1 + (int)__reduce_min_sync(0xffffffffu, t == tmin ? (unsigned)lane : 99u);
+        bestsad[s] = tmin;
+        sec[s] = cur[s];
+        cur[s].row += cfg.site[st][site][0];
+        cur[s].col += cfg.site[st][site][1];
+        off_center[s] = 1;
+      }
+      if (!off_center[s]) center_steps[s]++;
+      int ns = st;
+      if (!moved && ns > 2) {
+        int next = cfg.radius[ns - 1];
+        while (next == cfg.radius[ns] && ns > 2) {
+          center_steps[s]++;
+          --ns;
+          next = cfg.radius[ns - 1];
+        }
+      }
+      step[s] = ns - 1;
+      if (lane < 16) g_cand[((ring + 2) % 3) * (kMaxRuns * 16) + r * 16 + lane] = 0;
+      publish(s);
+    }
+    ring = (ring + 1) % 3;
+    __syncthreads();
+  }
 }
 
 // calc_int_sad_list (mcomp.c:791) with costlist_has_sad == 0
 __device__ void sad_list(const Ctx &k, bool skip, Mv best, int *cl) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // centre first, then left, bottom, right, top
+  auto pos = [&](int i) {
+    const int dr = i == 2 ? 1 : (i == 4 ? -1 : 0), dc = i == 1 ? -1 : (i == 3 ? 1 : 0);
+    return Mv{ best.row + dr, best.col + dc };
+  };
+  const int segw = multi_segw(k);  // CTA-uniform
   __syncthreads();
-  if (warp < 5) {
-    const int dr = warp == 2 ? 1 : (warp == 4 ? -1 : 0);
-    const int dc = warp == 1 ? -1 : (warp == 3 ? 1 : 0);
-    const int r = best.row + dr, c = best.col + dc;
-    int v = INT_MAX;
-    if (warp == 0 || in_range(k, r, c)) v = (int)warp_sad(k, r, c, skip, lane) + sad_cost(k, r, c);
-    if (lane == 0) k.bcast[1 + warp] = v;
+  if (threadIdx.x < 8) g_cand[48 + threadIdx.x] = 0;
+  if (threadIdx.x < 32) {
+    if (segw) publish_candidates<16>(k, 5, pos);  // any SEGW > 0 publishes window addresses
+    else publish_candidates<0>(k, 5, pos);
   }
   __syncthreads();
-  for (int i = 0; i < 5; ++i) cl[i] = k.bcast[1 + i];
+  switch (segw) {
+    case 16: { LaneShare<16> ls; lane_share_init(k, skip, ls); eval_candidates<16>(k, skip, 5, g_cand + 48, ls); } break;
+    case 8: { LaneShare<8> ls; lane_share_init(k, skip, ls); eval_candidates<8>(k, skip, 5, g_cand + 48, ls); } break;
+    case 4: { LaneShare<4> ls; lane_share_init(k, skip, ls); eval_candidates<4>(k, skip, 5, g_cand + 48, ls); } break;
+    default: eval_candidates<0>(k, skip, 5, g_cand + 48, LaneShare<0>()); break;
+  }
+  __syncthreads();
+  for (int i = 0; i < 5; ++i) {
+    const Mv m = pos(i);
+    cl[i] = in_range(k, m.row, m.col) ? (int)g_cand[48 + i] + sad_cost(k, m.row, m.col) : INT_MAX;
+  }
 }
 
-// full_pixel_diamond (mcomp.c:1479-1526)
-__device__ int full_pixel_diamond(const Ctx &k, bool skip, Mv start, int step_param, int *cl,
-                                  Mv *best, Mv *second, bool has_second) {
-  int n, num00 = 0;
+// full_pixel_diamond (mcomp.c:1479-1526): all runs at once (diamond_runs), then the reference's
+// sequential bookkeeping replayed on their results -- which runs count (num00 skips), the
+// variance comparison between them, and second_best_mv handed from run to run (a run that
+// never moved leaves it as it found it).
+template <int SEGW>
+__device__ int full_pixel_diamond_t(const Ctx &k, bool skip, Mv start, int step_param, int *cl,
+                                    Mv *best, Mv *second, bool has_second) {
+  LaneShare<SEGW> ls;
+  if constexpr (SEGW > 0) lane_share_init(k, skip, ls);
   const Mv cs = clamp_mv(k, start);
   const unsigned start_sad = cta_value(k, [&](int ln) { return warp_sad(k, cs.row, cs.col, skip, ln); }) +
                              (unsigned)sad_cost(k, cs.row, cs.col);
-  diamond_search(k, skip, start, start_sad, step_param, &n, best, second, has_second);
-  int bestsme = var_cost(k, *best);
   const int further = k.sites->n_steps - 1 - step_param;
+  const int nruns = min(kMaxRuns, 1 + max(further, 0));
+#ifdef B200_ME_TIMING2
+  const long long tr0 = clock64();
+#endif
+  diamond_runs<SEGW>(k, skip, start, start_sad, step_param, nruns, ls);
+#ifdef B200_ME_TIMING2
+  const long long tr1 = clock64();
+  if (threadIdx.x == 0) g_bcast[14] = (int)((tr1 - tr0) >> 4);
+#endif
+  auto take_second = [&](int r) {
+    if (has_second && g_runres[r][6]) second->row = g_runres[r][2], second->col = g_runres[r][3];
+  };
+  int n = g_runres[0][5];
+  best->row = g_runres[0][0], best->col = g_runres[0][1];
+  take_second(0);
+  int bestsme = var_cost(k, *best);
   while (n < further) {
     ++n;
-    Mv tmp;
-    diamond_search(k, skip, start, start_sad, step_param + n, &num00, &tmp, second, has_second);
+    const Mv tmp = { g_runres[n][0], g_runres[n][1] };
+    take_second(n);
     const int sme = var_cost(k, tmp);
     if (sme < bestsme) {
       bestsme = sme;
       *best = tmp;
     }
-    if (num00) {
-      n += num00;
-      num00 = 0;
-    }
+    n += g_runres[n][5];
   }
+#ifdef B200_ME_TIMING2
+  const long long tr2 = clock64();
+#endif
   if (cl) sad_list(k, skip, *best, cl);
+#ifdef B200_ME_TIMING2
+  if (threadIdx.x == 0) g_bcast[13] = (int)((tr2 - tr1) >> 4), g_bcast[15] = (int)((clock64() - tr2) >> 4);
+#endif
   return bestsme;
+}
+
+__device__ int full_pixel_diamond(const Ctx &k, bool skip, Mv start, int step_param, int *cl,
+                                  Mv *best, Mv *second, bool has_second) {
+  switch (multi_segw(k)) {  // CTA-uniform
+    case 16: return full_pixel_diamond_t<16>(k, skip, start, step_param, cl, best, second, has_second);
+    case 8: return full_pixel_diamond_t<8>(k, skip, start, step_param, cl, best, second, has_second);
+    case 4: return full_pixel_diamond_t<4>(k, skip, start, step_param, cl, best, second, has_second);
+    default: return full_pixel_diamond_t<0>(k, skip, start, step_param, cl, best, second, has_second);
+  }
 }
 
 // ---- pattern_search family (mcomp.c:1017-1316) --------------------------------------
@@ -217,7 +298,7 @@ struct PatState {
 __device__ int pat_round(const Ctx &k, PatState &st, bool skip, int s, const int *chk, int n, int *cl,
                          bool marks) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  unsigned *cand = k.cand + st.pp;
+  unsigned *cand = g_cand + st.pp;
   st.pp ^= 32;
   if (warp < n) {
     const Mv o = pat_site(st.kind, s, chk ? chk[warp] : warp);
@@ -362,26 +443,10 @@ __device__ __noinline__ int pattern_search(const Ctx &k, bool skip, Mv start, in
 //   * step 4 / 8 / 16 (`mesh_strided_band`): candidates of one grid row are whole words
 //     apart, so a lane loads one long aligned strip of a reference row, shifts it once and
 //     slides the source row over it for JB horizontally adjacent candidates.
-// Both write `SAD + mv cost` of every candidate of a band of grid rows into k.cand[] in
+// Both write `SAD + mv cost` of every candidate of a band of grid rows into g_cand[] in
 // scan order (shared-memory atomics join the 32-pixel column segments of a block).
 // Preconditions (checked by the caller): 8-bit, window staged in shared memory, no row
 // skipping, bw >= 4 * SEGW, bh a multiple of 4.
-template <int N>
-__device__ __forceinline__ void load_words(const unsigned *p, unsigned (&o)[N]) {
-  if constexpr (N >= 4) {
-#pragma unroll
-    for (int v = 0; v < N / 4; ++v) {
-      const uint4 t = reinterpret_cast<const uint4 *>(p)[v];
-      o[4 * v] = t.x, o[4 * v + 1] = t.y, o[4 * v + 2] = t.z, o[4 * v + 3] = t.w;
-    }
-  } else if constexpr (N == 2) {
-    const uint2 t = *reinterpret_cast<const uint2 *>(p);
-    o[0] = t.x, o[1] = t.y;
-  } else {
-    o[0] = p[0];
-  }
-}
-
 constexpr int kRB = 4;  // vertically adjacent candidates per lane (step 1)
 constexpr int kJB = 4;  // horizontally adjacent candidates per lane (step 4 / 8 / 16)
 
@@ -442,7 +507,7 @@ __device__ void mesh1_band(const Ctx &k, int row0, int nrows, int col0, int nc) 
         if (c < nk) {
           unsigned v = acc[c];
           if (seg == 0) v += (unsigned)sad_cost(k, row + c, col);
-          atomicAdd(&k.cand[(rg * kRB + c) * nc + ci], v);
+          atomicAdd(&g_cand[(rg * kRB + c) * nc + ci], v);
         }
     }
   }
@@ -491,7 +556,7 @@ __device__ void mesh_strided_band_t(const Ctx &k, int row0, int nrows, int col0,
         if (ci < nc) {
           unsigned t = acc[j];
           if (seg == 0) t += (unsigned)sad_cost(k, row, col + j * step);
-          atomicAdd(&k.cand[ri * nc + ci], t);
+          atomicAdd(&g_cand[ri * nc + ci], t);
         }
       }
     }
@@ -515,7 +580,7 @@ __device__ __forceinline__ void mesh_strided_band(const Ctx &k, int row0, int nr
   }
 }
 
-// 0: no fast path for this stage; otherwise fills k.cand[0..nrows*nc) (must be zeroed)
+// 0: no fast path for this stage; otherwise fills g_cand[0..nrows*nc) (must be zeroed)
 __device__ __forceinline__ bool mesh_band_fast(const Ctx &k, int row0, int nrows, int col0, int nc,
                                                int step) {
   const int bw = k.d.bw;
@@ -577,7 +642,7 @@ __device__ int mesh_search(const Ctx &k, bool skip, Mv start, int range, int ste
   for (int base = 0; base < total; base += chunk) {
     const int cnt = min(chunk, total - base);
     if (fast) {
-      for (int j = threadIdx.x; j < cnt; j += kThreads) k.cand[j] = 0;
+      for (int j = threadIdx.x; j < cnt; j += kThreads) g_cand[j] = 0;
       __syncthreads();
       const int ri0 = base / nc;
       mesh_band_fast(k, start.row + r0 + ri0 * step, cnt / nc, start.col + c0, nc, step);
@@ -587,7 +652,7 @@ __device__ int mesh_search(const Ctx &k, bool skip, Mv start, int range, int ste
         const int ri = idx / nc, ci = idx - ri * nc;
         const int r = start.row + r0 + ri * step, c = start.col + c0 + ci * step;
         const unsigned t = warp_sad(k, r, c, skip, lane) + (unsigned)sad_cost(k, r, c);
-        if (lane == 0) k.cand[j] = t;
+        if (lane == 0) g_cand[j] = t;
       }
     }
     __syncthreads();
@@ -602,7 +667,7 @@ __device__ int mesh_search(const Ctx &k, bool skip, Mv start, int range, int ste
       const int lo = threadIdx.x * PER;
       unsigned cv[PER];
 #pragma unroll
-      for (int j = 0; j < PER; ++j) cv[j] = lo + j < cnt ? k.cand[lo + j] : 0xffffffffu;
+      for (int j = 0; j < PER; ++j) cv[j] = lo + j < cnt ? g_cand[lo + j] : 0xffffffffu;
       int win = INT_MAX, pi = INT_MAX;
       unsigned wv = best_sad;
       for (int pass = 0; pass < 2; ++pass) {
@@ -616,13 +681,13 @@ __device__ int mesh_search(const Ctx &k, bool skip, Mv start, int range, int ste
         const unsigned mv = __reduce_min_sync(0xffffffffu, bv);
         const int mi = (int)__reduce_min_sync(0xffffffffu, bv == mv ? (unsigned)bi : 0x7fffffffu);
         if (lane == 0) {
-          k.red[warp] = (long long)(((unsigned long long)mv << 32) | (unsigned)mi);
+          g_red[warp] = (long long)(((unsigned long long)mv << 32) | (unsigned)mi);
         }
         __syncthreads();
         unsigned long long m = ~0ull;
 #pragma unroll
         for (int w = 0; w < kWarps; ++w) {
-          const unsigned long long t = (unsigned long long)k.red[w];
+          const unsigned long long t = (unsigned long long)g_red[w];
           m = t < m ? t : m;
         }
         const int idx = (int)(unsigned)m;
@@ -630,22 +695,22 @@ __device__ int mesh_search(const Ctx &k, bool skip, Mv start, int range, int ste
           win = idx;
           wv = (unsigned)(m >> 32);
           if (win == INT_MAX || !has_second) break;  // CTA-uniform
-          __syncthreads();  // k.red is reused by the second pass
+          __syncthreads();  // g_red is reused by the second pass
         } else {
           pi = idx;
         }
       }
       if (threadIdx.x == 0) {
-        k.bcast[8] = win;
-        k.bcast[9] = (int)wv;
-        k.bcast[10] = pi;
+        g_bcast[8] = win;
+        g_bcast[9] = (int)wv;
+        g_bcast[10] = pi;
       }
     }
     __syncthreads();
     {
-      const int win = k.bcast[8], pi = k.bcast[10];
+      const int win = g_bcast[8], pi = g_bcast[10];
       if (win != INT_MAX) {
-        best_sad = (unsigned)k.bcast[9];
+        best_sad = (unsigned)g_bcast[9];
         if (has_second) {
           if (pi != INT_MAX) {
             const int idx = base + pi, ri = idx / nc, ci = idx - ri * nc;
@@ -676,11 +741,23 @@ __device__ int full_pixel_exhaustive(const Ctx &k, bool skip, Mv start, int *cl,
   range = min(range, 256);
   interval = max(interval, range / divisor);
   if (k.d.flags & B200_ME_FINE_INTERVAL) interval = min(interval, 4);
+#ifdef B200_ME_TIMING
+  long long tm = clock64();
+#endif
   int bestsme = mesh_search(k, skip, *best, range, interval, best, second, has_second);
+#if defined(B200_ME_TIMING) && !defined(B200_ME_TIMING2)
+  g_bcast[13] = (int)((clock64() - tm) >> 4);
+#endif
   if (interval > 1 && range > 7) {
     for (int i = 1; i < 4; ++i) {
+#ifdef B200_ME_TIMING
+      tm = clock64();
+#endif
       bestsme = mesh_search(k, skip, *best, k.l->mesh_range[i], k.l->mesh_interval[i], best, second,
                             has_second);
+#if defined(B200_ME_TIMING) && !defined(B200_ME_TIMING2)
+      if (i < 3) g_bcast[13 + i] = (int)((clock64() - tm) >> 4);
+#endif
       if (k.l->mesh_interval[i] == 1) break;
     }
   }
@@ -691,7 +768,10 @@ __device__ int full_pixel_exhaustive(const Ctx &k, bool skip, Mv start, int *cl,
 
 __device__ __forceinline__ int ilog2i(int v) { return 31 - __clz(v); }
 
-// av1_full_pixel_search (mcomp.c:1755-1895), n-step / diamond family
+// av1_full_pixel_search (mcomp.c:1755-1895).  FAM 0: n-step / diamond family, FAM 1: the
+// pattern_search family -- separate kernel instances, so that neither carries the other's
+// registers (one kernel for everything spilled 450 bytes).
+template <int FAM>
 __device__ int full_pixel_search(const Ctx &k, bool skip, int *cl, Mv *best, Mv *second) {
   const Mv start = { k.d.start_row, k.d.start_col };
   const int mi_log2 = ilog2i(k.d.bw >> 2) + ilog2i(k.d.bh >> 2);
@@ -707,19 +787,22 @@ __device__ int full_pixel_search(const Ctx &k, bool skip, int *cl, Mv *best, Mv 
     {
       const int m = k.d.search_method, sp = k.d.step_param;
       int *pcl = (k.d.flags & B200_ME_COST_LIST) ? cl : nullptr;  // changes the BIGDIA family's last scale
-      if (m == B200_ME_HEX || m == B200_ME_BIGDIA || m == B200_ME_SQUARE)
-        var = pattern_search(k, skip, start, sp, true, pcl, best);
-      else if (m == B200_ME_FAST_HEX || m == B200_ME_FAST_DIAMOND)
-        var = pattern_search(k, skip, start, max(kMaxSteps - 2, sp), false, pcl, best);
-      else if (m == B200_ME_FAST_BIGDIA)
-        var = pattern_search(k, skip, start, max(kMaxSteps - 3, sp), false, pcl, best);
-      else if (m == B200_ME_VFAST_DIAMOND)
-        var = pattern_search(k, skip, start, max(kMaxSteps - 1, sp), false, pcl, best);
-      else
+      if constexpr (FAM == 1) {
+        if (m == B200_ME_HEX || m == B200_ME_BIGDIA || m == B200_ME_SQUARE)
+          var = pattern_search(k, skip, start, sp, true, pcl, best);
+        else if (m == B200_ME_FAST_HEX || m == B200_ME_FAST_DIAMOND)
+          var = pattern_search(k, skip, start, max(kMaxSteps - 2, sp), false, pcl, best);
+        else if (m == B200_ME_FAST_BIGDIA)
+          var = pattern_search(k, skip, start, max(kMaxSteps - 3, sp), false, pcl, best);
+        else
+          var = pattern_search(k, skip, start, max(kMaxSteps - 1, sp), false, pcl, best);
+      } else {
+        (void)m, (void)pcl;
         var = full_pixel_diamond(k, skip, start, sp, cl, best, second, true);
+      }
     }
 #ifdef B200_ME_TIMING
-    k.bcast[12] = (int)((clock64() - tq0) >> 4);
+    g_bcast[12] = (int)((clock64() - tq0) >> 4);
 #endif
     if (!run_mesh &&
         (k.d.search_method == B200_ME_NSTEP || k.d.search_method == B200_ME_NSTEP_8PT)) {
@@ -773,7 +856,7 @@ __device__ int refine_8p(const Ctx &k, bool skip, Mv *bestp) {
       const int r = best.row + nb[warp][0], c = best.col + nb[warp][1];
       unsigned v = 0xffffffffu;
       if (!((visited >> g) & 1) && in_range(k, r, c)) v = warp_sad(k, r, c, skip, lane);
-      if (lane == 0) k.cand[warp] = v;
+      if (lane == 0) g_cand[warp] = v;
     }
     __syncthreads();
     int best_site = -1;
@@ -781,7 +864,7 @@ __device__ int refine_8p(const Ctx &k, bool skip, Mv *bestp) {
       const int g = centre + nb[j][0] * kStride + nb[j][1];
       if ((visited >> g) & 1) continue;
       visited |= 1ull << g;
-      const unsigned v = k.cand[j];
+      const unsigned v = g_cand[j];
       if (v == 0xffffffffu || v >= best_sad) continue;
       const unsigned t = v + (unsigned)sad_cost(k, best.row + nb[j][0], best.col + nb[j][1]);
       if (t < best_sad) {
@@ -804,29 +887,61 @@ __host__ __device__ __forceinline__ int vec_pitch(int words) { return ((words + 
 // Stage the source block and (when it fits) the reachable reference window; fills in the
 // pixel views of `k`.  Layout for the vector SAD path: row pitches of 4 (mod 8) words and
 // 16-byte aligned row starts (needs a reference stride that is a multiple of 16 bytes).
-__device__ void stage_inputs(Ctx &k, unsigned char *smem, int window_budget, int extra) {
+__device__ void stage_inputs(Ctx &k, unsigned char *smem, int window_budget, int extra,
+                             const TmaCfg &tc, const CUtensorMap *tm_cur, const CUtensorMap *tm_ref) {
   const B200MeLaunch &l = *k.l;
   const int px = k.px, bw = k.d.bw, bh = k.d.bh;
   unsigned char *s_src = smem;
   const unsigned char *g_src = static_cast<const unsigned char *>(l.cur) + (size_t)k.d.src_offset * px;
   const int row_bytes = bw * px, row_words = row_bytes / 4;
+  const long long stride_b = (long long)l.ref_stride * px;
+  // window = limits box (+ `extra` pixels on every side) + block
+  const int wr0 = k.d.row_min - extra, wc0 = k.d.col_min - extra;
+  const int wh = k.d.row_max - k.d.row_min + 2 * extra + bh;
+  const int ww = k.d.col_max - k.d.col_min + 2 * extra + bw;
+  const unsigned char *g_ref0 = static_cast<const unsigned char *>(l.ref) + (size_t)k.d.ref_offset * px;
+  k.src = s_src;
+  k.ref0 = g_ref0;
+  k.ref_pitch = l.ref_stride;
+  k.fast = false;
+  k.staged = false;
+  const long long src_b = (long long)k.d.src_offset * px, cur_stride_b = (long long)l.cur_stride * px;
+  // byte position of the window's first pixel inside the reference buffer
+  const long long win_b = ((long long)k.d.ref_offset + (long long)wr0 * l.ref_stride + wc0) * px;
+  if (tc.use && row_words >= 4 && (src_b % cur_stride_b) % 16 == 0 && bh <= tc.src_rows &&
+      vec_pitch(row_words) <= tc.src_pitch_w && win_b >= 0 && wh > 0 && ww > 0) {
+    const int wy = (int)(win_b / stride_b), wxb = (int)(win_b - (long long)wy * stride_b);
+    const int lead = wxb & 15;
+    const int nbox = (wh + kTmaRows - 1) / kTmaRows;
+    const int src_bytes = (tc.src_rows * tc.src_pitch_w * 4 + 127) & ~127;
+    const int box_bytes = kTmaRows * tc.win_pitch_w * 4;
+    if ((lead + ww * px + 3) / 4 + 4 <= tc.win_pitch_w && (long long)nbox * box_bytes <= window_budget) {
+      if (threadIdx.x == 0) mbar_init(&g_mbar, 1);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        mbar_expect_tx(&g_mbar, (unsigned)(tc.src_rows * tc.src_pitch_w * 4 + nbox * box_bytes));
+        const int sy = (int)(src_b / cur_stride_b), sxb = (int)(src_b - (long long)sy * cur_stride_b);
+        tma_load_2d(smem, tm_cur, sxb >> 2, sy, &g_mbar);
+        for (int b = 0; b < nbox; ++b)
+          tma_load_2d(smem + src_bytes + b * box_bytes, tm_ref, (wxb - lead) >> 2, wy + b * kTmaRows, &g_mbar);
+      }
+      k.src_pitch_w = tc.src_pitch_w;
+      k.ref_pitch = tc.win_pitch_w * 4 / px;
+      k.ref0 = smem + src_bytes + lead + ((long long)(-wr0) * k.ref_pitch + (-wc0)) * px;
+      k.fast = true;
+      k.staged = true;
+      k.win0_off = src_bytes + lead + ((-wr0) * k.ref_pitch + (-wc0)) * px;
+      mbar_wait(&g_mbar, 0);
+      return;
+    }
+  }
+  // cooperative copy
   k.src_pitch_w = row_words >= 4 ? vec_pitch(row_words) : row_words;
   for (int i = threadIdx.x; i < bh * row_bytes; i += kThreads) {
     const int y = i / row_bytes, x = i - y * row_bytes;
     s_src[y * k.src_pitch_w * 4 + x] = g_src[(size_t)y * l.cur_stride * px + x];
   }
-  k.src = s_src;
   const int src_bytes = (bh * k.src_pitch_w * 4 + 15) & ~15;
-  const unsigned char *g_ref0 = static_cast<const unsigned char *>(l.ref) + (size_t)k.d.ref_offset * px;
-  k.ref0 = g_ref0;
-  k.ref_pitch = l.ref_stride;
-  k.fast = false;
-  k.staged = false;
-  // window = limits box (+ `extra` pixels on every side) + block
-  const int wr0 = k.d.row_min - extra, wc0 = k.d.col_min - extra;
-  const int wh = k.d.row_max - k.d.row_min + 2 * extra + bh;
-  const int ww = k.d.col_max - k.d.col_min + 2 * extra + bw;
-  const long long stride_b = (long long)l.ref_stride * px;
   const unsigned char *g0 = g_ref0 + ((long long)wr0 * l.ref_stride + wc0) * px;
   const bool vec = (stride_b & 15) == 0;
   const int lead = (int)(reinterpret_cast<unsigned long long>(g0) & (vec ? 15 : 3));
@@ -836,10 +951,12 @@ __device__ void stage_inputs(Ctx &k, unsigned char *smem, int window_budget, int
   if ((stride_b & 3) == 0 && need <= window_budget && wh > 0 && ww > 0) {
     unsigned *s_win = reinterpret_cast<unsigned *>(smem + src_bytes);
     const unsigned *ga = reinterpret_cast<const unsigned *>(g0 - lead);
-    const int copy_words = (lead + ww * px + 3) / 4 + 1;
-    for (int i = threadIdx.x; i < wh * copy_words; i += kThreads) {
-      const int y = i / copy_words, x = i - y * copy_words;
-      s_win[y * words + x] = ga[(long long)y * (stride_b >> 2) + x];
+    // exactly the words that hold window bytes: nothing is read past the window's right edge
+    // (the funnel shifts also touch the following word; its value is shifted out)
+    const int copy_words = (lead + ww * px + 3) / 4;
+    for (int i = threadIdx.x; i < wh * (copy_words + 1); i += kThreads) {
+      const int y = i / (copy_words + 1), x = i - y * (copy_words + 1);
+      s_win[y * words + x] = x < copy_words ? ga[(long long)y * (stride_b >> 2) + x] : 0u;
     }
     k.ref_pitch = words * 4 / px;
     k.ref0 = reinterpret_cast<unsigned char *>(s_win) + lead +
@@ -851,16 +968,20 @@ __device__ void stage_inputs(Ctx &k, unsigned char *smem, int window_budget, int
   __syncthreads();
 }
 
+__host__ __device__ __forceinline__ int me_family(int method) {
+  return method <= B200_ME_CLAMPED_DIAMOND ? 0 : (method == B200_ME_REFINE_8P ? 2 : 1);
+}
+
+template <int FAM>
 __global__ void __launch_bounds__(kThreads, 3) fullpel_kernel(const B200MeLaunch l, const Sites *sites4,
-                                                           int window_budget) {
-  __shared__ unsigned s_cand[kMaxCand + 16];
-  __shared__ int s_bcast[16];
-  __shared__ long long s_red[2 * kWarps];
+                                                           int window_budget, const TmaCfg tc,
+                                                           const __grid_constant__ CUtensorMap tm_cur,
+                                                           const __grid_constant__ CUtensorMap tm_ref) {
   const int bi = blockIdx.x;
-  Ctx k;
-  k.red = s_red;
+  load_desc(l, bi);
+  Ctx k(g_desc);
   k.l = &l;
-  k.d = l.blocks[bi];
+  if (me_family(k.d.search_method) != FAM) return;  // served by another instance of the launch
   init_costs(k);
   {  // the method's site table: read at every step of the search, keep it on chip
     const int *g = reinterpret_cast<const int *>(sites4 + (k.d.search_method & 3));
@@ -870,24 +991,35 @@ __global__ void __launch_bounds__(kThreads, 3) fullpel_kernel(const B200MeLaunch
   k.sites = &g_sites;
   k.px = l.highbd ? 2 : 1;
   k.sad_shift = l.highbd ? (l.bd == 10 ? 2 : (l.bd == 12 ? 4 : 0)) : 0;
-  k.cand = s_cand;
-  k.bcast = s_bcast;
 #ifdef B200_ME_TIMING
   const long long t_start = clock64();
 #endif
-  stage_inputs(k, me_smem, window_budget, 0);
+  // a block larger than the launch declared would overrun the shared memory sized from
+  // max_bw / max_bh: its search is refused (ret = INT_MAX, mv = INVALID)
+  if (k.d.bw > (l.max_bw > 0 ? l.max_bw : 128) || k.d.bh > (l.max_bh > 0 ? l.max_bh : 128)) {
+    if (threadIdx.x == 0) {
+      B200MeResult r;
+      memset(&r, 0, sizeof(r));
+      r.best_row = r.best_col = r.second_row = r.second_col = -32768;
+      r.ret = INT_MAX;
+      l.results[bi] = r;
+    }
+    return;
+  }
+  stage_inputs(k, me_smem, window_budget, 0, tc, &tm_cur, &tm_ref);
 #ifdef B200_ME_TIMING
+  if (threadIdx.x == 0) g_bcast[11] = 0, g_bcast[13] = 0, g_bcast[14] = 0, g_bcast[15] = 0;
   const long long t_staged = clock64();
 #endif
   Mv best, second;
   int cl[5];
   int var;
-  if (k.d.search_method == B200_ME_REFINE_8P) {
+  if constexpr (FAM == 2) {
     second.row = second.col = -32768;
     for (int i = 0; i < 5; ++i) cl[i] = 0;
     var = refine_8p(k, (k.d.flags & B200_ME_SKIP_SAD) != 0, &best);
   } else {
-    var = full_pixel_search(k, (k.d.flags & B200_ME_SKIP_SAD) != 0, cl, &best, &second);
+    var = full_pixel_search<FAM>(k, (k.d.flags & B200_ME_SKIP_SAD) != 0, cl, &best, &second);
   }
   if (threadIdx.x == 0) {
     B200MeResult r;
@@ -900,9 +1032,11 @@ __global__ void __launch_bounds__(kThreads, 3) fullpel_kernel(const B200MeLaunch
     r.distortion = 0;
     r.sse = 0;
 #ifdef B200_ME_TIMING
-    r.distortion = k.bcast[12];                          // diamond phase, cycles / 16
+    r.distortion = g_bcast[12];                          // diamond phase, cycles / 16
     r.sse = (unsigned)((clock64() - t_start) >> 4);      // whole search
     r.cost_list[4] = (int)((t_staged - t_start) >> 4);   // staging
+    r.cost_list[0] = g_bcast[11];
+    r.cost_list[1] = g_bcast[13], r.cost_list[2] = g_bcast[14], r.cost_list[3] = g_bcast[15];  // mesh stages
 #endif
     l.results[bi] = r;
   }

@@ -26,8 +26,8 @@ __constant__ unsigned char c_me_bil[8][2] = { { 128, 0 }, { 112, 16 }, { 96, 32 
 
 struct SubCtx {
   Ctx k;
+  __device__ explicit SubCtx(const B200MeBlock &desc) : k(desc) {}
   unsigned short *tmp;  // shared: (bh + 7) * bw horizontally filtered samples
-  long long *red;       // shared: 2 * kWarps partial sums
   int search_type;      // B200_USE_*
 };
 
@@ -111,15 +111,15 @@ __device__ unsigned cta_pref_error(const SubCtx &s, Mv mv, int mode, unsigned *s
   sse = (unsigned long long)warp_sum_ll((long long)sse);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (lane == 0) {
-    s.red[warp] = sum;
-    s.red[kWarps + warp] = (long long)sse;
+    g_red[warp] = sum;
+    g_red[kWarps + warp] = (long long)sse;
   }
   __syncthreads();
   long long tsum = 0;
   unsigned long long tsse = 0;
   for (int w = 0; w < kWarps; ++w) {
-    tsum += s.red[w];
-    tsse += (unsigned long long)s.red[kWarps + w];
+    tsum += g_red[w];
+    tsse += (unsigned long long)g_red[kWarps + w];
   }
   return finish_var(tsum, tsse, n, k.l->highbd != 0, k.l->bd, sse_out);
 }
@@ -285,20 +285,14 @@ __device__ void subpel_search_pruned(const SubCtx &s, SubState &st, int tree, co
 }
 
 __global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) {
-  __shared__ long long s_red[2 * kWarps];
-  __shared__ int s_bcast[16];
   const int bi = blockIdx.x;
-  SubCtx s;
+  load_desc(l, bi);
+  SubCtx s(g_desc);
   s.k.l = &l;
-  s.k.d = l.blocks[bi];
   init_costs(s.k);
   s.k.sites = nullptr;
   s.k.px = l.highbd ? 2 : 1;
   s.k.sad_shift = 0;
-  s.k.cand = nullptr;
-  s.k.bcast = s_bcast;
-  s.k.red = s_red;
-  s.red = s_red;
   s.search_type = (s.k.d.subpel >> 4) & 3;
   // the limits are sub-pel here: no window staging (window_budget 0), reference via L1/L2
   {

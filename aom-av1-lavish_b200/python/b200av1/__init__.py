@@ -254,7 +254,12 @@ class MeLaunch(C.Structure):
                 ("ref_stride", C.c_int), ("mesh_range", C.c_int * 4), ("mesh_interval", C.c_int * 4),
                 ("mvjcost", C.c_void_p), ("mvcost", C.c_void_p * 2), ("results", C.c_void_p),
                 ("window_bytes", C.c_int), ("max_bw", C.c_int), ("max_bh", C.c_int),
-                ("cost_lists", C.c_void_p), ("cost_list_stride", C.c_int)]
+                ("cost_lists", C.c_void_p), ("cost_list_stride", C.c_int), ("families", C.c_uint),
+                ("cur_rows", C.c_int), ("ref_rows", C.c_int), ("max_col_span", C.c_int),
+                ("max_row_span", C.c_int)]
+
+
+ME_FAMILY_NSTEP, ME_FAMILY_PATTERN, ME_FAMILY_REFINE = 1, 2, 4
 
 
 # ---- Hadamard / SATD / averages (include/b200av1.h) ----

@@ -279,6 +279,9 @@ def bench_me(ctx, dev, stream, steps, warmup, seed, frame_id, n_frames=8):
             l.mesh_range[i], l.mesh_interval[i] = r, it
         l.results = d_res.data_ptr()
         l.window_bytes, l.max_bw, l.max_bh = 48 * 1024, 64, 64
+        l.families = b200av1.ME_FAMILY_NSTEP
+        l.cur_rows, l.ref_rows = n_frames * h, n_frames * 2 * rh
+        l.max_col_span, l.max_row_span = 128, 128
         fn = b200av1.lib().b200_me_fullpel_launch if kind == 0 else b200av1.lib().b200_me_subpel_launch
         b200av1.check(fn(ctx.h, C.byref(l), C.c_void_p(stream.cuda_stream)))
 
@@ -287,9 +290,12 @@ def bench_me(ctx, dev, stream, steps, warmup, seed, frame_id, n_frames=8):
     torch.cuda.synchronize(dev)
     res = d_res.cpu().numpy().view(b200av1.MERESULT_DTYPE)
     if os.environ.get("B200_ME_DEBUG"):  # library built with -DB200_ME_TIMING (dev only)
-        print("ME timing (cycles): staging %.0f diamond %.0f total %.0f" % (
+        print("ME timing (cycles): staging %.0f diamond %.0f mesh %.0f / %.0f / %.0f total %.0f" % (
             16 * res["cost_list"][:, 4].mean(), 16.0 * res["distortion"].mean(),
-            16.0 * res["sse"].mean()), file=sys.stderr)
+            16.0 * res["cost_list"][:, 1].mean(), 16.0 * res["cost_list"][:, 2].mean(),
+            16.0 * res["cost_list"][:, 3].mean(), 16.0 * res["sse"].mean()), file=sys.stderr)
+        print("ME diamond: steps/search %.1f candidates/search %.1f" % (
+            (res["cost_list"][:, 0] & 255).mean(), (res["cost_list"][:, 0] >> 8).mean()), file=sys.stderr)
     sb = blocks.copy()
     sb["start_row"], sb["start_col"] = res["best_row"] * 8, res["best_col"] * 8
     sb["col_min"], sb["col_max"], sb["row_min"], sb["row_max"] = -512, 512, -512, 512

@@ -459,7 +459,21 @@ typedef struct {
                                     B200_ME_COST_LIST.  Pointing it at the full-pel launch's
                                     results[0].cost_list with stride 10 chains the two launches. */
   int cost_list_stride;          /* in int32 units; 0 = 5 */
+  /* ---- optional hints (0 = unknown); a zero-initialised struct behaves as before ---- */
+  unsigned families;             /* full-pel: B200_ME_FAMILY_* bits of the search methods present in
+                                    the batch; one kernel instance runs per family (0: all three
+                                    are launched and the CTAs of absent families exit at once) */
+  int cur_rows, ref_rows;        /* rows of the cur / ref plane buffers.  With both set, 16-byte
+                                    aligned bases and strides that are multiples of 16 bytes, the
+                                    source block and the search window are brought into shared
+                                    memory by the TMA engine (cp.async.bulk.tensor.2d) instead of
+                                    by the threads */
+  int max_col_span, max_row_span; /* largest col_max - col_min / row_max - row_min of the batch
+                                    (full-pel units): sizes the TMA box of the search window */
 } B200MeLaunch;
+#define B200_ME_FAMILY_NSTEP 1u   /* NSTEP, NSTEP_8PT, DIAMOND, CLAMPED_DIAMOND */
+#define B200_ME_FAMILY_PATTERN 2u /* HEX .. VFAST_DIAMOND (pattern_search) */
+#define B200_ME_FAMILY_REFINE 4u  /* B200_ME_REFINE_8P */
 /* av1_init_search_range (mcomp.c:239): step_param for a search of +-size pixels */
 int b200_me_init_search_range(int size);
 int b200_me_fullpel_launch(b200_ctx *ctx, const B200MeLaunch *launch, void *stream);

@@ -28,7 +28,7 @@ def upload_tables(ctx, tables):
     return (dj, d0, d1), (dj.ptr.value, d0.ptr.value + 4 * H.MV_TABLE_HALF, d1.ptr.value + 4 * H.MV_TABLE_HALF)
 
 
-def me_launch(ctx, cur, refb, params, tables_dev, subpel, window_bytes):
+def me_launch(ctx, cur, refb, params, tables_dev, subpel, window_bytes, tma=True):
     import b200av1
     n = len(params)
     blocks = np.zeros(n, b200av1.MEBLOCK_DTYPE)
@@ -70,6 +70,12 @@ def me_launch(ctx, cur, refb, params, tables_dev, subpel, window_bytes):
     l.mvjcost, l.mvcost[0], l.mvcost[1] = tables_dev
     l.results = d_res.ptr
     l.window_bytes = window_bytes
+    if tma and not subpel:
+        # plane extents + largest window of the batch: the TMA engine stages block and window
+        l.cur_rows, l.ref_rows = cur.shape[0], refb.shape[0]
+        l.max_col_span = max(1, max(p.col_max - p.col_min for p in params))
+        l.max_row_span = max(1, max(p.row_max - p.row_min for p in params))
+        l.max_bw, l.max_bh = max(p.bw for p in params), max(p.bh for p in params)
     if subpel and any(p.sp_have_cost_list for p in params):
         cls = np.array([list(p.sp_cost_list) for p in params], np.int32)
         d_cls = b200av1.to_device(ctx, cls)
@@ -94,9 +100,10 @@ def test_fullpel_batch_vs_oracle(ctx, bd):
             r = H.MeResult()
             O.av1o_full_pixel_search(C.byref(p), C.byref(r))
             exp.append(r)
-        # window staged in shared memory / forced through global memory: same answers
-        for window in (150 * 1024, 0):
-            got = me_launch(ctx, cur, refb, params, tdev, False, window)
+        # window staged in shared memory by the TMA engine / by the threads / forced through
+        # global memory: same answers
+        for window, tma in ((150 * 1024, True), (150 * 1024, False), (0, False)):
+            got = me_launch(ctx, cur, refb, params, tdev, False, window, tma)
             for i, (p, e) in enumerate(zip(params, exp)):
                 g = got[i]
                 tag = (trial, i, p.bw, p.bh, p.search_method, p.step_param, p.run_mesh_search,

@@ -8,4 +8,4 @@ ARCH="-gencode arch=compute_100a,code=sm_100a"
 $NVCC $ARCH -O3 -std=c++17 -lineinfo -Xcompiler -fPIC --expt-relaxed-constexpr -DB200_ME_TIMING \
   -c csrc/me.cu -o /tmp/me_timing.o
 $NVCC $ARCH -shared -o libb200av1_timing.so csrc/txq.o csrc/txq_inst_?.o csrc/blockops.o \
-  csrc/capi.o /tmp/me_timing.o csrc/rtcd.o -lcudart
+  csrc/capi.o csrc/compact.o csrc/hadamard.o csrc/quant_tables.o /tmp/me_timing.o csrc/rtcd.o -lcudart
