@@ -114,7 +114,7 @@ __device__ void diamond_runs(const Ctx &k, bool skip, Mv start, unsigned start_s
       publish_candidates<SEGW>(k, n, [&](int i) {
         return Mv{ c.row + cfg.site[st][i + 1][0], c.col + cfg.site[st][i + 1][1] };
       }, r * 16);
-      if (lane == 0) g_runn[r] = n;
+      if (lane == 0) g_runn[r] = n, atomicAdd(&g_bcast[24], n);
     } else if (lane == 0) {
       g_runn[r] = 0;
       g_runres[r][0] = cur[s].row, g_runres[r][1] = cur[s].col;
@@ -122,12 +122,17 @@ __device__ void diamond_runs(const Ctx &k, bool skip, Mv start, unsigned start_s
       g_runres[r][4] = (int)bestsad[s], g_runres[r][5] = center_steps[s], g_runres[r][6] = off_center[s];
     }
   };
-#pragma unroll
-  for (int s = 0; s < kSlots; ++s) publish(s);
+  // Run r > 0 starts one round per run later than run 0 (it has that many fewer steps, so the
+  // rounds do not grow): by then warp 0 knows whether run 0 is still on its centre after r
+  // steps -- if so num00 >= r and the reference never executes run r -- and either publishes
+  // run r's first candidates on its owner's behalf or leaves it out.
+  if (threadIdx.x < kMaxRuns) g_runn[threadIdx.x] = 0;
+  __syncthreads();
+  if (warp == 0) publish(0);
   __syncthreads();
   int ring = 0;
-  for (;;) {
-    if (!__any_sync(0xffffffffu, lane < nruns && g_runn[lane] > 0)) break;
+  for (int round = 0;; ++round) {
+    if (round >= nruns && !__any_sync(0xffffffffu, lane < nruns && g_runn[lane] > 0)) break;
     unsigned *cand = g_cand + ring * (kMaxRuns * 16);
     for (int r = 0; r < nruns; ++r) {
       const int n = g_runn[r];
@@ -139,7 +144,11 @@ __device__ void diamond_runs(const Ctx &k, bool skip, Mv start, unsigned start_s
 #pragma unroll
     for (int s = 0; s < kSlots; ++s) {
       const int r = warp + s * kWarps;
-      if (r >= nruns || step[s] < 0) continue;  // warp-uniform
+      if (r >= nruns || step[s] < 0 || r > round) continue;  // warp-uniform
+      if (r == round && r > 0 && g_runn[r] == 0) {  // left out by warp 0
+        step[s] = -1;
+        continue;
+      }
       const int st = step[s], n = cfg.per_step[st];
 #ifdef B200_ME_TIMING
       if (lane == 0) atomicAdd(&g_bcast[11], 1 + (n << 8));  // steps | candidates << 8
@@ -172,6 +181,14 @@ __device__ void diamond_runs(const Ctx &k, bool skip, Mv start, unsigned start_s
       step[s] = ns - 1;
       if (lane < 16) g_cand[((ring + 2) % 3) * (kMaxRuns * 16) + r * 16 + lane] = 0;
       publish(s);
+    }
+    if (warp == 0 && round + 1 < nruns && off_center[0]) {
+      // run 0 has left its centre within round + 1 steps: run round + 1 may be needed
+      const int r1 = round + 1, st1 = cfg.n_steps - (step_param + r1) - 1, n1 = cfg.per_step[st1];
+      publish_candidates<SEGW>(k, n1, [&](int i) {
+        return Mv{ start.row + cfg.site[st1][i + 1][0], start.col + cfg.site[st1][i + 1][1] };
+      }, r1 * 16);
+      if (lane == 0) g_runn[r1] = n1, atomicAdd(&g_bcast[24], n1);
     }
     ring = (ring + 1) % 3;
     __syncthreads();
@@ -630,6 +647,7 @@ __device__ int mesh_search(const Ctx &k, bool skip, Mv start, int range, int ste
     nc = (full & 3) ? full - 1 : full;
   }
   const int total = nr * nc;
+  if (threadIdx.x == 0) g_bcast[24] += total + 1;  // measurement: SAD candidates of this search
   // chunks of the scan: whole grid rows ("bands") for the register-blocked SAD maps,
   // kMaxCand candidates otherwise.  Chunk boundaries do not influence the decisions.
   const bool fast = mesh_fast_ok(k, skip, step, nc);
@@ -981,7 +999,8 @@ __global__ void __launch_bounds__(kThreads, 3) fullpel_kernel(const B200MeLaunch
   load_desc(l, bi);
   Ctx k(g_desc);
   k.l = &l;
-  if (me_family(k.d.search_method) != FAM) return;  // served by another instance of the launch
+  if (me_family(k.d.search_method) != FAM) return;
+  if (threadIdx.x == 0) g_bcast[24] = 0;  // served by another instance of the launch
   init_costs(k);
   {  // the method's site table: read at every step of the search, keep it on chip
     const int *g = reinterpret_cast<const int *>(sites4 + (k.d.search_method & 3));
@@ -1039,7 +1058,31 @@ __global__ void __launch_bounds__(kThreads, 3) fullpel_kernel(const B200MeLaunch
     r.cost_list[1] = g_bcast[13], r.cost_list[2] = g_bcast[14], r.cost_list[3] = g_bcast[15];  // mesh stages
 #endif
     l.results[bi] = r;
+    if (l.stats) {
+      atomicAdd(l.stats, (unsigned long long)g_bcast[24]);
+      atomicAdd(l.stats + 1, (unsigned long long)g_bcast[24] * (unsigned)(k.d.bw * k.d.bh));
+    }
   }
+}
+
+// Back-to-back VABSDIFF4.ACC on 8 independent accumulators per thread: the integer pipe's
+// measured SAD rate (b200_measure_sad_peak).
+__global__ void __launch_bounds__(256) sad_peak_kernel(unsigned *out, int iters, unsigned seed) {
+  unsigned a[8], x = seed + threadIdx.x, y = seed * 3 + blockIdx.x;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) a[i] = 0;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) a[i] = sad4_acc(x + i, y, a[i]);
+    }
+    x += a[0] & 1;
+  }
+  unsigned t = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) t += a[i];
+  if (t == 0x12345678u) out[0] = t;
 }
 
 }  // namespace me

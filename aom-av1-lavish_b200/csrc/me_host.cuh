@@ -194,3 +194,97 @@ extern "C" int b200_me_init_search_range(int size) {
   while ((size << sr) < 1023) sr++;  // MAX_FULL_PEL_VAL
   return sr < b200::me::kMaxSteps - 2 ? sr : b200::me::kMaxSteps - 2;
 }
+
+extern "C" int b200_measure_sad_peak(b200_ctx *ctx, double *gabsdiff_per_s) {
+  if (!ctx || !gabsdiff_per_s) return B200_EINVAL;
+  B200_CUDA_TRY(cudaSetDevice(ctx->device));
+  unsigned *d = nullptr;
+  B200_CUDA_TRY(cudaMalloc(&d, 16));
+  cudaEvent_t e0, e1;
+  B200_CUDA_TRY(cudaEventCreate(&e0));
+  B200_CUDA_TRY(cudaEventCreate(&e1));
+  const int grid = ctx->sm_count * 8, iters = 4096;
+  float best = 1e30f;
+  for (int rep = 0; rep < 5; ++rep) {
+    B200_CUDA_TRY(cudaEventRecord(e0, ctx->stream));
+    b200::me::sad_peak_kernel<<<grid, 256, 0, ctx->stream>>>(d, iters, 17u + rep);
+    B200_CUDA_TRY(cudaEventRecord(e1, ctx->stream));
+    B200_CUDA_TRY(cudaEventSynchronize(e1));
+    float ms = 0;
+    B200_CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+    if (rep > 0 && ms < best) best = ms;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d);
+  const double ops = (double)grid * 256 * iters * 32 * 4;  // 32 VABSDIFF4 per iteration, 4 pixels each
+  *gabsdiff_per_s = ops / (best * 1e-3) / 1e9;
+  return B200_OK;
+}
+
+extern "C" int b200_me_batch_host(b200_ctx *ctx, const B200MeLaunch *hl, size_t cur_bytes, size_t ref_bytes,
+                                  const B200MeBlock *subpel_blocks, B200MeResult *fullpel_out,
+                                  B200MeResult *subpel_out) {
+  if (!ctx || !hl || hl->n_blocks < 0 || !hl->blocks || !hl->cur || !hl->ref) return B200_EINVAL;
+  if (hl->n_blocks == 0) return B200_OK;
+  B200_CUDA_TRY(cudaSetDevice(ctx->device));
+  const size_t n = (size_t)hl->n_blocks;
+  const size_t tab = (size_t)(2 * 16383 + 1) * sizeof(int);
+  const bool costs = hl->mvcost[0] && hl->mvcost[1] && hl->mvjcost;
+  size_t off = 0;
+  auto carve = [&](size_t bytes) {
+    const size_t o = off;
+    off += (bytes + 255) & ~(size_t)255;
+    return o;
+  };
+  const size_t o_cur = carve(cur_bytes), o_ref = carve(ref_bytes), o_blk = carve(n * sizeof(B200MeBlock));
+  const size_t o_sub = carve(subpel_blocks ? n * sizeof(B200MeBlock) : 0);
+  const size_t o_rf = carve(n * sizeof(B200MeResult)), o_rs = carve(subpel_blocks ? n * sizeof(B200MeResult) : 0);
+  const size_t o_j = carve(costs ? 4 * sizeof(int) : 0), o_c0 = carve(costs ? tab : 0), o_c1 = carve(costs ? tab : 0);
+  int rc = b200::scratch_reserve(ctx, off);
+  if (rc != B200_OK) return rc;
+  char *base = (char *)ctx->d_scratch;
+  cudaStream_t s = ctx->stream;
+  B200_CUDA_TRY(cudaMemcpyAsync(base + o_cur, hl->cur, cur_bytes, cudaMemcpyHostToDevice, s));
+  B200_CUDA_TRY(cudaMemcpyAsync(base + o_ref, hl->ref, ref_bytes, cudaMemcpyHostToDevice, s));
+  B200_CUDA_TRY(cudaMemcpyAsync(base + o_blk, hl->blocks, n * sizeof(B200MeBlock), cudaMemcpyHostToDevice, s));
+  if (subpel_blocks)
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_sub, subpel_blocks, n * sizeof(B200MeBlock), cudaMemcpyHostToDevice, s));
+  B200MeLaunch dl = *hl;
+  dl.blocks = (const B200MeBlock *)(base + o_blk);
+  dl.cur = base + o_cur;
+  dl.ref = base + o_ref;
+  dl.results = (B200MeResult *)(base + o_rf);
+  dl.cost_lists = nullptr;
+  dl.start_from = nullptr;
+  dl.stats = nullptr;
+  dl.mvjcost = nullptr;
+  dl.mvcost[0] = dl.mvcost[1] = nullptr;
+  if (costs) {
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_j, hl->mvjcost, 4 * sizeof(int), cudaMemcpyHostToDevice, s));
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_c0, hl->mvcost[0] - 16383, tab, cudaMemcpyHostToDevice, s));
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_c1, hl->mvcost[1] - 16383, tab, cudaMemcpyHostToDevice, s));
+    dl.mvjcost = (const int *)(base + o_j);
+    dl.mvcost[0] = (const int *)(base + o_c0) + 16383;
+    dl.mvcost[1] = (const int *)(base + o_c1) + 16383;
+  }
+  rc = b200_me_fullpel_launch(ctx, &dl, s);
+  if (rc != B200_OK) return rc;
+  if (fullpel_out)
+    B200_CUDA_TRY(cudaMemcpyAsync(fullpel_out, base + o_rf, n * sizeof(B200MeResult), cudaMemcpyDeviceToHost, s));
+  if (subpel_blocks) {
+    B200MeLaunch sl = dl;
+    sl.blocks = (const B200MeBlock *)(base + o_sub);
+    sl.start_from = (const B200MeResult *)(base + o_rf);
+    sl.results = (B200MeResult *)(base + o_rs);
+    // the pruned trees read the full-pel cost list in place
+    sl.cost_lists = &((const B200MeResult *)(base + o_rf))->cost_list[0];
+    sl.cost_list_stride = sizeof(B200MeResult) / sizeof(int32_t);
+    rc = b200_me_subpel_launch(ctx, &sl, s);
+    if (rc != B200_OK) return rc;
+    if (subpel_out)
+      B200_CUDA_TRY(cudaMemcpyAsync(subpel_out, base + o_rs, n * sizeof(B200MeResult), cudaMemcpyDeviceToHost, s));
+  }
+  B200_CUDA_TRY(cudaStreamSynchronize(s));
+  return B200_OK;
+}

@@ -29,6 +29,7 @@ struct SubCtx {
   __device__ explicit SubCtx(const B200MeBlock &desc) : k(desc) {}
   unsigned short *tmp;  // shared: (bh + 7) * bw horizontally filtered samples
   int search_type;      // B200_USE_*
+  Mv start;             // 1/8 pel: the descriptor's start mv, or 8 x the chained full-pel result
 };
 
 __device__ __forceinline__ int ref_px(const Ctx &k, const unsigned char *p, long long idx) {
@@ -155,8 +156,7 @@ __device__ void subpel_search(const SubCtx &s, SubState &st) {
   const int mode = s.search_type != B200_USE_2_TAPS_ORIG ? 2 : 1;
   const int round = min(B200_FULL_PEL - forced_stop, 3 - !allow_hp);
   int hstep = 4;  // INIT_SUBPEL_STEP_SIZE
-  st.best.row = k.d.start_row;
-  st.best.col = k.d.start_col;
+  st.best = s.start;
   unsigned sse;
   const unsigned e = cta_pref_error(s, st.best, mode == 2 ? 2 : 0, &sse);
   st.distortion = (int)e;
@@ -243,8 +243,7 @@ __device__ void subpel_search_pruned(const SubCtx &s, SubState &st, int tree, co
   const int forced_stop = k.d.subpel & 3, iters_per_step = (k.d.subpel >> 2) & 3;
   const int allow_hp = (k.d.flags & B200_ME_ALLOW_HP) != 0;
   int hstep = 4;
-  st.best.row = k.d.start_row;
-  st.best.col = k.d.start_col;
+  st.best = s.start;
   const Mv start = st.best;
   unsigned sse;
   const unsigned e = cta_pref_error(s, st.best, 0, &sse);  // setup_center_error :2781
@@ -294,6 +293,8 @@ __global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) 
   s.k.px = l.highbd ? 2 : 1;
   s.k.sad_shift = 0;
   s.search_type = (s.k.d.subpel >> 4) & 3;
+  s.start = Mv{ s.k.d.start_row, s.k.d.start_col };
+  if (l.start_from) s.start = Mv{ l.start_from[bi].best_row * 8, l.start_from[bi].best_col * 8 };
   // the limits are sub-pel here: no window staging (window_budget 0), reference via L1/L2
   {
     const int px = s.k.px, bw = s.k.d.bw, bh = s.k.d.bh;

@@ -256,7 +256,7 @@ class MeLaunch(C.Structure):
                 ("window_bytes", C.c_int), ("max_bw", C.c_int), ("max_bh", C.c_int),
                 ("cost_lists", C.c_void_p), ("cost_list_stride", C.c_int), ("families", C.c_uint),
                 ("cur_rows", C.c_int), ("ref_rows", C.c_int), ("max_col_span", C.c_int),
-                ("max_row_span", C.c_int)]
+                ("max_row_span", C.c_int), ("start_from", C.c_void_p), ("stats", C.c_void_p)]
 
 
 ME_FAMILY_NSTEP, ME_FAMILY_PATTERN, ME_FAMILY_REFINE = 1, 2, 4

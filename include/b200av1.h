@@ -470,6 +470,13 @@ typedef struct {
                                     by the threads */
   int max_col_span, max_row_span; /* largest col_max - col_min / row_max - row_min of the batch
                                     (full-pel units): sizes the TMA box of the search window */
+  const B200MeResult *start_from; /* sub-pel launch, device: when set, block i starts at 8 x the
+                                    full-pel result start_from[i].best_{row,col} instead of its
+                                    descriptor's start mv (chains b200_me_fullpel_launch into
+                                    b200_me_subpel_launch without a host round trip, as
+                                    av1_single_motion_search does, motion_search_facade.c:120-494) */
+  unsigned long long *stats;     /* full-pel launch, device, optional: [0] += SAD candidates evaluated,
+                                    [1] += pixels compared (measurement only) */
 } B200MeLaunch;
 #define B200_ME_FAMILY_NSTEP 1u   /* NSTEP, NSTEP_8PT, DIAMOND, CLAMPED_DIAMOND */
 #define B200_ME_FAMILY_PATTERN 2u /* HEX .. VFAST_DIAMOND (pattern_search) */
@@ -478,6 +485,20 @@ typedef struct {
 int b200_me_init_search_range(int size);
 int b200_me_fullpel_launch(b200_ctx *ctx, const B200MeLaunch *launch, void *stream);
 int b200_me_subpel_launch(b200_ctx *ctx, const B200MeLaunch *launch, void *stream);
+/* Host-buffer motion search of one batch (what `e2e` times for the search half): `launch`
+ * describes the batch with HOST pointers in blocks / cur / ref / mvjcost / mvcost (cost tables
+ * optional; mvcost pointers are centred, each table spans -MV_MAX..MV_MAX = 2 * 16383 + 1 ints);
+ * cur_bytes / ref_bytes are the plane buffer sizes.  Copies everything to the device, runs the
+ * full-pel launch and, when subpel_blocks is given, the sub-pel launch chained on the full-pel
+ * result (start_from), copies fullpel_out / subpel_out (n_blocks each, either may be NULL)
+ * back and synchronises. */
+int b200_me_batch_host(b200_ctx *ctx, const B200MeLaunch *launch, size_t cur_bytes, size_t ref_bytes,
+                       const B200MeBlock *subpel_blocks, B200MeResult *fullpel_out,
+                       B200MeResult *subpel_out);
+/* Measured rate of the integer pipe on this device: VABSDIFF4 with accumulate (the SAD
+ * instruction) issued back to back from every SM, in G pixel-absdiffs per second.  The
+ * denominator of the motion search's int-ALU roofline. */
+int b200_measure_sad_peak(b200_ctx *ctx, double *gabsdiff_per_s);
 
 #ifdef __cplusplus
 }
