@@ -68,6 +68,7 @@ def make_residual_frames(frame_ids, seed):
     planes = [(1920, 1080), (960, 540), (960, 540)]
     frame_elems = sum(w * h for w, h in planes)
     out = np.zeros((len(frame_ids), frame_elems), np.int16)
+    luma = np.zeros((len(frame_ids), 1080, 1920), np.uint8)
     rng0 = np.random.default_rng(seed)
     base = [synth.smooth_frame(rng0, w, h, 8) for (w, h) in planes]
     for i, f in enumerate(frame_ids):
@@ -75,10 +76,12 @@ def make_residual_frames(frame_ids, seed):
         o = 0
         for (w, h), s in zip(planes, base):
             src = np.roll(s, (f * 2, f * 3), (0, 1))
+            if o == 0:
+                luma[i] = src
             pred = synth.pred_from(rng, src, 8)
             out[i, o:o + w * h] = (src.astype(np.int16) - pred.astype(np.int16)).reshape(-1)
             o += w * h
-    return out, planes
+    return out, planes, luma
 
 
 def make_descriptors(ts, n_frames, planes, frame_elems, seed):
@@ -222,113 +225,130 @@ def cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed, n_threads, sizes=r
 
 # ------------------------------------------------------------------ ME workload ----
 ME_BORDER = 160  # AOM_ENC_NO_SCALE_BORDER, aom_scale/yv12config.h:28-32
+ME_MESH = ((64, 8), (28, 4), (15, 1), (7, 1))  # speed_features.c:25-33 (good quality)
 
 
-def bench_me(ctx, dev, stream, steps, warmup, seed, frame_id, n_frames=8):
-    """BASELINE configs[2]: full-pel (NSTEP + mesh {64,8},{28,4},{15,1}) and sub-pel (8-tap
-    tree) search of every 64x64 superblock of `n_frames` 1080p 8-bit frames against 2
-    references each, +-64 range, L1 (HD) mv cost.  All frames and references live in one
-    plane pool (stacked vertically), so ONE launch per kernel covers the whole batch.
-    Returns device-timed ms per frame for both kernels."""
-    import torch
-    import b200av1
-    import synth
-    rng = np.random.default_rng([seed, frame_id, 77])
-    w, h = 1920, 1080
-    base = synth.smooth_frame(rng, w, h, 8)
-    rstride, rh = w + 2 * ME_BORDER, h + 2 * ME_BORDER
-    curs = np.zeros((n_frames, h, w), np.uint8)
-    refs = np.zeros((n_frames * 2, rh, rstride), np.uint8)
-    for f in range(n_frames):
-        curs[f] = np.roll(base, (f * 2, f * 3), (0, 1))
-        for r in range(2):
-            dy, dx = int(rng.integers(-20, 21)), int(rng.integers(-20, 21))
-            ref = np.roll(curs[f], (dy, dx), (0, 1)).astype(np.int16) + \
-                np.rint(rng.normal(0, 2, (h, w))).astype(np.int16)
-            refs[f * 2 + r] = np.pad(np.clip(ref, 0, 255).astype(np.uint8), ME_BORDER, mode="edge")
-    sbs = [(bx, by) for by in range(0, h - 63, 64) for bx in range(0, w - 63, 64)]
-    n_sb = len(sbs)
-    n = n_sb * 2 * n_frames
-    blocks = np.zeros(n, b200av1.MEBLOCK_DTYPE)
-    i = 0
-    for f in range(n_frames):
-        for r in range(2):
-            for (bx, by) in sbs:
-                b = blocks[i]
-                b["src_offset"] = (f * h + by) * w + bx
-                b["ref_offset"] = ((f * 2 + r) * rh + by + ME_BORDER) * rstride + bx + ME_BORDER
-                i += 1
-    blocks["col_min"], blocks["col_max"], blocks["row_min"], blocks["row_max"] = -64, 64, -64, 64
-    blocks["bw"], blocks["bh"] = 64, 64
-    blocks["search_method"] = 0  # B200_ME_NSTEP
-    blocks["flags"] = b200av1.ME_RUN_MESH
-    blocks["mv_cost_type"] = 3  # MV_COST_L1_HDRES
-    blocks["sad_per_bit"], blocks["error_per_bit"] = 40, 90
-    blocks["step_param"] = b200av1.lib().b200_me_init_search_range(64)
-    d_cur = torch.from_numpy(curs.reshape(-1)).to(dev)
-    d_ref = torch.from_numpy(refs.reshape(-1)).to(dev)
-    d_blk = torch.from_numpy(blocks.view(np.uint8)).to(dev)
-    d_res = torch.zeros(n * 40, dtype=torch.uint8, device=dev)
+class MeWork:
+    """BASELINE configs[2] on a set of frames: every 64x64 superblock of each frame against 2
+    reference frames, +-64 range clipped to the bordered reference, NSTEP + 4-stage mesh, L1 (HD)
+    mv cost; the sub-pel tree (8 taps, 1/8 pel, 2 iterations per step) starts at the full-pel
+    result.  All frames and references live in one plane pool (stacked vertically), so ONE launch
+    per kernel covers the whole set.  References are the frame translated by a random mv plus
+    noise, a function of (seed, frame id, reference) only."""
 
-    def launch(kind, d_blocks):
+    def __init__(self, luma, frame_ids, seed, bd=8):
+        import b200av1
+        self.bd = bd
+        F, h, w = luma.shape
+        self.F, self.h, self.w = F, h, w
+        self.rstride, self.rh = w + 2 * ME_BORDER, h + 2 * ME_BORDER
+        self.cur = np.ascontiguousarray(luma)
+        self.refs = np.zeros((F * 2, self.rh, self.rstride), luma.dtype)
+        hi = (1 << bd) - 1
+        for i, f in enumerate(frame_ids):
+            rng = np.random.default_rng([seed, int(f), 77])
+            for r in range(2):
+                dy, dx = int(rng.integers(-20, 21)), int(rng.integers(-20, 21))
+                noise = rng.integers(-3 << (bd - 8), (3 << (bd - 8)) + 1, (h, w), dtype=np.int16)
+                ref = np.roll(luma[i], (dy, dx), (0, 1)).astype(np.int16) + noise
+                self.refs[i * 2 + r] = np.pad(np.clip(ref, 0, hi).astype(luma.dtype), ME_BORDER, mode="edge")
+        self.sbs = [(bx, by) for by in range(0, h - 63, 64) for bx in range(0, w - 63, 64)]
+        self.n_sb = len(self.sbs)
+        self.per_frame = 2 * self.n_sb
+        self.n = self.per_frame * F
+        self.blocks = self._blocks(range(F), pooled=True)
+        self.sub = self._sub(self.blocks)
+        self.step_param = int(b200av1.lib().b200_me_init_search_range(64))
+
+    def _blocks(self, frames, pooled):
+        """full-pel descriptors of `frames` (pool indices); pooled=False: offsets relative to a
+        single frame's own cur / 2-reference buffers (the host-buffer call ships one frame)"""
+        import b200av1
+        h, w, rh, rs = self.h, self.w, self.rh, self.rstride
+        blocks = np.zeros(self.per_frame * len(frames), b200av1.MEBLOCK_DTYPE)
+        i = 0
+        for j, f in enumerate(frames):
+            fc, fr = (f, f * 2) if pooled else (0, 0)
+            for r in range(2):
+                for (bx, by) in self.sbs:
+                    b = blocks[i]
+                    b["src_offset"] = (fc * h + by) * w + bx
+                    b["ref_offset"] = ((fr + r) * rh + by + ME_BORDER) * rs + bx + ME_BORDER
+                    i += 1
+        blocks["col_min"], blocks["col_max"], blocks["row_min"], blocks["row_max"] = -64, 64, -64, 64
+        blocks["bw"], blocks["bh"] = 64, 64
+        blocks["search_method"] = 0  # B200_ME_NSTEP
+        blocks["flags"] = b200av1.ME_RUN_MESH
+        blocks["mv_cost_type"] = 3  # MV_COST_L1_HDRES
+        blocks["sad_per_bit"], blocks["error_per_bit"] = 40, 90
+        blocks["step_param"] = b200av1.lib().b200_me_init_search_range(64)
+        return blocks
+
+    @staticmethod
+    def _sub(blocks):
+        import b200av1
+        sb = blocks.copy()
+        sb["col_min"], sb["col_max"], sb["row_min"], sb["row_max"] = -512, 512, -512, 512
+        sb["flags"] = b200av1.ME_ALLOW_HP
+        sb["subpel"] = 0 | (2 << 2) | (3 << 4)  # EIGHTH_PEL, 2 iters/step, USE_8_TAPS
+        return sb
+
+    def launch_struct(self, blocks_ptr, cur_ptr, ref_ptr, res_ptr, n, cur_rows, ref_rows):
+        import b200av1
         l = b200av1.MeLaunch()
-        l.highbd, l.bd, l.n_blocks = 0, 8, n
-        l.blocks, l.cur, l.ref = d_blocks.data_ptr(), d_cur.data_ptr(), d_ref.data_ptr()
-        l.cur_stride, l.ref_stride = w, rstride
-        for i, (r, it) in enumerate(((64, 8), (28, 4), (15, 1), (7, 1))):
+        l.highbd, l.bd, l.n_blocks = int(self.bd > 8), self.bd, n
+        l.blocks, l.cur, l.ref = blocks_ptr, cur_ptr, ref_ptr
+        l.cur_stride, l.ref_stride = self.w, self.rstride
+        for i, (r, it) in enumerate(ME_MESH):
             l.mesh_range[i], l.mesh_interval[i] = r, it
-        l.results = d_res.data_ptr()
-        l.window_bytes, l.max_bw, l.max_bh = 48 * 1024, 64, 64
+        l.results = res_ptr
+        l.window_bytes, l.max_bw, l.max_bh = (48 if self.bd == 8 else 88) * 1024, 64, 64
         l.families = b200av1.ME_FAMILY_NSTEP
-        l.cur_rows, l.ref_rows = n_frames * h, n_frames * 2 * rh
+        l.cur_rows, l.ref_rows = cur_rows, ref_rows
         l.max_col_span, l.max_row_span = 128, 128
-        fn = b200av1.lib().b200_me_fullpel_launch if kind == 0 else b200av1.lib().b200_me_subpel_launch
-        b200av1.check(fn(ctx.h, C.byref(l), C.c_void_p(stream.cuda_stream)))
+        return l
 
-    # full-pel once (untimed) to build the sub-pel descriptors from its results
-    launch(0, d_blk)
-    torch.cuda.synchronize(dev)
-    res = d_res.cpu().numpy().view(b200av1.MERESULT_DTYPE)
-    if os.environ.get("B200_ME_DEBUG"):  # library built with -DB200_ME_TIMING (dev only)
-        print("ME timing (cycles): staging %.0f diamond %.0f mesh %.0f / %.0f / %.0f total %.0f" % (
-            16 * res["cost_list"][:, 4].mean(), 16.0 * res["distortion"].mean(),
-            16.0 * res["cost_list"][:, 1].mean(), 16.0 * res["cost_list"][:, 2].mean(),
-            16.0 * res["cost_list"][:, 3].mean(), 16.0 * res["sse"].mean()), file=sys.stderr)
-        print("ME diamond: steps/search %.1f candidates/search %.1f" % (
-            (res["cost_list"][:, 0] & 255).mean(), (res["cost_list"][:, 0] >> 8).mean()), file=sys.stderr)
-    sb = blocks.copy()
-    sb["start_row"], sb["start_col"] = res["best_row"] * 8, res["best_col"] * 8
-    sb["col_min"], sb["col_max"], sb["row_min"], sb["row_max"] = -512, 512, -512, 512
-    sb["flags"] = b200av1.ME_ALLOW_HP
-    sb["subpel"] = 0 | (2 << 2) | (3 << 4)  # EIGHTH_PEL, 2 iters/step, USE_8_TAPS
-    d_sub = torch.from_numpy(sb.view(np.uint8)).to(dev)
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-    t_full = t_sub = 0.0
-    for it in range(warmup + steps):
-        ev[0].record(stream)
-        launch(0, d_blk)
-        ev[1].record(stream)
-        launch(1, d_sub)
-        ev[2].record(stream)
-        torch.cuda.synchronize(dev)
-        if it >= warmup:
-            t_full += ev[0].elapsed_time(ev[1])
-            t_sub += ev[1].elapsed_time(ev[2])
-    t_full /= steps * n_frames  # ms per frame
-    t_sub /= steps * n_frames
-    # mesh candidates per search (lower bound of the SAD work; diamond steps come on top):
-    # 17x17 @8, 15x15 @4, 31 rows x 30 cols @1 (the reference's tail-loop quirk)
-    cands = 17 * 17 + 15 * 15 + 31 * 30
-    per_frame = 2 * n_sb
-    return {"workload": "config[2]: %d frames x 1080p 8-bit, %d 64x64 SBs x 2 refs per frame, +-64, "
-                        "NSTEP+mesh, 8-tap sub-pel; one launch per kernel" % (n_frames, n_sb),
-            "fullpel_ms_per_frame": t_full, "subpel_ms_per_frame": t_sub,
-            "frames_per_s": 1e3 / (t_full + t_sub),
-            "mesh_gabsdiff_per_s": per_frame * cands * 4096 / (t_full * 1e-3) / 1e9,
-            "unique_bytes_per_frame": per_frame * (4096 + 192 * 192 + 64),
-            "unique_GBps": per_frame * (4096 + 192 * 192 + 64) / (t_full * 1e-3) / 1e9,
-            "launches_per_step": 2, "frames_per_launch": n_frames}
+    def cpu_params(self, H, frame):
+        """harness.MeParams of every search of pool frame `frame` (host pointers)"""
+        out = (H.MeParams * self.per_frame)()
+        esz = self.cur.itemsize
+        i = 0
+        for r in range(2):
+            ref = self.refs[frame * 2 + r]
+            for (bx, by) in self.sbs:
+                p = out[i]
+                p.src = self.cur.ctypes.data + ((frame * self.h + by) * self.w + bx) * esz
+                p.ref = ref.ctypes.data + ((by + ME_BORDER) * self.rstride + bx + ME_BORDER) * esz
+                p.src_stride, p.ref_stride = self.w, self.rstride
+                p.bw, p.bh, p.highbd, p.bd = 64, 64, int(self.bd > 8), self.bd
+                p.col_min, p.col_max, p.row_min, p.row_max = -64, 64, -64, 64
+                p.search_method, p.step_param, p.run_mesh_search = 0, self.step_param, 1
+                for k, (rg, it) in enumerate(ME_MESH):
+                    p.mesh_range[k], p.mesh_interval[k] = rg, it
+                p.mv_cost_type, p.sad_per_bit, p.error_per_bit = 3, 40, 90
+                p.want_cost_list = p.want_second_best = 1
+                p.allow_hp, p.forced_stop, p.iters_per_step, p.subpel_search_type = 1, 0, 2, 3
+                p.sp_col_min, p.sp_col_max, p.sp_row_min, p.sp_row_max = -512, 512, -512, 512
+                i += 1
+        return out
 
+
+def cpu_run_me(H, O, R, work, frame, n_threads):
+    """one frame's searches (full-pel + sub-pel) through the CPU path: the reference's own
+    av1_full_pixel_search / av1_find_best_sub_pixel_tree (oracle/_ref via ref_shim.c) when
+    built, else the oracle's restatement.  Returns (seconds, full results, sub results)."""
+    params = work.cpu_params(H, frame)
+    n = work.per_frame
+    rf, rs = (H.MeResult * n)(), (H.MeResult * n)()
+    if R is not None:
+        full = C.cast(R.refshim_full_pixel_search, C.c_void_p)
+        sub = C.cast(R.refshim_find_best_sub_pixel_tree, C.c_void_p)
+    else:
+        full = C.cast(O.av1o_full_pixel_search, C.c_void_p)
+        sub = C.cast(O.av1o_find_best_sub_pixel_tree, C.c_void_p)
+    t0 = time.perf_counter()
+    O.av1o_drv_me(full, sub, params, n, rf, rs, n_threads)
+    return time.perf_counter() - t0, rf, rs
 
 
 def bench_hbd4k(ctx, dev, stream, steps, warmup, seed, n_frames=3):
@@ -457,6 +477,247 @@ def build_qrows(bd):
     return rows
 
 
+def pinned(nbytes, dtype):
+    """numpy view of page-locked host memory (b200_malloc_host); lives until process exit"""
+    import b200av1
+    p = C.c_void_p()
+    b200av1.check(b200av1.lib().b200_malloc_host(C.c_size_t(max(nbytes, 16)), C.byref(p)))
+    n = nbytes // np.dtype(dtype).itemsize
+    return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(max(nbytes, 16),)).view(dtype)[:n]
+
+
+def pinned_copy(a):
+    out = pinned(a.nbytes, a.dtype)
+    out[:] = a.reshape(-1)
+    return out.reshape(a.shape)
+
+
+def combined(r_txq, r_me):
+    """frame-equiv/s for txfm+quant+ME = FE / (t_txq + t_me): one
+    frame-equivalent passes through the transform+quantise stage once (rate r_txq, FE/s averaged
+    over the 19 size passes) and through the motion search once (rate r_me, frames/s)."""
+    return 1.0 / (1.0 / r_txq + 1.0 / r_me)
+
+
+def me_mismatches(H, got_full, got_sub, rf, rs, n):
+    bad = 0
+    for i in range(n):
+        g, e = got_full[i], rf[i]
+        if (int(g["best_row"]), int(g["best_col"]), int(g["second_row"]), int(g["second_col"]),
+                tuple(int(v) for v in g["cost_list"]), int(g["ret"])) != e.key():
+            bad += 1
+        g, e = got_sub[i], rs[i]
+        if (int(g["best_row"]), int(g["best_col"]), int(g["ret"]), int(g["distortion"]),
+                int(g["sse"])) != e.key(True):
+            bad += 1
+    return bad
+
+
+def bench_config5(ctx, dev, stream, rank, world, seed, total_frames, batch, e2e_frames):
+    """BASELINE configs[4]: `total_frames` synthetic 4K 10-bit 4:2:0 frames, frame i -> rank
+    i mod world (strong scaling); every frame goes through the fused subtract + txfm +
+    av1_highbd_quantize_fp + av1_highbd_block_error sweep over all 19 TX sizes (uint16 planes)
+    and through the high-bit-depth motion search of all its 64x64 superblocks against 2
+    references.  Resident: frames uploaded in batches of `batch` (untimed), launches timed with
+    CUDA events.  e2e: the first `e2e_frames` frames of the rank through the host-buffer calls
+    (b200_txq_batch_host_compact + b200_me_batch_host), copies inside the timed region."""
+    import torch
+    import b200av1
+    from b200av1 import shard
+    ids = shard.frames_of_rank(total_frames, rank, world)
+    planes = [(3840, 2160), (1920, 1080), (1920, 1080)]
+    frame_elems = sum(w * h for w, h in planes)
+    rng = np.random.default_rng([seed, 5000])
+    base, noise = [], []
+    for _ in range(2):  # two base pictures; frame i = base[i % 2] panned by i
+        pl = []
+        for (w, h) in planes:
+            low = rng.integers(100, 900, (h // 8 + 1, w // 8 + 1))
+            pl.append((np.kron(low, np.ones((8, 8), np.int64))[:h, :w] + rng.integers(-8, 9, (h, w))).astype(np.int16))
+        base.append(pl)
+    for (w, h) in planes:  # one noise plane per picture plane, panned per frame (cheap and seeded)
+        noise.append(rng.integers(-12, 13, (h, w), dtype=np.int16))
+
+    def frame(i):
+        srcs, preds = [], []
+        for img, nz in zip(base[i % 2], noise):
+            s0 = np.roll(img, (3 * i % 64, 5 * i % 64), (0, 1))
+            pr = np.roll(s0, (1, 1), (0, 1)) + np.roll(nz, (7 * i % 97, 11 * i % 89), (0, 1))
+            srcs.append(np.clip(s0, 0, 1023).astype(np.uint16).reshape(-1))
+            preds.append(np.clip(pr, 0, 1023).astype(np.uint16).reshape(-1))
+        return np.concatenate(srcs), np.concatenate(preds)
+
+    qrows = build_qrows(10)
+    d_qrows = torch.from_numpy(qrows.view(np.uint8)).to(dev)
+    # descriptors of one batch (identical for every batch: offsets are batch-relative)
+    n_out = batch * frame_elems
+    d_coeff, d_qc, d_dq = (torch.empty(n_out, dtype=torch.int32, device=dev) for _ in range(3))
+    d_src = torch.empty(batch * frame_elems, dtype=torch.int16, device=dev)
+    d_pred = torch.empty(batch * frame_elems, dtype=torch.int16, device=dev)
+    launches, keep, txq_bytes, txq_samples = [], [], 0, 0
+    one_frame_blocks, one_frame_preds, out_off = [], [], 0
+    for ts in range(19):
+        blocks, samples = make_descriptors(ts, batch, planes, frame_elems, seed + 5)
+        preds = np.zeros(blocks.size, b200av1.TXPRED_DTYPE)
+        preds["pred_offset"], preds["pred_stride"] = blocks["src_offset"], blocks["src_stride"]
+        d_blocks = torch.from_numpy(blocks.view(np.uint8)).to(dev)
+        d_preds = torch.from_numpy(preds.view(np.uint8)).to(dev)
+        d_eob = torch.zeros(blocks.size, dtype=torch.int16, device=dev)
+        d_dist = torch.zeros(blocks.size * 2, dtype=torch.int64, device=dev)
+        keep += [d_blocks, d_preds, d_eob, d_dist]
+        l = b200av1.TxqLaunch()
+        l.tx_size, l.in_kind, l.q_kind, l.bd = ts, b200av1.IN_PIXELS16, b200av1.Q_FP_HBD, 10
+        l.flags = b200av1.TXQ_STORE_COEFF | b200av1.TXQ_BLOCK_ERROR
+        l.n_blocks = int(blocks.size)
+        l.blocks, l.preds = d_blocks.data_ptr(), d_preds.data_ptr()
+        l.src, l.pred, l.qrows = d_src.data_ptr(), d_pred.data_ptr(), d_qrows.data_ptr()
+        l.coeff, l.qcoeff, l.dqcoeff = d_coeff.data_ptr(), d_qc.data_ptr(), d_dq.data_ptr()
+        l.eob, l.dist = d_eob.data_ptr(), d_dist.data_ptr()
+        launches.append(l)
+        txq_bytes += blocks.size * (TX_W[ts] * TX_H[ts] * 4 + max_eob(ts) * 12 + 18)
+        txq_samples += samples
+        if e2e_frames:
+            b1, _s = make_descriptors(ts, 1, planes, frame_elems, seed + 5)
+            b1["out_offset"] += out_off
+            out_off += b1.size * max_eob(ts)
+            p1 = np.zeros(b1.size, b200av1.TXPRED_DTYPE)
+            p1["pred_offset"], p1["pred_stride"] = b1["src_offset"], b1["src_stride"]
+            one_frame_blocks.append(b1)
+            one_frame_preds.append(p1)
+    # motion search of a batch: cur = luma plane of each frame inside d_src (stride 3840)
+    w, h = planes[0]
+    rs, rh = w + 2 * ME_BORDER, h + 2 * ME_BORDER
+    sbs = [(bx, by) for by in range(0, h - 63, 64) for bx in range(0, w - 63, 64)]
+    per_frame = 2 * len(sbs)
+
+    def me_blocks(nf, frame_stride_elems):
+        blocks = np.zeros(per_frame * nf, b200av1.MEBLOCK_DTYPE)
+        i = 0
+        for f in range(nf):
+            for r in range(2):
+                for (bx, by) in sbs:
+                    blocks[i]["src_offset"] = f * frame_stride_elems + by * w + bx
+                    blocks[i]["ref_offset"] = ((f * 2 + r) * rh + by + ME_BORDER) * rs + bx + ME_BORDER
+                    i += 1
+        blocks["col_min"], blocks["col_max"], blocks["row_min"], blocks["row_max"] = -64, 64, -64, 64
+        blocks["bw"], blocks["bh"] = 64, 64
+        blocks["flags"] = b200av1.ME_RUN_MESH
+        blocks["mv_cost_type"] = 3
+        blocks["sad_per_bit"], blocks["error_per_bit"] = 40, 90
+        blocks["step_param"] = b200av1.lib().b200_me_init_search_range(64)
+        return blocks
+
+    mb = me_blocks(batch, frame_elems)
+    d_mb = torch.from_numpy(mb.view(np.uint8)).to(dev)
+    d_msub = torch.from_numpy(MeWork._sub(mb).view(np.uint8)).to(dev)
+    d_refs = torch.empty(batch * 2 * rh * rs, dtype=torch.int16, device=dev)
+    d_rf = torch.zeros(mb.size * 40, dtype=torch.uint8, device=dev)
+    d_rsub = torch.zeros(mb.size * 40, dtype=torch.uint8, device=dev)
+
+    def me_launch(kind):
+        l = b200av1.MeLaunch()
+        l.highbd, l.bd, l.n_blocks = 1, 10, int(mb.size)
+        l.blocks = (d_mb if kind == 0 else d_msub).data_ptr()
+        l.cur, l.ref = d_src.data_ptr(), d_refs.data_ptr()
+        l.cur_stride, l.ref_stride = w, rs
+        for i, (r, it) in enumerate(ME_MESH):
+            l.mesh_range[i], l.mesh_interval[i] = r, it
+        l.results = (d_rf if kind == 0 else d_rsub).data_ptr()
+        l.window_bytes, l.max_bw, l.max_bh = 88 * 1024, 64, 64
+        l.families = b200av1.ME_FAMILY_NSTEP
+        # cur rows: the luma planes sit frame_elems apart inside d_src (not a multiple of the
+        # stride times rows only when chroma follows): describe the pool as rows of 3840 samples
+        l.cur_rows, l.ref_rows = batch * frame_elems // w, batch * 2 * rh
+        l.max_col_span, l.max_row_span = 128, 128
+        if kind == 1:
+            l.start_from = d_rf.data_ptr()
+        fn = b200av1.lib().b200_me_fullpel_launch if kind == 0 else b200av1.lib().b200_me_subpel_launch
+        b200av1.check(fn(ctx.h, C.byref(l), C.c_void_p(stream.cuda_stream)))
+
+    def make_refs(i, cur_luma):
+        frng = np.random.default_rng([seed, 5000 + int(i), 9])
+        out = np.zeros((2, rh, rs), np.uint16)
+        for r in range(2):
+            dy, dx = int(frng.integers(-20, 21)), int(frng.integers(-20, 21))
+            ref = np.roll(cur_luma, (dy, dx), (0, 1)).astype(np.int16) + np.roll(noise[0], (13 * i + r, 3 * i + 5 * r), (0, 1))
+            out[r] = np.pad(np.clip(ref, 0, 1023).astype(np.uint16), ME_BORDER, mode="edge")
+        return out
+
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    t_txq = t_me = 0.0
+    n_done = 0
+    e2e_t = e2e_n = 0
+    e2e_h2d = e2e_d2h = 0
+    lib = b200av1.lib()
+    if e2e_frames:
+        eblocks = pinned_copy(np.concatenate(one_frame_blocks))
+        epreds = pinned_copy(np.concatenate(one_frame_preds))
+        h_levels = pinned(out_off * 4, np.int32)
+        h_loff = np.zeros(eblocks.size + 1, np.uint32)
+        h_eob = np.zeros(eblocks.size, np.uint16)
+        h_dist = np.zeros((eblocks.size, 2), np.int64)
+        h_src, h_pred = pinned(frame_elems * 2, np.uint16), pinned(frame_elems * 2, np.uint16)
+        h_refs = pinned(2 * rh * rs * 2, np.uint16)
+        emb = pinned_copy(me_blocks(1, frame_elems))
+        esub = pinned_copy(MeWork._sub(emb))
+        h_rf = np.zeros(emb.size, b200av1.MERESULT_DTYPE)
+        h_rs = np.zeros(emb.size, b200av1.MERESULT_DTYPE)
+    for b0 in range(0, len(ids), batch):
+        chunk = ids[b0:b0 + batch]
+        hs = np.zeros((batch, frame_elems), np.uint16)
+        hp = np.zeros((batch, frame_elems), np.uint16)
+        hr = np.zeros((batch * 2, rh, rs), np.uint16)
+        for j, i in enumerate(chunk):
+            hs[j], hp[j] = frame(i)
+            hr[2 * j:2 * j + 2] = make_refs(i, hs[j][:w * h].reshape(h, w))
+            if e2e_n < e2e_frames:
+                # ---- e2e: this frame through the host-buffer calls, copies inside the timed region
+                h_src[:], h_pred[:], h_refs[:] = hs[j], hp[j], hr[2 * j:2 * j + 2].reshape(-1)
+                torch.cuda.synchronize(dev)
+                t0 = time.perf_counter()
+                d2h = ctx.txq_batch_host_compact(b200av1.IN_PIXELS16, b200av1.Q_FP_HBD, 10,
+                                                 b200av1.TXQ_BLOCK_ERROR, eblocks, epreds, h_src, h_pred, qrows,
+                                                 out_off, h_levels, h_loff, h_eob, h_dist)
+                hl = b200av1.MeLaunch()
+                hl.highbd, hl.bd, hl.n_blocks = 1, 10, int(emb.size)
+                hl.blocks, hl.cur, hl.ref = emb.ctypes.data, h_src.ctypes.data, h_refs.ctypes.data
+                hl.cur_stride, hl.ref_stride = w, rs
+                for k, (rg, it) in enumerate(ME_MESH):
+                    hl.mesh_range[k], hl.mesh_interval[k] = rg, it
+                hl.window_bytes, hl.max_bw, hl.max_bh = 88 * 1024, 64, 64
+                hl.families = b200av1.ME_FAMILY_NSTEP
+                hl.cur_rows, hl.ref_rows = h, 2 * rh
+                hl.max_col_span, hl.max_row_span = 128, 128
+                b200av1.check(lib.b200_me_batch_host(ctx.h, C.byref(hl), C.c_size_t(w * h * 2),
+                                                     C.c_size_t(h_refs.nbytes), C.c_void_p(esub.ctypes.data),
+                                                     C.c_void_p(h_rf.ctypes.data), C.c_void_p(h_rs.ctypes.data)))
+                e2e_t += time.perf_counter() - t0
+                e2e_n += 1
+                e2e_h2d += 2 * frame_elems * 2 + eblocks.nbytes + epreds.nbytes + w * h * 2 + h_refs.nbytes + 2 * emb.nbytes
+                e2e_d2h += d2h + 2 * h_rf.nbytes
+        d_src.copy_(torch.from_numpy(hs.reshape(-1).view(np.int16)))
+        d_pred.copy_(torch.from_numpy(hp.reshape(-1).view(np.int16)))
+        d_refs.copy_(torch.from_numpy(hr.reshape(-1).view(np.int16)))
+        torch.cuda.synchronize(dev)
+        reps = 2 if b0 == 0 else 1  # the first batch once untimed (warm-up)
+        for rep in range(reps):
+            ev[0].record(stream)
+            for l in launches:
+                ctx.txq_launch(l, stream.cuda_stream)
+            ev[1].record(stream)
+            me_launch(0)
+            me_launch(1)
+            ev[2].record(stream)
+            torch.cuda.synchronize(dev)
+        frac = len(chunk) / batch  # a last partial batch still runs `batch` frames of work
+        t_txq += ev[0].elapsed_time(ev[1]) * frac
+        t_me += ev[1].elapsed_time(ev[2]) * frac
+        n_done += len(chunk)
+    return {"frames_rank": n_done, "t_txq_ms": t_txq, "t_me_ms": t_me, "txq_samples_per_frame": txq_samples / batch,
+            "txq_bytes_per_frame": txq_bytes / batch, "me_searches_per_frame": per_frame,
+            "e2e_s": e2e_t, "e2e_frames": e2e_n, "e2e_h2d": e2e_h2d, "e2e_d2h": e2e_d2h}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -467,8 +728,9 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--force-exact", action="store_true", help="always take the 64-bit half_btf path")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--no-me", action="store_true", help="skip the motion-search section")
-    ap.add_argument("--no-extras", action="store_true", help="skip the config[3] 4K 10-bit and Hadamard sections")
+    ap.add_argument("--no-me", action="store_true", help="(debug) time the transform half only")
+    ap.add_argument("--no-extras", action="store_true", help="skip the config[3] / config[4] / Hadamard sections")
+    ap.add_argument("--config5-frames", type=int, default=120, help="frames of the 4K 10-bit batch (all ranks)")
     ap.add_argument("--sizes", default="", help="comma list of tx sizes (debug)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -477,11 +739,14 @@ def main():
     sizes = [int(s) for s in args.sizes.split(",")] if args.sizes else list(range(19))
     seed = 2001
     metric = "1080p frame-equiv/s for txfm+quant+ME SAD; HBM GB/s as % of B200 peak"
-    config = {"workload": "txq_sweep_1080p_8bit: fused fwd txfm + quantize_fp over all %d TX sizes, "
-                          "%d synthetic 1080p 4:2:0 frames per GPU per launch" % (len(sizes), args.frames),
+    config = {"workload": "txq_me_1080p_8bit: per GPU %d synthetic 1080p 4:2:0 frames; each step = fused fwd txfm + "
+                          "quantize_fp over all %d TX sizes of every frame (configs[1]) + full-pel (NSTEP + 4-stage "
+                          "mesh, +-64) and sub-pel (8-tap tree) motion search of every 64x64 superblock against 2 "
+                          "references (configs[2]); value = 1 / (1/txq FE/s + 1/ME frames/s)" % (args.frames, len(sizes)),
               "frames_per_gpu": args.frames, "tx_sizes": len(sizes), "quantizer": "av1_quantize_fp",
-              "qindex_set": QINDEXES, "l2": "inputs (%.0f MB/GPU) larger than L2; outputs streamed"
-                                            % (args.frames * FE_SAMPLES * 2 / 1e6),
+              "qindex_set": QINDEXES, "me": "960 searches/frame: 480 SBs x 2 refs, MV_COST_L1_HDRES",
+              "l2": "inputs (%.0f MB residual + %.0f MB planes per GPU) larger than L2; outputs streamed"
+                    % (args.frames * FE_SAMPLES * 2 / 1e6, args.frames * (1920 * 1080 + 2 * 2240 * 1400) / 1e6),
               "parallelism": "frames sharded over %d GPU(s), no collective" % world,
               "butterflies": "exact64 (forced)" if args.force_exact else "guarded (32-bit when |residual|<=4094, proved exact; else 64-bit)"}
 
@@ -490,26 +755,31 @@ def main():
         if rank != 0:
             return 0
         H, O, R = load_cpu_libs()
-        frames, planes = make_residual_frames(1, seed)
+        frames, planes, luma = make_residual_frames(1, seed)
         frame_elems = frames.shape[1]
         n_threads = os.cpu_count() or 1
+        work = MeWork(luma, [0], seed)
         for _ in range(min(args.warmup, 1)):
             cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed, n_threads, sizes)
-        tt, ss = 0.0, 0
+        tt, ss, tm = 0.0, 0, 0.0
         for _ in range(args.steps):
-            t, s, _o = cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed, n_threads, sizes)
+            t, s_, _o = cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed, n_threads, sizes)
             tt += t
-            ss += s
-        val = ss / FE_SAMPLES / tt
+            ss += s_
+            tm += cpu_run_me(H, O, R, work, 0, n_threads)[0]
+        r_txq, r_me = ss / FE_SAMPLES / tt, args.steps / tm
+        val = combined(r_txq, r_me)
         kind = "reference" if R is not None else "port"
         line = {"impl": "reference", "metric": metric, "value": val, "unit": "1080p frame-equiv/s",
                 "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": tt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+                "ms_per_step": (tt + tm) / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "int32", "data": "synthetic", "config": config,
+                "txq_fe_per_s": r_txq, "me_frames_per_s": r_me,
                 "cpu_baseline": {"value": val, "unit": "1080p frame-equiv/s", "cores": n_threads,
                                  "kind": kind,
-                                 "sample": "per step: 1 frame x %d TX sizes (%.1f FE) through "
-                                           "av1_fwd_txfm2d_*_c + av1_quantize_fp*_c"
+                                 "sample": "per step: 1 frame x %d TX sizes (%.1f FE) through av1_fwd_txfm2d_*_c + "
+                                           "av1_quantize_fp*_c, and the frame's 960 searches through "
+                                           "av1_full_pixel_search + av1_find_best_sub_pixel_tree (generic C build)"
                                            % (len(sizes), ss / args.steps / FE_SAMPLES)},
                 "e2e": {"value": val, "unit": "1080p frame-equiv/s", "h2d_bytes_per_step": 0,
                         "d2h_bytes_per_step": 0}}
@@ -527,11 +797,18 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
     ctx = b200av1.Context(local_rank)
+    lib = b200av1.lib()
     stream = torch.cuda.Stream(device=dev)
+
+    def allmax(v):
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
     from b200av1 import shard
     frame_ids = shard.frames_of_rank(args.frames * world, rank, world)
-    frames, planes = make_residual_frames(frame_ids, seed)
+    frames, planes, luma = make_residual_frames(frame_ids, seed)
     frame_elems = frames.shape[1]
     d_src = torch.from_numpy(frames.reshape(-1)).to(dev)
     qrows = build_qrows_product()
@@ -567,13 +844,40 @@ def main():
         launches.append(l)
     sptr = stream.cuda_stream
 
+    # ---- motion search of the same frames (their luma planes), resident in HBM
+    work = None
+    if not args.no_me:
+        work = MeWork(luma, frame_ids, seed)
+        d_cur = torch.from_numpy(work.cur.reshape(-1)).to(dev)
+        d_ref = torch.from_numpy(work.refs.reshape(-1)).to(dev)
+        d_mblk = torch.from_numpy(work.blocks.view(np.uint8)).to(dev)
+        d_msub = torch.from_numpy(work.sub.view(np.uint8)).to(dev)
+        d_rfull = torch.zeros(work.n * 40, dtype=torch.uint8, device=dev)
+        d_rsub = torch.zeros(work.n * 40, dtype=torch.uint8, device=dev)
+        d_stats = torch.zeros(2, dtype=torch.int64, device=dev)
+        l_full = work.launch_struct(d_mblk.data_ptr(), d_cur.data_ptr(), d_ref.data_ptr(), d_rfull.data_ptr(),
+                                    work.n, work.F * work.h, work.F * 2 * work.rh)
+        l_full.stats = d_stats.data_ptr()
+        l_sub = work.launch_struct(d_msub.data_ptr(), d_cur.data_ptr(), d_ref.data_ptr(), d_rsub.data_ptr(),
+                                   work.n, work.F * work.h, work.F * 2 * work.rh)
+        l_sub.start_from = d_rfull.data_ptr()  # chained on the device: start = 8 x full-pel best
+
+    n_txq = len(launches)
+
     def step(events=None):
         for i, l in enumerate(launches):
             if events is not None:
                 events[i].record(stream)
             ctx.txq_launch(l, sptr)
         if events is not None:
-            events[len(launches)].record(stream)
+            events[n_txq].record(stream)
+        if work is not None:
+            b200av1.check(lib.b200_me_fullpel_launch(ctx.h, C.byref(l_full), C.c_void_p(sptr)))
+            if events is not None:
+                events[n_txq + 1].record(stream)
+            b200av1.check(lib.b200_me_subpel_launch(ctx.h, C.byref(l_sub), C.c_void_p(sptr)))
+        if events is not None:
+            events[n_txq + 2].record(stream)
 
     def barrier():
         torch.cuda.synchronize(dev)
@@ -585,8 +889,9 @@ def main():
         for _ in range(args.warmup):
             step()
     barrier()
-    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(launches) + 1)]
-          for _ in range(args.steps)]
+    if work is not None:
+        d_stats.zero_()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(n_txq + 3)] for _ in range(args.steps)]
     sampler = ClockSampler(local_rank)
     sampler.start()
     barrier()
@@ -594,87 +899,130 @@ def main():
         step(ev[k])
     barrier()
     clocks = sampler.stop()
-    step_ms = [ev[k][0].elapsed_time(ev[k][len(launches)]) for k in range(args.steps)]
-    total_ms = ev[0][0].elapsed_time(ev[args.steps - 1][len(launches)])
-    kern_ms = np.zeros(len(launches))
+    step_ms = [ev[k][0].elapsed_time(ev[k][n_txq + 2]) for k in range(args.steps)]
+    total_ms = ev[0][0].elapsed_time(ev[args.steps - 1][n_txq + 2])
+    kern_ms = np.zeros(n_txq)
+    t_txq = t_full = t_sub = 0.0
     for k in range(args.steps):
-        for i in range(len(launches)):
+        for i in range(n_txq):
             kern_ms[i] += ev[k][i].elapsed_time(ev[k][i + 1])
+        t_txq += ev[k][0].elapsed_time(ev[k][n_txq])
+        t_full += ev[k][n_txq].elapsed_time(ev[k][n_txq + 1])
+        t_sub += ev[k][n_txq + 1].elapsed_time(ev[k][n_txq + 2])
     kern_ms /= args.steps
-    t_local = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t_local, op=dist.ReduceOp.MAX)
-    total_ms_max = float(t_local.item())
+    total_ms_max = allmax(total_ms)
+    t_txq_max, t_me_max = allmax(t_txq), allmax(t_full + t_sub)
     fe_per_step_rank = total_samples / FE_SAMPLES
-    value = fe_per_step_rank * world * args.steps / (total_ms_max / 1e3)
+    r_txq = fe_per_step_rank * world * args.steps / (t_txq_max / 1e3)
+    if work is not None:
+        r_me = args.frames * world * args.steps / (t_me_max / 1e3)
+        value = combined(r_txq, r_me)
+        stats = d_stats.cpu().numpy()
+        sad_pixels_per_step = float(stats[1]) / args.steps
+    else:
+        r_me, value = None, r_txq
 
-    # ---- e2e: the same sweep through the host-buffer C-ABI call (1 frame / step)
+    # ---- e2e: the same work through the host-buffer C-ABI calls, 1 frame per step:
+    # b200_txq_batch_host_compact (19 sizes; levels in scan order up to eob come back) and
+    # b200_me_batch_host (planes + descriptors up, 2 x 40 B per search back)
     e2e = None
     if args.e2e_steps > 0:
         eb, e_samples = [], 0
         out_off = 0
         for ts in sizes:
-            b, s = make_descriptors(ts, 1, planes, frame_elems, seed + rank)
+            b, s_ = make_descriptors(ts, 1, planes, frame_elems, seed + rank)
             b["out_offset"] += out_off
             out_off += b.size * max_eob(ts)
             eb.append(b)
-            e_samples += s
-        eblocks = np.concatenate(eb)
-        lib = b200av1.lib()
+            e_samples += s_
+        eblocks = pinned_copy(np.concatenate(eb))
+        h_src = pinned_copy(frames[0])
+        h_levels = pinned(out_off * 2, np.int16)
+        h_loff = pinned((eblocks.size + 1) * 4, np.uint32)
+        h_eob = pinned(eblocks.size * 2, np.uint16)
+        d2h_txq = [0]
+        if work is not None:
+            e_mblk = pinned_copy(work._blocks([0], pooled=False))
+            e_msub = pinned_copy(MeWork._sub(e_mblk))
+            h_cur = pinned_copy(work.cur[0])
+            h_ref = pinned_copy(work.refs[0:2])
+            h_rf = pinned(e_mblk.size * 40, b200av1.MERESULT_DTYPE)
+            h_rs = pinned(e_mblk.size * 40, b200av1.MERESULT_DTYPE)
+            hl = work.launch_struct(e_mblk.ctypes.data, h_cur.ctypes.data, h_ref.ctypes.data, None,
+                                    int(e_mblk.size), work.h, 2 * work.rh)
 
-        def pinned(nbytes, dtype):
-            p = C.c_void_p()
-            b200av1.check(lib.b200_malloc_host(C.c_size_t(nbytes), C.byref(p)))
-            n = nbytes // np.dtype(dtype).itemsize
-            return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(nbytes,)).view(dtype)[:n], p
+        def e2e_txq():
+            d2h_txq[0] = ctx.txq_batch_host_compact(0, b200av1.Q_FP, 8, flags & ~b200av1.TXQ_STORE_COEFF, eblocks,
+                                                    None, h_src, None, qrows, out_off, h_levels, h_loff, h_eob)
 
-        h_src, p1 = pinned(frame_elems * 2, np.int16)
-        h_src[:] = frames[0]
-        h_coeff, p2 = pinned(out_off * 4, np.int32)
-        h_qc, p3 = pinned(out_off * 4, np.int32)
-        h_dq, p4 = pinned(out_off * 4, np.int32)
-        h_eob = np.zeros(eblocks.size, np.uint16)
-        h_blk, p5 = pinned(eblocks.nbytes, np.uint8)  # the descriptor queue is pinned too
-        h_blk[:] = eblocks.view(np.uint8)
-        eblocks = h_blk.view(TXBLOCK_DTYPE)
+        def e2e_me():
+            b200av1.check(lib.b200_me_batch_host(ctx.h, C.byref(hl), C.c_size_t(h_cur.nbytes),
+                                                 C.c_size_t(h_ref.nbytes), C.c_void_p(e_msub.ctypes.data),
+                                                 C.c_void_p(h_rf.ctypes.data), C.c_void_p(h_rs.ctypes.data)))
 
-        def e2e_step():
-            ctx.txq_batch_host(0, b200av1.Q_FP, 8, flags, eblocks, None, h_src, None, qrows,
-                               h_coeff, h_qc, h_dq, h_eob, None)
-
-        e2e_step()
+        e2e_txq()
+        if work is not None:
+            e2e_me()
         barrier()
-        t0 = time.perf_counter()
+        te_txq = te_me = 0.0
         for _ in range(args.e2e_steps):
-            e2e_step()
+            t0 = time.perf_counter()
+            e2e_txq()
+            t1 = time.perf_counter()
+            if work is not None:
+                e2e_me()
+            t2 = time.perf_counter()
+            te_txq += t1 - t0
+            te_me += t2 - t1
         torch.cuda.synchronize(dev)
-        dt = time.perf_counter() - t0
-        t_e = torch.tensor([dt], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
-        e2e = {"value": e_samples / FE_SAMPLES * world * args.e2e_steps / float(t_e.item()),
-               "unit": "1080p frame-equiv/s",
-               "h2d_bytes_per_step": int(frame_elems * 2 + eblocks.nbytes + qrows.nbytes),
-               "d2h_bytes_per_step": int(out_off * 12 + eblocks.size * 2),
-               "note": "b200_txq_batch_host: pinned host buffers, 1 frame x %d sizes per step; "
-                       "descriptor bucketing + H2D + %d launches + D2H (per tx-size group, overlapped "
-                       "on a second stream) inside the timed region" % (len(sizes), len(sizes))}
-        for p in (p1, p2, p3, p4):
-            pass  # pinned buffers live until process exit
-
-    me = None
-    if not args.no_me:
-        me = bench_me(ctx, dev, stream, max(2, args.steps // 2), 2, seed, frame_ids[0])
-        t_me = torch.tensor([me["fullpel_ms_per_frame"] + me["subpel_ms_per_frame"]],
-                            dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t_me, op=dist.ReduceOp.MAX)
-        me["frames_per_s_all_gpus"] = world * 1e3 / float(t_me.item())
+        te_txq, te_me = allmax(te_txq), allmax(te_me)
+        re_txq = e_samples / FE_SAMPLES * world * args.e2e_steps / te_txq
+        h2d = int(frame_elems * 2 + eblocks.nbytes + qrows.nbytes)
+        d2h = int(d2h_txq[0])
+        if work is not None:
+            re_me = world * args.e2e_steps / te_me
+            e2e_value = combined(re_txq, re_me)
+            h2d += int(h_cur.nbytes + h_ref.nbytes + 2 * e_mblk.nbytes)
+            d2h += int(2 * h_rf.nbytes)
+        else:
+            re_me, e2e_value = None, re_txq
+        e2e = {"value": e2e_value, "unit": "1080p frame-equiv/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "txq_fe_per_s": re_txq, "me_frames_per_s": re_me,
+               "d2h_dense_bytes_per_step": int(out_off * 12 + eblocks.size * 2),
+               "note": "per step: 1 frame through b200_txq_batch_host_compact (pinned host buffers; descriptor "
+                       "bucketing + H2D + %d launches + on-device packing + D2H of eob, offsets and the levels in "
+                       "scan order up to eob) and b200_me_batch_host (cur + 2 reference planes + descriptors H2D, "
+                       "full-pel + chained sub-pel launch, 2 x 40 B per search D2H), all inside the timed region"
+                       % len(sizes)}
 
     extras = None
-    if not args.no_extras and world == 1:
-        extras = {"hadamard": bench_hadamard(ctx, dev, stream, max(2, args.steps // 2), 2, d_src, args.frames),
-                  "hbd4k": bench_hbd4k(ctx, dev, stream, max(2, args.steps // 2), 2, seed)}
+    if not args.no_extras:
+        extras = {}
+        if world == 1:
+            extras["hadamard"] = bench_hadamard(ctx, dev, stream, max(2, args.steps // 2), 2, d_src, args.frames)
+            extras["hbd4k"] = bench_hbd4k(ctx, dev, stream, max(2, args.steps // 2), 2, seed)
+        # BASELINE configs[4] at every N: 120 frames over the ranks
+        del d_coeff, d_qc, d_dq
+        torch.cuda.empty_cache()
+        c5 = bench_config5(ctx, dev, stream, rank, world, seed, args.config5_frames, 4, 2)
+        t5_txq, t5_me = allmax(c5["t_txq_ms"]), allmax(c5["t_me_ms"])
+        te5 = allmax(c5["e2e_s"] / max(c5["e2e_frames"], 1))
+        fe4k = 3840 * 2160 * 3 // 2
+        r5_txq = c5["txq_samples_per_frame"] / fe4k * args.config5_frames / (t5_txq / 1e3)
+        r5_me = args.config5_frames / (t5_me / 1e3)
+        extras["config5"] = {
+            "workload": "configs[4]: %d synthetic 4K 10-bit 4:2:0 frames, frame i -> GPU i mod %d (strong scaling); "
+                        "fused subtract + txfm + av1_highbd_quantize_fp + av1_highbd_block_error over all 19 TX sizes "
+                        "from uint16 planes + high-bit-depth motion search (1980 64x64 SBs x 2 refs, +-64, NSTEP + "
+                        "mesh + 8-tap sub-pel) per frame" % (args.config5_frames, world),
+            "frames_total": args.config5_frames, "txq_fe4k_per_s": r5_txq, "me_frames4k_per_s": r5_me,
+            "fe4k_per_s": combined(r5_txq, r5_me),
+            "txq_GBps_per_gpu": c5["txq_bytes_per_frame"] * c5["frames_rank"] / (c5["t_txq_ms"] / 1e3) / 1e9,
+            "ms_txq_max_rank": t5_txq, "ms_me_max_rank": t5_me,
+            "e2e_fe4k_per_s": world / te5 if te5 > 0 else None,
+            "e2e_sample": "%d frames per rank through b200_txq_batch_host_compact + b200_me_batch_host" % c5["e2e_frames"],
+            "e2e_h2d_bytes_per_frame": c5["e2e_h2d"] // max(c5["e2e_frames"], 1),
+            "e2e_d2h_bytes_per_frame": c5["e2e_d2h"] // max(c5["e2e_frames"], 1)}
 
     if rank != 0:
         if world > 1:
@@ -695,44 +1043,75 @@ def main():
                         "frac": round(ps["bytes"] / (ms / 1e3) / 1e9 / peak, 3)})
     traffic = None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tp):
+    if os.path.exists(tp) and len(sizes) == 19:
         try:
             tj = json.load(open(tp))
-            # ncu capture was taken at tj["frames_per_launch"] frames; DRAM bytes scale with frames
-            traffic = tj["txq_kernel_dram_bytes_per_step_at_8_frames"] * args.frames / tj["frames_per_launch"]
+            # ncu capture (one --set full pass per kernel) at tj["frames_per_launch"] frames per launch;
+            # DRAM bytes scale with the frames
+            traffic = tj["txq_kernel_dram_bytes_per_step"] * args.frames / tj["frames_per_launch"]
+            assert traffic >= 0.95 * total_bytes, "DRAM traffic below the algorithmic bytes"
         except (OSError, ValueError, KeyError):
             traffic = None
+    roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": achieved / peak, "traffic": traffic,
+            "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+            "kernel": "txq_kernel<W,H> (19 instances, one launch each per step); "
+                      "algorithmic bytes = 2 B/sample in + 12 B/kept coeff out + 2 B/block",
+            "bytes_per_step": int(total_bytes),
+            "share_of_step": float(t_txq / (t_txq + t_full + t_sub))}
+    me = None
+    if work is not None:
+        sad_peak = C.c_double(0)
+        b200av1.check(lib.b200_measure_sad_peak(ctx.h, C.byref(sad_peak)))
+        full_s = t_full / args.steps / 1e3
+        unique = work.n * (4096 + 192 * 192 + 64)
+        me = {"fullpel_ms_per_frame": t_full / args.steps / args.frames,
+              "subpel_ms_per_frame": t_sub / args.steps / args.frames,
+              "frames_per_s_per_gpu": args.frames * args.steps / ((t_full + t_sub) / 1e3),
+              "searches_per_frame": work.per_frame, "launches_per_step": 2, "frames_per_launch": args.frames}
+        roof["me"] = {"bound": "int_alu", "kernel": "fullpel_kernel<0> (n-step + mesh), %.0f %% of the step"
+                                                    % (100 * t_full / (t_txq + t_full + t_sub)),
+                      "achieved": sad_pixels_per_step / full_s / 1e9, "peak": sad_peak.value,
+                      "unit": "G pixel-absdiff/s", "frac": sad_pixels_per_step / full_s / 1e9 / sad_peak.value,
+                      "peak_source": "b200_measure_sad_peak: VABSDIFF4.ACC issued back to back on every SM, this run",
+                      "sad_pixels_per_step": sad_pixels_per_step,
+                      "unique_bytes_per_step": unique, "unique_GBps": unique / full_s / 1e9,
+                      "hbm_frac": unique / full_s / 1e9 / peak}
     line = {"metric": metric, "value": value, "unit": "1080p frame-equiv/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms_max / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
             "data": "synthetic", "config": config, "clocks": clocks,
-            "gpu_launches": len(launches) * args.steps,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic,
-                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
-                         "kernel": "txq_kernel<W,H> (19 instances, one launch each per step); "
-                                   "algorithmic bytes = 2 B/sample in + 12 B/kept coeff out + 2 B/block",
-                         "bytes_per_step": int(total_bytes)},
-            "kernels": kernels, "e2e": e2e, "me": me, "extras": extras,
+            "gpu_launches": (n_txq + (2 if work is not None else 0)) * args.steps,
+            "txq_fe_per_s": r_txq, "me_frames_per_s": r_me,
+            "roofline": roof, "kernels": kernels, "e2e": e2e, "me": me, "extras": extras,
             "step_ms_min_max": [float(min(step_ms)), float(max(step_ms))]}
 
     # ---- cpu_baseline (rank 0, N = 1 only) + full-size parity of frame 0
     if world == 1 and not args.no_cpu:
         H, O, R = load_cpu_libs()
         n_threads = os.cpu_count() or 1
-        t, s, outs = cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed + rank, n_threads,
-                                   sizes, keep_outputs=True)  # warm-up pass; its outputs feed the parity check
-        reps, t, s = 8, 0.0, 0
+        t, s_, outs = cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed + rank, n_threads,
+                                    sizes, keep_outputs=True)  # warm-up pass; its outputs feed the parity check
+        reps, t, s_ = 4, 0.0, 0
         for _ in range(reps):  # a bounded sample, long enough to average the thread start-up noise out
             ti, si, _o = cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed + rank, n_threads, sizes)
             t += ti
-            s += si
-        line["cpu_baseline"] = {"value": s / FE_SAMPLES / t, "unit": "1080p frame-equiv/s",
-                                "cores": n_threads, "kind": "reference" if R is not None else "port",
-                                "sample": "%d x (1 frame x %d TX sizes) = %.1f FE after one warm-up pass, "
-                                          "av1_fwd_txfm2d_*_c + av1_quantize_fp*_c on %d host threads"
-                                          % (reps, len(sizes), s / FE_SAMPLES, n_threads)}
-        # parity at full size: GPU (host-buffer call, frame 0) vs CPU outputs, bit-exact
+            s_ += si
+        c_txq = s_ / FE_SAMPLES / t
+        kind = "reference" if R is not None else "port"
+        cb = {"unit": "1080p frame-equiv/s", "cores": n_threads, "kind": kind, "txq_fe_per_s": c_txq}
+        sample = "%d x (1 frame x %d TX sizes) = %.1f FE after one warm-up pass, av1_fwd_txfm2d_*_c + " \
+                 "av1_quantize_fp*_c" % (reps, len(sizes), s_ / FE_SAMPLES)
+        if work is not None:
+            tm, rf, rs = cpu_run_me(H, O, R, work, 0, n_threads)
+            cb["me_frames_per_s"] = 1.0 / tm
+            cb["value"] = combined(c_txq, 1.0 / tm)
+            sample += "; 1 frame = %d searches through av1_full_pixel_search + av1_find_best_sub_pixel_tree" % work.per_frame
+        else:
+            cb["value"] = c_txq
+        cb["sample"] = sample + " (generic C build of the reference) on %d host threads" % n_threads
+        line["cpu_baseline"] = cb
+        # parity at full size: GPU (host-buffer calls, frame 0) vs CPU outputs, bit-exact
         ok = True
         for ts in sizes:
             blocks, coeff, qc, dq, eob = outs[ts]
@@ -742,6 +1121,10 @@ def main():
                                None)
             ok = ok and all(np.array_equal(a, b) for a, b in zip(g, (coeff, qc, dq, eob)))
         line["parity_full_frame"] = "bit-exact" if ok else "MISMATCH"
+        if work is not None and args.e2e_steps > 0:
+            bad = me_mismatches(H, h_rf, h_rs, rf, rs, work.per_frame)
+            line["parity_me_full_frame"] = "bit-exact (%d searches, full-pel + sub-pel)" % work.per_frame \
+                if bad == 0 else "MISMATCH in %d results" % bad
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

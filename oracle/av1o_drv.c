@@ -148,3 +148,48 @@ int av1o_drv_txq_fp(void *fwd, void *quant, int highbd, int bd, int tx_size,
   free(th);
   return 0;
 }
+
+/* ---- motion search: full-pel search, then the sub-pel tree started at its result, for a
+ * list of searches on a pthread pool.  `full` / `sub` are either the reference's own
+ * av1_full_pixel_search / av1_find_best_sub_pixel_tree behind oracle/ref_shim.c
+ * (refshim_full_pixel_search / refshim_find_best_sub_pixel_tree) or this oracle's
+ * restatement (av1o_full_pixel_search / av1o_find_best_sub_pixel_tree): same signature. */
+#include "av1o_me.h"
+typedef void (*me_fn)(const Av1oMeParams *p, Av1oMeResult *r);
+typedef struct {
+  me_fn full, sub;
+  Av1oMeParams *params;
+  Av1oMeResult *rfull, *rsub;
+  int n, tid, n_threads;
+  volatile int *next;
+} MeJob;
+
+static void *me_worker(void *arg) {
+  MeJob *j = (MeJob *)arg;
+  for (;;) {
+    const int i = __sync_fetch_and_add(j->next, 1); /* searches differ a lot in cost: dynamic split */
+    if (i >= j->n) break;
+    Av1oMeParams p = j->params[i];
+    j->full(&p, &j->rfull[i]);
+    if (j->sub) {
+      p.sp_start_row = j->rfull[i].best_row * 8;
+      p.sp_start_col = j->rfull[i].best_col * 8;
+      j->sub(&p, &j->rsub[i]);
+    }
+  }
+  return NULL;
+}
+
+void av1o_drv_me(void *full, void *sub, Av1oMeParams *params, int n, Av1oMeResult *rfull,
+                 Av1oMeResult *rsub, int n_threads) {
+  if (n_threads < 1) n_threads = 1;
+  if (n_threads > 256) n_threads = 256;
+  pthread_t th[256];
+  MeJob jobs[256];
+  volatile int next = 0;
+  for (int t = 0; t < n_threads; ++t) {
+    jobs[t] = (MeJob){ (me_fn)full, (me_fn)sub, params, rfull, rsub, n, t, n_threads, &next };
+    pthread_create(&th[t], NULL, me_worker, &jobs[t]);
+  }
+  for (int t = 0; t < n_threads; ++t) pthread_join(th[t], NULL);
+}
