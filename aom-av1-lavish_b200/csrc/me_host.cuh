@@ -69,7 +69,7 @@ int me_init_device(b200_ctx *ctx) {
   B200_CUDA_TRY(cudaFuncSetAttribute(me::fullpel_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      200 * 1024));
   B200_CUDA_TRY(cudaFuncSetAttribute(me::subpel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     100 * 1024));
+                                     200 * 1024));
   return B200_OK;
 }
 
@@ -182,7 +182,14 @@ extern "C" int b200_me_subpel_launch(b200_ctx *ctx, const B200MeLaunch *l, void 
   cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
   // source block + horizontally filtered rows (bh + 7) * bw * 2 bytes
   const int mbw = l->max_bw > 0 ? l->max_bw : 128, mbh = l->max_bh > 0 ? l->max_bh : 128;
-  const size_t smem = (size_t)mbw * mbh * (l->highbd ? 2 : 1) + 16 + (size_t)(mbh + 7) * mbw * 2;
+  size_t smem = (size_t)mbw * mbh * (l->highbd ? 2 : 1) + 16 + (size_t)(mbh + 7) * mbw * 2;
+  if (!l->highbd) {
+    // 8-bit fast path (me_subpel.cuh): reference window + transposed source + 4 transposed
+    // intermediates, laid out after the generic regions
+    smem = (smem + 15) & ~(size_t)15;
+    smem += (size_t)(mbh + 9) * ((((mbw + 9 + 3 + 3) & ~3) + 4)) + (size_t)mbw * b200::me::odd_word_pitch(mbh) +
+            4 * (size_t)mbw * b200::me::odd_word_pitch(mbh + 8) + 64;
+  }
   b200::me::subpel_kernel<<<l->n_blocks, b200::me::kThreads, smem, s>>>(*l);
   B200_CUDA_TRY(cudaGetLastError());
   return B200_OK;

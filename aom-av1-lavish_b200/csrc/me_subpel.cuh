@@ -125,6 +125,178 @@ __device__ unsigned cta_pref_error(const SubCtx &s, Mv mv, int mode, unsigned *s
   return finish_var(tsum, tsse, n, k.l->highbd != 0, k.l->bd, sse_out);
 }
 
+// ---- 8-bit fast path of upsampled_pref_error (mode 2) -----------------------------------
+// The scalar path above spends ~60 instructions per predicted pixel (byte loads of the
+// reference through L1, 16 multiply-adds, one candidate at a time with three CTA barriers
+// each).  Here the reachable reference window ((bw + 9) x (bh + 9): the tree never leaves
+// +-7/8 pel around its start) and the TRANSPOSED source block are staged in shared memory once
+// per search, and up to four candidates are evaluated per pass:
+//   stage 1  horizontal 8-tap filter, 4 vertically adjacent outputs per thread: the 8 bytes
+//            under the taps come from 3 aligned words + 2 PRMT (per-lane selector), the taps are
+//            two packed s8x4 words, 2 DP4A per output; the clipped u8 results are packed into
+//            one word of the TRANSPOSED intermediate tmpT[x][y] (odd word pitch: conflict-free)
+//   stage 2  vertical filter along tmpT rows: 3 words + 6 PRMT + 8 DP4A for 4 outputs, then
+//            VABSDIFF4 against the transposed source word, sse += DP4A(d, d), sum += DP4A(p, 1)
+// about 20 instructions per pixel.  sum(src) is formed once per search.  Integer-pel
+// components skip their filter stage exactly like aom_upsampled_pred_c (reconinter_enc.c:452).
+struct SubFast {
+  bool on;
+  int win_off, win_pitch;  // byte offset in me_smem of window pixel (r_lo, c_lo); row pitch in bytes
+  int r_lo, c_lo;          // full-pel position (relative to the block) of the window's first pixel
+  int srcT_off, sp;        // transposed source block: srcT[x * sp + y]
+  int tmpT_off, pt, tmpT_size;
+  int sum_src;
+};
+__shared__ unsigned g_sacc[4][2];  // per candidate of a pass: sum of the prediction, sse
+
+__device__ __forceinline__ int dp4a_us(unsigned a, unsigned b, int c) {
+  int d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ unsigned clip8(int v) { return (unsigned)min(max(v, 0), 255); }
+__device__ __forceinline__ unsigned pack_taps(const short *k) {
+  return (unsigned)(k[0] & 0xff) | ((unsigned)(k[1] & 0xff) << 8) | ((unsigned)(k[2] & 0xff) << 16) |
+         ((unsigned)(k[3] & 0xff) << 24);
+}
+__host__ __device__ __forceinline__ int odd_word_pitch(int bytes) {
+  const int w = (bytes + 3) >> 2;
+  return ((w & 1) ? w : w + 1) * 4;
+}
+
+// Stages window + transposed source.  `fast_off`: first free byte of me_smem; mbw / mbh: the
+// launch's largest block (sizes the regions exactly like the host).
+__device__ void subfast_init(const SubCtx &s, SubFast &f, int fast_off, int mbw, int mbh) {
+  const Ctx &k = s.k;
+  const B200MeLaunch &l = *k.l;
+  const int bw = k.d.bw, bh = k.d.bh;
+  f.on = false;
+  const long long stride_b = l.ref_stride;
+  if (k.px != 1 || (stride_b & 3) || bw > mbw || bh > mbh) return;
+  f.r_lo = ((s.start.row - 7) >> 3) - 3;
+  f.c_lo = ((s.start.col - 7) >> 3) - 3;
+  const int wh = bh + 9, ww = bw + 9;
+  const unsigned char *g0 = k.ref0 + (long long)f.r_lo * stride_b + f.c_lo;
+  const int lead = (int)(reinterpret_cast<unsigned long long>(g0) & 3);
+  f.win_pitch = ((mbw + 9 + 3 + 3) & ~3) + 4;
+  const int win_bytes = (mbh + 9) * f.win_pitch;
+  f.sp = odd_word_pitch(mbh);
+  f.pt = odd_word_pitch(mbh + 8);
+  f.tmpT_size = mbw * f.pt;
+  f.srcT_off = fast_off + win_bytes;
+  f.tmpT_off = f.srcT_off + mbw * f.sp;
+  unsigned *s_win = reinterpret_cast<unsigned *>(me_smem + fast_off);
+  const unsigned *ga = reinterpret_cast<const unsigned *>(g0 - lead);
+  const int cw = (lead + ww + 3) >> 2, pw = f.win_pitch >> 2;
+  for (int i = threadIdx.x; i < wh * cw; i += kThreads) {
+    const int y = i / cw, x = i - y * cw;
+    s_win[y * pw + x] = ga[(long long)y * (stride_b >> 2) + x];
+  }
+  f.win_off = fast_off + lead;
+  // transposed source + its sum
+  unsigned part = 0;
+  for (int i = threadIdx.x; i < bw * bh; i += kThreads) {
+    const int y = i / bw, x = i - y * bw;
+    const unsigned v = k.src[i];
+    me_smem[f.srcT_off + x * f.sp + y] = (unsigned char)v;
+    part += v;
+  }
+  part = warp_sum_u(part);
+  if (threadIdx.x == 0) g_bcast[2] = 0;
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) atomicAdd(reinterpret_cast<unsigned *>(&g_bcast[2]), part);
+  __syncthreads();
+  f.sum_src = g_bcast[2];
+  f.on = true;
+}
+
+// variance of (pred(mv[c]) - src) for the m <= 4 candidates with valid[c]: var_out / sse_out
+__device__ void subfast_eval(const SubCtx &s, const SubFast &f, const Mv *mv, const bool *valid, int m,
+                             unsigned *var_out, unsigned *sse_out) {
+  const Ctx &k = s.k;
+  const int bw = k.d.bw, bh = k.d.bh, lbw = 31 - __clz(bw);
+  const int set = s.search_type == B200_USE_2_TAPS ? 0 : (s.search_type == B200_USE_4_TAPS ? 1 : 2);
+  __syncthreads();  // previous readers of tmpT / g_sacc
+  if (threadIdx.x < 8) (&g_sacc[0][0])[threadIdx.x] = 0;
+  // ---- stage 1: horizontal
+  for (int c = 0; c < m; ++c) {
+    if (!valid[c]) continue;
+    const int fr = mv[c].row >> 3, fc = mv[c].col >> 3, sx = mv[c].col & 7, sy = mv[c].row & 7;
+    const int top = sy ? 3 : 0, ih = sy ? bh + 7 : bh, ngy = (ih + 3) >> 2;
+    const int row0 = fr - f.r_lo - top;
+    unsigned char *tmpT = me_smem + f.tmpT_off + c * f.tmpT_size;
+    if (sx) {
+      const unsigned klo = pack_taps(c_me_taps[set][sx]), khi = pack_taps(c_me_taps[set][sx] + 4);
+      const int col0 = fc - f.c_lo - 3;
+      for (int g = threadIdx.x; g < (ngy << lbw); g += kThreads) {
+        const int x = g & (bw - 1), yg = g >> lbw;
+        const int b0 = f.win_off + (row0 + 4 * yg) * f.win_pitch + col0 + x;
+        const unsigned sel = 0x3210u + 0x1111u * (unsigned)(b0 & 3);
+        const unsigned *w = reinterpret_cast<const unsigned *>(me_smem + (b0 & ~3));
+        const int pw = f.win_pitch >> 2;
+        unsigned out = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const unsigned w0 = w[j * pw], w1 = w[j * pw + 1], w2 = w[j * pw + 2];
+          const int a = dp4a_us(__byte_perm(w1, w2, sel), khi, dp4a_us(__byte_perm(w0, w1, sel), klo, 64));
+          out |= clip8(a >> 7) << (8 * j);
+        }
+        *reinterpret_cast<unsigned *>(tmpT + x * f.pt + 4 * yg) = out;
+      }
+    } else {
+      const int col0 = fc - f.c_lo;
+      for (int g = threadIdx.x; g < (ngy << lbw); g += kThreads) {
+        const int x = g & (bw - 1), yg = g >> lbw;
+        const unsigned char *p = me_smem + f.win_off + (row0 + 4 * yg) * f.win_pitch + col0 + x;
+        const unsigned out = (unsigned)p[0] | ((unsigned)p[f.win_pitch] << 8) |
+                             ((unsigned)p[2 * f.win_pitch] << 16) | ((unsigned)p[3 * f.win_pitch] << 24);
+        *reinterpret_cast<unsigned *>(tmpT + x * f.pt + 4 * yg) = out;
+      }
+    }
+  }
+  __syncthreads();
+  // ---- stage 2: vertical + variance sums
+  for (int c = 0; c < m; ++c) {
+    if (!valid[c]) continue;
+    const int sy = mv[c].row & 7;
+    const unsigned char *tmpT = me_smem + f.tmpT_off + c * f.tmpT_size;
+    const unsigned klo = pack_taps(c_me_taps[set][sy]), khi = pack_taps(c_me_taps[set][sy] + 4);
+    unsigned sum = 0, sse = 0;
+    for (int g = threadIdx.x; g < ((bh >> 2) << lbw); g += kThreads) {
+      const int x = g & (bw - 1), yg = g >> lbw;
+      const unsigned *v = reinterpret_cast<const unsigned *>(tmpT + x * f.pt + 4 * yg);
+      unsigned p;
+      if (sy) {
+        const unsigned v0 = v[0], v1 = v[1], v2 = v[2];
+        const int a0 = dp4a_us(v1, khi, dp4a_us(v0, klo, 64));
+        const int a1 = dp4a_us(__byte_perm(v1, v2, 0x4321), khi, dp4a_us(__byte_perm(v0, v1, 0x4321), klo, 64));
+        const int a2 = dp4a_us(__byte_perm(v1, v2, 0x5432), khi, dp4a_us(__byte_perm(v0, v1, 0x5432), klo, 64));
+        const int a3 = dp4a_us(__byte_perm(v1, v2, 0x6543), khi, dp4a_us(__byte_perm(v0, v1, 0x6543), klo, 64));
+        p = clip8(a0 >> 7) | (clip8(a1 >> 7) << 8) | (clip8(a2 >> 7) << 16) | (clip8(a3 >> 7) << 24);
+      } else {
+        p = v[0];
+      }
+      const unsigned sv = *reinterpret_cast<const unsigned *>(me_smem + f.srcT_off + x * f.sp + 4 * yg);
+      const unsigned d = __vabsdiffu4(p, sv);
+      sse = __dp4a(d, d, sse);
+      sum = __dp4a(p, 0x01010101u, sum);
+    }
+    sum = warp_sum_u(sum);
+    sse = warp_sum_u(sse);
+    if ((threadIdx.x & 31) == 0) {
+      atomicAdd(&g_sacc[c][0], sum);
+      atomicAdd(&g_sacc[c][1], sse);
+    }
+  }
+  __syncthreads();
+  for (int c = 0; c < m; ++c) {
+    if (!valid[c]) continue;
+    unsigned sse32;
+    var_out[c] = finish_var((long long)(int)g_sacc[c][0] - f.sum_src, g_sacc[c][1], bw * bh, false, 8, &sse32);
+    sse_out[c] = sse32;
+  }
+}
+
 struct SubState {
   Mv best;
   unsigned besterr, sse;
@@ -149,7 +321,43 @@ __device__ unsigned check_better(const SubCtx &s, SubState &st, Mv mv, int mode,
   return cost;
 }
 
-__device__ void subpel_search(const SubCtx &s, SubState &st) {
+// check_better on up to 4 probes at once: the probes inside the limits are evaluated together
+// (fast path) and then folded into the state in order, exactly as consecutive check_better calls
+// would (the probe positions of a level do not depend on each other's outcome).
+__device__ void check_better_n(const SubCtx &s, const SubFast &f, SubState &st, const Mv *mv, int m, int mode,
+                               unsigned *cost, int *better) {
+  const Ctx &k = s.k;
+  if (!(f.on && mode == 2)) {
+    for (int c = 0; c < m; ++c) cost[c] = check_better(s, st, mv[c], mode, better);
+    return;
+  }
+  bool valid[4];
+  unsigned var[4], sse[4];
+  bool any = false;
+  for (int c = 0; c < m; ++c) {
+    valid[c] = !(mv[c].col < k.d.col_min || mv[c].col > k.d.col_max || mv[c].row < k.d.row_min ||
+                 mv[c].row > k.d.row_max);
+    any = any || valid[c];
+  }
+  if (any) subfast_eval(s, f, mv, valid, m, var, sse);
+  for (int c = 0; c < m; ++c) {
+    if (!valid[c]) {
+      cost[c] = (unsigned)INT_MAX;
+      continue;
+    }
+    const int mse = (int)var[c];
+    cost[c] = (unsigned)err_cost(k, mv[c].row, mv[c].col) + (unsigned)mse;
+    if (cost[c] < st.besterr) {
+      st.besterr = cost[c];
+      st.best = mv[c];
+      st.distortion = mse;
+      st.sse = sse[c];
+      if (better) *better |= 1;
+    }
+  }
+}
+
+__device__ void subpel_search(const SubCtx &s, const SubFast &f, SubState &st) {
   const Ctx &k = s.k;
   const int forced_stop = k.d.subpel & 3, iters_per_step = (k.d.subpel >> 2) & 3;
   const int allow_hp = (k.d.flags & B200_ME_ALLOW_HP) != 0;
@@ -157,34 +365,36 @@ __device__ void subpel_search(const SubCtx &s, SubState &st) {
   const int round = min(B200_FULL_PEL - forced_stop, 3 - !allow_hp);
   int hstep = 4;  // INIT_SUBPEL_STEP_SIZE
   st.best = s.start;
-  unsigned sse;
-  const unsigned e = cta_pref_error(s, st.best, mode == 2 ? 2 : 0, &sse);
+  unsigned sse, e;
+  if (f.on && mode == 2) {
+    const bool one = true;
+    subfast_eval(s, f, &st.best, &one, 1, &e, &sse);
+  } else {
+    e = cta_pref_error(s, st.best, mode == 2 ? 2 : 0, &sse);
+  }
   st.distortion = (int)e;
   st.sse = sse;
   st.besterr = e + (unsigned)err_cost(k, st.best.row, st.best.col);
   for (int iter = 0; iter < round; ++iter) {
     const Mv c = st.best;
     // first_level_check(_fast): four cardinals, then the diagonal of the better halves
-    const Mv l = { c.row, c.col - hstep }, r = { c.row, c.col + hstep };
-    const Mv t = { c.row - hstep, c.col }, b = { c.row + hstep, c.col };
-    const unsigned left = check_better(s, st, l, mode, nullptr);
-    const unsigned right = check_better(s, st, r, mode, nullptr);
-    const unsigned up = check_better(s, st, t, mode, nullptr);
-    const unsigned down = check_better(s, st, b, mode, nullptr);
+    const Mv card[4] = { { c.row, c.col - hstep }, { c.row, c.col + hstep }, { c.row - hstep, c.col },
+                         { c.row + hstep, c.col } };
+    unsigned cost[4];
+    check_better_n(s, f, st, card, 4, mode, cost, nullptr);
+    const unsigned left = cost[0], right = cost[1], up = cost[2], down = cost[3];
     Mv diag = { up <= down ? -hstep : hstep, left <= right ? -hstep : hstep };
     const Mv dm = { c.row + diag.row, c.col + diag.col };
-    check_better(s, st, dm, mode, nullptr);
+    check_better_n(s, f, st, &dm, 1, mode, cost, nullptr);
     // second_level_check_v2
     if (!(c.row == st.best.row && c.col == st.best.col) && iters_per_step > 1) {
       if (c.row == st.best.row) diag.row = -diag.row;
       else if (c.col == st.best.col) diag.col = -diag.col;
-      const Mv rb = { st.best.row + diag.row, st.best.col };
-      const Mv cb = { st.best.row, st.best.col + diag.col };
+      const Mv two[2] = { { st.best.row + diag.row, st.best.col }, { st.best.row, st.best.col + diag.col } };
       const Mv db = { st.best.row + diag.row, st.best.col + diag.col };
       int better = 0;
-      check_better(s, st, rb, mode, &better);
-      check_better(s, st, cb, mode, &better);
-      if (better) check_better(s, st, db, mode, &better);
+      check_better_n(s, f, st, two, 2, mode, cost, &better);
+      if (better) check_better_n(s, f, st, &db, 1, mode, cost, &better);
     }
     hstep >>= 1;
   }
@@ -315,7 +525,12 @@ __global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) 
   SubState st;
   const int tree = s.k.d.search_method;
   if (tree == B200_SUBPEL_TREE) {
-    subpel_search(s, st);
+    SubFast f;
+    f.on = false;
+    const int mbw = l.max_bw > 0 ? l.max_bw : 128, mbh = l.max_bh > 0 ? l.max_bh : 128;
+    if (s.search_type != B200_USE_2_TAPS_ORIG && !l.highbd && s.k.d.bw >= 4)
+      subfast_init(s, f, (mbw * mbh + 16 + (mbh + 7) * mbw * 2 + 15) & ~15, mbw, mbh);
+    subpel_search(s, f, st);
   } else {
     int cl[5];
     const bool have = (s.k.d.flags & B200_ME_COST_LIST) && l.cost_lists;
