@@ -40,18 +40,24 @@ TXBLOCK_DTYPE = np.dtype([("src_offset", "<u4"), ("out_offset", "<u4"), ("src_st
                           ("reserved", "<u2")])
 
 
+# tx-type sets of INTER blocks, the ones an encoder batches: av1_get_ext_tx_set_type
+# (av1/common/blockd.h:1097-1107, is_inter = 1, reduced_tx_set = 0) + av1_ext_tx_used (:1036-1043).
+# They are also the only types the reference's SIMD transforms implement for each size.
+_SET_DCTONLY = (0,)
+_SET_DCT_IDTX = (0, 9)
+_SET_DTT9_IDTX_1DDCT = tuple(range(12))
+_SET_ALL16 = tuple(range(16))
+
+
 def valid_types(ts):
-    out = []
-    for tt in range(16):
-        ok = True
-        for dim, kind in ((TX_H[ts], VTX[tt]), (TX_W[ts], HTX[tt])):
-            if dim == 64 and kind != 0:
-                ok = False
-            if dim == 32 and kind in (1, 2):
-                ok = False
-        if ok:
-            out.append(tt)
-    return out
+    up = max(TX_W[ts], TX_H[ts])
+    if up > 32:
+        return list(_SET_DCTONLY)
+    if up == 32:
+        return list(_SET_DCT_IDTX)
+    if min(TX_W[ts], TX_H[ts]) == 16:
+        return list(_SET_DTT9_IDTX_1DDCT)
+    return list(_SET_ALL16)
 
 
 def max_eob(ts):
@@ -183,32 +189,88 @@ class ClockSampler:
 def load_cpu_libs():
     import harness as H
     O = H.oracle()
-    R = H.ref()
+    R = H.ref_avx2() or H.ref()
     return H, O, R
+
+
+def run_configs0():
+    """BASELINE configs[0]: the reference's own encoder, `aomenc --cpu-used=6 --good`, one thread, on the
+    synthetic 352x288 8-bit 4:2:0 10-frame clip of baseline/gen_y4m.py (oracle/_ref/aomenc*, built by
+    oracle/mk_ref.py).  Context for the CPU baseline; not part of the metric."""
+    import subprocess
+    import tempfile
+    here = os.path.dirname(os.path.abspath(__file__))
+    sys.path.insert(0, os.path.join(here, "baseline"))
+    out = {}
+    try:
+        import gen_y4m
+        with tempfile.TemporaryDirectory() as td:
+            clip = os.path.join(td, "cif.y4m")
+            gen_y4m.write_y4m(clip)
+            for name in ("aomenc", "aomenc_avx2"):
+                exe = os.path.join(here, "oracle", "_ref", name)
+                if not os.path.exists(exe) or (name == "aomenc_avx2" and " avx2 " not in open("/proc/cpuinfo").read().replace("\n", " ")):
+                    continue
+                t0 = time.perf_counter()
+                r = subprocess.run([exe, "--cpu-used=6", "--good", "--threads=1", "--limit=10", "-q", "-o",
+                                    os.path.join(td, name + ".ivf"), clip], capture_output=True, timeout=300)
+                dt = time.perf_counter() - t0
+                if r.returncode == 0:
+                    out[name] = {"seconds": round(dt, 3), "fps": round(10 / dt, 2),
+                                 "bytes": os.path.getsize(os.path.join(td, name + ".ivf"))}
+    except Exception as e:  # reported, never fatal to the bench line
+        out["error"] = repr(e)[:200]
+    if out:
+        out["cmd"] = "aomenc --cpu-used=6 --good --threads=1 --limit=10, 352x288 8-bit 4:2:0 synthetic y4m, 10 frames, 2 passes"
+    return out
+
+
+def cpu_kind(R):
+    """cpu_baseline.kind: the reference built with its x86 intrinsics (AVX2 dispatch; assembler-only
+    kernels in C, see oracle/mk_ref.py), its generic C build, or the oracle port."""
+    if R is None:
+        return "port"
+    return "reference-avx2" if R.refshim_simd() else "reference"
+
+
+def cpu_desc(R):
+    return {"port": "oracle restatement", "reference": "generic C build of the reference",
+            "reference-avx2": "reference built with its SSE2..AVX2 intrinsics, run-time dispatch; the kernels "
+                              "that exist only as assembler run as C"}[cpu_kind(R)]
+
+
+def aligned_zeros(n, dtype, align=64):
+    """The reference's SIMD flavours use aligned loads/stores on the encoder's 32-byte aligned buffers."""
+    item = np.dtype(dtype).itemsize
+    raw = np.zeros(n * item + align, np.uint8)
+    off = (-raw.ctypes.data) % align
+    return raw[off:off + n * item].view(dtype)
 
 
 def cpu_run_sweep(H, O, R, frames, planes, frame_elems, seed, n_threads, sizes=range(19),
                   keep_outputs=False):
     """One frame per size through the CPU path.  Returns (seconds, samples, outputs)."""
-    rows = (H.QRow * (3 * len(QINDEXES)))()
+    rows_mem = aligned_zeros(C.sizeof(H.QRow) * 3 * len(QINDEXES), np.uint8)  # SIMD quantisers load rows aligned
+    rows = (H.QRow * (3 * len(QINDEXES))).from_buffer(rows_mem)
     for pl in range(3):
         for qi, q in enumerate(QINDEXES):
             O.av1o_build_qrow(8, q, pl, 0, C.byref(rows[pl * len(QINDEXES) + qi]))
     total_t, total_samples, outs = 0.0, 0, {}
-    src = np.ascontiguousarray(frames[:1].reshape(-1))
+    src = aligned_zeros(frames[:1].size, frames.dtype)
+    src[:] = frames[:1].reshape(-1)
     for ts in sizes:
         blocks, samples = make_descriptors(ts, 1, planes, frame_elems, seed)
         n = blocks.size
         ne = n * max_eob(ts)
-        coeff = np.zeros(ne, np.int32)
-        qc = np.zeros(ne, np.int32)
-        dq = np.zeros(ne, np.int32)
+        coeff = aligned_zeros(ne, np.int32)
+        qc = aligned_zeros(ne, np.int32)
+        dq = aligned_zeros(ne, np.int32)
         eob = np.zeros(n, np.uint16)
         if R is not None:
-            fwd = C.cast(getattr(R, "av1_fwd_txfm2d_%dx%d_c" % (TX_W[ts], TX_H[ts])), C.c_void_p)
-            ls = H.log_scale(ts)
-            qn = ["av1_quantize_fp_c", "av1_quantize_fp_32x32_c", "av1_quantize_fp_64x64_c"][ls]
-            quant = C.cast(getattr(R, qn), C.c_void_p)
+            # av1_lowbd_fwd_txfm (hybrid_fwd_txfm.c:236) and av1_quantize_fp* as the encoder's own
+            # dispatch binds them: the _c flavours in the generic build, SSE4.1/AVX2 in the avx2 one
+            fwd = C.c_void_p(R.refshim_fwd_txfm_fn(ts, 0))
+            quant = C.c_void_p(R.refshim_quantize_fp_fn(H.log_scale(ts), 0))
         else:
             fwd, quant = None, None
         t0 = time.perf_counter()
@@ -769,7 +831,7 @@ def main():
             tm += cpu_run_me(H, O, R, work, 0, n_threads)[0]
         r_txq, r_me = ss / FE_SAMPLES / tt, args.steps / tm
         val = combined(r_txq, r_me)
-        kind = "reference" if R is not None else "port"
+        kind = cpu_kind(R)
         line = {"impl": "reference", "metric": metric, "value": val, "unit": "1080p frame-equiv/s",
                 "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": (tt + tm) / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
@@ -777,10 +839,10 @@ def main():
                 "txq_fe_per_s": r_txq, "me_frames_per_s": r_me,
                 "cpu_baseline": {"value": val, "unit": "1080p frame-equiv/s", "cores": n_threads,
                                  "kind": kind,
-                                 "sample": "per step: 1 frame x %d TX sizes (%.1f FE) through av1_fwd_txfm2d_*_c + "
-                                           "av1_quantize_fp*_c, and the frame's 960 searches through "
-                                           "av1_full_pixel_search + av1_find_best_sub_pixel_tree (generic C build)"
-                                           % (len(sizes), ss / args.steps / FE_SAMPLES)},
+                                 "sample": "per step: 1 frame x %d TX sizes (%.1f FE) through av1_lowbd_fwd_txfm + "
+                                           "av1_quantize_fp*, and the frame's 960 searches through "
+                                           "av1_full_pixel_search + av1_find_best_sub_pixel_tree (%s)"
+                                           % (len(sizes), ss / args.steps / FE_SAMPLES, cpu_desc(R))},
                 "e2e": {"value": val, "unit": "1080p frame-equiv/s", "h2d_bytes_per_step": 0,
                         "d2h_bytes_per_step": 0}}
         print(json.dumps(line))
@@ -1098,10 +1160,10 @@ def main():
             t += ti
             s_ += si
         c_txq = s_ / FE_SAMPLES / t
-        kind = "reference" if R is not None else "port"
+        kind = cpu_kind(R)
         cb = {"unit": "1080p frame-equiv/s", "cores": n_threads, "kind": kind, "txq_fe_per_s": c_txq}
-        sample = "%d x (1 frame x %d TX sizes) = %.1f FE after one warm-up pass, av1_fwd_txfm2d_*_c + " \
-                 "av1_quantize_fp*_c" % (reps, len(sizes), s_ / FE_SAMPLES)
+        sample = "%d x (1 frame x %d TX sizes) = %.1f FE after one warm-up pass, av1_lowbd_fwd_txfm + " \
+                 "av1_quantize_fp*" % (reps, len(sizes), s_ / FE_SAMPLES)
         if work is not None:
             tm, rf, rs = cpu_run_me(H, O, R, work, 0, n_threads)
             cb["me_frames_per_s"] = 1.0 / tm
@@ -1109,7 +1171,19 @@ def main():
             sample += "; 1 frame = %d searches through av1_full_pixel_search + av1_find_best_sub_pixel_tree" % work.per_frame
         else:
             cb["value"] = c_txq
-        cb["sample"] = sample + " (generic C build of the reference) on %d host threads" % n_threads
+        cb["sample"] = sample + " (%s) on %d host threads" % (cpu_desc(R), n_threads)
+        Rc = H.ref()
+        if Rc is not None and Rc is not R:  # the generic C build beside it, one pass
+            tc, sc_, _o = cpu_run_sweep(H, O, Rc, frames, planes, frame_elems, seed + rank, n_threads, sizes)
+            gc = {"kind": "reference", "txq_fe_per_s": sc_ / FE_SAMPLES / tc}
+            if work is not None:
+                tmc = cpu_run_me(H, O, Rc, work, 0, n_threads)[0]
+                gc["me_frames_per_s"] = 1.0 / tmc
+                gc["value"] = combined(gc["txq_fe_per_s"], 1.0 / tmc)
+            cb["generic_c"] = gc
+        cfg0 = run_configs0()
+        if cfg0:
+            cb["configs0_aomenc"] = cfg0
         line["cpu_baseline"] = cb
         # parity at full size: GPU (host-buffer calls, frame 0) vs CPU outputs, bit-exact
         ok = True

@@ -53,7 +53,9 @@ typedef struct {
 static void *drv_worker(void *arg) {
   DrvJob *j = (DrvJob *)arg;
   /* the reference transform uses its output as scratch for the full W*H block */
-  int32_t *tmp = (int32_t *)malloc(sizeof(int32_t) * (size_t)(j->full_coeffs + 64));
+  /* 64-byte aligned like the encoder's own coefficient buffers (the SIMD flavours use aligned stores) */
+  void *tmp_raw = malloc(sizeof(int32_t) * (size_t)(j->full_coeffs + 64) + 64);
+  int32_t *tmp = (int32_t *)(((uintptr_t)tmp_raw + 63) & ~(uintptr_t)63);
   const int per = (j->n_blocks + j->n_threads - 1) / j->n_threads;
   const int lo = j->tid * per, hi = lo + per > j->n_blocks ? j->n_blocks : lo + per;
   for (int i = lo; i < hi; ++i) {
@@ -74,7 +76,7 @@ static void *drv_worker(void *arg) {
                               j->dqcoeff + b->out_offset, r->dequant, &j->eob[i],
                               j->scan[cls], j->iscan[cls]);
   }
-  free(tmp);
+  free(tmp_raw);
   return NULL;
 }
 

@@ -13,6 +13,7 @@
 #include "config/aom_config.h"
 #include "config/aom_dsp_rtcd.h"
 #include "config/av1_rtcd.h"
+#include "config/aom_scale_rtcd.h"
 
 #include "av1/common/av1_common_int.h"
 #include "av1/common/blockd.h"
@@ -23,18 +24,26 @@
 
 /* high-bit-depth SADs as the encoder sees them: >> 2 at 10 bit, >> 4 at 12 bit
  * (av1/encoder/encoder_utils.h:153-208) */
-#define SHIM_FNS(W, H)                                                                        \
+/* REFSHIM_DISPATCH (the avx2 flavour, oracle/mk_ref.py): every kernel goes through the
+ * reference's own run-time dispatch names instead of the `_c` flavour. */
+#ifdef REFSHIM_DISPATCH
+#define RF(name) name
+#else
+#define RF(name) name##_c
+#endif
+
+#define SHIM_FNS(W, H)                                                                         \
   static unsigned sad##W##x##H##_b10(const uint8_t *a, int as, const uint8_t *b, int bs) {     \
-    return aom_highbd_sad##W##x##H##_c(a, as, b, bs) >> 2;                                     \
+    return RF(aom_highbd_sad##W##x##H)(a, as, b, bs) >> 2;                                     \
   }                                                                                            \
   static unsigned sad##W##x##H##_b12(const uint8_t *a, int as, const uint8_t *b, int bs) {     \
-    return aom_highbd_sad##W##x##H##_c(a, as, b, bs) >> 4;                                     \
+    return RF(aom_highbd_sad##W##x##H)(a, as, b, bs) >> 4;                                     \
   }                                                                                            \
   static unsigned sads##W##x##H##_b10(const uint8_t *a, int as, const uint8_t *b, int bs) {    \
-    return aom_highbd_sad_skip_##W##x##H##_c(a, as, b, bs) >> 2;                               \
+    return RF(aom_highbd_sad_skip_##W##x##H)(a, as, b, bs) >> 2;                               \
   }                                                                                            \
   static unsigned sads##W##x##H##_b12(const uint8_t *a, int as, const uint8_t *b, int bs) {    \
-    return aom_highbd_sad_skip_##W##x##H##_c(a, as, b, bs) >> 4;                               \
+    return RF(aom_highbd_sad_skip_##W##x##H)(a, as, b, bs) >> 4;                               \
   }                                                                                            \
   static void sad4##W##x##H##_b10(const uint8_t *a, int as, const uint8_t *const b[4], int bs, \
                                   uint32_t *o) {                                               \
@@ -59,26 +68,26 @@
   static int fill##W##x##H(aom_variance_fn_ptr_t *f, int highbd, int bd) {                     \
     memset(f, 0, sizeof(*f));                                                                  \
     if (!highbd) {                                                                             \
-      f->sdf = aom_sad##W##x##H##_c;                                                           \
-      f->sdsf = aom_sad_skip_##W##x##H##_c;                                                    \
-      f->vf = aom_variance##W##x##H##_c;                                                       \
-      f->svf = aom_sub_pixel_variance##W##x##H##_c;                                            \
+      f->sdf = RF(aom_sad##W##x##H);                                                           \
+      f->sdsf = RF(aom_sad_skip_##W##x##H);                                                    \
+      f->vf = RF(aom_variance##W##x##H);                                                       \
+      f->svf = RF(aom_sub_pixel_variance##W##x##H);                                            \
       f->sdx4df = aom_sad##W##x##H##x4d_c;                                                     \
       f->sdx3df = aom_sad##W##x##H##x3d_c;                                                     \
       f->sdsx4df = aom_sad_skip_##W##x##H##x4d_c;                                              \
     } else if (bd == 10) {                                                                     \
       f->sdf = sad##W##x##H##_b10;                                                             \
       f->sdsf = sads##W##x##H##_b10;                                                           \
-      f->vf = aom_highbd_10_variance##W##x##H##_c;                                             \
-      f->svf = aom_highbd_10_sub_pixel_variance##W##x##H##_c;                                  \
+      f->vf = RF(aom_highbd_10_variance##W##x##H);                                             \
+      f->svf = RF(aom_highbd_10_sub_pixel_variance##W##x##H);                                  \
       f->sdx4df = sad4##W##x##H##_b10;                                                         \
       f->sdx3df = sad4##W##x##H##_b10;                                                         \
       f->sdsx4df = sads4##W##x##H##_b10;                                                       \
     } else {                                                                                   \
       f->sdf = sad##W##x##H##_b12;                                                             \
       f->sdsf = sads##W##x##H##_b12;                                                           \
-      f->vf = aom_highbd_12_variance##W##x##H##_c;                                             \
-      f->svf = aom_highbd_12_sub_pixel_variance##W##x##H##_c;                                  \
+      f->vf = RF(aom_highbd_12_variance##W##x##H);                                             \
+      f->svf = RF(aom_highbd_12_sub_pixel_variance##W##x##H);                                  \
       f->sdx4df = sad4##W##x##H##_b12;                                                         \
       f->sdx3df = sad4##W##x##H##_b12;                                                         \
       f->sdsx4df = sads4##W##x##H##_b12;                                                       \
@@ -335,3 +344,57 @@ void refshim_quantize_fp_qm(const int32_t *coeff, intptr_t n, const int16_t *zbi
   else
     av1_quantize_fp_facade(coeff, n, &p, qcoeff, dqcoeff, eob, &sc, &qp);
 }
+
+/* ---- function pointers for the timed CPU baseline (oracle/av1o_drv.c) -------------------------
+ * The transform as the encoder reaches it: av1_fwd_txfm (hybrid_fwd_txfm.c:231) ->
+ * av1_lowbd_fwd_txfm / av1_highbd_fwd_txfm, i.e. the SIMD flavours in the avx2 build. */
+#include "av1/encoder/hybrid_fwd_txfm.h"
+
+#define SHIM_TX(TS)                                                                                   \
+  static void fwd_lb_##TS(const int16_t *in, int32_t *out, int stride, TX_TYPE t, int bd) {           \
+    TxfmParam p;                                                                                      \
+    memset(&p, 0, sizeof(p));                                                                         \
+    p.tx_type = t, p.tx_size = (TX_SIZE)TS, p.bd = bd, p.tx_set_type = EXT_TX_SET_ALL16;              \
+    av1_lowbd_fwd_txfm(in, out, stride, &p);                                                          \
+  }                                                                                                   \
+  static void fwd_hb_##TS(const int16_t *in, int32_t *out, int stride, TX_TYPE t, int bd) {           \
+    TxfmParam p;                                                                                      \
+    memset(&p, 0, sizeof(p));                                                                         \
+    p.tx_type = t, p.tx_size = (TX_SIZE)TS, p.bd = bd, p.is_hbd = 1, p.tx_set_type = EXT_TX_SET_ALL16; \
+    av1_highbd_fwd_txfm(in, out, stride, &p);                                                         \
+  }
+SHIM_TX(0) SHIM_TX(1) SHIM_TX(2) SHIM_TX(3) SHIM_TX(4) SHIM_TX(5) SHIM_TX(6) SHIM_TX(7) SHIM_TX(8) SHIM_TX(9)
+SHIM_TX(10) SHIM_TX(11) SHIM_TX(12) SHIM_TX(13) SHIM_TX(14) SHIM_TX(15) SHIM_TX(16) SHIM_TX(17) SHIM_TX(18)
+
+typedef void (*shim_fwd_fn)(const int16_t *, int32_t *, int, TX_TYPE, int);
+void *refshim_fwd_txfm_fn(int tx_size, int highbd) {
+#define E(TS) { fwd_lb_##TS, fwd_hb_##TS }
+  static const shim_fwd_fn tab[19][2] = { E(0), E(1), E(2), E(3), E(4), E(5), E(6), E(7), E(8), E(9), E(10),
+                                          E(11), E(12), E(13), E(14), E(15), E(16), E(17), E(18) };
+#undef E
+  if (tx_size < 0 || tx_size >= 19) return NULL;
+  return (void *)tab[tx_size][highbd != 0];
+}
+
+void *refshim_quantize_fp_fn(int log_scale, int highbd) {
+  if (highbd) return (void *)av1_highbd_quantize_fp;
+  return log_scale == 0 ? (void *)av1_quantize_fp
+                        : log_scale == 1 ? (void *)av1_quantize_fp_32x32 : (void *)av1_quantize_fp_64x64;
+}
+
+/* 1 when this library was built with the x86 intrinsics and run-time dispatch */
+int refshim_simd(void) {
+#ifdef REFSHIM_DISPATCH
+  return 1;
+#else
+  return 0;
+#endif
+}
+
+#ifdef REFSHIM_DISPATCH
+__attribute__((constructor)) static void shim_rtcd_init(void) {
+  aom_dsp_rtcd();
+  av1_rtcd();
+  aom_scale_rtcd();
+}
+#endif

@@ -67,12 +67,39 @@ def have_ref():
     return os.path.exists(REF_LIB)
 
 
+def _shim_protos(lib):
+    for n in ("refshim_fwd_txfm_fn", "refshim_quantize_fp_fn"):
+        getattr(lib, n).restype = C.c_void_p
+        getattr(lib, n).argtypes = [C.c_int, C.c_int]
+    return lib
+
+
 def ref():
     """The reference's own C functions (oracle/_ref), or None when not built."""
     global _ref
     if _ref is None and have_ref():
-        _ref = C.CDLL(REF_LIB)
+        _ref = _shim_protos(C.CDLL(REF_LIB))
     return _ref
+
+
+REF_AVX2_LIB = os.path.join(os.path.dirname(REF_LIB), "libaomref_avx2.so")
+_ref_avx2 = None
+
+
+def host_has_avx2():
+    try:
+        return " avx2 " in open("/proc/cpuinfo").read().replace("\n", " ")
+    except OSError:
+        return False
+
+
+def ref_avx2():
+    """The reference built with its x86 intrinsics and run-time dispatch (oracle/mk_ref.py, avx2
+    flavour), or None when not built / the host has no AVX2."""
+    global _ref_avx2
+    if _ref_avx2 is None and os.path.exists(REF_AVX2_LIB) and host_has_avx2():
+        _ref_avx2 = _shim_protos(C.CDLL(REF_AVX2_LIB))
+    return _ref_avx2
 
 
 class QRow(C.Structure):
