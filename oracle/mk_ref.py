@@ -216,6 +216,8 @@ def build_flavour(flavour):
             for s in sorted(glob.glob(os.path.join(REF, d, "*.c"))):
                 if os.path.relpath(s, REF) not in X86_EXCLUDE:
                     x86.append((s, isa_flag(s)))
+        # plain-C statements of the assembler-only 1-D filter helpers (see the file's header)
+        x86.append((os.path.join(HERE, "ref_asm_fallback.c"), []))
         pass1, _failed = compile_all(x86, os.path.join(root, "obj_pass1"), incs, [])
         asm_only, tainted = asm_dependent(pass1)
         n = rewrite_rtcd(cfgdir, tainted)
@@ -291,7 +293,8 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     targets = [os.path.join(OUT, n) for n in ("libaomref.so", "libaomref_avx2.so", "aomenc", "aomenc_avx2")]
     newest = max(os.path.getmtime(__file__), os.path.getmtime(os.path.join(HERE, "ref_shim.c")),
-                 os.path.getmtime(os.path.join(HERE, "av1o_me.h")))
+                 os.path.getmtime(os.path.join(HERE, "av1o_me.h")),
+                 os.path.getmtime(os.path.join(HERE, "ref_asm_fallback.c")))
     if all(os.path.exists(t) and os.path.getmtime(t) > newest for t in targets) and "--force" not in sys.argv:
         print("mk_ref: up to date")
         return 0

@@ -47,22 +47,22 @@
   }                                                                                            \
   static void sad4##W##x##H##_b10(const uint8_t *a, int as, const uint8_t *const b[4], int bs, \
                                   uint32_t *o) {                                               \
-    aom_highbd_sad##W##x##H##x4d_c(a, as, b, bs, o);                                           \
+    RF(aom_highbd_sad##W##x##H##x4d)(a, as, b, bs, o);                                         \
     for (int i = 0; i < 4; ++i) o[i] >>= 2;                                                    \
   }                                                                                            \
   static void sad4##W##x##H##_b12(const uint8_t *a, int as, const uint8_t *const b[4], int bs, \
                                   uint32_t *o) {                                               \
-    aom_highbd_sad##W##x##H##x4d_c(a, as, b, bs, o);                                           \
+    RF(aom_highbd_sad##W##x##H##x4d)(a, as, b, bs, o);                                         \
     for (int i = 0; i < 4; ++i) o[i] >>= 4;                                                    \
   }                                                                                            \
   static void sads4##W##x##H##_b10(const uint8_t *a, int as, const uint8_t *const b[4],        \
                                    int bs, uint32_t *o) {                                      \
-    aom_highbd_sad_skip_##W##x##H##x4d_c(a, as, b, bs, o);                                     \
+    RF(aom_highbd_sad_skip_##W##x##H##x4d)(a, as, b, bs, o);                                   \
     for (int i = 0; i < 4; ++i) o[i] >>= 2;                                                    \
   }                                                                                            \
   static void sads4##W##x##H##_b12(const uint8_t *a, int as, const uint8_t *const b[4],        \
                                    int bs, uint32_t *o) {                                      \
-    aom_highbd_sad_skip_##W##x##H##x4d_c(a, as, b, bs, o);                                     \
+    RF(aom_highbd_sad_skip_##W##x##H##x4d)(a, as, b, bs, o);                                   \
     for (int i = 0; i < 4; ++i) o[i] >>= 4;                                                    \
   }                                                                                            \
   static int fill##W##x##H(aom_variance_fn_ptr_t *f, int highbd, int bd) {                     \
@@ -72,9 +72,9 @@
       f->sdsf = RF(aom_sad_skip_##W##x##H);                                                    \
       f->vf = RF(aom_variance##W##x##H);                                                       \
       f->svf = RF(aom_sub_pixel_variance##W##x##H);                                            \
-      f->sdx4df = aom_sad##W##x##H##x4d_c;                                                     \
-      f->sdx3df = aom_sad##W##x##H##x3d_c;                                                     \
-      f->sdsx4df = aom_sad_skip_##W##x##H##x4d_c;                                              \
+      f->sdx4df = RF(aom_sad##W##x##H##x4d);                                                   \
+      f->sdx3df = RF(aom_sad##W##x##H##x3d);                                                   \
+      f->sdsx4df = RF(aom_sad_skip_##W##x##H##x4d);                                            \
     } else if (bd == 10) {                                                                     \
       f->sdf = sad##W##x##H##_b10;                                                             \
       f->sdsf = sads##W##x##H##_b10;                                                           \
