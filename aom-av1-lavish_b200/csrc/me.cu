@@ -76,11 +76,28 @@ __shared__ int g_cdp[kMaxRuns * 16];        // n-step: their positions, (row & 0
 __shared__ int g_runn[kMaxRuns];            // n-step: candidates of run r in this round (0 = finished)
 __shared__ int g_runres[kMaxRuns][8];       // n-step: per run {best row, col, second row, col, sad, num00, moved}
 // Copies descriptor `bi` into shared memory (11 words) and synchronises the CTA.
+// With l.start_from the start mv comes from an earlier launch's result instead (see
+// B200MeLaunch.start_from / start_group): full-pel results x 8 for the sub-pel kernel,
+// GET_MV_RAWPEL (mv.h:28) of sub-pel results for the full-pel kernel.
+template <bool FULLPEL>
 __device__ __forceinline__ void load_desc(const B200MeLaunch &l, int bi) {
   static_assert(sizeof(B200MeBlock) == 44, "descriptor is 11 words");
   if (threadIdx.x < 11)
     reinterpret_cast<int *>(&g_desc)[threadIdx.x] = reinterpret_cast<const int *>(l.blocks + bi)[threadIdx.x];
   __syncthreads();
+  if (l.start_from) {
+    if (threadIdx.x == 0) {
+      const B200MeResult &r = l.start_from[l.start_group > 1 ? bi / l.start_group : bi];
+      if (FULLPEL) {
+        g_desc.start_row = (int16_t)((r.best_row + 3 + (r.best_row >= 0)) >> 3);
+        g_desc.start_col = (int16_t)((r.best_col + 3 + (r.best_col >= 0)) >> 3);
+      } else {
+        g_desc.start_row = (int16_t)(r.best_row * 8);
+        g_desc.start_col = (int16_t)(r.best_col * 8);
+      }
+    }
+    __syncthreads();
+  }
 }
 
 // Dynamic shared memory of both kernels: source block at offset 0, then the staged reference

@@ -996,7 +996,7 @@ __global__ void __launch_bounds__(kThreads, 3) fullpel_kernel(const B200MeLaunch
                                                            const __grid_constant__ CUtensorMap tm_cur,
                                                            const __grid_constant__ CUtensorMap tm_ref) {
   const int bi = blockIdx.x;
-  load_desc(l, bi);
+  load_desc<true>(l, bi);
   Ctx k(g_desc);
   k.l = &l;
   if (me_family(k.d.search_method) != FAM) return;

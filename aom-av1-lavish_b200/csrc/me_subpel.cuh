@@ -495,7 +495,7 @@ __device__ void subpel_search_pruned(const SubCtx &s, SubState &st, int tree, co
 
 __global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) {
   const int bi = blockIdx.x;
-  load_desc(l, bi);
+  load_desc<false>(l, bi);
   SubCtx s(g_desc);
   s.k.l = &l;
   init_costs(s.k);
@@ -504,7 +504,6 @@ __global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) 
   s.k.sad_shift = 0;
   s.search_type = (s.k.d.subpel >> 4) & 3;
   s.start = Mv{ s.k.d.start_row, s.k.d.start_col };
-  if (l.start_from) s.start = Mv{ l.start_from[bi].best_row * 8, l.start_from[bi].best_col * 8 };
   // the limits are sub-pel here: no window staging (window_budget 0), reference via L1/L2
   {
     const int px = s.k.px, bw = s.k.d.bw, bh = s.k.d.bh;

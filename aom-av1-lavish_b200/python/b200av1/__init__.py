@@ -256,7 +256,8 @@ class MeLaunch(C.Structure):
                 ("window_bytes", C.c_int), ("max_bw", C.c_int), ("max_bh", C.c_int),
                 ("cost_lists", C.c_void_p), ("cost_list_stride", C.c_int), ("families", C.c_uint),
                 ("cur_rows", C.c_int), ("ref_rows", C.c_int), ("max_col_span", C.c_int),
-                ("max_row_span", C.c_int), ("start_from", C.c_void_p), ("stats", C.c_void_p)]
+                ("max_row_span", C.c_int), ("start_from", C.c_void_p), ("stats", C.c_void_p),
+                ("start_group", C.c_int)]
 
 
 ME_FAMILY_NSTEP, ME_FAMILY_PATTERN, ME_FAMILY_REFINE = 1, 2, 4
@@ -279,3 +280,69 @@ class HadamardLaunch(C.Structure):
 class AvgLaunch(C.Structure):
     _fields_ = [("op", C.c_int), ("highbd", C.c_int), ("n_blocks", C.c_int), ("blocks", C.c_void_p),
                 ("a", C.c_void_p), ("b", C.c_void_p), ("out", C.c_void_p)]
+
+
+# ---- frame tier + block queue (csrc/queue.cu) -----------------------------------------
+class TfParams(C.Structure):
+    """B200TfParams (include/b200av1.h): tf_motion_search's parameter set-up."""
+    _fields_ = [("bw", C.c_int), ("bh", C.c_int), ("border_in_pixels", C.c_int), ("search_method", C.c_int),
+                ("step_param", C.c_int), ("mv_cost_type", C.c_int), ("mesh_range", C.c_int * 4),
+                ("mesh_interval", C.c_int * 4), ("force_mesh_thresh", C.c_int), ("prune_mesh_search", C.c_int),
+                ("mesh_search_mv_diff_threshold", C.c_int), ("use_downsampled_sad", C.c_int),
+                ("sad_per_bit", C.c_int), ("error_per_bit", C.c_int), ("allow_hp", C.c_int),
+                ("iters_per_step", C.c_int), ("subpel_tree", C.c_int), ("want_cost_list", C.c_int)]
+
+
+TF_RESULT_DTYPE = np.dtype([("block_mv", "<i2", (2,)), ("block_mse", "<i4"), ("sub_mv", "<i2", (4, 2)),
+                            ("sub_mse", "<i4", (4,)), ("ref_mv", "<i2", (2,))])
+assert TF_RESULT_DTYPE.itemsize == 44
+
+
+def tf_default_params(width, height):
+    p = TfParams()
+    lib().b200_queue_tf_default_params(width, height, C.byref(p))
+    return p
+
+
+class Frame:
+    """b200_frame: a luma plane on the device with its replicated border."""
+
+    def __init__(self, ctx, y, border, bd=8):
+        y = np.ascontiguousarray(y)
+        assert y.ndim == 2 and y.dtype == (np.uint8 if bd == 8 else np.uint16)
+        self.ctx, self.h = ctx, C.c_void_p()
+        self.height, self.width = y.shape
+        self.border, self.bd = border, bd
+        check(lib().b200_frame_upload(ctx.h, vp(y), y.shape[1], y.shape[1], y.shape[0], border, bd,
+                                      C.byref(self.h)))
+
+    def download(self):
+        out = np.zeros((self.height + 2 * self.border, self.width + 2 * self.border),
+                       np.uint8 if self.bd == 8 else np.uint16)
+        check(lib().b200_frame_download(self.ctx.h, self.h, vp(out)))
+        return out
+
+    def free(self):
+        if self.h:
+            lib().b200_frame_free(self.ctx.h, self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def queue_tf_motion_search(ctx, cur, ref, params, ref_mvs=None):
+    """b200_queue_tf_motion_search: every TF block of the frame pair; returns a TF_RESULT_DTYPE array."""
+    rows = (cur.height + params.bh - 1) // params.bh
+    cols = (cur.width + params.bw - 1) // params.bw
+    out = np.zeros(rows * cols, TF_RESULT_DTYPE)
+    mv = None
+    if ref_mvs is not None:
+        mv = np.ascontiguousarray(ref_mvs, np.int16)
+        assert mv.size == 2 * rows * cols
+    check(lib().b200_queue_tf_motion_search(ctx.h, cur.h, ref.h, C.byref(params), vp(mv) if mv is not None else None,
+                                            vp(out)))
+    return out.reshape(rows, cols)

@@ -481,6 +481,51 @@ def bench_hbd4k(ctx, dev, stream, steps, warmup, seed, n_frames=3):
             "launches_per_step": 19}
 
 
+def bench_tf_queue(ctx, luma, seed, n_threads, reps=3):
+    """The first consumer of the block queue: tf_motion_search over one 1080p
+    frame pair -- 8160 16x16 blocks + 32640 8x8 sub-blocks, full-pel NSTEP + mesh and 8-tap sub-pel each
+    (temporal_filter.c:88-260) -- as ONE b200_queue_tf_motion_search call (host planes in, per-block
+    results out: uploads, border extension, 4 chained launches, D2H all inside the timed region), next
+    to the reference's per-block loop (:804-872) on the host threads, results compared."""
+    import b200av1
+    H, _O, R = load_cpu_libs()
+    cur = np.ascontiguousarray(luma[0])
+    rng = np.random.default_rng([seed, 77])
+    ref = np.roll(cur, (3, -5), (0, 1)).astype(np.int16) + rng.integers(-3, 4, cur.shape)
+    ref = np.clip(ref, 0, 255).astype(np.uint8)
+    h, w = cur.shape
+    p = b200av1.tf_default_params(w, h)
+    got, t_e2e, t_res = None, [], []
+    for _ in range(reps + 1):
+        t0 = time.perf_counter()
+        fc, fr = b200av1.Frame(ctx, cur, p.border_in_pixels), b200av1.Frame(ctx, ref, p.border_in_pixels)
+        got = b200av1.queue_tf_motion_search(ctx, fc, fr, p)
+        t_e2e.append(time.perf_counter() - t0)
+        t0 = time.perf_counter()
+        b200av1.queue_tf_motion_search(ctx, fc, fr, p)
+        t_res.append(time.perf_counter() - t0)
+        fc.free()
+        fr.free()
+    out = {"workload": "tf_motion_search over one 1080p 8-bit frame pair: %d blocks of 16x16 + 4 x 8x8 each = %d searches"
+                       % (got.size, got.size * 5),
+           "gpu_e2e_ms": min(t_e2e[1:]) * 1e3, "gpu_frames_resident_ms": min(t_res[1:]) * 1e3,
+           "launches_per_pair": 5, "h2d_bytes": int(2 * cur.nbytes + got.size * 10 * 44),
+           "d2h_bytes": int(got.size * 10 * 40)}
+    if R is not None:
+        cb, rb = np.pad(cur, p.border_in_pixels, mode="edge"), np.pad(ref, p.border_in_pixels, mode="edge")
+        off = p.border_in_pixels * cb.shape[1] + p.border_in_pixels
+        want = np.zeros(got.size, b200av1.TF_RESULT_DTYPE)
+        t0 = time.perf_counter()
+        R.refshim_tf_motion_search_frame_mt(C.c_void_p(cb.ctypes.data + off), C.c_void_p(rb.ctypes.data + off),
+                                            cb.shape[1], w, h, 0, 8, C.byref(p), None, C.c_void_p(want.ctypes.data),
+                                            n_threads)
+        out["cpu_ms"] = (time.perf_counter() - t0) * 1e3
+        out["cpu"] = "%s, %d threads over block rows" % (cpu_kind(R), n_threads)
+        out["parity"] = "bit-exact" if all(np.array_equal(got.reshape(-1)[n], want[n]) for n in want.dtype.names) \
+            else "MISMATCH"
+    return out
+
+
 def bench_hadamard(ctx, dev, stream, steps, warmup, d_src, n_frames):
     """Hadamard + SATD over the luma residual of the resident 1080p frames (the TPL /
     tx-prune cost, aom_dsp/avg.c): coefficient + SATD output, and SATD only."""
@@ -1063,6 +1108,8 @@ def main():
         if world == 1:
             extras["hadamard"] = bench_hadamard(ctx, dev, stream, max(2, args.steps // 2), 2, d_src, args.frames)
             extras["hbd4k"] = bench_hbd4k(ctx, dev, stream, max(2, args.steps // 2), 2, seed)
+            if not args.no_cpu:
+                extras["tf_queue"] = bench_tf_queue(ctx, luma, seed, os.cpu_count() or 1)
         # BASELINE configs[4] at every N: 120 frames over the ranks
         del d_coeff, d_qc, d_dq
         torch.cuda.empty_cache()

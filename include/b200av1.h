@@ -477,6 +477,11 @@ typedef struct {
                                     av1_single_motion_search does, motion_search_facade.c:120-494) */
   unsigned long long *stats;     /* full-pel launch, device, optional: [0] += SAD candidates evaluated,
                                     [1] += pixels compared (measurement only) */
+  int start_group;               /* with start_from: block i reads start_from[i / start_group] (0 = 1).
+                                    In a FULL-PEL launch start_from holds SUB-pel results (1/8 pel) and
+                                    the block starts at get_fullmv_from_mv() of it (mv.h:79) -- the
+                                    4 sub-blocks of tf_motion_search start at their parent block's
+                                    refined mv (temporal_filter.c:198), start_group = 4 */
 } B200MeLaunch;
 #define B200_ME_FAMILY_NSTEP 1u   /* NSTEP, NSTEP_8PT, DIAMOND, CLAMPED_DIAMOND */
 #define B200_ME_FAMILY_PATTERN 2u /* HEX .. VFAST_DIAMOND (pattern_search) */
@@ -495,6 +500,63 @@ int b200_me_subpel_launch(b200_ctx *ctx, const B200MeLaunch *launch, void *strea
 int b200_me_batch_host(b200_ctx *ctx, const B200MeLaunch *launch, size_t cur_bytes, size_t ref_bytes,
                        const B200MeBlock *subpel_blocks, B200MeResult *fullpel_out,
                        B200MeResult *subpel_out);
+/* ---------------------------------------------- frame tier + encoder block queue ------ */
+/* SURVEY.md section 8b tier 3 / rows a25, a26, f1: what an encoder's frame loop binds instead of
+ * its per-block loops.  A b200_frame is one luma plane resident on the device with its replicated
+ * border (aom_extend_frame_borders, aom_scale/generic/yv12extend.c:223: the motion search reads up
+ * to `border` pixels outside the picture); the queue calls build every descriptor of a frame on
+ * the host, run ONE chained launch sequence, and scatter the results back. */
+typedef struct b200_frame b200_frame;
+/* y: host pointer to pixel (0,0) of a width x height plane of uint8 (bd == 8) or uint16 samples,
+ * `stride` in pixels; the border is replicated on the device, the host buffer needs none. */
+int b200_frame_upload(b200_ctx *ctx, const void *y, int stride, int width, int height, int border, int bd,
+                      b200_frame **frame);
+int b200_frame_free(b200_ctx *ctx, b200_frame *frame);
+/* reads the bordered device plane back (tests): out holds (height + 2*border) rows of
+ * (width + 2*border) pixels */
+int b200_frame_download(b200_ctx *ctx, const b200_frame *frame, void *out);
+
+/* tf_motion_search (av1/encoder/temporal_filter.c:88-260) for every TF_BLOCK_SIZE block of a frame
+ * pair, the loop of av1_tf_do_filtering_row (:804-872): full-pel NSTEP + mesh and the 8-tap
+ * sub-pel refinement of the whole block, then of its 4 sub-blocks started at the block's refined
+ * mv, the split decision (tf_determine_block_partition, :275) and the ref_mv hand-down rule
+ * (:255-259).  Four chained launches per frame pair, no host round trip in between. */
+typedef struct {
+  int bw, bh;                 /* TF_BLOCK_SIZE (temporal_filter.h:31): 16x16; sub-blocks are bw/2 x bh/2 */
+  int border_in_pixels;       /* cpi->oxcf.border_in_pixels, av1_set_mv_{row,col}_limits (mcomp.h:227-251) */
+  int search_method;          /* B200_ME_NSTEP (temporal_filter.c:134) */
+  int step_param;             /* av1_init_search_range(max(width, height)) (:112) */
+  int mv_cost_type;           /* B200_MV_COST_L1_* by min(width, height) (:116-119) */
+  int mesh_range[4], mesh_interval[4]; /* sf.mv_sf.mesh_patterns */
+  int force_mesh_thresh;      /* sf.mv_sf.exhaustive_searches_thresh */
+  int prune_mesh_search;      /* (:152-156) */
+  int mesh_search_mv_diff_threshold;
+  int use_downsampled_sad;    /* sf.mv_sf.use_downsampled_sad (applies when bh >= 16, mcomp.c:135) */
+  int sad_per_bit, error_per_bit; /* x->sadperbit, x->errorperbit */
+  int allow_hp;               /* cm->features.allow_high_precision_mv */
+  int iters_per_step;         /* sf.mv_sf.subpel_iters_per_step */
+  int subpel_tree;            /* B200_SUBPEL_TREE*: cpi->mv_search_params.find_fractional_mv_step */
+  int want_cost_list;         /* cond_cost_list(cpi, cost_list) != NULL */
+} B200TfParams;
+typedef struct {
+  int16_t block_mv[2];  /* row, col, 1/8 pel: the whole block's refined mv */
+  int32_t block_mse;
+  int16_t sub_mv[4][2]; /* subblock_mvs after the split decision */
+  int32_t sub_mse[4];   /* subblock_mses after the split decision */
+  int16_t ref_mv[2];    /* *ref_mv handed to the next frame of the window */
+} B200TfResult; /* 44 bytes */
+/* temporal_filter.c:112-119 defaults for a width x height frame + the good-quality speed features */
+void b200_queue_tf_default_params(int width, int height, B200TfParams *params);
+/* ref_mvs: 2 x int16 (row, col; 1/8 pel) per block in raster order, or NULL for kZeroMv;
+ * out: ceil(height / bh) * ceil(width / bw) results in raster order (host). */
+int b200_queue_tf_motion_search(b200_ctx *ctx, const b200_frame *to_filter, const b200_frame *ref,
+                                const B200TfParams *params, const int16_t *ref_mvs, B200TfResult *out);
+/* The descriptors b200_queue_tf_motion_search builds, without touching the device (tests, and
+ * callers that want to launch themselves): stage 0 = whole blocks, stage 1 = sub-blocks; full[]
+ * and sub[] take n (stage 0) or 4n (stage 1) descriptors.  Returns the count written. */
+int b200_queue_tf_describe(int width, int height, int frame_pitch, int frame_origin, const B200TfParams *params,
+                           const int16_t *ref_mvs, int stage, B200MeBlock *full, B200MeBlock *sub);
+
 /* Measured rate of the integer pipe on this device: VABSDIFF4 with accumulate (the SAD
  * instruction) issued back to back from every SM, in G pixel-absdiffs per second.  The
  * denominator of the motion search's int-ALU roofline. */

@@ -88,6 +88,27 @@ void av1o_refining_search_8p(const Av1oMeParams *p, Av1oMeResult *r);
 /* av1_init_search_range (mcomp.c:239) */
 int av1o_init_search_range(int size);
 
+/* ---- temporal-filter motion search of a whole frame pair (tests/test_queue_tf_gpu.py) ----
+ * Same layout as B200TfParams / B200TfResult (include/b200av1.h).  The reference side is
+ * refshim_tf_motion_search_frame (oracle/ref_shim.c): the block loop of av1_tf_do_filtering_row
+ * (temporal_filter.c:804-872) around a restatement of tf_motion_search's parameter set-up
+ * (:88-260, the function is static and wants a whole AV1_COMP) that calls the reference's own
+ * av1_set_mv_{row,col}_limits, av1_set_mv_search_range, av1_set_subpel_mv_search_range,
+ * av1_full_pixel_search and av1_find_best_sub_pixel_tree*. */
+typedef struct {
+  int bw, bh, border_in_pixels, search_method, step_param, mv_cost_type;
+  int mesh_range[4], mesh_interval[4];
+  int force_mesh_thresh, prune_mesh_search, mesh_search_mv_diff_threshold, use_downsampled_sad;
+  int sad_per_bit, error_per_bit, allow_hp, iters_per_step, subpel_tree, want_cost_list;
+} Av1oTfParams;
+typedef struct {
+  int16_t block_mv[2];
+  int32_t block_mse;
+  int16_t sub_mv[4][2];
+  int32_t sub_mse[4];
+  int16_t ref_mv[2];
+} Av1oTfResult;
+
 #ifdef __cplusplus
 }
 #endif

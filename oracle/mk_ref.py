@@ -73,6 +73,14 @@ ISA_FLAGS = [("avx2", "-mavx2"), ("avx", "-mavx"), ("sse4_2", "-msse4.2"), ("sse
              ("ssse3", "-mssse3"), ("sse3", "-msse3"), ("sse2", "-msse2"), ("sse", "-msse"), ("mmx", "-mmmx")]
 
 
+def write_if_changed(path, text):
+    """Generated headers keep their mtime when nothing changed, so the object cache stays valid."""
+    if os.path.exists(path) and open(path).read() == text:
+        return
+    with open(path, "w") as f:
+        f.write(text)
+
+
 def write_config(cfgdir, flavour):
     text = open(os.path.join(REF, "build/cmake/aom_config_defaults.cmake")).read()
     vals = {}
@@ -81,20 +89,17 @@ def write_config(cfgdir, flavour):
     vals.update(COMMON_OVERRIDES)
     vals.update(FLAVOURS[flavour]["cfg"])
     keep = ("ARCH_", "AOM_ARCH_", "HAVE_", "CONFIG_", "INLINE", "DECODE_", "FORCE_", "STATIC_")
-    with open(os.path.join(cfgdir, "aom_config.h"), "w") as f:
-        f.write("/* written by oracle/mk_ref.py from aom_config_defaults.cmake (%s target) */\n" % flavour)
-        f.write("#ifndef AOM_CONFIG_H_\n#define AOM_CONFIG_H_\n")
-        for k, v in vals.items():
-            if k.startswith(keep):
-                f.write("#define %s %s\n" % (k, v))
-        f.write("#endif\n")
-    with open(os.path.join(cfgdir, "aom_version.h"), "w") as f:
-        f.write("#ifndef AOM_VERSION_H_\n#define AOM_VERSION_H_\n#define VERSION_MAJOR 3\n#define VERSION_MINOR 6\n"
+    text = "/* written by oracle/mk_ref.py from aom_config_defaults.cmake (%s target) */\n" % flavour
+    text += "#ifndef AOM_CONFIG_H_\n#define AOM_CONFIG_H_\n"
+    for k, v in vals.items():
+        if k.startswith(keep):
+            text += "#define %s %s\n" % (k, v)
+    write_if_changed(os.path.join(cfgdir, "aom_config.h"), text + "#endif\n")
+    write_if_changed(os.path.join(cfgdir, "aom_version.h"), "#ifndef AOM_VERSION_H_\n#define AOM_VERSION_H_\n#define VERSION_MAJOR 3\n#define VERSION_MINOR 6\n"
                 "#define VERSION_PATCH 0\n#define VERSION_EXTRA \"lavish-ref\"\n"
                 "#define VERSION_PACKED ((VERSION_MAJOR << 16) | (VERSION_MINOR << 8) | (VERSION_PATCH))\n"
                 "#define VERSION_STRING_NOSP \"3.6.0-lavish-ref\"\n#define VERSION_STRING \" 3.6.0-lavish-ref\"\n#endif\n")
-    with open(os.path.join(cfgdir, "aom_config.c"), "w") as f:
-        f.write('#include "aom/aom_codec.h"\nstatic const char *const cfg = "oracle/mk_ref.py %s";\n'
+    write_if_changed(os.path.join(cfgdir, "aom_config.c"), '#include "aom/aom_codec.h"\nstatic const char *const cfg = "oracle/mk_ref.py %s";\n'
                 "const char *aom_codec_build_config(void) { return cfg; }\n" % flavour)
 
 
@@ -104,8 +109,7 @@ def write_rtcd(cfgdir, arch):
         out = subprocess.run(["perl", os.path.join(REF, "build/cmake/rtcd.pl"), "--arch=" + arch, "--sym=" + sym,
                               "--config=" + os.path.join(cfgdir, "aom_config.h"), os.path.join(REF, defs)],
                              check=True, capture_output=True, text=True).stdout
-        with open(os.path.join(cfgdir, sym + ".h"), "w") as f:
-            f.write(out)
+        write_if_changed(os.path.join(cfgdir, sym + ".h.gen"), out)
 
 
 def isa_flag(path):
@@ -116,15 +120,20 @@ def isa_flag(path):
     return ["-msse2"]
 
 
-def compile_all(srcs, objdir, incs, defs):
+def compile_all(srcs, objdir, incs, defs, hdrdir):
     os.makedirs(objdir, exist_ok=True)
     jobs = []
     for s, extra in srcs:
         o = os.path.join(objdir, os.path.relpath(s, "/").replace("/", "_")[:-2] + ".o")
         jobs.append((s, o, extra))
 
+    newest_hdr = max([os.path.getmtime(__file__)] + [os.path.getmtime(p) for p in glob.glob(os.path.join(hdrdir, "*.h"))]
+                     + [os.path.getmtime(p) for p in glob.glob(os.path.join(HERE, "*.h"))])
+
     def one(job):
         s, o, extra = job
+        if os.path.exists(o) and os.path.getmtime(o) > max(os.path.getmtime(s), newest_hdr):
+            return o, 0, ""
         r = subprocess.run(["gcc", "-O2", "-fPIC", "-ffunction-sections", "-std=gnu99", "-D_GNU_SOURCE", "-DNDEBUG", "-w", "-c"] + defs +
                            extra + incs + [s, "-o", o], capture_output=True, text=True)
         return o, r.returncode, r.stderr
@@ -185,7 +194,7 @@ def rewrite_rtcd(cfgdir, tainted):
     for name in ("av1_rtcd.h", "aom_dsp_rtcd.h", "aom_scale_rtcd.h"):
         path = os.path.join(cfgdir, name)
         out = []
-        for line in open(path).read().splitlines():
+        for line in open(path + ".gen").read().splitlines():
             m = re.match(r"#define (\w+) (\w+)$", line)
             if m and m.group(2) in tainted:
                 line = "#define %s %s_c" % (m.group(1), m.group(1))
@@ -197,8 +206,7 @@ def rewrite_rtcd(cfgdir, tainted):
                     continue
                 line = "    %s = %s_c;" % (m.group(2), m.group(2))
             out.append(line)
-        with open(path, "w") as f:
-            f.write("\n".join(out) + "\n")
+        write_if_changed(path, "\n".join(out) + "\n")
     return n
 
 
@@ -218,11 +226,16 @@ def build_flavour(flavour):
                     x86.append((s, isa_flag(s)))
         # plain-C statements of the assembler-only 1-D filter helpers (see the file's header)
         x86.append((os.path.join(HERE, "ref_asm_fallback.c"), []))
-        pass1, _failed = compile_all(x86, os.path.join(root, "obj_pass1"), incs, [])
+        for name in ("av1_rtcd.h", "aom_dsp_rtcd.h", "aom_scale_rtcd.h"):
+            if not os.path.exists(os.path.join(cfgdir, name)):
+                rewrite_rtcd(cfgdir, set())
+        pass1, _failed = compile_all(x86, os.path.join(root, "obj_pass1"), incs, [], cfgdir)
         asm_only, tainted = asm_dependent(pass1)
         n = rewrite_rtcd(cfgdir, tainted)
         print("mk_ref[avx2]: %d assembler-only helpers; %d dependent wrappers, %d dispatch entries routed to _c"
               % (len(asm_only), len(tainted), n))
+    else:
+        rewrite_rtcd(cfgdir, set())
     srcs = []
     for d in LIB_DIRS:
         for s in sorted(glob.glob(os.path.join(REF, d, "*.c"))):
@@ -232,7 +245,7 @@ def build_flavour(flavour):
     srcs += [(os.path.join(REF, s), []) for s in LIB_EXTRA]
     srcs.append((os.path.join(cfgdir, "aom_config.c"), []))
     srcs.append((os.path.join(HERE, "ref_shim.c"), ["-DREFSHIM_DISPATCH"] if flavour == "avx2" else []))
-    objs, failed = compile_all(srcs, os.path.join(root, "obj"), incs, [])
+    objs, failed = compile_all(srcs, os.path.join(root, "obj"), incs, [], cfgdir)
     # intrinsics files that need a configuration this build leaves off simply stay out
     hard = [f for f in failed if "/x86/" not in f[0]]
     if hard:
@@ -276,7 +289,7 @@ def build_flavour(flavour):
           % (flavour, len(objs), len(syms), len(stubs), lib))
     # the encoder CLI on top of the library
     app_objs, app_failed = compile_all([(os.path.join(REF, s), []) for s in APP_SOURCES],
-                                       os.path.join(root, "obj_app"), incs, [])
+                                       os.path.join(root, "obj_app"), incs, [], cfgdir)
     if app_failed:
         for s, err in app_failed[:3]:
             sys.stderr.write("mk_ref: %s\n%s\n" % (s, err[-1500:]))

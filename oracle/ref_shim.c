@@ -7,6 +7,7 @@
  * calls the UNMODIFIED av1_full_pixel_search / av1_find_best_sub_pixel_tree, so that the
  * oracle's motion-search restatement can be pinned against the reference itself.
  */
+#include <pthread.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -343,6 +344,169 @@ void refshim_quantize_fp_qm(const int32_t *coeff, intptr_t n, const int16_t *zbi
     av1_highbd_quantize_fp_facade(coeff, n, &p, qcoeff, dqcoeff, eob, &sc, &qp);
   else
     av1_quantize_fp_facade(coeff, n, &p, qcoeff, dqcoeff, eob, &sc, &qp);
+}
+
+/* ---- temporal filter: tf_motion_search over a frame pair ---------------------------------
+ * cur / ref point at picture pixel (0,0) of planes that carry at least border_in_pixels of
+ * replicated border around them (as YV12 buffers do), same stride. */
+static void tf_fill(Av1oMeParams *P, const Av1oTfParams *tp, const void *cur, const void *ref, int stride,
+                    int highbd, int bd, int x, int y, int bw, int bh, const FullMvLimits *mb_limits,
+                    FULLPEL_MV start) {
+  const MV baseline = kZeroMv; /* temporal_filter.c:124 */
+  memset(P, 0, sizeof(*P));
+  const int px = highbd ? 2 : 1;
+  P->src = (const uint8_t *)cur + ((size_t)y * stride + x) * px;
+  P->ref = (const uint8_t *)ref + ((size_t)y * stride + x) * px;
+  P->src_stride = P->ref_stride = stride;
+  P->bw = bw, P->bh = bh, P->highbd = highbd, P->bd = bd;
+  FullMvLimits fl = *mb_limits;
+  av1_set_mv_search_range(&fl, &baseline); /* mcomp.c:150 via av1_make_default_fullpel_ms_params */
+  P->col_min = fl.col_min, P->col_max = fl.col_max, P->row_min = fl.row_min, P->row_max = fl.row_max;
+  P->search_method = tp->search_method;
+  P->step_param = tp->step_param;
+  P->run_mesh_search = 1; /* :149 */
+  P->prune_mesh_search = tp->prune_mesh_search;
+  P->mesh_search_mv_diff_threshold = tp->mesh_search_mv_diff_threshold;
+  P->force_mesh_thresh = tp->force_mesh_thresh;
+  for (int i = 0; i < 4; ++i) P->mesh_range[i] = tp->mesh_range[i], P->mesh_interval[i] = tp->mesh_interval[i];
+  P->use_skip_sad = tp->use_downsampled_sad && bh >= 16; /* mcomp.c:134-135 */
+  P->mv_cost_type = tp->mv_cost_type;
+  P->sad_per_bit = tp->sad_per_bit, P->error_per_bit = tp->error_per_bit;
+  P->start_row = start.row, P->start_col = start.col;
+  P->want_cost_list = tp->want_cost_list;
+  SubpelMvLimits sl;
+  av1_set_subpel_mv_search_range(&sl, mb_limits, &baseline); /* mcomp.c:181 */
+  P->sp_col_min = sl.col_min, P->sp_col_max = sl.col_max, P->sp_row_min = sl.row_min, P->sp_row_max = sl.row_max;
+  P->allow_hp = tp->allow_hp;
+  P->forced_stop = EIGHTH_PEL;          /* :161 */
+  P->subpel_search_type = USE_8_TAPS;   /* :113 */
+  P->iters_per_step = tp->iters_per_step;
+  P->sp_tree = tp->subpel_tree;
+}
+
+/* one full-pel + sub-pel search as tf_motion_search runs it; returns `error`, mv in *best */
+static unsigned tf_search(Av1oMeParams *P, MV *best) {
+  Av1oMeResult rf, rs;
+  fullpel_common(P, &rf, 0);
+  Av1oMeParams S = *P;
+  S.mv_cost_type = AV1O_COST_NONE; /* :166 */
+  S.sp_start_row = rf.best_row * 8, S.sp_start_col = rf.best_col * 8;
+  S.sp_have_cost_list = P->want_cost_list;
+  memcpy(S.sp_cost_list, rf.cost_list, sizeof(S.sp_cost_list));
+  subpel_common(&S, &rs, S.sp_tree);
+  best->row = (int16_t)rs.best_row, best->col = (int16_t)rs.best_col;
+  return (unsigned)rs.ret;
+}
+
+typedef struct {
+  const void *cur, *ref;
+  int stride, width, height, highbd, bd;
+  const Av1oTfParams *tp;
+  const int16_t *ref_mvs;
+  Av1oTfResult *out;
+  volatile int *next_row;
+} TfJob;
+
+/* rows of blocks are independent (av1_tf_do_filtering_row is the encoder's own unit of
+ * multi-threading, ethread.c tf_worker_hook): threads take rows dynamically */
+static void *tf_rows_worker(void *arg) {
+  const TfJob *j = (const TfJob *)arg;
+  const void *cur = j->cur, *ref = j->ref;
+  const int stride = j->stride, width = j->width, height = j->height, highbd = j->highbd, bd = j->bd;
+  const Av1oTfParams *tp = j->tp;
+  const int16_t *ref_mvs = j->ref_mvs;
+  Av1oTfResult *out = j->out;
+  CommonModeInfoParams mi;
+  memset(&mi, 0, sizeof(mi));
+  mi.mi_rows = ((height + 7) & ~7) >> MI_SIZE_LOG2; /* av1_set_mb_mi */
+  mi.mi_cols = ((width + 7) & ~7) >> MI_SIZE_LOG2;
+  const int mb_rows = (height + tp->bh - 1) / tp->bh, mb_cols = (width + tp->bw - 1) / tp->bw;
+  const int min_frame_size = AOMMIN(width, height);
+  const int mb_pels = tp->bw * tp->bh, sw = tp->bw >> 1, sh = tp->bh >> 1, sub_pels = sw * sh;
+  for (;;) {
+    const int mb_row = __sync_fetch_and_add(j->next_row, 1);
+    if (mb_row >= mb_rows) break;
+    FullMvLimits lim;
+    av1_set_mv_row_limits(&mi, &lim, mb_row * (tp->bh >> MI_SIZE_LOG2), tp->bh >> MI_SIZE_LOG2,
+                          tp->border_in_pixels); /* :846-848 */
+    for (int mb_col = 0; mb_col < mb_cols; ++mb_col) {
+      av1_set_mv_col_limits(&mi, &lim, mb_col * (tp->bw >> MI_SIZE_LOG2), tp->bw >> MI_SIZE_LOG2,
+                            tp->border_in_pixels); /* :850-852 */
+      const int bi = mb_row * mb_cols + mb_col;
+      Av1oTfResult *o = &out[bi];
+      MV ref_mv = kZeroMv;
+      if (ref_mvs) ref_mv.row = ref_mvs[2 * bi], ref_mv.col = ref_mvs[2 * bi + 1];
+      Av1oMeParams P;
+      MV block_mv;
+      tf_fill(&P, tp, cur, ref, stride, highbd, bd, mb_col * tp->bw, mb_row * tp->bh, tp->bw, tp->bh, &lim,
+              get_fullmv_from_mv(&ref_mv));
+      const unsigned error = tf_search(&P, &block_mv);
+      const int block_mse = (int)DIVIDE_AND_ROUND(error, mb_pels); /* :172 */
+      ref_mv = block_mv;
+      MV sub_mv[4];
+      int sub_mse[4];
+      for (int k = 0; k < 4; ++k) {
+        tf_fill(&P, tp, cur, ref, stride, highbd, bd, mb_col * tp->bw + (k & 1) * sw, mb_row * tp->bh + (k >> 1) * sh,
+                sw, sh, &lim, get_fullmv_from_mv(&ref_mv)); /* :198 */
+        const unsigned e = tf_search(&P, &sub_mv[k]);
+        sub_mse[k] = (int)DIVIDE_AND_ROUND(e, sub_pels);
+      }
+      /* tf_determine_block_partition (:275-297, static) */
+      int mn = INT_MAX, mx = INT_MIN;
+      int64_t sum = 0;
+      for (int k = 0; k < 4; ++k) {
+        sum += sub_mse[k];
+        mn = AOMMIN(mn, sub_mse[k]);
+        mx = AOMMAX(mx, sub_mse[k]);
+      }
+      if (((block_mse * 15 < sum * 4) && mx - mn < 48) || ((block_mse * 14 < sum * 4) && mx - mn < 24))
+        for (int k = 0; k < 4; ++k) sub_mv[k] = block_mv, sub_mse[k] = block_mse;
+      const int thresh = (min_frame_size >= 720) ? 12 : 3; /* :255-259 */
+      if (block_mse > (thresh << (bd - 8))) ref_mv = kZeroMv;
+      o->block_mv[0] = block_mv.row, o->block_mv[1] = block_mv.col;
+      o->block_mse = block_mse;
+      for (int k = 0; k < 4; ++k) o->sub_mv[k][0] = sub_mv[k].row, o->sub_mv[k][1] = sub_mv[k].col, o->sub_mse[k] = sub_mse[k];
+      o->ref_mv[0] = ref_mv.row, o->ref_mv[1] = ref_mv.col;
+    }
+  }
+  return NULL;
+}
+
+void refshim_tf_motion_search_frame_mt(const void *cur, const void *ref, int stride, int width, int height,
+                                       int highbd, int bd, const Av1oTfParams *tp, const int16_t *ref_mvs,
+                                       Av1oTfResult *out, int n_threads) {
+  volatile int next_row = 0;
+  TfJob job = { cur, ref, stride, width, height, highbd, bd, tp, ref_mvs, out, &next_row };
+  if (n_threads < 1) n_threads = 1;
+  if (n_threads > 256) n_threads = 256;
+  pthread_t th[256];
+  for (int t = 1; t < n_threads; ++t) pthread_create(&th[t], NULL, tf_rows_worker, &job);
+  tf_rows_worker(&job);
+  for (int t = 1; t < n_threads; ++t) pthread_join(th[t], NULL);
+}
+
+void refshim_tf_motion_search_frame(const void *cur, const void *ref, int stride, int width, int height,
+                                    int highbd, int bd, const Av1oTfParams *tp, const int16_t *ref_mvs,
+                                    Av1oTfResult *out) {
+  refshim_tf_motion_search_frame_mt(cur, ref, stride, width, height, highbd, bd, tp, ref_mvs, out, 1);
+}
+
+/* the limits tf_motion_search hands to its searches for block (mb_row, mb_col):
+ * out = full-pel {col_min, col_max, row_min, row_max}, then the sub-pel four */
+void refshim_tf_limits(int width, int height, int bw, int bh, int border, int mb_row, int mb_col, int *out) {
+  CommonModeInfoParams mi;
+  memset(&mi, 0, sizeof(mi));
+  mi.mi_rows = ((height + 7) & ~7) >> MI_SIZE_LOG2;
+  mi.mi_cols = ((width + 7) & ~7) >> MI_SIZE_LOG2;
+  FullMvLimits lim;
+  av1_set_mv_limits(&mi, &lim, mb_row * (bh >> MI_SIZE_LOG2), mb_col * (bw >> MI_SIZE_LOG2), bh >> MI_SIZE_LOG2,
+                    bw >> MI_SIZE_LOG2, border);
+  const MV zero = kZeroMv;
+  SubpelMvLimits sl;
+  av1_set_subpel_mv_search_range(&sl, &lim, &zero);
+  av1_set_mv_search_range(&lim, &zero);
+  out[0] = lim.col_min, out[1] = lim.col_max, out[2] = lim.row_min, out[3] = lim.row_max;
+  out[4] = sl.col_min, out[5] = sl.col_max, out[6] = sl.row_min, out[7] = sl.row_max;
 }
 
 /* ---- function pointers for the timed CPU baseline (oracle/av1o_drv.c) -------------------------
