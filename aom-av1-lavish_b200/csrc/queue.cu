@@ -7,6 +7,7 @@
 //                                 (av1/encoder/temporal_filter.c:88-260, loop :804-872)
 //   b200_queue_tpl_*              TPL motion_estimation + txfm_quant_rdcost
 //                                 (av1/encoder/tpl_model.c:228-304)
+#include <limits.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -345,6 +346,207 @@ extern "C" int b200_queue_tf_motion_search(b200_ctx *ctx, const b200_frame *cur,
     const int thresh = (min_dim >= 720 ? 12 : 3) << (cur->bd - 8);
     o.ref_mv[0] = block_mse > thresh ? 0 : o.block_mv[0];
     o.ref_mv[1] = block_mse > thresh ? 0 : o.block_mv[1];
+  }
+  return B200_OK;
+}
+
+// ---------------------------------------------------------------------------- TPL ----
+extern "C" void b200_queue_tpl_default_params(int width, int height, B200TplParams *p) {
+  memset(p, 0, sizeof(*p));
+  const int min_dim = width < height ? width : height;
+  p->bw = p->bh = 16;                   // tpl_data->tpl_bsize_1d = 16 (tpl_model.c:158)
+  p->border_in_pixels = 160;
+  p->search_method = B200_ME_NSTEP;     // tpl_sf.search_method (speed_features.c init_tpl_sf)
+  p->step_param = 0;                    // tpl_sf.reduce_first_step_size = 0
+  p->forced_stop = B200_EIGHTH_PEL;     // tpl_sf.subpel_force_stop
+  p->mv_cost_type = B200_MV_COST_ENTROPY;
+  const int range[4] = { 64, 28, 15, 7 }, interval[4] = { 8, 4, 1, 1 };
+  for (int i = 0; i < 4; ++i) p->mesh_range[i] = range[i], p->mesh_interval[i] = interval[i];
+  p->force_mesh_thresh = min_dim >= 720 ? 1 << 25 : 1 << 20;
+  p->sad_per_bit = 16, p->error_per_bit = 10;
+  p->iters_per_step = 2;
+  p->subpel_tree = B200_SUBPEL_TREE;
+  p->want_cost_list = 0;                // cond_cost_list(cpi, cost_list): sf.mv_sf.use_fullpel_costlist (:283-289)
+}
+
+static int tpl_grid(int width, int height, const B200TplParams *p, int *rows, int *cols) {
+  if (!p || p->bw < 4 || p->bh < 4 || (p->bw & (p->bw - 1)) || (p->bh & (p->bh - 1)) || p->bw > 128 || p->bh > 128)
+    return B200_EINVAL;
+  const int mi_rows = ((height + 7) & ~7) >> 2, mi_cols = ((width + 7) & ~7) >> 2;
+  *rows = (mi_rows * 4 + p->bh - 1) / p->bh;  // for (mi_row = 0; mi_row < mi_rows; mi_row += mi_height) (:1376)
+  *cols = (mi_cols * 4 + p->bw - 1) / p->bw;
+  return B200_OK;
+}
+
+extern "C" int b200_queue_tpl_describe(int width, int height, int pitch, int origin, const B200TplParams *p,
+                                       const int16_t *center_mvs, B200MeBlock *full, B200MeBlock *sub) {
+  int rows, cols;
+  if (tpl_grid(width, height, p, &rows, &cols) != B200_OK || !full || !sub) return -1;
+  const int mi_rows = ((height + 7) & ~7) >> 2, mi_cols = ((width + 7) & ~7) >> 2;
+  int n = 0;
+  for (int r = 0; r < rows; ++r)
+    for (int c = 0; c < cols; ++c, ++n) {
+      const int mv_row = center_mvs ? center_mvs[2 * n] : 0, mv_col = center_mvs ? center_mvs[2 * n + 1] : 0;
+      const Limits lim = block_limits(mi_rows, mi_cols, r * (p->bh >> 2), c * (p->bw >> 2), p->bh >> 2, p->bw >> 2,
+                                      p->border_in_pixels);
+      B200MeBlock d;
+      memset(&d, 0, sizeof(d));
+      d.src_offset = d.ref_offset = (uint32_t)(origin + r * p->bh * pitch + c * p->bw);
+      d.bw = (uint8_t)p->bw, d.bh = (uint8_t)p->bh;
+      d.sad_per_bit = p->sad_per_bit, d.error_per_bit = p->error_per_bit;
+      d.force_mesh_thresh = p->force_mesh_thresh;
+      d.mesh_mv_diff_threshold = 4;
+      d.ref_mv_row = (int16_t)mv_row, d.ref_mv_col = (int16_t)mv_col;  // ref_mv = center_mv (:278)
+      B200MeBlock f = d;
+      put_limits(&f, fullpel_range(lim, mv_row, mv_col));
+      f.start_row = (int16_t)rawpel(mv_row), f.start_col = (int16_t)rawpel(mv_col);  // :259
+      f.search_method = (uint8_t)p->search_method;
+      f.step_param = (uint8_t)p->step_param;
+      f.mv_cost_type = (uint8_t)p->mv_cost_type;
+      f.flags = (p->prune_mesh_search ? B200_ME_PRUNE_MESH : 0) |
+                (p->use_downsampled_sad && p->bh >= 16 ? B200_ME_SKIP_SAD : 0) |
+                (p->want_cost_list ? B200_ME_COST_LIST : 0);
+      full[n] = f;
+      B200MeBlock s = d;
+      put_limits(&s, subpel_range(lim, mv_row, mv_col));
+      s.search_method = (uint8_t)p->subpel_tree;
+      s.mv_cost_type = B200_MV_COST_NONE;  // :294
+      s.flags = (p->allow_hp ? B200_ME_ALLOW_HP : 0) | (p->want_cost_list ? B200_ME_COST_LIST : 0);
+      s.subpel = (uint8_t)(p->forced_stop | (p->iters_per_step << 2) | (B200_USE_2_TAPS << 4));  // :292-293
+      sub[n] = s;
+    }
+  return n;
+}
+
+extern "C" int b200_queue_tpl_motion_estimation(b200_ctx *ctx, const b200_frame *cur, const b200_frame *ref,
+                                                const B200TplParams *p, const int16_t *center_mvs,
+                                                B200TplMeResult *out) {
+  if (!ctx || !cur || !ref || !p || !out) return B200_EINVAL;
+  if (cur->width != ref->width || cur->height != ref->height || cur->pitch != ref->pitch ||
+      cur->border != ref->border || cur->bd != ref->bd) {
+    set_error("b200_queue_tpl_motion_estimation: the two frames differ in geometry");
+    return B200_EINVAL;
+  }
+  int rows, cols;
+  if (tpl_grid(cur->width, cur->height, p, &rows, &cols) != B200_OK) return B200_EINVAL;
+  if (cur->border < p->border_in_pixels || cur->border < p->bw) {
+    set_error("b200_queue_tpl_motion_estimation: frame border %d smaller than border_in_pixels %d", cur->border,
+              p->border_in_pixels);
+    return B200_EINVAL;
+  }
+  B200_CUDA_TRY(cudaSetDevice(ctx->device));
+  const int n = rows * cols;
+  std::vector<B200MeBlock> desc((size_t)2 * n);
+  if (b200_queue_tpl_describe(cur->width, cur->height, cur->pitch, cur->origin, p, center_mvs, desc.data(),
+                              desc.data() + n) != n)
+    return B200_EINVAL;
+  const bool costs = p->mvjcost && p->mvcost[0] && p->mvcost[1];
+  const size_t tab = (size_t)(2 * 16383 + 1) * sizeof(int);
+  size_t off = 0;
+  auto carve = [&](size_t bytes) {
+    const size_t o = off;
+    off += (bytes + 255) & ~(size_t)255;
+    return o;
+  };
+  const size_t o_desc = carve(desc.size() * sizeof(B200MeBlock)), o_res = carve((size_t)2 * n * sizeof(B200MeResult));
+  const size_t o_j = carve(costs ? 16 : 0), o_c0 = carve(costs ? tab : 0), o_c1 = carve(costs ? tab : 0);
+  int rc = scratch_reserve(ctx, off);
+  if (rc != B200_OK) return rc;
+  char *base = (char *)ctx->d_scratch;
+  cudaStream_t s = ctx->stream;
+  B200_CUDA_TRY(cudaMemcpyAsync(base + o_desc, desc.data(), desc.size() * sizeof(B200MeBlock), cudaMemcpyHostToDevice, s));
+  B200MeLaunch l;
+  memset(&l, 0, sizeof(l));
+  if (costs) {
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_j, p->mvjcost, 16, cudaMemcpyHostToDevice, s));
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_c0, p->mvcost[0] - 16383, tab, cudaMemcpyHostToDevice, s));
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_c1, p->mvcost[1] - 16383, tab, cudaMemcpyHostToDevice, s));
+    l.mvjcost = (const int *)(base + o_j);
+    l.mvcost[0] = (const int *)(base + o_c0) + 16383;
+    l.mvcost[1] = (const int *)(base + o_c1) + 16383;
+  }
+  l.highbd = cur->bd > 8, l.bd = cur->bd;
+  l.cur = cur->d_plane, l.ref = ref->d_plane;
+  l.cur_stride = l.ref_stride = cur->pitch;
+  l.cur_rows = l.ref_rows = cur->rows;
+  for (int i = 0; i < 4; ++i) l.mesh_range[i] = p->mesh_range[i], l.mesh_interval[i] = p->mesh_interval[i];
+  l.families = p->search_method <= B200_ME_CLAMPED_DIAMOND ? B200_ME_FAMILY_NSTEP : B200_ME_FAMILY_PATTERN;
+  l.n_blocks = n;
+  l.max_bw = p->bw, l.max_bh = p->bh;
+  l.blocks = (const B200MeBlock *)(base + o_desc);
+  l.results = (B200MeResult *)(base + o_res);
+  rc = b200_me_fullpel_launch(ctx, &l, s);
+  if (rc != B200_OK) return rc;
+  B200MeLaunch sl = l;
+  sl.blocks = l.blocks + n;
+  sl.results = l.results + n;
+  sl.start_from = l.results;  // subpel_start_mv = get_mv_from_fullmv(&best_mv->as_fullmv) (:295)
+  sl.cost_lists = p->want_cost_list ? &l.results->cost_list[0] : nullptr;
+  sl.cost_list_stride = sizeof(B200MeResult) / sizeof(int32_t);
+  rc = b200_me_subpel_launch(ctx, &sl, s);
+  if (rc != B200_OK) return rc;
+  std::vector<B200MeResult> res((size_t)n);
+  B200_CUDA_TRY(cudaMemcpyAsync(res.data(), sl.results, (size_t)n * sizeof(B200MeResult), cudaMemcpyDeviceToHost, s));
+  B200_CUDA_TRY(cudaStreamSynchronize(s));
+  for (int i = 0; i < n; ++i) {
+    out[i].mv[0] = res[i].best_row, out[i].mv[1] = res[i].best_col;
+    out[i].sme = (uint32_t)res[i].ret;
+  }
+  return B200_OK;
+}
+
+extern "C" int b200_queue_tpl_txfm_quant_rdcost(b200_ctx *ctx, const void *src, int src_stride, const void *pred,
+                                                int pred_stride, int rows, int cols, int bd, int tx_size,
+                                                const B200QRow *qrow, B200TplRdResult *out) {
+  if (!ctx || !src || !pred || !qrow || !out || rows <= 0 || cols <= 0) return B200_EINVAL;
+  if (tx_size < B200_TX_4X4 || tx_size > B200_TX_32X32 || (bd != 8 && bd != 10 && bd != 12)) {
+    set_error("b200_queue_tpl_txfm_quant_rdcost: square tx sizes 4x4..32x32 and bd 8/10/12 only");
+    return B200_EINVAL;
+  }
+  const int w = tx_info(tx_size).w, n = rows * cols, per = w * w;
+  if (src_stride < cols * w || pred_stride < cols * w || src_stride > 65535 || pred_stride > 65535) return B200_EINVAL;
+  std::vector<B200TxBlock> blocks((size_t)n);
+  std::vector<B200TxPred> preds((size_t)n);
+  for (int r = 0; r < rows; ++r)
+    for (int c = 0; c < cols; ++c) {
+      const int i = r * cols + c;
+      memset(&blocks[i], 0, sizeof(B200TxBlock));
+      memset(&preds[i], 0, sizeof(B200TxPred));
+      blocks[i].src_offset = (uint32_t)(r * w * src_stride + c * w);
+      blocks[i].out_offset = (uint32_t)i * per;
+      blocks[i].src_stride = (uint16_t)src_stride;
+      blocks[i].tx_size = (uint8_t)tx_size;
+      blocks[i].tx_type = 0;  // DCT_DCT: av1_quick_txfm (hybrid_fwd_txfm.c), scan_order of DCT_DCT (:103)
+      preds[i].pred_offset = (uint32_t)(r * w * pred_stride + c * w);
+      preds[i].pred_stride = (uint16_t)pred_stride;
+    }
+  const bool hbd = bd > 8;
+  const size_t out_elems = (size_t)n * per;
+  std::vector<unsigned char> levels(out_elems * (hbd ? 4 : 2));
+  std::vector<uint32_t> offs((size_t)n + 1);
+  std::vector<uint16_t> eob((size_t)n);
+  std::vector<int64_t> dist((size_t)2 * n);
+  const int rc = b200_txq_batch_host_compact(
+      ctx, hbd ? B200_IN_PIXELS16 : B200_IN_PIXELS8, hbd ? B200_Q_FP_HBD : B200_Q_FP, bd, B200_TXQ_BLOCK_ERROR,
+      blocks.data(), preds.data(), n, src, (size_t)src_stride * rows * w, pred, (size_t)pred_stride * rows * w, qrow, 1,
+      out_elems, levels.data(), out_elems, offs.data(), eob.data(), dist.data(), nullptr, nullptr);
+  if (rc != B200_OK) return rc;
+  const int shift = tx_size == B200_TX_32X32 ? 0 : 2;  // get_quantize_error (:107)
+  for (int i = 0; i < n; ++i) {
+    // rate_estimator (:207-226): the levels are already in scan order
+    int rate = 1;
+    for (int k = 0; k < eob[i]; ++k) {
+      const int q = hbd ? ((const int32_t *)levels.data())[offs[i] + k] : ((const int16_t *)levels.data())[offs[i] + k];
+      const unsigned a = (unsigned)(q < 0 ? -q : q);
+      int msb = 0;
+      for (unsigned v = a + 1; v >>= 1;) ++msb;  // get_msb(abs_level + 1)
+      rate += msb + 1 + (a > 0);
+    }
+    out[i].rate_cost = rate << 9;  // AV1_PROB_COST_SHIFT
+    out[i].eob = eob[i];
+    const int64_t err = dist[2 * i] >> shift, sse = dist[2 * i + 1] >> shift;
+    out[i].recon_error = err > 1 ? err : 1;
+    out[i].sse = sse > 1 ? sse : 1;
   }
   return B200_OK;
 }

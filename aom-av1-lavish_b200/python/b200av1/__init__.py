@@ -346,3 +346,49 @@ def queue_tf_motion_search(ctx, cur, ref, params, ref_mvs=None):
     check(lib().b200_queue_tf_motion_search(ctx.h, cur.h, ref.h, C.byref(params), vp(mv) if mv is not None else None,
                                             vp(out)))
     return out.reshape(rows, cols)
+
+
+class TplParams(C.Structure):
+    """B200TplParams (include/b200av1.h): TPL motion_estimation's parameter set-up."""
+    _fields_ = [("bw", C.c_int), ("bh", C.c_int), ("border_in_pixels", C.c_int), ("search_method", C.c_int),
+                ("step_param", C.c_int), ("forced_stop", C.c_int), ("mv_cost_type", C.c_int),
+                ("mesh_range", C.c_int * 4), ("mesh_interval", C.c_int * 4), ("force_mesh_thresh", C.c_int),
+                ("prune_mesh_search", C.c_int), ("use_downsampled_sad", C.c_int), ("sad_per_bit", C.c_int),
+                ("error_per_bit", C.c_int), ("allow_hp", C.c_int), ("iters_per_step", C.c_int),
+                ("subpel_tree", C.c_int), ("want_cost_list", C.c_int), ("mvjcost", C.c_void_p),
+                ("mvcost", C.c_void_p * 2)]
+
+
+TPL_ME_DTYPE = np.dtype([("mv", "<i2", (2,)), ("sme", "<u4")])
+TPL_RD_DTYPE = np.dtype([("rate_cost", "<i4"), ("eob", "<i4"), ("recon_error", "<i8"), ("sse", "<i8")])
+assert TPL_ME_DTYPE.itemsize == 8 and TPL_RD_DTYPE.itemsize == 24
+
+
+def tpl_default_params(width, height):
+    p = TplParams()
+    lib().b200_queue_tpl_default_params(width, height, C.byref(p))
+    return p
+
+
+def tpl_grid(width, height, params):
+    mi_rows, mi_cols = ((height + 7) & ~7) >> 2, ((width + 7) & ~7) >> 2
+    return (mi_rows * 4 + params.bh - 1) // params.bh, (mi_cols * 4 + params.bw - 1) // params.bw
+
+
+def queue_tpl_motion_estimation(ctx, cur, ref, params, center_mvs=None):
+    rows, cols = tpl_grid(cur.width, cur.height, params)
+    out = np.zeros(rows * cols, TPL_ME_DTYPE)
+    mv = None if center_mvs is None else np.ascontiguousarray(center_mvs, np.int16)
+    check(lib().b200_queue_tpl_motion_estimation(ctx.h, cur.h, ref.h, C.byref(params),
+                                                 vp(mv) if mv is not None else None, vp(out)))
+    return out.reshape(rows, cols)
+
+
+def queue_tpl_txfm_quant_rdcost(ctx, src, pred, rows, cols, bd, tx_size, qrow):
+    """src / pred: 2-D host planes (uint8 or uint16); qrow: one QROW_DTYPE record."""
+    src, pred = np.ascontiguousarray(src), np.ascontiguousarray(pred)
+    out = np.zeros(rows * cols, TPL_RD_DTYPE)
+    q = np.ascontiguousarray(qrow)
+    check(lib().b200_queue_tpl_txfm_quant_rdcost(ctx.h, vp(src), src.shape[1], vp(pred), pred.shape[1], rows, cols,
+                                                 bd, tx_size, vp(q), vp(out)))
+    return out.reshape(rows, cols)

@@ -557,6 +557,52 @@ int b200_queue_tf_motion_search(b200_ctx *ctx, const b200_frame *to_filter, cons
 int b200_queue_tf_describe(int width, int height, int frame_pitch, int frame_origin, const B200TfParams *params,
                            const int16_t *ref_mvs, int stage, B200MeBlock *full, B200MeBlock *sub);
 
+/* TPL model (av1/encoder/tpl_model.c): motion_estimation (:249-304) for every block of a frame
+ * against one reference, each from a caller-supplied centre mv (mode_estimation takes them from the
+ * neighbouring blocks' results, :640-690 -- a caller runs one call per candidate / wavefront), and
+ * txfm_quant_rdcost (:228-247) up to its rate / distortion outputs for every block of a frame. */
+typedef struct {
+  int bw, bh;                 /* tpl block size (tpl_data->tpl_bsize_1d): 16x16 */
+  int border_in_pixels;       /* tpl_data->border_in_pixels (:1353, :1381) */
+  int search_method;          /* tpl_sf.search_method */
+  int step_param;             /* min(tpl_sf.reduce_first_step_size, MAX_MVSEARCH_STEPS - 2) (:267-268) */
+  int forced_stop;            /* tpl_sf.subpel_force_stop (B200_EIGHTH_PEL ..) */
+  int mv_cost_type;           /* B200_MV_COST_ENTROPY is what init_mv_cost_params leaves (mcomp.c:42) */
+  int mesh_range[4], mesh_interval[4];
+  int force_mesh_thresh;      /* sf.mv_sf.exhaustive_searches_thresh (NSTEP may escalate to the mesh) */
+  int prune_mesh_search;
+  int use_downsampled_sad;
+  int sad_per_bit, error_per_bit;
+  int allow_hp, iters_per_step, subpel_tree, want_cost_list;
+  const int *mvjcost;         /* host, 4 entries, or NULL (then mv cost terms are 0) */
+  const int *mvcost[2];       /* host, centred: index -MV_MAX..MV_MAX */
+} B200TplParams;
+typedef struct {
+  int16_t mv[2];   /* row, col, 1/8 pel: best_mv->as_mv */
+  uint32_t sme;    /* motion_estimation's return value (bestsme) */
+} B200TplMeResult; /* 8 bytes */
+void b200_queue_tpl_default_params(int width, int height, B200TplParams *params);
+/* out: ceil(mi_rows * 4 / bh) * ceil(mi_cols * 4 / bw) results, raster order */
+int b200_queue_tpl_motion_estimation(b200_ctx *ctx, const b200_frame *cur, const b200_frame *ref,
+                                     const B200TplParams *params, const int16_t *center_mvs,
+                                     B200TplMeResult *out);
+int b200_queue_tpl_describe(int width, int height, int frame_pitch, int frame_origin, const B200TplParams *params,
+                            const int16_t *center_mvs, B200MeBlock *full, B200MeBlock *sub);
+typedef struct {
+  int32_t rate_cost;   /* rate_estimator(qcoeff, eob, tx_size) (:207-226) */
+  int32_t eob;
+  int64_t recon_error; /* max(av1_block_error(coeff, dqcoeff) >> shift, 1) (:97-135) */
+  int64_t sse;         /* max(ssz >> shift, 1) */
+} B200TplRdResult; /* 24 bytes */
+/* src / pred: HOST planes of uint8 (bd 8) or uint16 samples holding rows x cols blocks of the square
+ * tx_size (B200_TX_4X4 .. B200_TX_32X32) from their first sample; qrow: the plane-0 quantiser row of
+ * the frame's qindex.  Subtract, DCT_DCT, av1_quantize_fp / av1_highbd_quantize_fp and the block
+ * error run fused on the device; the levels come back in the compact form and the rate is
+ * accumulated from them on the host. */
+int b200_queue_tpl_txfm_quant_rdcost(b200_ctx *ctx, const void *src, int src_stride, const void *pred,
+                                     int pred_stride, int rows, int cols, int bd, int tx_size,
+                                     const B200QRow *qrow, B200TplRdResult *out);
+
 /* Measured rate of the integer pipe on this device: VABSDIFF4 with accumulate (the SAD
  * instruction) issued back to back from every SM, in G pixel-absdiffs per second.  The
  * denominator of the motion search's int-ALU roofline. */

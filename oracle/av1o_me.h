@@ -109,6 +109,25 @@ typedef struct {
   int16_t ref_mv[2];
 } Av1oTfResult;
 
+/* ---- TPL: motion_estimation / txfm_quant_rdcost over a frame (tests/test_queue_tpl_gpu.py) ----
+ * Layouts of B200TplParams / B200TplMeResult / B200TplRdResult (include/b200av1.h). */
+typedef struct {
+  int bw, bh, border_in_pixels, search_method, step_param, forced_stop, mv_cost_type;
+  int mesh_range[4], mesh_interval[4];
+  int force_mesh_thresh, prune_mesh_search, use_downsampled_sad;
+  int sad_per_bit, error_per_bit, allow_hp, iters_per_step, subpel_tree, want_cost_list;
+  const int *mvjcost;
+  const int *mvcost[2];
+} Av1oTplParams;
+typedef struct {
+  int16_t mv[2];
+  uint32_t sme;
+} Av1oTplMeResult;
+typedef struct {
+  int32_t rate_cost, eob;
+  int64_t recon_error, sse;
+} Av1oTplRdResult;
+
 #ifdef __cplusplus
 }
 #endif

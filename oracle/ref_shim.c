@@ -509,6 +509,127 @@ void refshim_tf_limits(int width, int height, int bw, int bh, int border, int mb
   out[4] = sl.col_min, out[5] = sl.col_max, out[6] = sl.row_min, out[7] = sl.row_max;
 }
 
+/* ---- TPL: motion_estimation (tpl_model.c:249-304) for every block of a frame, each from its
+ * centre mv, with the reference's own limit helpers and searches ------------------------- */
+void refshim_tpl_motion_estimation_frame(const void *cur, const void *ref, int stride, int width, int height,
+                                         int highbd, int bd, const Av1oTplParams *tp, const int16_t *center_mvs,
+                                         Av1oTplMeResult *out) {
+  CommonModeInfoParams mi;
+  memset(&mi, 0, sizeof(mi));
+  mi.mi_rows = ((height + 7) & ~7) >> MI_SIZE_LOG2;
+  mi.mi_cols = ((width + 7) & ~7) >> MI_SIZE_LOG2;
+  const int mi_h = tp->bh >> MI_SIZE_LOG2, mi_w = tp->bw >> MI_SIZE_LOG2;
+  const int px = highbd ? 2 : 1;
+  int n = 0;
+  for (int mi_row = 0; mi_row < mi.mi_rows; mi_row += mi_h)      /* :1376 */
+    for (int mi_col = 0; mi_col < mi.mi_cols; mi_col += mi_w, ++n) { /* :1349 */
+      FullMvLimits lim;
+      av1_set_mv_limits(&mi, &lim, mi_row, mi_col, mi_h, mi_w, tp->border_in_pixels); /* :1353, :1381 */
+      MV center = kZeroMv;
+      if (center_mvs) center.row = center_mvs[2 * n], center.col = center_mvs[2 * n + 1];
+      Av1oMeParams P;
+      memset(&P, 0, sizeof(P));
+      const size_t off = ((size_t)mi_row * MI_SIZE * stride + (size_t)mi_col * MI_SIZE) * px;
+      P.src = (const uint8_t *)cur + off, P.ref = (const uint8_t *)ref + off;
+      P.src_stride = P.ref_stride = stride;
+      P.bw = tp->bw, P.bh = tp->bh, P.highbd = highbd, P.bd = bd;
+      FullMvLimits fl = lim;
+      av1_set_mv_search_range(&fl, &center); /* av1_make_default_fullpel_ms_params, mcomp.c:150 */
+      P.col_min = fl.col_min, P.col_max = fl.col_max, P.row_min = fl.row_min, P.row_max = fl.row_max;
+      P.search_method = tp->search_method;
+      P.step_param = tp->step_param;
+      P.prune_mesh_search = tp->prune_mesh_search;
+      P.mesh_search_mv_diff_threshold = 4;
+      P.force_mesh_thresh = tp->force_mesh_thresh;
+      for (int i = 0; i < 4; ++i) P.mesh_range[i] = tp->mesh_range[i], P.mesh_interval[i] = tp->mesh_interval[i];
+      P.use_skip_sad = tp->use_downsampled_sad && tp->bh >= 16;
+      P.mv_cost_type = tp->mv_cost_type;
+      P.ref_mv_row = center.row, P.ref_mv_col = center.col;
+      P.sad_per_bit = tp->sad_per_bit, P.error_per_bit = tp->error_per_bit;
+      P.mvjcost = tp->mvjcost, P.mvcost0 = tp->mvcost[0], P.mvcost1 = tp->mvcost[1];
+      const FULLPEL_MV start = get_fullmv_from_mv(&center); /* :259 */
+      P.start_row = start.row, P.start_col = start.col;
+      P.want_cost_list = tp->want_cost_list;
+      Av1oMeResult rf, rs;
+      fullpel_common(&P, &rf, 0);
+      SubpelMvLimits sl;
+      av1_set_subpel_mv_search_range(&sl, &lim, &center);
+      P.sp_col_min = sl.col_min, P.sp_col_max = sl.col_max, P.sp_row_min = sl.row_min, P.sp_row_max = sl.row_max;
+      P.allow_hp = tp->allow_hp;
+      P.forced_stop = tp->forced_stop;       /* :292 */
+      P.subpel_search_type = USE_2_TAPS;     /* :293 */
+      P.iters_per_step = tp->iters_per_step;
+      P.mv_cost_type = AV1O_COST_NONE;       /* :294 */
+      P.sp_start_row = rf.best_row * 8, P.sp_start_col = rf.best_col * 8;
+      P.sp_tree = tp->subpel_tree;
+      P.sp_have_cost_list = tp->want_cost_list;
+      memcpy(P.sp_cost_list, rf.cost_list, sizeof(P.sp_cost_list));
+      subpel_common(&P, &rs, P.sp_tree);
+      out[n].mv[0] = (int16_t)rs.best_row, out[n].mv[1] = (int16_t)rs.best_col;
+      out[n].sme = (uint32_t)rs.ret;
+    }
+}
+
+/* txfm_quant_rdcost (tpl_model.c:228-247) up to its outputs, for rows x cols blocks of a plane pair:
+ * av1_subtract_block, av1_quick_txfm, get_quantize_error's av1_(highbd_)quantize_fp_facade +
+ * av1_(highbd_)block_error -- all the reference's own -- and rate_estimator (:207-226, static) */
+#include "av1/encoder/encodemb.h"
+#include "av1/encoder/rdopt.h"
+void refshim_tpl_txfm_quant_rdcost(const void *src, int src_stride, const void *pred, int pred_stride, int rows,
+                                   int cols, int bd, int tx_size, const int16_t *qrow /* 7 x 8 int16, B200QRow */,
+                                   Av1oTplRdResult *out) {
+  const int highbd = bd > 8, w = tx_size_wide[tx_size];
+  const int pix_num = 1 << num_pels_log2_lookup[txsize_to_bsize[tx_size]];
+  BitDepthInfo bd_info;
+  bd_info.bit_depth = bd, bd_info.use_highbitdepth_buf = highbd;
+  int16_t *src_diff = (int16_t *)aom_memalign(32, sizeof(int16_t) * pix_num);
+  tran_low_t *coeff = (tran_low_t *)aom_memalign(32, sizeof(tran_low_t) * pix_num * 3);
+  tran_low_t *qcoeff = coeff + pix_num, *dqcoeff = qcoeff + pix_num;
+  /* B200QRow: zbin, round, quant, quant_shift, round_fp, quant_fp, dequant (DC, AC entry each) -> the
+   * 8-wide rows the quantisers read: [0] = DC, [1..7] = AC */
+  int16_t tab[7][8] __attribute__((aligned(16)));
+  for (int f = 0; f < 7; ++f)
+    for (int k = 0; k < 8; ++k) tab[f][k] = qrow[2 * f + (k != 0)];
+  MACROBLOCK_PLANE p;
+  memset(&p, 0, sizeof(p));
+  p.zbin_QTX = tab[0], p.round_QTX = tab[1], p.quant_QTX = tab[2], p.quant_shift_QTX = tab[3];
+  p.round_fp_QTX = tab[4], p.quant_fp_QTX = tab[5], p.dequant_QTX = tab[6];
+  const SCAN_ORDER *const scan_order = &av1_scan_orders[tx_size][DCT_DCT];
+  const int shift = tx_size == TX_32X32 ? 0 : 2;
+  for (int r = 0; r < rows; ++r)
+    for (int c = 0; c < cols; ++c) {
+      Av1oTplRdResult *o = &out[r * cols + c];
+      const size_t so = (size_t)r * w * src_stride + (size_t)c * w, po = (size_t)r * w * pred_stride + (size_t)c * w;
+      uint8_t *s8 = highbd ? CONVERT_TO_BYTEPTR((uint16_t *)src + so) : (uint8_t *)src + so;
+      uint8_t *p8 = highbd ? CONVERT_TO_BYTEPTR((uint16_t *)pred + po) : (uint8_t *)pred + po;
+      av1_subtract_block(bd_info, w, w, src_diff, w, s8, src_stride, p8, pred_stride);
+      av1_quick_txfm(0, (TX_SIZE)tx_size, bd_info, src_diff, w, coeff);
+      QUANT_PARAM qp;
+      av1_setup_quant((TX_SIZE)tx_size, 0, AV1_XFORM_QUANT_FP, 0, &qp);
+      uint16_t eob;
+      int64_t sse, err;
+      if (highbd) {
+        av1_highbd_quantize_fp_facade(coeff, pix_num, &p, qcoeff, dqcoeff, &eob, scan_order, &qp);
+        err = av1_highbd_block_error(coeff, dqcoeff, pix_num, &sse, bd) >> shift;
+      } else {
+        av1_quantize_fp_facade(coeff, pix_num, &p, qcoeff, dqcoeff, &eob, scan_order, &qp);
+        err = av1_block_error(coeff, dqcoeff, pix_num, &sse) >> shift;
+      }
+      o->recon_error = AOMMAX(err, 1);
+      sse >>= shift;
+      o->sse = AOMMAX(sse, 1);
+      int rate_cost = 1;
+      for (int idx = 0; idx < eob; ++idx) {
+        const unsigned abs_level = abs(qcoeff[scan_order->scan[idx]]);
+        rate_cost += get_msb(abs_level + 1) + 1 + (abs_level > 0);
+      }
+      o->rate_cost = rate_cost << AV1_PROB_COST_SHIFT;
+      o->eob = eob;
+    }
+  aom_free(src_diff);
+  aom_free(coeff);
+}
+
 /* ---- function pointers for the timed CPU baseline (oracle/av1o_drv.c) -------------------------
  * The transform as the encoder reaches it: av1_fwd_txfm (hybrid_fwd_txfm.c:231) ->
  * av1_lowbd_fwd_txfm / av1_highbd_fwd_txfm, i.e. the SIMD flavours in the avx2 build. */
