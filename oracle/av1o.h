@@ -53,6 +53,21 @@ void av1o_fwd_txfm2d(const int16_t *input, int32_t *output, int stride, int tx_s
 void av1o_fwht4x4(const int16_t *input, int32_t *output, int stride);
 void av1o_round_shift_array(int32_t *arr, int size, int bit);
 
+/* ---- inverse transforms, reconstruction, pixel-domain distortion (av1o_itxfm.c) -------- */
+/* 1-D inverse kernels (av1_inv_txfm1d.c): kind 0=DCT 1=ADST 2=IDENTITY, range_bits = stage range */
+void av1o_inv_txfm1d(int kind, int n, const int32_t *in, int32_t *out, int range_bits);
+/* av1_inv_txfm2d_add_WxH_c (av1_inv_txfm2d.c:234): input = kept coefficients, column-major */
+void av1o_inv_txfm2d_add(const int32_t *input, uint16_t *dest, int stride, int tx_size, int tx_type,
+                         int bd);
+void av1o_iwht4x4_add(const int32_t *input, uint16_t *dest, int stride, int eob, int bd);
+/* av1_inverse_transform_block (idct.c:303) on uint8 / uint16 pixel buffers */
+void av1o_recon_block(const int32_t *dqcoeff, const void *pred, int pred_stride, void *recon,
+                      int recon_stride, int tx_size, int tx_type, int eob, int lossless, int highbd,
+                      int bd);
+/* dist_block_px_domain (tx_search.c:969): 16 * sse over the visible region */
+int64_t av1o_dist_block_px(const void *src, int src_stride, const void *recon, int recon_stride,
+                           int vis_w, int vis_h, int highbd, int bd);
+
 /* ---- Hadamard / SATD / averages (av1o_avg.c; aom_dsp/avg.c) -------------------- */
 /* n x n Hadamard; kind 0 aom_hadamard_NxN_c (n 4..32), 1 aom_hadamard_lp_NxN_c (n 8, 16; int16
  * values widened), 2 aom_highbd_hadamard_NxN_c (n 8..32) */
