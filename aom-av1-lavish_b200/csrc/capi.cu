@@ -49,6 +49,7 @@ static int ctx_init(b200_ctx *ctx) {
   if (rc == B200_OK) rc = blockops_init_device(ctx);
   if (rc == B200_OK) rc = me_init_device(ctx);
   if (rc == B200_OK) rc = compact_init_device(ctx);
+  if (rc == B200_OK) rc = itx_init_device(ctx);
   return rc;
 }
 

@@ -72,6 +72,8 @@ int txq_launch(b200_ctx *ctx, const B200TxqLaunch &l, cudaStream_t s);
 int blockops_init_device(b200_ctx *ctx);
 int me_init_device(b200_ctx *ctx);
 int compact_init_device(b200_ctx *ctx);
+int itx_init_device(b200_ctx *ctx);
+int itx_launch(b200_ctx *ctx, const B200ItxLaunch &l, cudaStream_t s);
 // element offset of the scan tables of `tx_size` inside d_scan / d_iscan (3 classes of
 // max_eob entries each, see txq.cu) and the scan class of a tx_type
 size_t scan_dev_offset(int tx_size);

@@ -43,6 +43,13 @@ class TxqLaunch(C.Structure):
                 ("dqcoeff", C.c_void_p), ("eob", C.c_void_p), ("dist", C.c_void_p)]
 
 
+class ItxLaunch(C.Structure):
+    _fields_ = [("tx_size", C.c_int), ("highbd", C.c_int), ("bd", C.c_int), ("n_blocks", C.c_int),
+                ("blocks", C.c_void_p), ("preds", C.c_void_p), ("dqcoeff", C.c_void_p),
+                ("eob", C.c_void_p), ("src", C.c_void_p), ("pred", C.c_void_p),
+                ("recon", C.c_void_p), ("dist", C.c_void_p)]
+
+
 class CompactLaunch(C.Structure):
     _fields_ = [("n_blocks", C.c_int), ("blocks", C.c_void_p), ("qcoeff", C.c_void_p),
                 ("eob", C.c_void_p), ("wide", C.c_int), ("levels", C.c_void_p),

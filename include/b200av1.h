@@ -119,7 +119,9 @@ typedef struct {
   uint16_t qrow;       /* index into the B200QRow table */
   uint8_t tx_size;     /* B200_TX_* ; all blocks of one launch share it */
   uint8_t tx_type;     /* B200_*_* */
-  uint16_t reserved;
+  uint16_t reserved;   /* b200_txq_launch: ignored.  b200_itx_launch: visible part of the block for
+                          the distortion (get_txb_dimensions, av1/encoder/tx_search.c:940): 0 = whole
+                          block, else visible_cols | visible_rows << 8 */
 } B200TxBlock; /* 16 bytes */
 
 /* Companion entry when the kernel forms the residual itself (fused
@@ -185,6 +187,34 @@ int b200_txq_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int bd, unsigned
                         int32_t *coeff, int32_t *qcoeff, int32_t *dqcoeff,
                         size_t out_elems, uint16_t *eob, int64_t *dist);
 
+
+/* ------------------------------ inverse transform + reconstruction + distortion ---- */
+/* av1_inverse_transform_block (av1/common/idct.c:303; av1_inv_txfm_add_c
+ * :283, av1_highbd_inv_txfm_add_c :216, av1_inv_txfm2d_add_WxH_c av1/common/av1_inv_txfm2d.c:234-460)
+ * followed by dist_block_px_domain (av1/encoder/tx_search.c:969) for a batch of same-size blocks, so
+ * that a tx-type search evaluated on the device returns distortions instead of coefficients.
+ * The launch reads the SAME descriptor arrays as the b200_txq_launch that produced dqcoeff / eob:
+ * blocks[i].out_offset locates the dequantised coefficients, blocks[i].src_offset / src_stride the
+ * source block, preds[i] the prediction block; recon (optional) is a plane with the prediction's
+ * geometry (it may be the prediction plane itself: in-place, like the reference's dst buffer);
+ * dist[i] (optional) = 16 * SSE(source, reconstruction) over the visible part of the block, rounded
+ * by 2 (bd - 8) bits for uint16 pixels as the high-bit-depth variance functions do.  A block whose
+ * eob is 0 reconstructs to its prediction (idct.c:307).  uint8 pixels (highbd = 0) imply bd = 8. */
+typedef struct {
+  int tx_size;               /* all n_blocks blocks have this size */
+  int highbd;                /* 0: uint8 pixel planes, 1: uint16 */
+  int bd;                    /* 8, 10 or 12 */
+  int n_blocks;
+  const B200TxBlock *blocks; /* device */
+  const B200TxPred *preds;   /* device */
+  const int32_t *dqcoeff;    /* device: as b200_txq_launch wrote it (column-major kept region) */
+  const uint16_t *eob;       /* device, n_blocks entries, or NULL (every block is inverse transformed) */
+  const void *src;           /* device source plane (needed for dist) */
+  const void *pred;          /* device prediction plane */
+  void *recon;               /* device, or NULL */
+  int64_t *dist;             /* device, n_blocks entries, or NULL */
+} B200ItxLaunch;
+int b200_itx_launch(b200_ctx *ctx, const B200ItxLaunch *launch, void *stream);
 
 /* ------------------------------------------------ compact result format ---------- */
 /* What the encoder consumes after the quantiser is the levels in SCAN order up to eob

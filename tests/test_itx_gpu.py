@@ -1,0 +1,181 @@
+"""GPU parity of b200_itx_launch (inverse transform + reconstruction + pixel-domain distortion,
+SURVEY.md section 8f rank 3) against the oracle restatement of av1_inverse_transform_block
+(av1/common/idct.c:303) and dist_block_px_domain (av1/encoder/tx_search.c:969), bit-exact, for all
+19 sizes x valid types at 8 / 10 / 12 bit, uint8 and uint16 pixels; and chained behind the fused
+forward launch on the same descriptors (txq -> itx on the device)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import harness as H
+import synth
+from harness import i32p, ptr
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import b200av1
+    c = b200av1.Context(0)
+    yield c
+    c.close()
+
+
+def _oracle_itx(blocks, preds, dq, eob, src, pred, highbd, bd, want_dist=True):
+    O = H.oracle()
+    O.av1o_dist_block_px.restype = C.c_int64
+    recon = pred.copy()
+    dist = np.zeros(len(blocks), np.int64)
+    for i, (b, p) in enumerate(zip(blocks, preds)):
+        ts, tt = int(b["tx_size"]), int(b["tx_type"])
+        w, h = H.TX_W[ts], H.TX_H[ts]
+        c = np.ascontiguousarray(dq[int(b["out_offset"]):int(b["out_offset"]) + H.max_eob(ts)])
+        po, ps = int(p["pred_offset"]), int(p["pred_stride"])
+        isz = pred.itemsize
+        O.av1o_recon_block(ptr(c, i32p), C.c_void_p(pred.ctypes.data + po * isz), ps,
+                           C.c_void_p(recon.ctypes.data + po * isz), ps, ts, tt,
+                           int(eob[i]) if eob is not None else 1, 0, highbd, bd)
+        vis = int(b["reserved"])
+        vw, vh = (vis & 255, vis >> 8) if vis else (w, h)
+        if want_dist:
+            dist[i] = O.av1o_dist_block_px(C.c_void_p(src.ctypes.data + int(b["src_offset"]) * isz),
+                                           int(b["src_stride"]), C.c_void_p(recon.ctypes.data + po * isz), ps,
+                                           vw, vh, highbd, bd)
+    return recon, dist
+
+
+def _run_itx(ctx, ts, highbd, bd, blocks, preds, dq, eob, src, pred, in_place=False, want_recon=True):
+    import b200av1
+    d_blocks, d_preds = b200av1.to_device(ctx, blocks), b200av1.to_device(ctx, preds)
+    d_dq = b200av1.to_device(ctx, dq)
+    d_eob = b200av1.to_device(ctx, eob) if eob is not None else None
+    d_src, d_pred = b200av1.to_device(ctx, src), b200av1.to_device(ctx, pred)
+    d_recon = d_pred if in_place else b200av1.to_device(ctx, np.zeros_like(pred))
+    d_dist = b200av1.to_device(ctx, np.full(len(blocks), -1, np.int64))
+    l = b200av1.ItxLaunch(ts, highbd, bd, len(blocks), d_blocks.ptr, d_preds.ptr, d_dq.ptr,
+                          d_eob.ptr if d_eob else None, d_src.ptr, d_pred.ptr,
+                          d_recon.ptr if want_recon else None, d_dist.ptr)
+    b200av1.check(b200av1.lib().b200_itx_launch(ctx.h, C.byref(l), None))
+    ctx.sync()
+    recon = b200av1.to_host(ctx, d_recon, pred.dtype, pred.size).reshape(pred.shape)
+    dist = b200av1.to_host(ctx, d_dist, np.int64, len(blocks))
+    return recon, dist
+
+
+def _coeff_block(rng, ts, tt, bd, mode):
+    n = H.max_eob(ts)
+    w, h = H.TX_W[ts], H.TX_H[ts]
+    if mode == 0:
+        resid = rng.integers(-(1 << bd) + 1, 1 << bd, (h, w)).astype(np.int16)
+        c = H.oracle_fwd_txfm2d(resid, w, ts, tt, bd)
+        q = int(rng.integers(1, 200))
+        return ((c // q) * q).astype(np.int32)
+    if mode == 1:
+        lim = 1 << (bd + 7)
+        return rng.integers(-lim, lim, n).astype(np.int32)
+    if mode == 2:
+        c = np.zeros(n, np.int32)
+        k = int(rng.integers(1, 4))
+        c[rng.integers(0, n, k)] = rng.integers(-(1 << (bd + 6)), 1 << (bd + 6), k)
+        return c
+    return rng.integers(-(1 << 31), (1 << 31) - 1, n).astype(np.int32)  # any int32: exercises the clamps
+
+
+@pytest.mark.parametrize("highbd,bd", [(0, 8), (1, 8), (1, 10), (1, 12)])
+@pytest.mark.parametrize("ts", range(H.N_TX_SIZES))
+def test_itx_launch_all_types_vs_oracle(ctx, ts, highbd, bd):
+    import b200av1
+    rng = np.random.default_rng(8100 + ts * 4 + bd + highbd)
+    w, h, n = H.TX_W[ts], H.TX_H[ts], H.max_eob(ts)
+    types = [t for t in range(16) if H.tx_valid(ts, t)]
+    nb = 3 * len(types) + 5  # ragged against the warp tile
+    dt = np.uint16 if highbd else np.uint8
+    stride_s, stride_p = w * 3 + 16, w * 3 + 48
+    rows = (nb + 2) // 3
+    src = rng.integers(0, 1 << bd, (rows * h, stride_s)).astype(dt)
+    pred = rng.integers(0, 1 << bd, (rows * h, stride_p)).astype(dt)
+    pred[: h] = (1 << bd) - 1  # saturating rows
+    pred[h: 2 * h] = 0
+    blocks = np.zeros(nb, b200av1.TXBLOCK_DTYPE)
+    preds = np.zeros(nb, b200av1.TXPRED_DTYPE)
+    dq = np.zeros(nb * n + 7, np.int32)
+    eob = np.zeros(nb, np.uint16)
+    for i in range(nb):
+        tt = types[i % len(types)]
+        r, c = i // 3, i % 3
+        vis = 0
+        if i % 5 == 4:
+            vis = max(w - 4 * (i % 3), 4) | (max(h - 4 * ((i // 3) % 3), 4) << 8)
+        blocks[i] = (r * h * stride_s + c * w, i * n + 3, stride_s, 0, ts, tt, vis)
+        preds[i] = (r * h * stride_p + c * w, stride_p, 0)
+        cb = _coeff_block(rng, ts, tt, bd, i % 4)
+        eob[i] = 0 if i % 7 == 6 else max(1, int(np.count_nonzero(cb)))
+        dq[i * n + 3: i * n + 3 + n] = cb
+    want_recon, want_dist = _oracle_itx(blocks, preds, dq, eob, src.reshape(-1), pred.reshape(-1), highbd, bd)
+    got_recon, got_dist = _run_itx(ctx, ts, highbd, bd, blocks, preds, dq, eob, src, pred)
+    mask = np.zeros(pred.shape, bool)
+    for i in range(nb):
+        r, c = i // 3, i % 3
+        mask[r * h:(r + 1) * h, c * w:(c + 1) * w] = True
+    assert np.array_equal(got_recon[mask], want_recon.reshape(pred.shape)[mask]), H.TX_NAMES[ts]
+    assert not got_recon[~mask].any(), "wrote outside the blocks"
+    assert np.array_equal(got_dist, want_dist), H.TX_NAMES[ts]
+    # in place over the prediction plane, no eob array, distortion only
+    want2, dist2 = _oracle_itx(blocks, preds, dq, None, src.reshape(-1), pred.reshape(-1), highbd, bd)
+    got2, gdist2 = _run_itx(ctx, ts, highbd, bd, blocks, preds, dq, None, src, pred, in_place=True)
+    assert np.array_equal(got2[mask], want2.reshape(pred.shape)[mask])
+    assert np.array_equal(gdist2, dist2)
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+def test_txq_then_itx_chained_on_device(ctx, bd):
+    """forward + quantise launch, then the inverse launch on the SAME descriptor arrays and the dqcoeff /
+    eob the first launch left on the device: dist = dist_block_px_domain of every block."""
+    import b200av1
+    rng = np.random.default_rng(8400 + bd)
+    w, h, stride = 128, 64, 160
+    dt = np.uint8 if bd == 8 else np.uint16
+    srcp = np.zeros((h, stride), dt)
+    srcp[:, :w] = synth.smooth_frame(rng, w, h, bd)
+    predp = np.zeros((h, stride), dt)
+    predp[:, :w] = synth.pred_from(rng, srcp[:, :w], bd)
+    rows = [H.oracle_qrow(bd, q) for q in (60, 200)]
+    qrows = np.array([b200av1.qrow_from_oracle(r) for r in rows], b200av1.QROW_DTYPE)
+    q_kind = b200av1.Q_FP if bd == 8 else b200av1.Q_FP_HBD
+    in_kind = b200av1.IN_PIXELS8 if bd == 8 else b200av1.IN_PIXELS16
+    for ts in (0, 2, 3, 4, 6, 9, 17):
+        W, Hh, n = H.TX_W[ts], H.TX_H[ts], H.max_eob(ts)
+        offs = synth.tile_blocks(w, h, stride, W, Hh)
+        types = [t for t in range(16) if H.tx_valid(ts, t)]
+        blocks = np.zeros(len(offs), b200av1.TXBLOCK_DTYPE)
+        preds = np.zeros(len(offs), b200av1.TXPRED_DTYPE)
+        for i in range(len(offs)):
+            blocks[i] = (offs[i], i * n, stride, i % 2, ts, types[i % len(types)], 0)
+            preds[i] = (offs[i], stride, 0)
+        out_elems = len(offs) * n
+        d_blocks, d_preds = b200av1.to_device(ctx, blocks), b200av1.to_device(ctx, preds)
+        d_src, d_pred = b200av1.to_device(ctx, srcp), b200av1.to_device(ctx, predp)
+        d_q = b200av1.to_device(ctx, qrows)
+        d_qc, d_dq = b200av1.DevBuf(ctx, out_elems * 4), b200av1.DevBuf(ctx, out_elems * 4)
+        d_eob = b200av1.DevBuf(ctx, len(blocks) * 2)
+        d_dist = b200av1.DevBuf(ctx, len(blocks) * 8)
+        d_recon = b200av1.to_device(ctx, np.zeros_like(predp))
+        fl = b200av1.TxqLaunch(ts, in_kind, q_kind, bd, 0, len(blocks), d_blocks.ptr, d_preds.ptr,
+                               d_src.ptr, d_pred.ptr, d_q.ptr, None, d_qc.ptr, d_dq.ptr, d_eob.ptr, None)
+        ctx.txq_launch(fl)
+        il = b200av1.ItxLaunch(ts, int(bd > 8), bd, len(blocks), d_blocks.ptr, d_preds.ptr, d_dq.ptr,
+                               d_eob.ptr, d_src.ptr, d_pred.ptr, d_recon.ptr, d_dist.ptr)
+        b200av1.check(b200av1.lib().b200_itx_launch(ctx.h, C.byref(il), None))
+        ctx.sync()
+        got_dist = b200av1.to_host(ctx, d_dist, np.int64, len(blocks))
+        got_recon = b200av1.to_host(ctx, d_recon, dt, predp.size).reshape(predp.shape)
+        r = H.oracle_txq_batch(srcp.reshape(-1), blocks, rows, q_kind, bd, out_elems, in_kind,
+                               predp.reshape(-1), preds)
+        want_recon, want_dist = _oracle_itx(blocks, preds, r[2], r[3], srcp.reshape(-1), predp.reshape(-1),
+                                            int(bd > 8), bd)
+        assert np.array_equal(got_dist, want_dist), H.TX_NAMES[ts]
+        assert np.array_equal(got_recon[:, :w], want_recon.reshape(predp.shape)[:, :w]), H.TX_NAMES[ts]
+        # sanity: reconstruction error is far below the prediction error at these quantisers
+        assert got_dist.sum() < 16 * ((srcp.astype(np.int64) - predp) ** 2).sum() or bd > 8
