@@ -18,6 +18,74 @@ static ItxKernelInfo g_itx[B200_TX_SIZES_ALL][2];
 static int g_itx_ctas[B200_TX_SIZES_ALL][2];
 static std::once_flag g_itx_once;
 
+
+// av1_highbd_iwht4x4_16_add_c / av1_highbd_iwht4x4_1_add_c (av1_inv_txfm2d.c:20-109) behind the eob
+// switch of av1_highbd_iwht4x4_add (idct.c): the lossless 4x4 inverse, one lane per block.
+template <int PX>
+__global__ void iwht_kernel(const ItxArgs a) {
+  using pix_t = typename std::conditional<PX == 1, uint8_t, uint16_t>::type;
+  const int bi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (bi >= a.n_blocks) return;
+  const B200TxBlock d = load_desc(a.blocks + bi);
+  const B200TxPred pd = a.preds[bi];
+  const int eob = a.eob ? a.eob[bi] : 16;
+  const int32_t *in = a.dqcoeff + d.out_offset;
+  int32_t res[16];
+  if (eob > 1) {
+    int32_t o[16];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      int32_t aa = in[i] >> 2, c = in[4 + i] >> 2, dd = in[8 + i] >> 2, b = in[12 + i] >> 2;
+      aa += c, dd -= b;
+      const int32_t e = (aa - dd) >> 1;
+      b = e - b, c = e - c, aa -= b, dd += c;
+      o[i] = aa, o[4 + i] = b, o[8 + i] = c, o[12 + i] = dd;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      int32_t aa = o[4 * i], c = o[4 * i + 1], dd = o[4 * i + 2], b = o[4 * i + 3];
+      aa += c, dd -= b;
+      const int32_t e = (aa - dd) >> 1;
+      b = e - b, c = e - c, aa -= b, dd += c;
+      res[i] = aa, res[4 + i] = b, res[8 + i] = c, res[12 + i] = dd;
+    }
+  } else if (eob == 1) {
+    int32_t a1 = in[0] >> 2;
+    const int32_t e1 = a1 >> 1;
+    a1 -= e1;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int32_t t = i == 0 ? a1 : e1, e = t >> 1;
+      res[i] = t - e, res[4 + i] = e, res[8 + i] = e, res[12 + i] = e;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) res[i] = 0;
+  }
+  const int pmax = (1 << a.bd) - 1;
+  const int vis_w = d.reserved ? (d.reserved & 255) : 4, vis_h = d.reserved ? (d.reserved >> 8) : 4;
+  unsigned long long sse = 0;
+#pragma unroll
+  for (int r = 0; r < 4; ++r)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const size_t po = (size_t)pd.pred_offset + (size_t)r * pd.pred_stride + c;
+      const int v = min(max((int)static_cast<const pix_t *>(a.pred)[po] + res[4 * r + c], 0), pmax);
+      if (a.recon) static_cast<pix_t *>(a.recon)[po] = (pix_t)v;
+      if (a.src && c < vis_w && r < vis_h) {
+        const int df = (int)static_cast<const pix_t *>(a.src)[(size_t)d.src_offset + (size_t)r * d.src_stride + c] - v;
+        sse += (unsigned)(df * df);
+      }
+    }
+  if (a.dist) {
+    if (PX == 2 && a.bd > 8) {
+      const int sh = 2 * (a.bd - 8);
+      sse = (sse + (1ull << (sh - 1))) >> sh;
+    }
+    a.dist[bi] = 16 * (long long)(unsigned)sse;
+  }
+}
+
 int itx_init_device(b200_ctx *ctx) {
   (void)ctx;
   std::call_once(g_itx_once, [] {
@@ -74,6 +142,16 @@ int itx_launch(b200_ctx *ctx, const B200ItxLaunch &l, cudaStream_t s) {
   a.dist = l.dist;
   a.n_blocks = l.n_blocks;
   a.bd = l.bd;
+  if (l.lossless) {
+    if (l.tx_size != B200_TX_4X4) {
+      set_error("b200_itx_launch: lossless blocks are 4x4 (WHT)");
+      return B200_EINVAL;
+    }
+    if (l.highbd) iwht_kernel<2><<<(l.n_blocks + 127) / 128, 128, 0, s>>>(a);
+    else iwht_kernel<1><<<(l.n_blocks + 127) / 128, 128, 0, s>>>(a);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+  }
   const int n_tiles = (l.n_blocks + e.bpw - 1) / e.bpw;
   int grid = (n_tiles + kWarpsPerCta - 1) / kWarpsPerCta;
   const int resident = ctx->sm_count * g_itx_ctas[l.tx_size][k];

@@ -356,6 +356,57 @@ void subtract_one(int hb, int rows, int cols, int16_t *diff, ptrdiff_t diff_stri
   CKCUDA(cudaStreamSynchronize(s));
 }
 
+// ------------------------------------------------------------ inverse transforms ----
+// one block: dst (host, uint8 or uint16) += inverse(dqcoeff), through b200_itx_launch in place
+void inv_txfm_one(int ts, int tx_type, const int32_t *dqcoeff, void *dst, int stride, int bd, int highbd,
+                  int lossless, int eob) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  b200_ctx *c = ctx0();
+  const int w = b200_tx_wide(ts), h = b200_tx_high(ts), n = lossless ? 16 : b200_tx_max_eob(ts);
+  const size_t px = highbd ? 2 : 1;
+  if (!lossless && !b200_tx_valid(ts, tx_type)) {
+    set_error("inverse transform: tx_type %d has no %dx%d transform", tx_type, w, h);
+    fatal(__func__);
+  }
+  if (eob == 0) return;  // av1_inverse_transform_block (idct.c:307)
+  Arena a(c, (size_t)w * h * px + (size_t)n * 4 + 1024);
+  char *d_dst = a.take<char>((size_t)w * h * px);
+  int32_t *d_dq = a.take<int32_t>(n);
+  B200TxBlock *d_blk = a.take<B200TxBlock>(1);
+  B200TxPred *d_pred = a.take<B200TxPred>(1);
+  uint16_t *d_eob = a.take<uint16_t>(1);
+  B200TxBlock blk;
+  memset(&blk, 0, sizeof(blk));
+  blk.tx_size = (uint8_t)ts;
+  blk.tx_type = (uint8_t)tx_type;
+  B200TxPred pd;
+  memset(&pd, 0, sizeof(pd));
+  pd.pred_stride = (uint16_t)w;
+  const uint16_t e16 = (uint16_t)(eob < 0 ? n : eob);
+  cudaStream_t s = c->stream;
+  CKCUDA(cudaMemcpy2DAsync(d_dst, w * px, dst, (size_t)stride * px, w * px, h, cudaMemcpyHostToDevice, s));
+  CKCUDA(cudaMemcpyAsync(d_dq, dqcoeff, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+  CKCUDA(cudaMemcpyAsync(d_blk, &blk, sizeof(blk), cudaMemcpyHostToDevice, s));
+  CKCUDA(cudaMemcpyAsync(d_pred, &pd, sizeof(pd), cudaMemcpyHostToDevice, s));
+  CKCUDA(cudaMemcpyAsync(d_eob, &e16, sizeof(e16), cudaMemcpyHostToDevice, s));
+  B200ItxLaunch l;
+  memset(&l, 0, sizeof(l));
+  l.tx_size = ts;
+  l.highbd = highbd;
+  l.bd = bd;
+  l.n_blocks = 1;
+  l.blocks = d_blk;
+  l.preds = d_pred;
+  l.dqcoeff = d_dq;
+  l.eob = d_eob;
+  l.pred = d_dst;
+  l.recon = d_dst;
+  l.lossless = lossless;
+  CK(itx_launch(c, l, s));
+  CKCUDA(cudaMemcpy2DAsync(dst, (size_t)stride * px, d_dst, w * px, w * px, h, cudaMemcpyDeviceToHost, s));
+  CKCUDA(cudaStreamSynchronize(s));
+}
+
 }  // namespace
 
 // ================================================================== exported =====
@@ -387,13 +438,49 @@ B200_DEF_FWD_TXFM(32, 8)
 B200_DEF_FWD_TXFM(16, 64)
 B200_DEF_FWD_TXFM(64, 16)
 
+void av1_fwht4x4_b200(const int16_t *input, b200_tran_low_t *output, int stride);
 void av1_lowbd_fwd_txfm_b200(const int16_t *src_diff, b200_tran_low_t *coeff, int diff_stride,
                              B200TxfmParam *p) {
-  if (p->lossless) {
-    set_error("av1_lowbd_fwd_txfm_b200: lossless (WHT) is outside the accelerated path");
-    fatal(__func__);
+  if (p->lossless) {  // av1_lowbd_fwd_txfm_c -> av1_highbd_fwd_txfm -> highbd_fwd_txfm_4x4 (hybrid_fwd_txfm.c:85-93)
+    av1_fwht4x4_b200(src_diff, coeff, diff_stride);
+    return;
   }
   fwd_txfm_one(p->tx_size, src_diff, coeff, diff_stride, p->tx_type);
+}
+
+#define B200_DEF_INV_TXFM(W, H)                                                                  \
+  void av1_inv_txfm2d_add_##W##x##H##_b200(const int32_t *input, uint16_t *output, int stride,  \
+                                           uint8_t tx_type, int bd) {                            \
+    inv_txfm_one(tx_size_of(W, H), tx_type, input, output, stride, bd, 1, 0, -1);                \
+  }
+B200_DEF_INV_TXFM(4, 4)
+B200_DEF_INV_TXFM(8, 8)
+B200_DEF_INV_TXFM(16, 16)
+B200_DEF_INV_TXFM(32, 32)
+B200_DEF_INV_TXFM(64, 64)
+B200_DEF_INV_TXFM(4, 8)
+B200_DEF_INV_TXFM(8, 4)
+B200_DEF_INV_TXFM(8, 16)
+B200_DEF_INV_TXFM(16, 8)
+B200_DEF_INV_TXFM(16, 32)
+B200_DEF_INV_TXFM(32, 16)
+B200_DEF_INV_TXFM(32, 64)
+B200_DEF_INV_TXFM(64, 32)
+B200_DEF_INV_TXFM(4, 16)
+B200_DEF_INV_TXFM(16, 4)
+B200_DEF_INV_TXFM(8, 32)
+B200_DEF_INV_TXFM(32, 8)
+B200_DEF_INV_TXFM(16, 64)
+B200_DEF_INV_TXFM(64, 16)
+// av1_inv_txfm_add (idct.c:283) / av1_highbd_inv_txfm_add (:216): dst holds the prediction
+void av1_inv_txfm_add_b200(const b200_tran_low_t *dqcoeff, uint8_t *dst, int stride, const B200TxfmParam *p) {
+  inv_txfm_one(p->tx_size, p->tx_type, dqcoeff, dst, stride, p->bd, 0, p->lossless, p->lossless ? p->eob : -1);
+}
+void av1_highbd_inv_txfm_add_b200(const b200_tran_low_t *input, uint8_t *dest8, int stride,
+                                  const B200TxfmParam *p) {
+  // CONVERT_TO_SHORTPTR (aom_ports/mem.h:79)
+  inv_txfm_one(p->tx_size, p->tx_type, input, (void *)(((uintptr_t)dest8) << 1), stride, p->bd, 1, p->lossless,
+               p->lossless ? p->eob : -1);
 }
 
 #define QA coeff_ptr, n_coeffs, zbin_ptr, round_ptr, quant_ptr, quant_shift_ptr, qcoeff_ptr, \

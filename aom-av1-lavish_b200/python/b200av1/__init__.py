@@ -47,7 +47,7 @@ class ItxLaunch(C.Structure):
     _fields_ = [("tx_size", C.c_int), ("highbd", C.c_int), ("bd", C.c_int), ("n_blocks", C.c_int),
                 ("blocks", C.c_void_p), ("preds", C.c_void_p), ("dqcoeff", C.c_void_p),
                 ("eob", C.c_void_p), ("src", C.c_void_p), ("pred", C.c_void_p),
-                ("recon", C.c_void_p), ("dist", C.c_void_p)]
+                ("recon", C.c_void_p), ("dist", C.c_void_p), ("lossless", C.c_int)]
 
 
 class CompactLaunch(C.Structure):

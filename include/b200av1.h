@@ -213,6 +213,9 @@ typedef struct {
   const void *pred;          /* device prediction plane */
   void *recon;               /* device, or NULL */
   int64_t *dist;             /* device, n_blocks entries, or NULL */
+  int lossless;              /* 1: tx_size is B200_TX_4X4 and the blocks take the lossless inverse WHT,
+                                av1_highbd_iwht4x4_16_add / _1_add by eob (av1_inv_txfm2d.c:20-109;
+                                dqcoeff in the WHT's own row-major order, hybrid_fwd_txfm.c:24) */
 } B200ItxLaunch;
 int b200_itx_launch(b200_ctx *ctx, const B200ItxLaunch *launch, void *stream);
 

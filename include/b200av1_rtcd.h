@@ -64,10 +64,40 @@ B200_DECL_FWD_TXFM(8, 32)
 B200_DECL_FWD_TXFM(32, 8)
 B200_DECL_FWD_TXFM(16, 64)
 B200_DECL_FWD_TXFM(64, 16)
-/* av1_lowbd_fwd_txfm (av1_rtcd_defs.pl:349; hybrid_fwd_txfm.c:241): size switch.
- * txfm_param->lossless (WHT) is not part of this path and is rejected (abort). */
+/* av1_lowbd_fwd_txfm (av1_rtcd_defs.pl:349; hybrid_fwd_txfm.c:241): size switch;
+ * txfm_param->lossless takes the WHT (av1_fwht4x4_b200). */
 void av1_lowbd_fwd_txfm_b200(const int16_t *src_diff, b200_tran_low_t *coeff, int diff_stride,
                              B200TxfmParam *txfm_param);
+
+/* ---- inverse transforms: av1_rtcd_defs.pl:137-141 (av1_inv_txfm_add, av1_highbd_inv_txfm_add),
+ * :182-219 (av1_inv_txfm2d_add_WxH); output / dst holds the prediction and receives the
+ * reconstruction; lossless blocks take av1_highbd_iwht4x4_{16,1}_add by txfm_param->eob ---- */
+#define B200_DECL_INV_TXFM(W, H)                                                                 \
+  void av1_inv_txfm2d_add_##W##x##H##_b200(const int32_t *input, uint16_t *output, int stride,  \
+                                           uint8_t tx_type, int bd);
+B200_DECL_INV_TXFM(4, 4)
+B200_DECL_INV_TXFM(8, 8)
+B200_DECL_INV_TXFM(16, 16)
+B200_DECL_INV_TXFM(32, 32)
+B200_DECL_INV_TXFM(64, 64)
+B200_DECL_INV_TXFM(4, 8)
+B200_DECL_INV_TXFM(8, 4)
+B200_DECL_INV_TXFM(8, 16)
+B200_DECL_INV_TXFM(16, 8)
+B200_DECL_INV_TXFM(16, 32)
+B200_DECL_INV_TXFM(32, 16)
+B200_DECL_INV_TXFM(32, 64)
+B200_DECL_INV_TXFM(64, 32)
+B200_DECL_INV_TXFM(4, 16)
+B200_DECL_INV_TXFM(16, 4)
+B200_DECL_INV_TXFM(8, 32)
+B200_DECL_INV_TXFM(32, 8)
+B200_DECL_INV_TXFM(16, 64)
+B200_DECL_INV_TXFM(64, 16)
+void av1_inv_txfm_add_b200(const b200_tran_low_t *dqcoeff, uint8_t *dst, int stride,
+                           const B200TxfmParam *txfm_param);
+void av1_highbd_inv_txfm_add_b200(const b200_tran_low_t *input, uint8_t *dest, int stride,
+                                  const B200TxfmParam *txfm_param);
 
 /* ---- quantisers: av1_rtcd_defs.pl:334-347,428; aom_dsp_rtcd_defs.pl:655-694 ---- */
 #define B200_QUANT_ARGS                                                                       \

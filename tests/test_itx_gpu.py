@@ -179,3 +179,98 @@ def test_txq_then_itx_chained_on_device(ctx, bd):
         assert np.array_equal(got_recon[:, :w], want_recon.reshape(predp.shape)[:, :w]), H.TX_NAMES[ts]
         # sanity: reconstruction error is far below the prediction error at these quantisers
         assert got_dist.sum() < 16 * ((srcp.astype(np.int64) - predp) ** 2).sum() or bd > 8
+
+
+@pytest.mark.parametrize("highbd,bd", [(0, 8), (1, 10), (1, 12)])
+def test_itx_lossless_wht_vs_oracle(ctx, highbd, bd):
+    """lossless blocks: av1_highbd_iwht4x4_16_add / _1_add by eob (av1_inv_txfm2d.c:20-109)"""
+    import b200av1
+    O = H.oracle()
+    O.av1o_dist_block_px.restype = C.c_int64
+    rng = np.random.default_rng(8600 + bd)
+    nb, stride = 301, 4 * 301 + 8
+    dt = np.uint16 if highbd else np.uint8
+    src = rng.integers(0, 1 << bd, (4, stride)).astype(dt)
+    pred = rng.integers(0, 1 << bd, (4, stride)).astype(dt)
+    blocks = np.zeros(nb, b200av1.TXBLOCK_DTYPE)
+    preds = np.zeros(nb, b200av1.TXPRED_DTYPE)
+    dq = rng.integers(-(1 << (bd + 3)), 1 << (bd + 3), nb * 16).astype(np.int32)
+    eob = rng.integers(0, 17, nb).astype(np.uint16)
+    eob[:3] = (0, 1, 2)
+    want = pred.copy()
+    want_dist = np.zeros(nb, np.int64)
+    for i in range(nb):
+        blocks[i] = (4 * i, 16 * i, stride, 0, 0, 0, 0)
+        preds[i] = (4 * i, stride, 0)
+        c = np.ascontiguousarray(dq[16 * i:16 * i + 16])
+        isz = pred.itemsize
+        O.av1o_recon_block(ptr(c, i32p), C.c_void_p(pred.ctypes.data + 4 * i * isz), stride,
+                           C.c_void_p(want.ctypes.data + 4 * i * isz), stride, 0, 0, int(eob[i]), 1, highbd, bd)
+        want_dist[i] = O.av1o_dist_block_px(C.c_void_p(src.ctypes.data + 4 * i * isz), stride,
+                                            C.c_void_p(want.ctypes.data + 4 * i * isz), stride, 4, 4, highbd, bd)
+    d = [b200av1.to_device(ctx, x) for x in (blocks, preds, dq, eob, src, pred)]
+    d_recon = b200av1.to_device(ctx, np.zeros_like(pred))
+    d_dist = b200av1.DevBuf(ctx, nb * 8)
+    l = b200av1.ItxLaunch(0, highbd, bd, nb, d[0].ptr, d[1].ptr, d[2].ptr, d[3].ptr, d[4].ptr, d[5].ptr,
+                          d_recon.ptr, d_dist.ptr, 1)
+    b200av1.check(b200av1.lib().b200_itx_launch(ctx.h, C.byref(l), None))
+    ctx.sync()
+    got = b200av1.to_host(ctx, d_recon, dt, pred.size).reshape(pred.shape)
+    assert np.array_equal(got[:, :4 * nb], want[:, :4 * nb])
+    assert np.array_equal(b200av1.to_host(ctx, d_dist, np.int64, nb), want_dist)
+
+
+class TxfmParam(C.Structure):  # aom_dsp/txfm_common.h:89-101 == B200TxfmParam
+    _fields_ = [("tx_type", C.c_uint8), ("tx_size", C.c_uint8), ("lossless", C.c_int), ("bd", C.c_int),
+                ("is_hbd", C.c_int), ("tx_set_type", C.c_uint8), ("eob", C.c_int)]
+
+
+def test_inverse_dropins_vs_oracle(ctx):
+    """av1_inv_txfm2d_add_WxH_b200, av1_inv_txfm_add_b200, av1_highbd_inv_txfm_add_b200 (one block per
+    call, host buffers) and the lossless route of av1_lowbd_fwd_txfm_b200"""
+    import b200av1
+    from harness import i16p, u8p, u16p
+    L, O = b200av1.lib(), H.oracle()
+    rng = np.random.default_rng(8700)
+    for ts in range(H.N_TX_SIZES):
+        w, h = H.TX_W[ts], H.TX_H[ts]
+        stride = w + 8
+        types = [t for t in range(16) if H.tx_valid(ts, t)]
+        for tt in (types[0], types[-1], types[len(types) // 2]):
+            for bd in (8, 10, 12):
+                c = _coeff_block(rng, ts, tt, bd, int(rng.integers(0, 3)))
+                pred = rng.integers(0, 1 << bd, (h, stride)).astype(np.uint16)
+                a, b = pred.copy(), pred.copy()
+                getattr(L, "av1_inv_txfm2d_add_%dx%d_b200" % (w, h))(ptr(c, i32p), ptr(a, u16p), stride,
+                                                                     C.c_uint8(tt), bd)
+                O.av1o_inv_txfm2d_add(ptr(c, i32p), ptr(b, u16p), stride, ts, tt, bd)
+                assert np.array_equal(a, b), (ts, tt, bd)
+            c = _coeff_block(rng, ts, tt, 8, 0)
+            pred8 = rng.integers(0, 256, (h, stride)).astype(np.uint8)
+            a8, b8 = pred8.copy(), pred8.copy()
+            p = TxfmParam(tt, ts, 0, 8, 0, 0, int(np.count_nonzero(c)) or 1)
+            L.av1_inv_txfm_add_b200(ptr(c, i32p), ptr(a8, u8p), stride, C.byref(p))
+            O.av1o_recon_block(ptr(c, i32p), pred8.ctypes.data_as(C.c_void_p), stride,
+                               b8.ctypes.data_as(C.c_void_p), stride, ts, tt, 1, 0, 0, 8)
+            assert np.array_equal(a8[:, :w], b8[:, :w]) and np.array_equal(a8[:, w:], pred8[:, w:])
+            pred16 = rng.integers(0, 1024, (h, stride)).astype(np.uint16)
+            a16, b16 = pred16.copy(), pred16.copy()
+            c = _coeff_block(rng, ts, tt, 10, 0)
+            p = TxfmParam(tt, ts, 0, 10, 1, 0, 1)
+            L.av1_highbd_inv_txfm_add_b200(ptr(c, i32p), C.cast(C.c_void_p(a16.ctypes.data >> 1), u8p), stride,
+                                           C.byref(p))
+            O.av1o_inv_txfm2d_add(ptr(c, i32p), ptr(b16, u16p), stride, ts, tt, 10)
+            assert np.array_equal(a16, b16)
+    # lossless: forward WHT through av1_lowbd_fwd_txfm_b200, inverse through av1_inv_txfm_add_b200
+    resid = rng.integers(-255, 256, (4, 12)).astype(np.int16)
+    co, cw = np.zeros(16, np.int32), np.zeros(16, np.int32)
+    p = TxfmParam(0, 0, 1, 8, 0, 0, 16)
+    L.av1_lowbd_fwd_txfm_b200(ptr(resid, i16p), ptr(co, i32p), 12, C.byref(p))
+    O.av1o_fwht4x4(ptr(resid, i16p), ptr(cw, i32p), 12)
+    assert np.array_equal(co, cw)
+    pred8 = rng.integers(0, 256, (4, 12)).astype(np.uint8)
+    a8, b8 = pred8.copy(), pred8.copy()
+    L.av1_inv_txfm_add_b200(ptr(co, i32p), ptr(a8, u8p), 12, C.byref(p))
+    O.av1o_recon_block(ptr(co, i32p), pred8.ctypes.data_as(C.c_void_p), 12, b8.ctypes.data_as(C.c_void_p), 12,
+                       0, 0, 16, 1, 0, 8)
+    assert np.array_equal(a8[:, :4], b8[:, :4])
