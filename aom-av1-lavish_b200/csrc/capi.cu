@@ -180,7 +180,7 @@ int scratch_reserve(b200_ctx *ctx, size_t bytes) {
 
 namespace b200 {
 // Grow-only pinned host staging.
-static int host_scratch_reserve(b200_ctx *ctx, size_t bytes) {
+int host_scratch_reserve(b200_ctx *ctx, size_t bytes) {
   if (bytes <= ctx->h_scratch_bytes) return B200_OK;
   B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
   B200_CUDA_TRY(cudaStreamSynchronize(ctx->copy_stream));

@@ -79,6 +79,7 @@ int itx_launch(b200_ctx *ctx, const B200ItxLaunch &l, cudaStream_t s);
 size_t scan_dev_offset(int tx_size);
 __host__ __device__ inline int scan_class_of(int tx_type) { return tx_type < 10 ? 0 : ((tx_type & 1) ? 2 : 1); }
 int scratch_reserve(b200_ctx *ctx, size_t bytes);
+int host_scratch_reserve(b200_ctx *ctx, size_t bytes);  // pinned staging (capi.cu)
 // hadamard.cu: single-call helpers behind the drop-in tier
 int int_pro_launch(b200_ctx *ctx, short *out, const unsigned char *ref, int ref_stride, int width,
                    int height, int norm, int col, cudaStream_t s);

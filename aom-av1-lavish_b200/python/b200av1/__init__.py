@@ -50,6 +50,22 @@ class ItxLaunch(C.Structure):
                 ("recon", C.c_void_p), ("dist", C.c_void_p), ("lossless", C.c_int)]
 
 
+TXSEARCH_DTYPE = np.dtype([("dist_px", "<i8"), ("dist_tx", "<i8"), ("ssz", "<i8"), ("rate_est", "<i4"),
+                           ("eob", "<u2"), ("reserved", "<u2")])
+assert TXSEARCH_DTYPE.itemsize == 32
+TXS_DIST_PX, TXS_DIST_TX, TXS_RATE_EST = 1, 2, 4
+
+
+def txsearch_batch_host(ctx, in_kind, q_kind, bd, want, blocks, preds, src, pred, qrows):
+    """b200_txsearch_batch_host: one TXSEARCH_DTYPE record per descriptor; returns (results, d2h_bytes)"""
+    out = np.zeros(len(blocks), TXSEARCH_DTYPE)
+    d2h = C.c_size_t(0)
+    check(lib().b200_txsearch_batch_host(ctx.h, in_kind, q_kind, bd, C.c_uint(want), vp(blocks), vp(preds),
+                                         len(blocks), vp(src), C.c_size_t(src.size), vp(pred),
+                                         C.c_size_t(pred.size), vp(qrows), len(qrows), vp(out), C.byref(d2h)))
+    return out, d2h.value
+
+
 class CompactLaunch(C.Structure):
     _fields_ = [("n_blocks", C.c_int), ("blocks", C.c_void_p), ("qcoeff", C.c_void_p),
                 ("eob", C.c_void_p), ("wide", C.c_int), ("levels", C.c_void_p),

@@ -219,6 +219,44 @@ typedef struct {
 } B200ItxLaunch;
 int b200_itx_launch(b200_ctx *ctx, const B200ItxLaunch *launch, void *stream);
 
+/* ------------------------------------- transform-type search on the device ------- */
+/* av1_cost_coeffs_txb_estimate (av1/encoder/txb_rdopt.c:547-582): the coefficient term of the
+ * Laplacian rate estimate av1_cost_coeffs_txb_laplacian (:626) that prune_txk_type /
+ * prune_txk_type_separ rank tx types with (tx_search.c:1179,1215,1302), for every block of a batch
+ * from the dense qcoeff a b200_txq_launch left on the device; rate[i] = 0 when eob[i] = 0 (the
+ * reference then takes txb_skip_cost instead, txb_rdopt.c:646). */
+typedef struct {
+  int n_blocks;
+  const B200TxBlock *blocks; /* device: tx_size, tx_type, out_offset are read */
+  const int32_t *qcoeff;     /* device */
+  const uint16_t *eob;       /* device */
+  int32_t *rate;             /* device out, n_blocks */
+} B200RateEstLaunch;
+int b200_rate_estimate_launch(b200_ctx *ctx, const B200RateEstLaunch *launch, void *stream);
+
+/* One descriptor per (block, candidate tx type) of search_tx_type (av1/encoder/tx_search.c:2047-2330):
+ * av1_xform_quant (encodemb.c:295) + dist_block_tx_domain (tx_search.c:1077) + the rate estimate
+ * above + dist_block_px_domain (tx_search.c:969) run chained on the device; 32 bytes per descriptor
+ * come back instead of the coefficient arrays.  src / pred are HOST pixel planes (uint8 for
+ * B200_IN_PIXELS8, uint16 for B200_IN_PIXELS16); blocks[i].out_offset is ignored; the encoder adds
+ * the context-dependent rate terms (txb_skip / tx-type / eob costs) from eob and tx_type. */
+#define B200_TXS_DIST_PX 1u  /* fill dist_px  (inverse transform + reconstruction + SSE) */
+#define B200_TXS_DIST_TX 2u  /* fill dist_tx / ssz (block error in the transform domain) */
+#define B200_TXS_RATE_EST 4u /* fill rate_est */
+typedef struct {
+  int64_t dist_px;  /* 16 * SSE(source, reconstruction), rounded for bd > 8 (dist_block_px_domain) */
+  int64_t dist_tx;  /* av1_block_error / av1_highbd_block_error return value (before the caller's shift) */
+  int64_t ssz;      /* its *ssz */
+  int32_t rate_est; /* av1_cost_coeffs_txb_estimate */
+  uint16_t eob;
+  uint16_t reserved;
+} B200TxSearchResult; /* 32 bytes */
+int b200_txsearch_batch_host(b200_ctx *ctx, int in_kind, int q_kind, int bd, unsigned want,
+                             const B200TxBlock *blocks, const B200TxPred *preds, int n_blocks,
+                             const void *src, size_t src_elems, const void *pred, size_t pred_elems,
+                             const B200QRow *qrows, int n_qrows, B200TxSearchResult *out,
+                             size_t *d2h_bytes);
+
 /* ------------------------------------------------ compact result format ---------- */
 /* What the encoder consumes after the quantiser is the levels in SCAN order up to eob
  * (av1_write_coeffs_txb / av1_cost_coeffs_txb, av1/encoder/encodetxb.c) and dqcoeff is a

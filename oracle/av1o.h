@@ -65,6 +65,8 @@ void av1o_recon_block(const int32_t *dqcoeff, const void *pred, int pred_stride,
                       int recon_stride, int tx_size, int tx_type, int eob, int lossless, int highbd,
                       int bd);
 /* dist_block_px_domain (tx_search.c:969): 16 * sse over the visible region */
+/* av1_cost_coeffs_txb_estimate (txb_rdopt.c:547) */
+int av1o_cost_coeffs_txb_estimate(const int32_t *qcoeff, int eob, int tx_size, int tx_type);
 int64_t av1o_dist_block_px(const void *src, int src_stride, const void *recon, int recon_stride,
                            int vis_w, int vis_h, int highbd, int bd);
 

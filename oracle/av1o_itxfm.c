@@ -337,3 +337,19 @@ int64_t av1o_dist_block_px(const void *src, int src_stride, const void *recon, i
   if (highbd && bd > 8) sse = (sse + ((uint64_t)1 << (2 * (bd - 8) - 1))) >> (2 * (bd - 8));
   return 16 * (int64_t)(unsigned)sse;
 }
+
+/* av1_cost_coeffs_txb_estimate (av1/encoder/txb_rdopt.c:547-582; costLUT / const_term / loge_par
+ * txb_rdopt_utils.h:31-37): the Laplacian rate estimate prune_txk_type / prune_txk_type_separ use
+ * (tx_search.c:1179,1215,1302).  scan = av1o_scan(tx_size, tx_type); eob >= 1. */
+int av1o_cost_coeffs_txb_estimate(const int32_t *qcoeff, int eob, int tx_size, int tx_type) {
+  static const int lut[15] = { -1143, 53, 545, 825, 1031, 1209, 1393, 1577, 1763, 1947, 2132, 2317, 2501, 2686, 2871 };
+  const int16_t *scan = av1o_scan(tx_size, tx_type);
+  const int const_term = 1 << 9, loge_par = ((14427 << 9) + 5000) / 10000;
+  int c = eob - 1;
+  int cost = (abs(qcoeff[scan[c]]) - 1) << (9 + 2);
+  for (c = eob - 2; c >= 0; --c) {
+    const int v = abs(qcoeff[scan[c]]);
+    cost += lut[v < 14 ? v : 14];
+  }
+  return cost + (const_term + loge_par) * (eob - 1);
+}

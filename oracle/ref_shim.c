@@ -667,6 +667,19 @@ void *refshim_quantize_fp_fn(int log_scale, int highbd) {
                         : log_scale == 1 ? (void *)av1_quantize_fp_32x32 : (void *)av1_quantize_fp_64x64;
 }
 
+/* ---- av1_cost_coeffs_txb_estimate (txb_rdopt.c:547) on a bare coefficient block: the function reads
+ * only x->plane[0].qcoeff and .eobs */
+#include "av1/encoder/txb_rdopt.h"
+int refshim_cost_coeffs_txb_estimate(const int32_t *qcoeff, int eob, int tx_size, int tx_type) {
+  MACROBLOCK *x = (MACROBLOCK *)aom_calloc(1, sizeof(*x));
+  uint16_t eobs[1] = { (uint16_t)eob };
+  x->plane[0].qcoeff = (tran_low_t *)qcoeff;
+  x->plane[0].eobs = eobs;
+  const int r = av1_cost_coeffs_txb_estimate(x, 0, 0, (TX_SIZE)tx_size, (TX_TYPE)tx_type);
+  aom_free(x);
+  return r;
+}
+
 /* 1 when this library was built with the x86 intrinsics and run-time dispatch */
 int refshim_simd(void) {
 #ifdef REFSHIM_DISPATCH

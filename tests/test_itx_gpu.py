@@ -274,3 +274,56 @@ def test_inverse_dropins_vs_oracle(ctx):
     O.av1o_recon_block(ptr(co, i32p), pred8.ctypes.data_as(C.c_void_p), 12, b8.ctypes.data_as(C.c_void_p), 12,
                        0, 0, 16, 1, 0, 8)
     assert np.array_equal(a8[:, :4], b8[:, :4])
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+def test_txsearch_batch_host_vs_oracle(ctx, bd):
+    """b200_txsearch_batch_host: every valid tx type of every block as one descriptor; eob, tx-domain
+    error, Laplacian rate estimate and pixel-domain distortion against the oracle, caller's order kept."""
+    import b200av1
+    O = H.oracle()
+    rng = np.random.default_rng(8800 + bd)
+    w, h, stride = 128, 64, 144
+    dt = np.uint8 if bd == 8 else np.uint16
+    srcp = np.zeros((h, stride), dt)
+    srcp[:, :w] = synth.smooth_frame(rng, w, h, bd)
+    predp = np.zeros((h, stride), dt)
+    predp[:, :w] = synth.pred_from(rng, srcp[:, :w], bd)
+    rows = [H.oracle_qrow(bd, q) for q in (30, 110, 220)]
+    qrows = np.array([b200av1.qrow_from_oracle(r) for r in rows], b200av1.QROW_DTYPE)
+    q_kind = b200av1.Q_B if bd == 8 else b200av1.Q_B_HBD  # prune_txk_type_separ quantises with _B
+    in_kind = b200av1.IN_PIXELS8 if bd == 8 else b200av1.IN_PIXELS16
+    recs, precs = [], []
+    for ts in (0, 5, 6, 1, 7, 8, 2, 13, 14, 3, 4):
+        W, Hh = H.TX_W[ts], H.TX_H[ts]
+        for k, off in enumerate(synth.tile_blocks(w, h, stride, W, Hh)[:6]):
+            for tt in range(16):
+                if H.tx_valid(ts, tt):
+                    recs.append((off, 0, stride, (k + tt) % 3, ts, tt, 0))
+                    precs.append((off, stride, 0))
+    blocks = np.array(recs, b200av1.TXBLOCK_DTYPE)
+    preds = np.array(precs, b200av1.TXPRED_DTYPE)
+    perm = rng.permutation(len(blocks))
+    blocks, preds = blocks[perm], preds[perm]
+    got, d2h = b200av1.txsearch_batch_host(ctx, in_kind, q_kind, bd, 7, blocks, preds, srcp, predp, qrows)
+    assert d2h == len(blocks) * 30
+    # oracle: dense outputs at offsets of our own choosing
+    ob = blocks.copy()
+    o = 0
+    for i in range(len(ob)):
+        ob[i]["out_offset"] = o
+        o += H.max_eob(int(ob[i]["tx_size"]))
+    r = H.oracle_txq_batch(srcp.reshape(-1), ob, rows, q_kind, bd, o, in_kind, predp.reshape(-1), preds)
+    coeff, qc, dq, eob, dist = r
+    assert np.array_equal(got["eob"], eob)
+    assert np.array_equal(got["dist_tx"], dist[:, 0]) and np.array_equal(got["ssz"], dist[:, 1])
+    _, want_px = _oracle_itx(ob, preds, dq, eob, srcp.reshape(-1), predp.reshape(-1), int(bd > 8), bd)
+    assert np.array_equal(got["dist_px"], want_px)
+    for i in range(len(ob)):
+        ts, tt = int(ob[i]["tx_size"]), int(ob[i]["tx_type"])
+        want = 0
+        if eob[i]:
+            q = np.ascontiguousarray(qc[int(ob[i]["out_offset"]):int(ob[i]["out_offset"]) + H.max_eob(ts)])
+            want = O.av1o_cost_coeffs_txb_estimate(ptr(q, i32p), int(eob[i]), ts, tt)
+        assert got["rate_est"][i] == want, (i, ts, tt)
+    assert (eob > 0).any() and (eob == 0).any() or bd > 8

@@ -140,3 +140,25 @@ def test_inverse_transform_block_and_px_dist(highbd, bd):
                     d = O.av1o_dist_block_px(src.ctypes.data_as(C.c_void_p), stride,
                                              b.ctypes.data_as(C.c_void_p), stride, vw, vh, highbd, bd)
                     assert d == 16 * (s & 0xffffffff), (tx_size, tx_type, vw, vh)
+
+
+def test_cost_coeffs_txb_estimate():
+    """av1_cost_coeffs_txb_estimate (txb_rdopt.c:547) through a bare MACROBLOCK (oracle/ref_shim.c)"""
+    R, O = H.ref(), H.oracle()
+    rng = np.random.default_rng(7500)
+    for ts in range(H.N_TX_SIZES):
+        n = H.max_eob(ts)
+        for tt in range(16):
+            if not H.tx_valid(ts, tt):
+                continue
+            scan, _ = H.oracle_scan(ts, tt)
+            for it in range(4):
+                q = np.zeros(n, np.int32)
+                eob = int(rng.integers(1, n + 1)) if it else 1
+                lv = rng.integers(-3, 4, eob) if it < 3 else rng.integers(-40000, 40000, eob)
+                q[scan[:eob]] = lv
+                if q[scan[eob - 1]] == 0:
+                    q[scan[eob - 1]] = 1 + it
+                a = R.refshim_cost_coeffs_txb_estimate(ptr(q, i32p), eob, ts, tt)
+                b = O.av1o_cost_coeffs_txb_estimate(ptr(q, i32p), eob, ts, tt)
+                assert a == b, (ts, tt, it)
