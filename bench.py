@@ -481,6 +481,132 @@ def bench_hbd4k(ctx, dev, stream, steps, warmup, seed, n_frames=3):
             "launches_per_step": 19}
 
 
+def hbm_peak_gbs():
+    """roofline denominator: the driver-measured copy bandwidth, else the profiling guide's fallback"""
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0))
+    except (OSError, ValueError):
+        return 6650.0
+
+
+def bench_itx(ctx, dev, stream, steps, warmup, seed, hbm_peak, n_frames=8):
+    """inverse transform + reconstruction + pixel-domain distortion of every block of
+    `n_frames` synthetic 1080p 8-bit 4:2:0 frames, all 19 TX sizes, chained on the descriptors, dqcoeff
+    and eob a fused forward launch (av1_quantize_fp from uint8 planes) left in HBM; then the transform-type
+    search through host buffers (b200_txsearch_batch_host): every valid tx type of every 8x8 and 16x16
+    luma block of one frame."""
+    import torch
+    import b200av1
+    planes = [(1920, 1080), (960, 540), (960, 540)]
+    frame_elems = sum(w * h for w, h in planes)
+    rng = np.random.default_rng([seed, 9001])
+    src = np.zeros((n_frames, frame_elems), np.uint8)
+    pred = np.zeros((n_frames, frame_elems), np.uint8)
+    for f in range(n_frames):
+        o = 0
+        for (w, h) in planes:
+            low = rng.integers(30, 220, (h // 8 + 1, w // 8 + 1))
+            img = np.kron(low, np.ones((8, 8), np.int64))[:h, :w] + rng.integers(-6, 7, (h, w))
+            pr = np.roll(img, (1, 1), (0, 1)) + rng.integers(-4, 5, (h, w))
+            src[f, o:o + w * h] = np.clip(img, 0, 255).reshape(-1)
+            pred[f, o:o + w * h] = np.clip(pr, 0, 255).reshape(-1)
+            o += w * h
+    d_src = torch.from_numpy(src.reshape(-1)).to(dev)
+    d_pred = torch.from_numpy(pred.reshape(-1)).to(dev)
+    d_recon = torch.empty_like(d_pred)
+    qrows = build_qrows(8)
+    d_qrows = torch.from_numpy(qrows.view(np.uint8)).to(dev)
+    n_out = n_frames * frame_elems
+    d_qc, d_dq = (torch.empty(n_out, dtype=torch.int32, device=dev) for _ in range(2))
+    fwd, inv, keep, per_size = [], [], [], []
+    for ts in range(19):
+        blocks, samples = make_descriptors(ts, n_frames, planes, frame_elems, seed + 9)
+        preds = np.zeros(blocks.size, b200av1.TXPRED_DTYPE)
+        preds["pred_offset"], preds["pred_stride"] = blocks["src_offset"], blocks["src_stride"]
+        d_blocks = torch.from_numpy(blocks.view(np.uint8)).to(dev)
+        d_preds = torch.from_numpy(preds.view(np.uint8)).to(dev)
+        d_eob = torch.zeros(blocks.size, dtype=torch.int16, device=dev)
+        d_dist = torch.zeros(blocks.size, dtype=torch.int64, device=dev)
+        keep += [d_blocks, d_preds, d_eob, d_dist]
+        l = b200av1.TxqLaunch()
+        l.tx_size, l.in_kind, l.q_kind, l.bd, l.flags = ts, b200av1.IN_PIXELS8, b200av1.Q_FP, 8, 0
+        l.n_blocks = int(blocks.size)
+        l.blocks, l.preds = d_blocks.data_ptr(), d_preds.data_ptr()
+        l.src, l.pred, l.qrows = d_src.data_ptr(), d_pred.data_ptr(), d_qrows.data_ptr()
+        l.qcoeff, l.dqcoeff, l.eob = d_qc.data_ptr(), d_dq.data_ptr(), d_eob.data_ptr()
+        fwd.append(l)
+        il = b200av1.ItxLaunch(ts, 0, 8, int(blocks.size), d_blocks.data_ptr(), d_preds.data_ptr(),
+                               d_dq.data_ptr(), d_eob.data_ptr(), d_src.data_ptr(), d_pred.data_ptr(),
+                               d_recon.data_ptr(), d_dist.data_ptr(), 0)
+        inv.append(il)
+        # algorithmic bytes: kept dqcoeff (4 B) + pred + src in, recon out (1 B each), eob 2 B + dist 8 B per block
+        per_size.append((blocks.size * (max_eob(ts) * 4 + TX_W[ts] * TX_H[ts] * 3 + 10), samples, d_eob))
+    lib = b200av1.lib()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    kernels, tot_ms, tot_bytes, tot_samples, coded = [], 0.0, 0, 0, []
+    for ts in range(19):
+        ctx.txq_launch(fwd[ts], stream.cuda_stream)  # dqcoeff / eob of this size (the buffers are shared)
+        ms = 0.0
+        for it in range(warmup + steps):
+            ev[0].record(stream)
+            b200av1.check(lib.b200_itx_launch(ctx.h, C.byref(inv[ts]), C.c_void_p(stream.cuda_stream)))
+            ev[1].record(stream)
+            torch.cuda.synchronize(dev)
+            if it >= warmup:
+                ms += ev[0].elapsed_time(ev[1])
+        ms /= steps
+        nbytes, samples, d_eob = per_size[ts]
+        coded.append(float((d_eob != 0).float().mean().item()))
+        gbps = nbytes / (ms * 1e-3) / 1e9
+        kernels.append({"tx": "%dx%d" % (TX_W[ts], TX_H[ts]), "ms": round(ms, 4), "GBps": round(gbps, 1),
+                        "frac": round(gbps / hbm_peak, 3), "coded_blocks": round(coded[-1], 3)})
+        tot_ms += ms
+        tot_bytes += nbytes
+        tot_samples += samples
+    out = {"workload": "%d synthetic 1080p 8-bit 4:2:0 frames, all 19 TX sizes: b200_itx_launch (inverse transform + "
+                       "reconstruction written + dist_block_px_domain) on the dqcoeff / eob of the fused forward launch"
+                       % n_frames,
+           "ms_per_sweep": tot_ms, "fe1080p_per_s": tot_samples / FE_SAMPLES / (tot_ms * 1e-3),
+           "GBps": tot_bytes / (tot_ms * 1e-3) / 1e9, "frac": tot_bytes / (tot_ms * 1e-3) / 1e9 / hbm_peak,
+           "bytes_per_sweep": int(tot_bytes), "launches_per_step": 19, "kernels": kernels,
+           "bytes_rule": "4 B per kept dqcoeff + 1 B pred + 1 B src in, 1 B recon out per sample, 10 B per block"}
+    # ---- transform-type search through host buffers: all valid types of the 8x8 / 16x16 luma blocks of a frame
+    recs = []
+    w, h = planes[0]
+    for ts in (1, 2):
+        W, Hh = TX_W[ts], TX_H[ts]
+        offs = (np.arange(h // Hh)[:, None] * Hh * w + np.arange(w // W)[None, :] * W).reshape(-1)
+        for tt in valid_types(ts):
+            b = np.zeros(offs.size, b200av1.TXBLOCK_DTYPE)
+            b["src_offset"], b["src_stride"], b["tx_size"], b["tx_type"] = offs, w, ts, tt
+            b["qrow"] = 2
+            recs.append(b)
+    sblocks = np.concatenate(recs)
+    spreds = np.zeros(sblocks.size, b200av1.TXPRED_DTYPE)
+    spreds["pred_offset"], spreds["pred_stride"] = sblocks["src_offset"], sblocks["src_stride"]
+    h_src, h_pred = pinned_copy(src[0, :w * h]), pinned_copy(pred[0, :w * h])
+    res, d2h = None, 0
+    t_best = None
+    for it in range(4):
+        t0 = time.perf_counter()
+        res, d2h = b200av1.txsearch_batch_host(ctx, b200av1.IN_PIXELS8, b200av1.Q_B, 8, 7, sblocks, spreds,
+                                               h_src, h_pred, qrows)
+        dt = time.perf_counter() - t0
+        if it and (t_best is None or dt < t_best):
+            t_best = dt
+    cand_samples = int(sum(TX_W[int(t)] * TX_H[int(t)] for t in sblocks["tx_size"]))
+    out["txsearch_e2e"] = {
+        "workload": "b200_txsearch_batch_host: every valid tx type (16 per block) of the %d 8x8 and 16x16 luma blocks "
+                    "of one 1080p frame = %d candidates; host planes in, {eob, tx-domain error, rate estimate, "
+                    "pixel-domain distortion} out" % (sblocks.size // 16, sblocks.size),
+        "ms": t_best * 1e3, "candidates_per_s": sblocks.size / t_best,
+        "fe1080p_per_s": cand_samples / FE_SAMPLES / t_best,
+        "h2d_bytes": int(h_src.nbytes + h_pred.nbytes + sblocks.nbytes + spreds.nbytes + qrows.nbytes),
+        "d2h_bytes": int(d2h), "d2h_bytes_dense_equivalent": int(cand_samples * 12 + sblocks.size * 2),
+        "coded_fraction": float((res["eob"] != 0).mean())}
+    return out
+
+
 def bench_tf_queue(ctx, luma, seed, n_threads, reps=3):
     """The first consumer of the block queue: tf_motion_search over one 1080p
     frame pair -- 8160 16x16 blocks + 32640 8x8 sub-blocks, full-pel NSTEP + mesh and 8-tap sub-pel each
@@ -1108,6 +1234,7 @@ def main():
         if world == 1:
             extras["hadamard"] = bench_hadamard(ctx, dev, stream, max(2, args.steps // 2), 2, d_src, args.frames)
             extras["hbd4k"] = bench_hbd4k(ctx, dev, stream, max(2, args.steps // 2), 2, seed)
+            extras["itx"] = bench_itx(ctx, dev, stream, max(2, args.steps // 2), 2, seed, hbm_peak_gbs())
             if not args.no_cpu:
                 extras["tf_queue"] = bench_tf_queue(ctx, luma, seed, os.cpu_count() or 1)
         # BASELINE configs[4] at every N: 120 frames over the ranks
