@@ -84,6 +84,28 @@ void av1o_int_pro_col(int16_t *vbuf, const uint8_t *ref, int ref_stride, int wid
                       int norm_factor);
 int av1o_vector_var(const int16_t *ref, const int16_t *src, int bwl);
 
+/* ---- compound / masked / OBMC SAD and variance (av1o_compound.c) ------------------ */
+enum { AV1O_BLEND_NONE = 0, AV1O_BLEND_AVG, AV1O_BLEND_DIST_WTD, AV1O_BLEND_MASK };
+typedef struct {
+  int w, h, highbd, bd;
+  const void *pre;          /* predictor plane (the reference functions' `ref` / interpolated `a` / `pre`) */
+  int pre_stride;
+  int subpel, xoff, yoff;   /* bilinear 1/8-pel interpolation of pre (the *_sub_pixel_* functions) */
+  const void *tgt;          /* the plane compared against (`src` / `b`) */
+  int tgt_stride;
+  int blend;                /* AV1O_BLEND_* */
+  const void *second_pred;  /* w-pitch block */
+  const uint8_t *mask;      /* AV1O_BLEND_MASK */
+  int mask_stride, invert_mask;
+  int fwd_offset, bck_offset; /* DIST_WTD_COMP_PARAMS */
+  const int32_t *wsrc, *obmc_mask; /* OBMC: w-pitch blocks */
+} Av1oCompound;
+void av1o_compound_pred(const Av1oCompound *c, void *comp_pred);
+unsigned av1o_compound_sad(const Av1oCompound *c);
+unsigned av1o_compound_variance(const Av1oCompound *c, unsigned *sse);
+unsigned av1o_obmc_sad(const Av1oCompound *c);
+unsigned av1o_obmc_variance(const Av1oCompound *c, unsigned *sse);
+
 /* ---- scan tables (av1o_scan.c) ----------------------------------------------- */
 /* scan / iscan of av1_scan_orders[tx_size][tx_type] (scan.c:1666); n = max_eob */
 const int16_t *av1o_scan(int tx_size, int tx_type);
