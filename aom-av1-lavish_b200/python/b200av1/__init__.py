@@ -239,6 +239,21 @@ class PixLaunch(C.Structure):
                 ("out", C.c_void_p)]
 
 
+PIXMASK_DTYPE = np.dtype([("mask_offset", "<u4"), ("mask_stride", "<u2"), ("invert_mask", "u1"),
+                          ("reserved", "u1")])
+assert PIXMASK_DTYPE.itemsize == 8
+(CMP_MASKED_SAD, CMP_MASKED_SUBPEL_VAR, CMP_SUBPEL_AVG_VAR, CMP_DIST_WTD_SUBPEL_AVG_VAR, CMP_DIST_WTD_SAD_AVG,
+ CMP_OBMC_SAD, CMP_OBMC_VAR, CMP_OBMC_SUBPEL_VAR, CMP_AVG_PRED, CMP_DIST_WTD_AVG_PRED, CMP_MASK_PRED) = range(11)
+
+
+class CompoundLaunch(C.Structure):
+    _fields_ = [("op", C.c_int), ("highbd", C.c_int), ("bd", C.c_int), ("n_blocks", C.c_int),
+                ("blocks", C.c_void_p), ("masks", C.c_void_p), ("pre", C.c_void_p), ("tgt", C.c_void_p),
+                ("second_pred", C.c_void_p), ("mask", C.c_void_p), ("wsrc", C.c_void_p),
+                ("obmc_mask", C.c_void_p), ("fwd_offset", C.c_int), ("bck_offset", C.c_int),
+                ("out", C.c_void_p), ("comp_pred", C.c_void_p)]
+
+
 class QuantLaunch(C.Structure):
     _fields_ = [("kind", C.c_int), ("n_blocks", C.c_int), ("blocks", C.c_void_p),
                 ("coeff", C.c_void_p), ("qrows", C.c_void_p), ("iscan", C.c_void_p),

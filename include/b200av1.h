@@ -387,6 +387,50 @@ typedef struct {
 } B200PixLaunch;
 int b200_pix_launch(b200_ctx *ctx, const B200PixLaunch *launch, void *stream);
 
+/* ------------------ compound / masked / OBMC SAD and variance ---- */
+/* The aom_variance_fn_ptr_t members (aom_dsp/variance.h:92-113) beyond sdf / vf / svf, one warp per
+ * block.  Operands: `pre` = the predictor plane at a_offset / a_stride (the reference functions' `ref`
+ * in the SAD family, the interpolated first argument `a` / `src` / `pre` in the variance family,
+ * `ref` in the builders); `tgt` = the plane compared against at b_offset / b_stride (`src` in the SAD
+ * family, `b` / `ref` in the variance family); second_pred, wsrc and obmc_mask are w-pitch blocks at
+ * aux_offset; the builders write a w-pitch block to comp_pred + b_offset.  out0 = SAD or variance,
+ * out1 = sse (variance ops). */
+enum {
+  B200_CMP_MASKED_SAD = 0,          /* aom_masked_sadWxH / aom_highbd_masked_sadWxH (sad_av1.c:42,122) */
+  B200_CMP_MASKED_SUBPEL_VAR,       /* aom_masked_sub_pixel_varianceWxH, highbd 8/10/12 (variance.c:769,838) */
+  B200_CMP_SUBPEL_AVG_VAR,          /* aom_sub_pixel_avg_varianceWxH (variance.c:147), highbd (:551-600) */
+  B200_CMP_DIST_WTD_SUBPEL_AVG_VAR, /* aom_dist_wtd_sub_pixel_avg_varianceWxH (variance.c:165), highbd (:603-665) */
+  B200_CMP_DIST_WTD_SAD_AVG,        /* aom_dist_wtd_sadWxH_avg (sad.c:57), highbd (:290) */
+  B200_CMP_OBMC_SAD,                /* aom_obmc_sadWxH / highbd (sad_av1.c:163-262) */
+  B200_CMP_OBMC_VAR,                /* aom_obmc_varianceWxH, highbd 8/10/12 (variance.c:933-960,1040-1125) */
+  B200_CMP_OBMC_SUBPEL_VAR,         /* aom_obmc_sub_pixel_varianceWxH, highbd (variance.c:962,1126) */
+  B200_CMP_AVG_PRED,                /* aom_comp_avg_pred / aom_highbd_comp_avg_pred (variance.c:285,708) */
+  B200_CMP_DIST_WTD_AVG_PRED,       /* aom_dist_wtd_comp_avg_pred / highbd (variance.c:300,725) */
+  B200_CMP_MASK_PRED                /* aom_comp_mask_pred / aom_highbd_comp_mask_pred (variance.c:749,816) */
+};
+typedef struct {
+  uint32_t mask_offset; /* bytes from `mask` to the block's first weight (0..64, AOM_BLEND_A64) */
+  uint16_t mask_stride;
+  uint8_t invert_mask;
+  uint8_t reserved;
+} B200PixMask; /* 8 bytes */
+typedef struct {
+  int op;      /* B200_CMP_* */
+  int highbd;  /* 0: uint8 pixels, 1: uint16 */
+  int bd;      /* 8 / 10 / 12 */
+  int n_blocks;
+  const B200PixBlock *blocks;   /* device; xoff / yoff = 1/8-pel bilinear offsets of the *_SUBPEL_* ops */
+  const B200PixMask *masks;     /* device, masked ops */
+  const void *pre, *tgt;        /* device pixel planes */
+  const void *second_pred;      /* device */
+  const uint8_t *mask;          /* device */
+  const int32_t *wsrc, *obmc_mask; /* device, OBMC ops (calc_target_weighted_pred, av1/encoder/rdopt.c) */
+  int fwd_offset, bck_offset;   /* DIST_WTD_COMP_PARAMS (av1_dist_wtd_comp_weight_assign) */
+  uint32_t *out;                /* device, 2 per block */
+  void *comp_pred;              /* device, builders */
+} B200CompoundLaunch;
+int b200_compound_launch(b200_ctx *ctx, const B200CompoundLaunch *launch, void *stream);
+
 /* aom_subtract_block / aom_highbd_subtract_block (aom_dsp/subtract.c:20,35) over a batch:
  * diff = a - b for every block (a = src, b = pred); diff rows are `w` apart. */
 typedef struct {
