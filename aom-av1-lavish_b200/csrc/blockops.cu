@@ -306,6 +306,8 @@ __device__ __forceinline__ void pix_block(const B200PixLaunch &l, const B200PixB
     out1 = sse32;
     if (op == B200_PIX_MSE) {
       out0 = sse32;
+    } else if (op == B200_PIX_VAR_SUM) {
+      out0 = (uint32_t)isum;
     } else {
       const int64_t mean2 = ((int64_t)isum * isum) / (d.w * d.h);
       if (hb && l.bd > 8) {
@@ -421,6 +423,24 @@ __global__ void __launch_bounds__(kWarps * 32) upsample_kernel(const B200Upsampl
   else upsample_block<uint8_t>(l, d, lane);
 }
 
+// av1_round_shift_array_c (av1/common/av1_txfm.c:71-87)
+__global__ void round_shift_array_kernel(int32_t *arr, int size, int bit) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= size) return;
+  if (bit > 0) {
+    arr[i] = (int32_t)(((int64_t)arr[i] + ((int64_t)1 << (bit - 1))) >> bit);
+  } else {
+    const int64_t v = (int64_t)arr[i] * ((int64_t)1 << (-bit));
+    arr[i] = (int32_t)(v > INT32_MAX ? INT32_MAX : (v < INT32_MIN ? INT32_MIN : v));
+  }
+}
+int round_shift_array_launch(b200_ctx *, int32_t *arr, int size, int bit, cudaStream_t s) {
+  if (size <= 0 || bit == 0) return B200_OK;
+  round_shift_array_kernel<<<(size + 255) / 256, 256, 0, s>>>(arr, size, bit);
+  B200_CUDA_TRY(cudaGetLastError());
+  return B200_OK;
+}
+
 int blockops_init_device(b200_ctx *) { return B200_OK; }
 
 static int grid_for(int n_blocks) { return (n_blocks + kWarps - 1) / kWarps; }
@@ -466,7 +486,7 @@ extern "C" int b200_block_error_launch(b200_ctx *ctx, const B200ErrLaunch *l, vo
 
 extern "C" int b200_pix_launch(b200_ctx *ctx, const B200PixLaunch *l, void *stream) {
   B200_LAUNCH_PROLOGUE(l)
-  if (!l->blocks || !l->a || !l->b || !l->out || l->op < 0 || l->op > B200_PIX_SSE ||
+  if (!l->blocks || !l->a || !l->b || !l->out || l->op < 0 || l->op > B200_PIX_VAR_SUM ||
       (l->op == B200_PIX_SAD_AVG && !l->aux)) {
     set_error("b200_pix_launch: missing buffer or bad op");
     return B200_EINVAL;

@@ -78,6 +78,7 @@ int itx_launch(b200_ctx *ctx, const B200ItxLaunch &l, cudaStream_t s);
 // max_eob entries each, see txq.cu) and the scan class of a tx_type
 size_t scan_dev_offset(int tx_size);
 __host__ __device__ inline int scan_class_of(int tx_type) { return tx_type < 10 ? 0 : ((tx_type & 1) ? 2 : 1); }
+int round_shift_array_launch(b200_ctx *ctx, int32_t *arr, int size, int bit, cudaStream_t s);
 int scratch_reserve(b200_ctx *ctx, size_t bytes);
 int host_scratch_reserve(b200_ctx *ctx, size_t bytes);  // pinned staging (capi.cu)
 // hadamard.cu: single-call helpers behind the drop-in tier

@@ -863,3 +863,5 @@ int aom_vector_var_b200(const int16_t *ref, const int16_t *src, int bwl) {
   return r;
 }
 }  // extern "C"
+
+#include "rtcd_compound.inc"

@@ -367,7 +367,8 @@ enum {
   B200_PIX_VAR = 3,      /* aom_varianceWxH (variance.c:123)          out0 = var, out1 = sse */
   B200_PIX_MSE = 4,      /* aom_mseWxH (variance.c:235)               out0 = sse, out1 = sse */
   B200_PIX_SUBPEL_VAR = 5, /* aom_sub_pixel_varianceWxH (variance.c:132)   out0 = var, out1 = sse */
-  B200_PIX_SSE = 6       /* aom_sse (aom_dsp/sse.c:19)         out0 = low 32, out1 = high 32 */
+  B200_PIX_SSE = 6,      /* aom_sse (aom_dsp/sse.c:19)         out0 = low 32, out1 = high 32 */
+  B200_PIX_VAR_SUM = 7   /* aom_get8x8var / aom_get16x16var (variance.c GET_VAR)  out0 = (int) sum, out1 = sse */
 };
 typedef struct {
   uint32_t a_offset, b_offset; /* pixels from the plane bases */

@@ -272,6 +272,146 @@ void aom_int_pro_col_b200(int16_t *vbuf, const uint8_t *ref, const int ref_strid
                           const int height, int norm_factor);
 int aom_vector_var_b200(const int16_t *ref, const int16_t *src, int bwl);
 
+/* ---- compound / masked / OBMC members: aom_dsp_rtcd_defs.pl:884-889 (highbd
+ *      _avg, dist_wtd), :1016-1032 (masked SAD), :1040-1060 (OBMC SAD), :1139-1141 (highbd x3d / skip
+ *      x4d), :1303-1304 (aom_get8x8var / 16x16var), :1370-1420 (OBMC variance), :1440-1465 (avg /
+ *      dist_wtd sub-pel variance), :1530-1560 (masked sub-pel variance, comp preds) ---- */
+typedef struct { /* DIST_WTD_COMP_PARAMS, aom_dsp/aom_dsp_common.h (layout-compatible) */
+  int use_dist_wtd_comp_avg;
+  int fwd_offset;
+  int bck_offset;
+} B200DistWtdCompParams;
+
+#define B200_DECL_HBD3(NAME, ARGS)               \
+  unsigned int aom_highbd_8_##NAME##_b200 ARGS;  \
+  unsigned int aom_highbd_10_##NAME##_b200 ARGS; \
+  unsigned int aom_highbd_12_##NAME##_b200 ARGS;
+#define B200_DECL_HBD_OBMC(NAME, ARGS)           \
+  unsigned int aom_highbd_##NAME##_b200 ARGS;    \
+  unsigned int aom_highbd_10_##NAME##_b200 ARGS; \
+  unsigned int aom_highbd_12_##NAME##_b200 ARGS;
+#define B200_MSVAR_ARGS                                                                                \
+  (const uint8_t *src, int src_stride, int xoffset, int yoffset, const uint8_t *ref, int ref_stride,   \
+   const uint8_t *second_pred, const uint8_t *msk, int msk_stride, int invert_mask, unsigned int *sse)
+#define B200_SVAVAR_ARGS                                                                               \
+  (const uint8_t *src_ptr, int source_stride, int xoffset, int yoffset, const uint8_t *ref_ptr,        \
+   int ref_stride, uint32_t *sse, const uint8_t *second_pred)
+#define B200_JSVAVAR_ARGS                                                                              \
+  (const uint8_t *src_ptr, int source_stride, int xoffset, int yoffset, const uint8_t *ref_ptr,        \
+   int ref_stride, uint32_t *sse, const uint8_t *second_pred, const B200DistWtdCompParams *jcp_param)
+#define B200_OVAR_ARGS \
+  (const uint8_t *pre, int pre_stride, const int32_t *wsrc, const int32_t *mask, unsigned int *sse)
+#define B200_OSVAR_ARGS                                                                                \
+  (const uint8_t *pre, int pre_stride, int xoffset, int yoffset, const int32_t *wsrc, const int32_t *mask, \
+   unsigned int *sse)
+#define B200_DECL_COMPOUND_FNS(W, H)                                                                          \
+  unsigned int aom_highbd_sad##W##x##H##_avg_b200(const uint8_t *src_ptr, int src_stride,                      \
+                                                  const uint8_t *ref_ptr, int ref_stride,                      \
+                                                  const uint8_t *second_pred);                                 \
+  void aom_highbd_sad##W##x##H##x3d_b200(const uint8_t *src_ptr, int src_stride,                               \
+                                         const uint8_t *const ref_ptr[], int ref_stride, uint32_t *sad_array); \
+  void aom_highbd_sad_skip_##W##x##H##x4d_b200(const uint8_t *src_ptr, int src_stride,                         \
+                                               const uint8_t *const ref_ptr[], int ref_stride,                 \
+                                               uint32_t *sad_array);                                           \
+  unsigned int aom_masked_sad##W##x##H##_b200(const uint8_t *src, int src_stride, const uint8_t *ref,          \
+                                              int ref_stride, const uint8_t *second_pred, const uint8_t *msk,  \
+                                              int msk_stride, int invert_mask);                                \
+  unsigned int aom_highbd_masked_sad##W##x##H##_b200(const uint8_t *src8, int src_stride, const uint8_t *ref8, \
+                                                     int ref_stride, const uint8_t *second_pred8,              \
+                                                     const uint8_t *msk, int msk_stride, int invert_mask);     \
+  unsigned int aom_masked_sub_pixel_variance##W##x##H##_b200 B200_MSVAR_ARGS;                                  \
+  B200_DECL_HBD3(masked_sub_pixel_variance##W##x##H, B200_MSVAR_ARGS)                                          \
+  uint32_t aom_sub_pixel_avg_variance##W##x##H##_b200 B200_SVAVAR_ARGS;                                        \
+  B200_DECL_HBD3(sub_pixel_avg_variance##W##x##H, B200_SVAVAR_ARGS)                                            \
+  uint32_t aom_dist_wtd_sub_pixel_avg_variance##W##x##H##_b200 B200_JSVAVAR_ARGS;                              \
+  B200_DECL_HBD3(dist_wtd_sub_pixel_avg_variance##W##x##H, B200_JSVAVAR_ARGS)                                  \
+  unsigned int aom_dist_wtd_sad##W##x##H##_avg_b200(const uint8_t *src_ptr, int src_stride,                    \
+                                                    const uint8_t *ref_ptr, int ref_stride,                    \
+                                                    const uint8_t *second_pred,                                \
+                                                    const B200DistWtdCompParams *jcp_param);                   \
+  unsigned int aom_highbd_dist_wtd_sad##W##x##H##_avg_b200(const uint8_t *src_ptr, int src_stride,             \
+                                                           const uint8_t *ref_ptr, int ref_stride,             \
+                                                           const uint8_t *second_pred,                         \
+                                                           const B200DistWtdCompParams *jcp_param);            \
+  unsigned int aom_obmc_sad##W##x##H##_b200(const uint8_t *pre, int pre_stride, const int32_t *wsrc,           \
+                                            const int32_t *mask);                                              \
+  unsigned int aom_highbd_obmc_sad##W##x##H##_b200(const uint8_t *pre, int pre_stride, const int32_t *wsrc,    \
+                                                   const int32_t *mask);                                       \
+  unsigned int aom_obmc_variance##W##x##H##_b200 B200_OVAR_ARGS;                                               \
+  unsigned int aom_obmc_sub_pixel_variance##W##x##H##_b200 B200_OSVAR_ARGS;                                    \
+  B200_DECL_HBD_OBMC(obmc_variance##W##x##H, B200_OVAR_ARGS)                                                   \
+  B200_DECL_HBD_OBMC(obmc_sub_pixel_variance##W##x##H, B200_OSVAR_ARGS)
+B200_DECL_COMPOUND_FNS(128, 128)
+B200_DECL_COMPOUND_FNS(128, 64)
+B200_DECL_COMPOUND_FNS(64, 128)
+B200_DECL_COMPOUND_FNS(64, 64)
+B200_DECL_COMPOUND_FNS(64, 32)
+B200_DECL_COMPOUND_FNS(32, 64)
+B200_DECL_COMPOUND_FNS(32, 32)
+B200_DECL_COMPOUND_FNS(32, 16)
+B200_DECL_COMPOUND_FNS(16, 32)
+B200_DECL_COMPOUND_FNS(16, 16)
+B200_DECL_COMPOUND_FNS(16, 8)
+B200_DECL_COMPOUND_FNS(8, 16)
+B200_DECL_COMPOUND_FNS(8, 8)
+B200_DECL_COMPOUND_FNS(8, 4)
+B200_DECL_COMPOUND_FNS(4, 8)
+B200_DECL_COMPOUND_FNS(4, 4)
+B200_DECL_COMPOUND_FNS(4, 16)
+B200_DECL_COMPOUND_FNS(16, 4)
+B200_DECL_COMPOUND_FNS(8, 32)
+B200_DECL_COMPOUND_FNS(32, 8)
+B200_DECL_COMPOUND_FNS(16, 64)
+B200_DECL_COMPOUND_FNS(64, 16)
+void aom_comp_avg_pred_b200(uint8_t *comp_pred, const uint8_t *pred, int width, int height,
+                            const uint8_t *ref, int ref_stride);
+void aom_highbd_comp_avg_pred_b200(uint8_t *comp_pred8, const uint8_t *pred8, int width, int height,
+                                   const uint8_t *ref8, int ref_stride);
+void aom_dist_wtd_comp_avg_pred_b200(uint8_t *comp_pred, const uint8_t *pred, int width, int height,
+                                     const uint8_t *ref, int ref_stride,
+                                     const B200DistWtdCompParams *jcp_param);
+void aom_highbd_dist_wtd_comp_avg_pred_b200(uint8_t *comp_pred8, const uint8_t *pred8, int width,
+                                            int height, const uint8_t *ref8, int ref_stride,
+                                            const B200DistWtdCompParams *jcp_param);
+void aom_comp_mask_pred_b200(uint8_t *comp_pred, const uint8_t *pred, int width, int height,
+                             const uint8_t *ref, int ref_stride, const uint8_t *mask, int mask_stride,
+                             int invert_mask);
+void aom_highbd_comp_mask_pred_b200(uint8_t *comp_pred8, const uint8_t *pred8, int width, int height,
+                                    const uint8_t *ref8, int ref_stride, const uint8_t *mask,
+                                    int mask_stride, int invert_mask);
+void aom_get8x8var_b200(const uint8_t *src_ptr, int source_stride, const uint8_t *ref_ptr, int ref_stride,
+                        unsigned int *sse, int *sum);
+void aom_get16x16var_b200(const uint8_t *src_ptr, int source_stride, const uint8_t *ref_ptr,
+                          int ref_stride, unsigned int *sse, int *sum);
+/* av1_round_shift_array (av1_rtcd_defs.pl:269) */
+void av1_round_shift_array_b200(int32_t *arr, int size, int bit);
+
+/* aom_variance_fn_ptr_t (aom_dsp/variance.h:92-113), member for member, and the filler that binds
+ * every member of one block size to its `_b200` flavour -- what av1/encoder/encoder.c:1336-1600
+ * (BFP / HIGHBD_BFP / MBFP / OBFP) does for the `_c` and SIMD flavours. */
+typedef struct {
+  unsigned int (*sdf)(const uint8_t *, int, const uint8_t *, int);
+  unsigned int (*sdsf)(const uint8_t *, int, const uint8_t *, int);
+  unsigned int (*sdaf)(const uint8_t *, int, const uint8_t *, int, const uint8_t *);
+  unsigned int (*vf)(const uint8_t *, int, const uint8_t *, int, unsigned int *);
+  unsigned int (*svf)(const uint8_t *, int, int, int, const uint8_t *, int, unsigned int *);
+  unsigned int (*svaf)(const uint8_t *, int, int, int, const uint8_t *, int, unsigned int *, const uint8_t *);
+  void (*sdx4df)(const uint8_t *, int, const uint8_t *const[], int, unsigned int *);
+  void (*sdx3df)(const uint8_t *, int, const uint8_t *const[], int, unsigned int *);
+  void (*sdsx4df)(const uint8_t *, int, const uint8_t *const[], int, unsigned int *);
+  unsigned int (*msdf)(const uint8_t *, int, const uint8_t *, int, const uint8_t *, const uint8_t *, int, int);
+  unsigned int (*msvf)(const uint8_t *, int, int, int, const uint8_t *, int, const uint8_t *, const uint8_t *,
+                       int, int, unsigned int *);
+  unsigned int (*osdf)(const uint8_t *, int, const int32_t *, const int32_t *);
+  unsigned int (*ovf)(const uint8_t *, int, const int32_t *, const int32_t *, unsigned int *);
+  unsigned int (*osvf)(const uint8_t *, int, int, int, const int32_t *, const int32_t *, unsigned int *);
+  unsigned int (*jsdaf)(const uint8_t *, int, const uint8_t *, int, const uint8_t *,
+                        const B200DistWtdCompParams *);
+  unsigned int (*jsvaf)(const uint8_t *, int, int, int, const uint8_t *, int, unsigned int *, const uint8_t *,
+                        const B200DistWtdCompParams *);
+} B200VarianceFnPtr;
+int b200_variance_fn_ptr(int block_width, int block_height, int highbd, int bd, B200VarianceFnPtr *vt);
+
 #ifdef __cplusplus
 }
 #endif
