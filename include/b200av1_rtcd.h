@@ -30,7 +30,13 @@ extern "C" {
 typedef int32_t b200_tran_low_t; /* tran_low_t, aom_dsp/aom_dsp_common.h:57 */
 typedef uint8_t b200_qm_val_t;   /* qm_val_t */
 
-/* TxfmParam, aom_dsp/txfm_common.h:84-101 (layout-compatible) */
+/* TxfmParam, aom_dsp/txfm_common.h:84-101 (layout-compatible).  Inside libaom (generated rtcd
+ * headers, tools/gen_rtcd_b200.py) define B200AV1_RTCD_USE_AOM_TYPES: the prototypes then use the
+ * encoder's own TxfmParam / DIST_WTD_COMP_PARAMS so that they are the very types of the add_proto
+ * lines they replace. */
+#ifdef B200AV1_RTCD_USE_AOM_TYPES
+typedef struct txfm_param B200TxfmParam;
+#else
 typedef struct {
   uint8_t tx_type;     /* TX_TYPE */
   uint8_t tx_size;     /* TX_SIZE */
@@ -40,6 +46,7 @@ typedef struct {
   uint8_t tx_set_type; /* TxSetType */
   int eob;
 } B200TxfmParam;
+#endif
 
 /* ---- forward transforms: av1_rtcd_defs.pl:351-399 (av1_fwd_txfm2d_WxH), :269 ---- */
 #define B200_DECL_FWD_TXFM(W, H)                                                           \
@@ -235,12 +242,21 @@ unsigned int aom_mse8x8_b200(const uint8_t *src_ptr, int source_stride, const ui
 /* ---- sub-pel predictor: av1_rtcd_defs.pl:282-285,309-312.  xd / cm / mv are only used by
  * the reference for scaled references; this flavour implements the unscaled branch
  * (reconinter_enc.c:461-495) and ignores them. ---- */
-void aom_upsampled_pred_b200(void *xd, const void *cm, int mi_row, int mi_col, const void *mv,
-                             uint8_t *comp_pred, int width, int height, int subpel_x_q3,
-                             int subpel_y_q3, const uint8_t *ref, int ref_stride,
+#ifdef B200AV1_RTCD_USE_AOM_TYPES
+#define B200_XD_T MACROBLOCKD
+#define B200_CM_T struct AV1Common
+#define B200_MV_T MV
+#else
+#define B200_XD_T void
+#define B200_CM_T void
+#define B200_MV_T void
+#endif
+void aom_upsampled_pred_b200(B200_XD_T *xd, const B200_CM_T *const cm, int mi_row, int mi_col,
+                             const B200_MV_T *const mv, uint8_t *comp_pred, int width, int height,
+                             int subpel_x_q3, int subpel_y_q3, const uint8_t *ref, int ref_stride,
                              int subpel_search);
-void aom_highbd_upsampled_pred_b200(void *xd, const void *cm, int mi_row, int mi_col,
-                                    const void *mv, uint8_t *comp_pred8, int width, int height,
+void aom_highbd_upsampled_pred_b200(B200_XD_T *xd, const B200_CM_T *const cm, int mi_row, int mi_col,
+                                    const B200_MV_T *const mv, uint8_t *comp_pred8, int width, int height,
                                     int subpel_x_q3, int subpel_y_q3, const uint8_t *ref8,
                                     int ref_stride, int bd, int subpel_search);
 /* ---- Hadamard / SATD / averages: aom_dsp_rtcd_defs.pl:1209-1279 (aom_dsp/avg.c), and the
@@ -276,11 +292,15 @@ int aom_vector_var_b200(const int16_t *ref, const int16_t *src, int bwl);
  *      _avg, dist_wtd), :1016-1032 (masked SAD), :1040-1060 (OBMC SAD), :1139-1141 (highbd x3d / skip
  *      x4d), :1303-1304 (aom_get8x8var / 16x16var), :1370-1420 (OBMC variance), :1440-1465 (avg /
  *      dist_wtd sub-pel variance), :1530-1560 (masked sub-pel variance, comp preds) ---- */
+#ifdef B200AV1_RTCD_USE_AOM_TYPES
+typedef DIST_WTD_COMP_PARAMS B200DistWtdCompParams;
+#else
 typedef struct { /* DIST_WTD_COMP_PARAMS, aom_dsp/aom_dsp_common.h (layout-compatible) */
   int use_dist_wtd_comp_avg;
   int fwd_offset;
   int bck_offset;
 } B200DistWtdCompParams;
+#endif
 
 #define B200_DECL_HBD3(NAME, ARGS)               \
   unsigned int aom_highbd_8_##NAME##_b200 ARGS;  \

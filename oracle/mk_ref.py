@@ -299,20 +299,55 @@ def build_flavour(flavour):
     print("mk_ref[%s]: built %s" % (flavour, exe))
 
 
+def build_b200_install():
+    """The `b200` RTCD flavour made executable (tools/gen_rtcd_b200.py): regenerated rtcd headers
+    (type-checked against include/b200av1_rtcd.h by compiling them) and libb200install.so, the run-time
+    binding for the already built avx2 reference library + aomenc_avx2."""
+    root = os.path.join(OUT, "rtcd_b200")
+    repo = os.path.dirname(HERE)
+    prod = os.path.join(repo, "aom-av1-lavish_b200", "libb200av1.so")
+    cfg = os.path.join(OUT, "avx2")
+    subprocess.run([sys.executable, os.path.join(repo, "tools", "gen_rtcd_b200.py"), "--ref", REF, "--config",
+                    os.path.join(cfg, "config"), "--out", root], check=True)
+    incs = ["-I" + root, "-I" + REF, "-I" + cfg, "-I" + os.path.join(repo, "include")]
+    for h in ("aom_dsp_rtcd", "av1_rtcd"):  # every _b200 prototype against the add_proto it replaces
+        chk = os.path.join(root, "chk_%s.c" % h)
+        with open(chk, "w") as f:
+            f.write('#define RTCD_C\n#include "config/aom_config.h"\n#include "config_b200/%s.h"\n' % h)
+        subprocess.run(["gcc", "-fsyntax-only", "-Werror", "-Wall", "-Wno-array-parameter", "-Wno-unused-function"]
+                       + incs + [chk], check=True)
+    if not os.path.exists(prod):
+        print("mk_ref: %s not built yet; libb200install.so skipped" % prod)
+        return
+    lib = os.path.join(OUT, "libb200install.so")
+    subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-Werror=incompatible-pointer-types", "-o", lib,
+                    os.path.join(root, "b200_rtcd_install.c"), os.path.join(HERE, "b200_install_shim.c")] + incs +
+                   [os.path.join(OUT, "libaomref_avx2.so"), prod, "-Wl,-rpath,$ORIGIN",
+                    "-Wl,-rpath,$ORIGIN/../../aom-av1-lavish_b200"], check=True)
+    print("mk_ref: built %s" % lib)
+
+
 def main():
     if not os.path.isdir(REF):
         print("mk_ref: %s absent; keeping any prebuilt oracle/_ref" % REF)
         return 0
     os.makedirs(OUT, exist_ok=True)
     targets = [os.path.join(OUT, n) for n in ("libaomref.so", "libaomref_avx2.so", "aomenc", "aomenc_avx2")]
+    install = os.path.join(OUT, "libb200install.so")
+    repo = os.path.dirname(HERE)
+    install_deps = [os.path.join(repo, "tools", "gen_rtcd_b200.py"), os.path.join(repo, "include", "b200av1_rtcd.h"),
+                    os.path.join(HERE, "b200_install_shim.c"), __file__]
     newest = max(os.path.getmtime(__file__), os.path.getmtime(os.path.join(HERE, "ref_shim.c")),
                  os.path.getmtime(os.path.join(HERE, "av1o_me.h")),
                  os.path.getmtime(os.path.join(HERE, "ref_asm_fallback.c")))
     if all(os.path.exists(t) and os.path.getmtime(t) > newest for t in targets) and "--force" not in sys.argv:
         print("mk_ref: up to date")
-        return 0
-    for flavour in ("generic", "avx2"):
-        build_flavour(flavour)
+    else:
+        for flavour in ("generic", "avx2"):
+            build_flavour(flavour)
+    if (not os.path.exists(install) or "--force" in sys.argv or
+            os.path.getmtime(install) < max([os.path.getmtime(p) for p in install_deps + targets[:2]])):
+        build_b200_install()
     return 0
 
 
