@@ -465,11 +465,31 @@ __device__ __noinline__ int pattern_search(const Ctx &k, bool skip, Mv start, in
 // Preconditions (checked by the caller): 8-bit, window staged in shared memory, no row
 // skipping, bw >= 4 * SEGW, bh a multiple of 4.
 constexpr int kRB = 4;  // vertically adjacent candidates per lane (step 1)
-constexpr int kJB = 4;  // horizontally adjacent candidates per lane (step 4 / 8 / 16)
+constexpr int kJB = 4;  // horizontally adjacent candidates per lane (step 4 / 8 / 16), 8-bit
+
+// One word of source against one word of reference.  PX = 1: four 8-bit pixels, one
+// VABSDIFF4.U8.ACC into a 32-bit total.  PX = 2 (uint16 planes): two pixels; sm_100 has no packed
+// 16-bit absolute difference (vabsdiff2 and the scalar half-word vabsdiff are emulated), but
+// |a - b| = max(a, b) - min(a, b) per half word, both VIMNMX.U16x2, and `acc + max - min` is ONE
+// IADD3 on the packed pair: no borrow crosses the halves because every half-word term is >= 0.
+// The packed halves hold at most 16 terms of 12 bits (16 * 4095 < 65536) before `sad_flush`
+// (IDP.2A) moves them into the 32-bit total.
+template <int PX>
+__device__ __forceinline__ unsigned sadw_acc(unsigned s, unsigned r, unsigned acc) {
+  if constexpr (PX == 1) return sad4_acc(s, r, acc);
+  else return acc + __vmaxu2(s, r) - __vminu2(s, r);
+}
+template <int PX>
+__device__ __forceinline__ void sad_flush(unsigned &acc, unsigned &tot) {
+  if constexpr (PX == 2) {
+    tot = __dp2a_lo(acc, 0x0101u, tot);
+    acc = 0;
+  }
+}
 
 // PHASE 0: first RB reference rows (source window filling), 1: steady state, 2: last RB - 1
 // rows (window draining).
-template <int SEGW, int PHASE>
+template <int SEGW, int PHASE, int PX>
 __device__ __forceinline__ void mesh1_chunk(int s_off, int src_pitch_b, int r_off, int pitch_b,
                                             unsigned sh, int t0, int tmax,
                                             unsigned (&sw)[kRB][SEGW], unsigned (&acc)[kRB]) {
@@ -490,65 +510,74 @@ __device__ __forceinline__ void mesh1_chunk(int s_off, int src_pitch_b, int r_of
       if (PHASE == 0 && c > u) continue;
       if (PHASE == 2 && c <= u) continue;
 #pragma unroll
-      for (int i = 0; i < SEGW; ++i) acc[c] = sad4_acc(sw[(u - c) & (kRB - 1)][i], rv[i], acc[c]);
+      for (int i = 0; i < SEGW; ++i) acc[c] = sadw_acc<PX>(sw[(u - c) & (kRB - 1)][i], rv[i], acc[c]);
     }
   }
 }
 
-template <int SEGW>
+template <int SEGW, int PX>
 __device__ void mesh1_band(const Ctx &k, int row0, int nrows, int col0, int nc) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int bh = k.d.bh, nseg = k.d.bw / (4 * SEGW);
+  const int bh = k.d.bh, nseg = k.d.bw * PX / (4 * SEGW);
   const int nrg = (nrows + kRB - 1) / kRB, ncc = (nc + 31) >> 5;
   const int ntask = nrg * nseg * ncc;
-  const int pitch_b = k.ref_pitch, src_pitch_b = k.src_pitch_w * 4;
+  const int pitch_b = k.ref_pitch * PX, src_pitch_b = k.src_pitch_w * 4;
   for (int task = warp; task < ntask; task += kWarps) {
     const int cc = task % ncc, seg = (task / ncc) % nseg, rg = task / (ncc * nseg);
     const int nk = min(kRB, nrows - rg * kRB);
     const int ci = cc * 32 + lane, cia = min(ci, nc - 1);
     const int row = row0 + rg * kRB, col = col0 + cia;
-    const int a = k.win0_off + row * pitch_b + col + seg * SEGW * 4;
+    const int a = k.win0_off + row * pitch_b + col * PX + seg * SEGW * 4;
     const int r_off = a & ~3, s_off = seg * SEGW * 4;
     const unsigned sh = (unsigned)(a & 3) * 8;
-    unsigned sw[kRB][SEGW], acc[kRB];
+    unsigned sw[kRB][SEGW], acc[kRB], tot[kRB];
 #pragma unroll
-    for (int c = 0; c < kRB; ++c) acc[c] = 0;
+    for (int c = 0; c < kRB; ++c) acc[c] = 0, tot[c] = 0;
     const int tmax = bh + nk - 1;
-    mesh1_chunk<SEGW, 0>(s_off, src_pitch_b, r_off, pitch_b, sh, 0, tmax, sw, acc);
-    for (int t0 = kRB; t0 < bh; t0 += kRB)
-      mesh1_chunk<SEGW, 1>(s_off, src_pitch_b, r_off, pitch_b, sh, t0, tmax, sw, acc);
-    mesh1_chunk<SEGW, 2>(s_off, src_pitch_b, r_off, pitch_b, sh, bh, tmax, sw, acc);
+    mesh1_chunk<SEGW, 0, PX>(s_off, src_pitch_b, r_off, pitch_b, sh, 0, tmax, sw, acc);
+    for (int t0 = kRB; t0 < bh; t0 += kRB) {
+#pragma unroll
+      for (int c = 0; c < kRB; ++c) sad_flush<PX>(acc[c], tot[c]);
+      mesh1_chunk<SEGW, 1, PX>(s_off, src_pitch_b, r_off, pitch_b, sh, t0, tmax, sw, acc);
+    }
+#pragma unroll
+    for (int c = 0; c < kRB; ++c) sad_flush<PX>(acc[c], tot[c]);
+    mesh1_chunk<SEGW, 2, PX>(s_off, src_pitch_b, r_off, pitch_b, sh, bh, tmax, sw, acc);
+#pragma unroll
+    for (int c = 0; c < kRB; ++c) sad_flush<PX>(acc[c], tot[c]);
     if (ci < nc) {
 #pragma unroll
       for (int c = 0; c < kRB; ++c)
         if (c < nk) {
-          unsigned v = acc[c];
-          if (seg == 0) v += (unsigned)sad_cost(k, row + c, col);
+          // PX = 2: raw partial sums; the caller shifts the block total (>> 2 / >> 4, the encoder's
+          // high-bit-depth SAD wrappers) and adds the mv cost once all segments have arrived
+          unsigned v = PX == 1 ? acc[c] : tot[c];
+          if (PX == 1 && seg == 0) v += (unsigned)sad_cost(k, row + c, col);
           atomicAdd(&g_cand[(rg * kRB + c) * nc + ci], v);
         }
     }
   }
 }
 
-template <int SEGW, int STEPW, int WO>
+template <int SEGW, int STEPW, int WO, int PX, int JB>
 __device__ void mesh_strided_band_t(const Ctx &k, int row0, int nrows, int col0, int nc, int step,
                                     unsigned sh) {
-  constexpr int NSH = SEGW + (kJB - 1) * STEPW;  // shifted words needed
-  constexpr int NV = (WO + NSH + 1 + 3) / 4;     // aligned uint4 loads covering them (+1 for the funnel)
+  constexpr int NSH = SEGW + (JB - 1) * STEPW;  // shifted words needed
+  constexpr int NV = (WO + NSH + 1 + 3) / 4;    // aligned uint4 loads covering them (+1 for the funnel)
   const int lane = threadIdx.x & 31, ylane = threadIdx.x & 7;
   const unsigned gmask = 0xffu << (lane & 24);
-  const int bh = k.d.bh, nseg = k.d.bw / (4 * SEGW);
-  const int ncg = (nc + kJB - 1) / kJB;
+  const int bh = k.d.bh, nseg = k.d.bw * PX / (4 * SEGW);
+  const int ncg = (nc + JB - 1) / JB;
   const int ntask = nrows * ncg * nseg;
-  const int pitch_b = k.ref_pitch, src_pitch_b = k.src_pitch_w * 4;
+  const int pitch_b = k.ref_pitch * PX, src_pitch_b = k.src_pitch_w * 4;
   for (int task = threadIdx.x >> 3; task < ntask; task += kThreads / 8) {
     const int seg = task % nseg, cg = (task / nseg) % ncg, ri = task / (nseg * ncg);
-    const int row = row0 + ri * step, col = col0 + cg * kJB * step;
-    const int r_off = (k.win0_off + row * pitch_b + col + seg * SEGW * 4) & ~15;
+    const int row = row0 + ri * step, col = col0 + cg * JB * step;
+    const int r_off = (k.win0_off + row * pitch_b + col * PX + seg * SEGW * 4) & ~15;
     const int s_off = seg * SEGW * 4;
-    unsigned acc[kJB];
+    unsigned acc[JB], tot[JB];
 #pragma unroll
-    for (int j = 0; j < kJB; ++j) acc[j] = 0;
+    for (int j = 0; j < JB; ++j) acc[j] = 0, tot[j] = 0;
     for (int y = ylane; y < bh; y += 8) {
       unsigned s[SEGW], r[4 * NV], v[NSH];
       load_words<SEGW>(smem_words(s_off + y * src_pitch_b), s);
@@ -556,23 +585,26 @@ __device__ void mesh_strided_band_t(const Ctx &k, int row0, int nrows, int col0,
 #pragma unroll
       for (int i = 0; i < NSH; ++i) v[i] = __funnelshift_r(r[WO + i], r[WO + i + 1], sh);
 #pragma unroll
-      for (int j = 0; j < kJB; ++j)
+      for (int j = 0; j < JB; ++j) {
 #pragma unroll
-        for (int i = 0; i < SEGW; ++i) acc[j] = sad4_acc(s[i], v[j * STEPW + i], acc[j]);
+        for (int i = 0; i < SEGW; ++i) acc[j] = sadw_acc<PX>(s[i], v[j * STEPW + i], acc[j]);
+        sad_flush<PX>(acc[j], tot[j]);  // SEGW <= 8 terms per half word and row
+      }
     }
 #pragma unroll
-    for (int j = 0; j < kJB; ++j) {
+    for (int j = 0; j < JB; ++j) {
+      if (PX == 2) acc[j] = tot[j];
       acc[j] += __shfl_xor_sync(gmask, acc[j], 1);
       acc[j] += __shfl_xor_sync(gmask, acc[j], 2);
       acc[j] += __shfl_xor_sync(gmask, acc[j], 4);
     }
     if (ylane == 0) {
 #pragma unroll
-      for (int j = 0; j < kJB; ++j) {
-        const int ci = cg * kJB + j;
+      for (int j = 0; j < JB; ++j) {
+        const int ci = cg * JB + j;
         if (ci < nc) {
           unsigned t = acc[j];
-          if (seg == 0) t += (unsigned)sad_cost(k, row, col + j * step);
+          if (PX == 1 && seg == 0) t += (unsigned)sad_cost(k, row, col + j * step);
           atomicAdd(&g_cand[ri * nc + ci], t);
         }
       }
@@ -580,46 +612,69 @@ __device__ void mesh_strided_band_t(const Ctx &k, int row0, int nrows, int col0,
   }
 }
 
-template <int SEGW, int STEPW>
+template <int SEGW, int STEPW, int PX, int JB>
 __device__ __forceinline__ void mesh_strided_band(const Ctx &k, int row0, int nrows, int col0, int nc,
                                                   int step) {
   // all candidates of a stage share the byte alignment (their columns differ by whole
-  // multiples of 16 pixels within a lane group and of 4 pixels overall)
-  const int a = k.win0_off + col0;
+  // multiples of 16 bytes within a lane group and of 4 bytes overall)
+  const int a = k.win0_off + col0 * PX;
   const unsigned sh = (unsigned)(a & 3) * 8;
-  // word offset inside the 16-byte chunk: candidates of one lane group start kJB * step
-  // pixels apart (a multiple of 16), grid rows start step * pitch apart (pitch % 16 == 0)
+  // word offset inside the 16-byte chunk: candidates of one lane group start JB * step
+  // pixels apart (a multiple of 16 bytes), grid rows start step * pitch apart (pitch % 16 == 0)
   switch ((a >> 2) & 3) {
-    case 0: mesh_strided_band_t<SEGW, STEPW, 0>(k, row0, nrows, col0, nc, step, sh); break;
-    case 1: mesh_strided_band_t<SEGW, STEPW, 1>(k, row0, nrows, col0, nc, step, sh); break;
-    case 2: mesh_strided_band_t<SEGW, STEPW, 2>(k, row0, nrows, col0, nc, step, sh); break;
-    default: mesh_strided_band_t<SEGW, STEPW, 3>(k, row0, nrows, col0, nc, step, sh); break;
+    case 0: mesh_strided_band_t<SEGW, STEPW, 0, PX, JB>(k, row0, nrows, col0, nc, step, sh); break;
+    case 1: mesh_strided_band_t<SEGW, STEPW, 1, PX, JB>(k, row0, nrows, col0, nc, step, sh); break;
+    case 2: mesh_strided_band_t<SEGW, STEPW, 2, PX, JB>(k, row0, nrows, col0, nc, step, sh); break;
+    default: mesh_strided_band_t<SEGW, STEPW, 3, PX, JB>(k, row0, nrows, col0, nc, step, sh); break;
   }
 }
 
 // 0: no fast path for this stage; otherwise fills g_cand[0..nrows*nc) (must be zeroed)
+// uint16 planes: 2 pixels per word, candidates step * 2 bytes apart; two candidates per lane in the
+// strided stages.  Not inlined: its register allocation stays out of the 8-bit paths of the kernel.
+__device__ __noinline__ void mesh_band_fast_hbd(const Ctx &k, int row0, int nrows, int col0, int nc, int step) {
+  if (step == 1) mesh1_band<4, 2>(k, row0, nrows, col0, nc);
+  else if (step == 4) mesh_strided_band<8, 2, 2, 2>(k, row0, nrows, col0, nc, step);
+  else if (step == 8) mesh_strided_band<8, 4, 2, 2>(k, row0, nrows, col0, nc, step);
+  else mesh_strided_band<8, 8, 2, 2>(k, row0, nrows, col0, nc, step);
+  // raw block sums -> encoder SAD (>> 2 / >> 4, encoder_utils.h:153-208) + mv cost
+  __syncthreads();
+  for (int j = threadIdx.x; j < nrows * nc; j += kThreads) {
+    const int ri = j / nc, ci = j - ri * nc;
+    g_cand[j] = (g_cand[j] >> k.sad_shift) + (unsigned)sad_cost(k, row0 + ri * step, col0 + ci * step);
+  }
+}
+
 __device__ __forceinline__ bool mesh_band_fast(const Ctx &k, int row0, int nrows, int col0, int nc,
                                                int step) {
   const int bw = k.d.bw;
+  if (k.px == 2) {
+    mesh_band_fast_hbd(k, row0, nrows, col0, nc, step);
+    return true;
+  }
   if (step == 1) {
-    if (bw >= 16) mesh1_band<4>(k, row0, nrows, col0, nc);  // 16-pixel segments: 64 registers suffice
-    else mesh1_band<2>(k, row0, nrows, col0, nc);
+    if (bw >= 16) mesh1_band<4, 1>(k, row0, nrows, col0, nc);  // 16-pixel segments: 64 registers suffice
+    else mesh1_band<2, 1>(k, row0, nrows, col0, nc);
     return true;
   }
   if (bw >= 32) {
-    if (step == 4) mesh_strided_band<8, 1>(k, row0, nrows, col0, nc, step);
-    else if (step == 8) mesh_strided_band<8, 2>(k, row0, nrows, col0, nc, step);
-    else mesh_strided_band<8, 4>(k, row0, nrows, col0, nc, step);
+    if (step == 4) mesh_strided_band<8, 1, 1, kJB>(k, row0, nrows, col0, nc, step);
+    else if (step == 8) mesh_strided_band<8, 2, 1, kJB>(k, row0, nrows, col0, nc, step);
+    else mesh_strided_band<8, 4, 1, kJB>(k, row0, nrows, col0, nc, step);
   } else {
-    if (step == 4) mesh_strided_band<4, 1>(k, row0, nrows, col0, nc, step);
-    else if (step == 8) mesh_strided_band<4, 2>(k, row0, nrows, col0, nc, step);
-    else mesh_strided_band<4, 4>(k, row0, nrows, col0, nc, step);
+    if (step == 4) mesh_strided_band<4, 1, 1, kJB>(k, row0, nrows, col0, nc, step);
+    else if (step == 8) mesh_strided_band<4, 2, 1, kJB>(k, row0, nrows, col0, nc, step);
+    else mesh_strided_band<4, 4, 1, kJB>(k, row0, nrows, col0, nc, step);
   }
   return true;
 }
 
 __device__ __forceinline__ bool mesh_fast_ok(const Ctx &k, bool skip, int step, int nc) {
-  if (skip || k.px != 1 || !k.staged || (k.d.bh & 3) || nc > kMaxCand) return false;
+  if (skip || !k.staged || (k.d.bh & 3) || nc > kMaxCand) return false;
+  if (k.px == 2) {
+    if (step == 1) return k.d.bw >= 8;  // 16 bytes = one 4-word segment
+    return k.fast && k.d.bw >= 16 && (step == 4 || step == 8 || step == 16);
+  }
   if (step == 1) return k.d.bw >= 8;
   // strided: 16-byte aligned window rows (vector loads), whole-word candidate spacing
   return k.fast && k.d.bw >= 16 && (step == 4 || step == 8 || step == 16);

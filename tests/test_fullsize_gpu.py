@@ -187,7 +187,7 @@ def test_config3_1080p_motion_search_full_frame(ctx, bd):
                 p.want_cost_list = p.want_second_best = 1
                 params.append(p)
         assert len(params) == 480
-        got = me_launch(ctx, cur, refb, params, tdev, False, 48 * 1024)
+        got = me_launch(ctx, cur, refb, params, tdev, False, (48 if bd == 8 else 88) * 1024)
         sub, exp_full = [], {}
         for i, p in enumerate(params):
             if i % step == 0:

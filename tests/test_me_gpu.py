@@ -188,23 +188,27 @@ MESH_PATTERNS = [  # speed_features.c:25-44
 ]
 
 
+@pytest.mark.parametrize("bd", [8, 10, 12])
 @pytest.mark.parametrize("pattern", range(len(MESH_PATTERNS)))
-def test_fullpel_mesh_patterns(ctx, pattern):
+def test_fullpel_mesh_patterns(ctx, pattern, bd):
     """Every mesh stage shape of the reference's tables through the register-blocked SAD
     maps (step 1: column lanes; step 4/8/16: strips) and the generic path (step 2, row
     skipping, 4/8-pixel blocks), forced mesh, limits clipped at the frame edge."""
     O = H.oracle()
-    rng = np.random.default_rng(900 + pattern)
+    rng = np.random.default_rng(900 + pattern + 17 * (bd - 8))
     tables = H.make_mv_cost_tables(4)
     keep, tdev = upload_tables(ctx, tables)
     mesh = MESH_PATTERNS[pattern]
     for trial in range(2):
-        cur, refb = M.make_frames(rng, 320, 256, 8, flat=(trial == 1))
+        cur, refb = M.make_frames(rng, 320, 256, bd, flat=(trial == 1))
+        if bd > 8 and trial == 0:  # extreme pixels: 64 rows of 12-bit extremes fill the packed 16-bit sums
+            cur[64:200, 32:224] = (1 << bd) - 1
+            refb[M.BORDER + 64:M.BORDER + 200, M.BORDER + 32:M.BORDER + 224] = 0
         params = []
         for (bw, bh) in [(64, 64), (32, 32), (16, 16), (128, 128), (8, 8), (16, 8), (64, 32), (32, 8),
                          (128, 64), (16, 64)]:
             for rep in range(3):
-                p = M.random_fullpel_params(rng, cur, refb, bw, bh, 8, tables)
+                p = M.random_fullpel_params(rng, cur, refb, bw, bh, bd, tables)
                 for i, (r, it) in enumerate(mesh):
                     p.mesh_range[i], p.mesh_interval[i] = r, it
                 p.run_mesh_search, p.prune_mesh_search = 1, 0
@@ -219,7 +223,7 @@ def test_fullpel_mesh_patterns(ctx, pattern):
             g = got[i]
             assert (int(g["best_row"]), int(g["best_col"]), int(g["second_row"]), int(g["second_col"]),
                     tuple(int(v) for v in g["cost_list"]), int(g["ret"])) == e.key(), \
-                (pattern, trial, i, p.bw, p.bh, p.use_skip_sad, p.fine_search_interval)
+                (pattern, bd, trial, i, p.bw, p.bh, p.use_skip_sad, p.fine_search_interval)
 
 
 @pytest.mark.parametrize("bd", [8, 10, 12])
