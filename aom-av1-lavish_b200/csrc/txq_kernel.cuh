@@ -128,7 +128,14 @@ struct SmemCfg {
 #else
   static constexpr int kFlight = S::kPlaneBytes;
 #endif
-  static constexpr int kStages = kFlight >= 2048 ? 2 : (kFlight >= 1024 ? 3 : 4);
+  // 64-point sizes: no staging ring at all.  Their tiles are 2-16 KB per operand, so two stages of a
+  // 4-warp CTA took 84-166 KB of shared memory and left 4-8 warps per SM resident (ncu round 2: 6-12 %
+  // warps active, the kernels wait instead of streaming); the column pass reads its samples straight
+  // from global memory instead (a lane's H loads are independent, consecutive lanes = consecutive
+  // columns of a row, so every request is a few full sectors) and occupancy doubles.
+  // (residual input: measured better only when the rows are 64 wide; 32x64 / 16x64 keep the ring)
+  static constexpr bool kDirect = W == 64 || (cx_max(W, H) == 64 && IN != B200_IN_RESIDUAL);
+  static constexpr int kStages = kDirect ? 0 : (kFlight >= 2048 ? 2 : (kFlight >= 1024 ? 3 : 4));
   static constexpr int kXposeBytes = cx_round_up(C::BPW * C::XS * 4, 16);
   // Output tiles (optional bulk-store path, -DB200_TXQ_BULK_OUT): the tile's coeff / qcoeff /
   // dqcoeff blocks are assembled in shared memory in the codec's storage order and leave
@@ -357,6 +364,45 @@ __device__ __forceinline__ void load_column(const unsigned char *stg, int c, int
   }
 }
 
+// Same, straight from global memory (SmemCfg::kDirect): column c of block d.
+template <int W, int H, int IN>
+__device__ __forceinline__ void load_column_direct(const TxqArgs &a, const B200TxBlock &d, int bi, int c,
+                                                   bool ud, int32_t *x, int32_t &mx, int32_t &mn) {
+  using C = TxCfg<W, H>;
+  if constexpr (IN == B200_IN_RESIDUAL) {
+    const int16_t *p = static_cast<const int16_t *>(a.src) + d.src_offset + c;
+#pragma unroll
+    for (int r = 0; r < H; ++r) x[r] = __ldg(p + (size_t)(ud ? H - 1 - r : r) * d.src_stride);
+  } else {
+    const B200TxPred pd = a.preds[bi];
+    if constexpr (IN == B200_IN_PIXELS8) {
+      const uint8_t *p = static_cast<const uint8_t *>(a.src) + d.src_offset + c;
+      const uint8_t *q = static_cast<const uint8_t *>(a.pred) + pd.pred_offset + c;
+#pragma unroll
+      for (int r = 0; r < H; ++r) {
+        const int rr = ud ? H - 1 - r : r;
+        x[r] = (int)__ldg(p + (size_t)rr * d.src_stride) - (int)__ldg(q + (size_t)rr * pd.pred_stride);
+      }
+    } else {
+      const uint16_t *p = static_cast<const uint16_t *>(a.src) + d.src_offset + c;
+      const uint16_t *q = static_cast<const uint16_t *>(a.pred) + pd.pred_offset + c;
+#pragma unroll
+      for (int r = 0; r < H; ++r) {
+        const int rr = ud ? H - 1 - r : r;
+        x[r] = (int16_t)((int)__ldg(p + (size_t)rr * d.src_stride) - (int)__ldg(q + (size_t)rr * pd.pred_stride));
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < H; ++r) {
+    if constexpr (IN != B200_IN_PIXELS8) {
+      mx = x[r] > mx ? x[r] : mx;
+      mn = x[r] < mn ? x[r] : mn;
+    }
+    x[r] = (int32_t)((uint32_t)x[r] << C::kUp);
+  }
+}
+
 // Column transform of one column (already in x) -> transpose tile of its block.
 template <int W, int H, bool EXACT>
 __device__ __forceinline__ void column_pass(int vt, int ht, int32_t *x, int32_t *tile, int c) {
@@ -460,24 +506,29 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) txq_kernel(const TxqArgs a)
   const bool force_exact = (a.flags & B200_TXQ_FORCE_EXACT) != 0;
 
   // prologue: fill NS-1 stages
+  if constexpr (!M::kDirect) {
 #pragma unroll
-  for (int s = 0; s < NS - 1; ++s) {
-    const int wt = wt0 + s * wstride;
-    if (wt < n_tiles) stage_tile<W, H, IN>(a, wt, wbase + s * M::kStageBytes, lane);
-    cp_async_commit();
+    for (int s = 0; s < NS - 1; ++s) {
+      const int wt = wt0 + s * wstride;
+      if (wt < n_tiles) stage_tile<W, H, IN>(a, wt, wbase + s * M::kStageBytes, lane);
+      cp_async_commit();
+    }
   }
 
   int it = 0;
   for (int wt = wt0; wt < n_tiles; wt += wstride, ++it) {
-    {  // keep the ring full: tile it+NS-1 goes to the stage consumed in the previous round
-      const int wtp = wt + (NS - 1) * wstride;
-      if (wtp < n_tiles)
-        stage_tile<W, H, IN>(a, wtp, wbase + ((it + NS - 1) % NS) * M::kStageBytes, lane);
-      cp_async_commit();
+    const unsigned char *stage = nullptr;
+    if constexpr (!M::kDirect) {
+      {  // keep the ring full: tile it+NS-1 goes to the stage consumed in the previous round
+        const int wtp = wt + (NS - 1) * wstride;
+        if (wtp < n_tiles)
+          stage_tile<W, H, IN>(a, wtp, wbase + ((it + NS - 1) % (NS > 0 ? NS : 1)) * M::kStageBytes, lane);
+        cp_async_commit();
+      }
+      cp_async_wait<(NS > 0 ? NS - 1 : 0)>();
+      __syncwarp();
+      stage = wbase + (it % (NS > 0 ? NS : 1)) * M::kStageBytes;
     }
-    cp_async_wait<NS - 1>();
-    __syncwarp();
-    const unsigned char *stage = wbase + (it % NS) * M::kStageBytes;
 
     // ---------------------------------------------------------------- column rounds
     bool tile_fast = !force_exact;
@@ -488,10 +539,21 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) txq_kernel(const TxqArgs a)
       const int bi = wt * C::TB + slot;
       const bool act = bi < a.n_blocks;
       int tx_type = 0;
-      if (act) tx_type = a.blocks[bi].tx_type & 15;
+      B200TxBlock dcol;
+      if (act) {
+        if constexpr (M::kDirect) {
+          dcol = load_desc(a.blocks + bi);
+          tx_type = dcol.tx_type & 15;
+        } else {
+          tx_type = a.blocks[bi].tx_type & 15;
+        }
+      }
       const int vt = vtx_of(tx_type), ht = htx_of(tx_type);
       int32_t x[H], mx = 0, mn = 0;
-      if (act) load_column<W, H, IN>(stage + slot * S::kSlotBytes, c, x, mx, mn);
+      if (act) {
+        if constexpr (M::kDirect) load_column_direct<W, H, IN>(a, dcol, bi, c, vt == 2, x, mx, mn);
+        else load_column<W, H, IN>(stage + slot * S::kSlotBytes, c, x, mx, mn);
+      }
       bool ok = !force_exact;
       if constexpr (IN != B200_IN_PIXELS8)
         ok = ok && __all_sync(0xffffffffu, mx <= kGuard && mn >= -kGuard);
@@ -635,7 +697,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) txq_kernel(const TxqArgs a)
     }
     __syncwarp();  // stage and transpose tile are reused by the next round
   }
-  cp_async_wait<0>();
+  if constexpr (!M::kDirect) cp_async_wait<0>();
   if constexpr (M::kBulkOut) bulk_wait_all();  // shared memory must outlive the last bulk reads
 }
 

@@ -90,7 +90,7 @@ def make_residual_frames(frame_ids, seed):
     return out, planes, luma
 
 
-def make_descriptors(ts, n_frames, planes, frame_elems, seed):
+def make_descriptors(ts, n_frames, planes, frame_elems, seed, bytes_per_sample=2, band_bytes=1 << 20):
     """all blocks of size ts tiling every plane of every frame, in batch-queue order"""
     rng = np.random.default_rng(seed * 100 + ts)
     W, Hh = TX_W[ts], TX_H[ts]
@@ -117,11 +117,19 @@ def make_descriptors(ts, n_frames, planes, frame_elems, seed):
     blocks["tx_size"] = ts
     # quantiser row = plane * 5 + qindex slot
     blocks["qrow"] = np.tile(planes_id, n_frames) * len(QINDEXES) + rng.integers(0, len(QINDEXES), n)
-    # batch-queue order: within each frame group the blocks by tx_type (warps stay on one
-    # code path) but keep frames apart, so that the 16 type groups of a frame re-touch the
-    # same ~6 MB of residual while it is still in L2
+    # batch-queue order: the queue walks the frame in bands of whole 64-row units per plane holding about
+    # band_bytes of input and groups the blocks of a band by tx_type (warps stay on one code path).  The
+    # 16 type groups of a band re-touch the same ~1 MB of input while it is still in L2 -- with whole
+    # frames as the unit (round 1) a 4K 10-bit frame pair is 50 MB and the type groups re-read it from
+    # DRAM (ncu: 3.3 x the algorithmic input bytes at 4x4, profiles/r2_hbd_v1_ncu_summary.md).  Smaller
+    # bands cost warps that straddle two tx types (a 64-row band of 1080p has ~150 4x16 blocks per type);
+    # raster order with the types mixed inside a warp is slower still (measured: 4x4 0.67 -> 0.57).
+    def band_rows(w):
+        return 64 * max(1, int(round(band_bytes / (w * bytes_per_sample * 64.0))))
     frame_id = np.repeat(np.arange(n_frames), per_frame)
-    order = np.lexsort((blocks["tx_type"], frame_id))
+    band = np.tile(np.concatenate([(np.arange(h // Hh) * Hh // band_rows(w)).repeat(w // W) + 1000 * pi
+                                   for pi, (w, h) in enumerate(planes)]), n_frames)
+    order = np.lexsort((blocks["tx_type"], band, frame_id))
     blocks = blocks[order]
     blocks["out_offset"] = np.arange(n, dtype=np.uint64) * max_eob(ts)
     samples = n * W * Hh
@@ -439,9 +447,9 @@ def bench_hbd4k(ctx, dev, stream, steps, warmup, seed, n_frames=3):
     d_qrows = torch.from_numpy(qrows.view(np.uint8)).to(dev)
     n_out = n_frames * frame_elems
     d_coeff, d_qc, d_dq = (torch.empty(n_out, dtype=torch.int32, device=dev) for _ in range(3))
-    launches, keep, tot_bytes, tot_samples = [], [], 0, 0
+    launches, keep, tot_bytes, tot_samples, size_bytes = [], [], 0, 0, []
     for ts in range(19):
-        blocks, samples = make_descriptors(ts, n_frames, planes, frame_elems, seed + 4)
+        blocks, samples = make_descriptors(ts, n_frames, planes, frame_elems, seed + 4, bytes_per_sample=4)
         preds = np.zeros(blocks.size, b200av1.TXPRED_DTYPE)
         preds["pred_offset"], preds["pred_stride"] = blocks["src_offset"], blocks["src_stride"]
         d_blocks = torch.from_numpy(blocks.view(np.uint8)).to(dev)
@@ -459,26 +467,33 @@ def bench_hbd4k(ctx, dev, stream, steps, warmup, seed, n_frames=3):
         l.eob, l.dist = d_eob.data_ptr(), d_dist.data_ptr()
         launches.append(l)
         # 2 + 2 B/sample in, 12 B/kept coeff out, 2 B eob + 16 B dist per block
-        tot_bytes += blocks.size * (TX_W[ts] * TX_H[ts] * 4 + max_eob(ts) * 12 + 18)
+        size_bytes.append(blocks.size * (TX_W[ts] * TX_H[ts] * 4 + max_eob(ts) * 12 + 18))
+        tot_bytes += size_bytes[-1]
         tot_samples += samples
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
-    ms = 0.0
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(len(launches) + 1)]
+    ms, per = 0.0, np.zeros(len(launches))
     for it in range(warmup + steps):
         ev[0].record(stream)
-        for l in launches:
+        for i, l in enumerate(launches):
             ctx.txq_launch(l, stream.cuda_stream)
-        ev[1].record(stream)
+            ev[i + 1].record(stream)
         torch.cuda.synchronize(dev)
         if it >= warmup:
-            ms += ev[0].elapsed_time(ev[1])
+            ms += ev[0].elapsed_time(ev[-1])
+            per += [ev[i].elapsed_time(ev[i + 1]) for i in range(len(launches))]
     ms /= steps
+    per /= steps
+    peak = hbm_peak_gbs()
+    kernels = [{"tx": "%dx%d" % (TX_W[ts], TX_H[ts]), "ms": round(float(per[ts]), 4),
+                "GBps": round(size_bytes[ts] / (per[ts] * 1e-3) / 1e9, 1),
+                "frac": round(size_bytes[ts] / (per[ts] * 1e-3) / 1e9 / peak, 3)} for ts in range(19)]
     fe4k = 3840 * 2160 * 3 // 2
     return {"workload": "config[3]: %d synthetic 4K 10-bit 4:2:0 frames, fused subtract + txfm + "
                         "av1_highbd_quantize_fp + av1_highbd_block_error, all 19 TX sizes" % n_frames,
             "ms_per_sweep": ms, "fe4k_per_s": tot_samples / fe4k / (ms * 1e-3),
             "fe1080p_per_s": tot_samples / FE_SAMPLES / (ms * 1e-3),
-            "GBps": tot_bytes / (ms * 1e-3) / 1e9, "bytes_per_sweep": int(tot_bytes),
-            "launches_per_step": 19}
+            "GBps": tot_bytes / (ms * 1e-3) / 1e9, "frac": tot_bytes / (ms * 1e-3) / 1e9 / peak,
+            "bytes_per_sweep": int(tot_bytes), "launches_per_step": 19, "kernels": kernels}
 
 
 def hbm_peak_gbs():
@@ -790,7 +805,7 @@ def bench_config5(ctx, dev, stream, rank, world, seed, total_frames, batch, e2e_
     launches, keep, txq_bytes, txq_samples = [], [], 0, 0
     one_frame_blocks, one_frame_preds, out_off = [], [], 0
     for ts in range(19):
-        blocks, samples = make_descriptors(ts, batch, planes, frame_elems, seed + 5)
+        blocks, samples = make_descriptors(ts, batch, planes, frame_elems, seed + 5, bytes_per_sample=4)
         preds = np.zeros(blocks.size, b200av1.TXPRED_DTYPE)
         preds["pred_offset"], preds["pred_stride"] = blocks["src_offset"], blocks["src_stride"]
         d_blocks = torch.from_numpy(blocks.view(np.uint8)).to(dev)
@@ -810,7 +825,7 @@ def bench_config5(ctx, dev, stream, rank, world, seed, total_frames, batch, e2e_
         txq_bytes += blocks.size * (TX_W[ts] * TX_H[ts] * 4 + max_eob(ts) * 12 + 18)
         txq_samples += samples
         if e2e_frames:
-            b1, _s = make_descriptors(ts, 1, planes, frame_elems, seed + 5)
+            b1, _s = make_descriptors(ts, 1, planes, frame_elems, seed + 5, bytes_per_sample=4)
             b1["out_offset"] += out_off
             out_off += b1.size * max_eob(ts)
             p1 = np.zeros(b1.size, b200av1.TXPRED_DTYPE)
@@ -965,6 +980,8 @@ def main():
     ap.add_argument("--no-extras", action="store_true", help="skip the config[3] / config[4] / Hadamard sections")
     ap.add_argument("--config5-frames", type=int, default=120, help="frames of the 4K 10-bit batch (all ranks)")
     ap.add_argument("--sizes", default="", help="comma list of tx sizes (debug)")
+    ap.add_argument("--only", default="", choices=["", "hbd4k", "itx", "hadamard"],
+                    help="(profiling) run one extras section alone and print its JSON")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -1032,6 +1049,16 @@ def main():
     ctx = b200av1.Context(local_rank)
     lib = b200av1.lib()
     stream = torch.cuda.Stream(device=dev)
+    if args.only:
+        if args.only == "hbd4k":
+            out = bench_hbd4k(ctx, dev, stream, args.steps, args.warmup, seed)
+        elif args.only == "itx":
+            out = bench_itx(ctx, dev, stream, args.steps, args.warmup, seed, hbm_peak_gbs())
+        else:
+            d_src = torch.from_numpy(make_residual_frames(range(args.frames), seed).reshape(-1)).to(dev)
+            out = bench_hadamard(ctx, dev, stream, args.steps, args.warmup, d_src, args.frames)
+        print(json.dumps({"only": args.only, "result": out}))
+        return 0
 
     def allmax(v):
         t = torch.tensor([v], dtype=torch.float64, device=dev)
@@ -1109,6 +1136,8 @@ def main():
             if events is not None:
                 events[n_txq + 1].record(stream)
             b200av1.check(lib.b200_me_subpel_launch(ctx.h, C.byref(l_sub), C.c_void_p(sptr)))
+        elif events is not None:
+            events[n_txq + 1].record(stream)
         if events is not None:
             events[n_txq + 2].record(stream)
 
