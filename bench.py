@@ -1204,14 +1204,17 @@ def main():
         h_eob = pinned(eblocks.size * 2, np.uint16)
         d2h_txq = [0]
         if work is not None:
-            e_mblk = pinned_copy(work._blocks([0], pooled=False))
+            # one host-buffer call carries E frames (their planes stacked like the resident pool): a single
+            # 1080p frame is 960 searches = 2.2 waves of resident CTAs, so calls of one frame time the tail
+            E = min(4, args.frames)
+            e_mblk = pinned_copy(work._blocks(range(E), pooled=True))
             e_msub = pinned_copy(MeWork._sub(e_mblk))
-            h_cur = pinned_copy(work.cur[0])
-            h_ref = pinned_copy(work.refs[0:2])
+            h_cur = pinned_copy(work.cur[0:E])
+            h_ref = pinned_copy(work.refs[0:2 * E])
             h_rf = pinned(e_mblk.size * 40, b200av1.MERESULT_DTYPE)
             h_rs = pinned(e_mblk.size * 40, b200av1.MERESULT_DTYPE)
             hl = work.launch_struct(e_mblk.ctypes.data, h_cur.ctypes.data, h_ref.ctypes.data, None,
-                                    int(e_mblk.size), work.h, 2 * work.rh)
+                                    int(e_mblk.size), E * work.h, 2 * E * work.rh)
 
         def e2e_txq():
             d2h_txq[0] = ctx.txq_batch_host_compact(0, b200av1.Q_FP, 8, flags & ~b200av1.TXQ_STORE_COEFF, eblocks,
@@ -1242,7 +1245,7 @@ def main():
         h2d = int(frame_elems * 2 + eblocks.nbytes + qrows.nbytes)
         d2h = int(d2h_txq[0])
         if work is not None:
-            re_me = world * args.e2e_steps / te_me
+            re_me = world * E * args.e2e_steps / te_me
             e2e_value = combined(re_txq, re_me)
             h2d += int(h_cur.nbytes + h_ref.nbytes + 2 * e_mblk.nbytes)
             d2h += int(2 * h_rf.nbytes)
@@ -1251,11 +1254,13 @@ def main():
         e2e = {"value": e2e_value, "unit": "1080p frame-equiv/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "txq_fe_per_s": re_txq, "me_frames_per_s": re_me,
                "d2h_dense_bytes_per_step": int(out_off * 12 + eblocks.size * 2),
+               "me_frames_per_call": E if work is not None else 0,
                "note": "per step: 1 frame through b200_txq_batch_host_compact (pinned host buffers; descriptor "
                        "bucketing + H2D + %d launches + on-device packing + D2H of eob, offsets and the levels in "
-                       "scan order up to eob) and b200_me_batch_host (cur + 2 reference planes + descriptors H2D, "
-                       "full-pel + chained sub-pel launch, 2 x 40 B per search D2H), all inside the timed region"
-                       % len(sizes)}
+                       "scan order up to eob) and %d frames through ONE b200_me_batch_host call (cur + 2 reference "
+                       "planes per frame + descriptors H2D, full-pel + chained sub-pel launch, 2 x 40 B per search "
+                       "D2H), all inside the timed region; the byte counts are those of one such step"
+                       % (len(sizes), E if work is not None else 0)}
 
     extras = None
     if not args.no_extras:
