@@ -256,8 +256,10 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
   }
   const size_t n = (size_t)n_blocks;
 
-  // ---- one pass over the queue: validate, bucket by (tx_size, tx_type) so that warps stay
-  // on one code path, and find the range of the output arrays each tx size writes
+  // ---- one pass over the queue: validate, bucket by tx_size (one launch per size; the caller's order
+  // inside a size is kept -- it is the caller that knows how to keep blocks of one tx type and of one
+  // neighbourhood together, e.g. type groups inside ~1 MB bands, see bench.py make_descriptors), and find
+  // the range of the output arrays each tx size writes
   constexpr int kKeys = B200_TX_SIZES_ALL * 16;
   static bool s_valid[kKeys];
   static size_t s_max_eob[B200_TX_SIZES_ALL];
@@ -277,8 +279,8 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
   bool in_order = true;
   unsigned prev_key = 0;
   for (size_t i = 0; i < n; ++i) {
-    const unsigned ts = blocks[i].tx_size, key = ts * 16u + blocks[i].tx_type;
-    if (ts >= B200_TX_SIZES_ALL || blocks[i].tx_type >= 16 || !s_valid[key]) {
+    const unsigned ts = blocks[i].tx_size, vkey = ts * 16u + blocks[i].tx_type, key = ts * 16u;
+    if (ts >= B200_TX_SIZES_ALL || blocks[i].tx_type >= 16 || !s_valid[vkey]) {
       set_error("b200_txq_batch_host: block %zu has invalid tx_size/tx_type %d/%d", i, (int)ts,
                 (int)blocks[i].tx_type);
       return B200_EINVAL;
@@ -325,7 +327,7 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
     B200TxBlock *sb = (B200TxBlock *)(hbase + ho_blocks);
     B200TxPred *sp = (B200TxPred *)(hbase + ho_preds);
     for (size_t i = 0; i < n; ++i) {
-      const uint32_t pos = cursor[blocks[i].tx_size * 16 + blocks[i].tx_type]++;
+      const uint32_t pos = cursor[blocks[i].tx_size * 16]++;
       order[pos] = (uint32_t)i;
       sb[pos] = blocks[i];
       if (has_pred) sp[pos] = preds[i];
