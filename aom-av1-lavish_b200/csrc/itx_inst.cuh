@@ -3,6 +3,7 @@
 // cosine / sine tables (static __constant__ in txfm1d.cuh) in its group function.
 #pragma once
 #include "itx_kernel.cuh"
+#include "itx_direct.cuh"
 #include "txq_inst.cuh"  // upload_txfm_constants()
 
 namespace b200 {
