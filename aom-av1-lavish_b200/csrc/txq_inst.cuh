@@ -49,6 +49,12 @@ static void fill_entries_small(TxqKernelInfo *e) {
     if (upload) return upload_txfm_constants();
 #define B200_TXQ_SIZE(ENUM, W, H) fill_entries<W, H>(table[ENUM]);
 #define B200_TXQ_SIZE_SMALL(ENUM, W, H) fill_entries_small<W, H>(table[ENUM]);
+// lane-owns-block kernel for the residual input, tiled kernel for the two-operand pixel inputs: used for
+// 16x4, whose lane-owned pixel kernel sits at 255 registers with spills (configs[3]: 0.42 -> 0.46 of the
+// roofline; 4x16 is the other way round, 0.39 lane-owned vs 0.31 tiled, and keeps the lane-owned one)
+#define B200_TXQ_SIZE_SMALL_RESID(ENUM, W, H) \
+  fill_entries<W, H>(table[ENUM]);            \
+  table[ENUM][B200_IN_RESIDUAL] = txq_small_kernel_info<W, H, B200_IN_RESIDUAL>();
 #define B200_TXQ_GROUP_END \
   return B200_OK;          \
   }                        \
