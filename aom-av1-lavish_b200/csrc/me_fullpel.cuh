@@ -489,13 +489,13 @@ __device__ __forceinline__ void sad_flush(unsigned &acc, unsigned &tot) {
 
 // PHASE 0: first RB reference rows (source window filling), 1: steady state, 2: last RB - 1
 // rows (window draining).
-template <int SEGW, int PHASE, int PX>
+template <int SEGW, int PHASE, int PX, int RB>
 __device__ __forceinline__ void mesh1_chunk(int s_off, int src_pitch_b, int r_off, int pitch_b,
                                             unsigned sh, int t0, int tmax,
-                                            unsigned (&sw)[kRB][SEGW], unsigned (&acc)[kRB]) {
+                                            unsigned (&sw)[RB][SEGW], unsigned (&acc)[RB]) {
 #pragma unroll
-  for (int u = 0; u < kRB; ++u) {
-    if (PHASE == 2 && u == kRB - 1) break;
+  for (int u = 0; u < RB; ++u) {
+    if (PHASE == 2 && u == RB - 1) break;
     const int t = t0 + u;
     if (PHASE == 2 && t >= tmax) break;  // warp-uniform
     if (PHASE != 2) load_words<SEGW>(smem_words(s_off + t * src_pitch_b), sw[u]);
@@ -506,54 +506,54 @@ __device__ __forceinline__ void mesh1_chunk(int s_off, int src_pitch_b, int r_of
 #pragma unroll
     for (int i = 0; i < SEGW; ++i) rv[i] = __funnelshift_r(r[i], r[i + 1], sh);
 #pragma unroll
-    for (int c = 0; c < kRB; ++c) {
+    for (int c = 0; c < RB; ++c) {
       if (PHASE == 0 && c > u) continue;
       if (PHASE == 2 && c <= u) continue;
 #pragma unroll
-      for (int i = 0; i < SEGW; ++i) acc[c] = sadw_acc<PX>(sw[(u - c) & (kRB - 1)][i], rv[i], acc[c]);
+      for (int i = 0; i < SEGW; ++i) acc[c] = sadw_acc<PX>(sw[(u - c) & (RB - 1)][i], rv[i], acc[c]);
     }
   }
 }
 
-template <int SEGW, int PX>
+template <int SEGW, int PX, int RB>
 __device__ void mesh1_band(const Ctx &k, int row0, int nrows, int col0, int nc) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int bh = k.d.bh, nseg = k.d.bw * PX / (4 * SEGW);
-  const int nrg = (nrows + kRB - 1) / kRB, ncc = (nc + 31) >> 5;
+  const int nrg = (nrows + RB - 1) / RB, ncc = (nc + 31) >> 5;
   const int ntask = nrg * nseg * ncc;
   const int pitch_b = k.ref_pitch * PX, src_pitch_b = k.src_pitch_w * 4;
   for (int task = warp; task < ntask; task += kWarps) {
     const int cc = task % ncc, seg = (task / ncc) % nseg, rg = task / (ncc * nseg);
-    const int nk = min(kRB, nrows - rg * kRB);
+    const int nk = min(RB, nrows - rg * RB);
     const int ci = cc * 32 + lane, cia = min(ci, nc - 1);
-    const int row = row0 + rg * kRB, col = col0 + cia;
+    const int row = row0 + rg * RB, col = col0 + cia;
     const int a = k.win0_off + row * pitch_b + col * PX + seg * SEGW * 4;
     const int r_off = a & ~3, s_off = seg * SEGW * 4;
     const unsigned sh = (unsigned)(a & 3) * 8;
-    unsigned sw[kRB][SEGW], acc[kRB], tot[kRB];
+    unsigned sw[RB][SEGW], acc[RB], tot[RB];
 #pragma unroll
-    for (int c = 0; c < kRB; ++c) acc[c] = 0, tot[c] = 0;
+    for (int c = 0; c < RB; ++c) acc[c] = 0, tot[c] = 0;
     const int tmax = bh + nk - 1;
-    mesh1_chunk<SEGW, 0, PX>(s_off, src_pitch_b, r_off, pitch_b, sh, 0, tmax, sw, acc);
-    for (int t0 = kRB; t0 < bh; t0 += kRB) {
+    mesh1_chunk<SEGW, 0, PX, RB>(s_off, src_pitch_b, r_off, pitch_b, sh, 0, tmax, sw, acc);
+    for (int t0 = RB; t0 < bh; t0 += RB) {
 #pragma unroll
-      for (int c = 0; c < kRB; ++c) sad_flush<PX>(acc[c], tot[c]);
-      mesh1_chunk<SEGW, 1, PX>(s_off, src_pitch_b, r_off, pitch_b, sh, t0, tmax, sw, acc);
+      for (int c = 0; c < RB; ++c) sad_flush<PX>(acc[c], tot[c]);
+      mesh1_chunk<SEGW, 1, PX, RB>(s_off, src_pitch_b, r_off, pitch_b, sh, t0, tmax, sw, acc);
     }
 #pragma unroll
-    for (int c = 0; c < kRB; ++c) sad_flush<PX>(acc[c], tot[c]);
-    mesh1_chunk<SEGW, 2, PX>(s_off, src_pitch_b, r_off, pitch_b, sh, bh, tmax, sw, acc);
+    for (int c = 0; c < RB; ++c) sad_flush<PX>(acc[c], tot[c]);
+    mesh1_chunk<SEGW, 2, PX, RB>(s_off, src_pitch_b, r_off, pitch_b, sh, bh, tmax, sw, acc);
 #pragma unroll
-    for (int c = 0; c < kRB; ++c) sad_flush<PX>(acc[c], tot[c]);
+    for (int c = 0; c < RB; ++c) sad_flush<PX>(acc[c], tot[c]);
     if (ci < nc) {
 #pragma unroll
-      for (int c = 0; c < kRB; ++c)
+      for (int c = 0; c < RB; ++c)
         if (c < nk) {
           // PX = 2: raw partial sums; the caller shifts the block total (>> 2 / >> 4, the encoder's
           // high-bit-depth SAD wrappers) and adds the mv cost once all segments have arrived
           unsigned v = PX == 1 ? acc[c] : tot[c];
           if (PX == 1 && seg == 0) v += (unsigned)sad_cost(k, row + c, col);
-          atomicAdd(&g_cand[(rg * kRB + c) * nc + ci], v);
+          atomicAdd(&g_cand[(rg * RB + c) * nc + ci], v);
         }
     }
   }
@@ -633,7 +633,7 @@ __device__ __forceinline__ void mesh_strided_band(const Ctx &k, int row0, int nr
 // uint16 planes: 2 pixels per word, candidates step * 2 bytes apart; two candidates per lane in the
 // strided stages.  Not inlined: its register allocation stays out of the 8-bit paths of the kernel.
 __device__ __noinline__ void mesh_band_fast_hbd(const Ctx &k, int row0, int nrows, int col0, int nc, int step) {
-  if (step == 1) mesh1_band<4, 2>(k, row0, nrows, col0, nc);
+  if (step == 1) mesh1_band<4, 2, 4>(k, row0, nrows, col0, nc);
   else if (step == 4) mesh_strided_band<8, 2, 2, 2>(k, row0, nrows, col0, nc, step);
   else if (step == 8) mesh_strided_band<8, 4, 2, 2>(k, row0, nrows, col0, nc, step);
   else mesh_strided_band<8, 8, 2, 2>(k, row0, nrows, col0, nc, step);
@@ -653,8 +653,11 @@ __device__ __forceinline__ bool mesh_band_fast(const Ctx &k, int row0, int nrows
     return true;
   }
   if (step == 1) {
-    if (bw >= 16) mesh1_band<4, 1>(k, row0, nrows, col0, nc);  // 16-pixel segments: 64 registers suffice
-    else mesh1_band<2, 1>(k, row0, nrows, col0, nc);
+    // (8 vertically adjacent candidates per lane -- mesh1_band<4, 1, 8> -- halve the loads and funnel shifts
+    // per accumulation but were slower on B200: 0.430 vs 0.409 ms per 1080p frame, the kernel's 80-register
+    // budget spills the 32-word source window)
+    if (bw >= 16) mesh1_band<4, 1, 4>(k, row0, nrows, col0, nc);
+    else mesh1_band<2, 1, 4>(k, row0, nrows, col0, nc);
     return true;
   }
   if (bw >= 32) {
