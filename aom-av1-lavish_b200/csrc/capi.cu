@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <mutex>
+#include <thread>
 #include <vector>
 
 #include "internal.h"
@@ -277,29 +278,71 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
   size_t g_lo[B200_TX_SIZES_ALL], g_hi[B200_TX_SIZES_ALL];
   for (int ts = 0; ts < B200_TX_SIZES_ALL; ++ts) g_lo[ts] = (size_t)-1, g_hi[ts] = 0;
   bool in_order = true;
-  unsigned prev_key = 0;
-  for (size_t i = 0; i < n; ++i) {
-    const unsigned ts = blocks[i].tx_size, vkey = ts * 16u + blocks[i].tx_type, key = ts * 16u;
-    if (ts >= B200_TX_SIZES_ALL || blocks[i].tx_type >= 16 || !s_valid[vkey]) {
-      set_error("b200_txq_batch_host: block %zu has invalid tx_size/tx_type %d/%d", i, (int)ts,
-                (int)blocks[i].tx_type);
-      return B200_EINVAL;
+  {
+    // a frame's queue is ~10^6 descriptors: the validation pass runs on a few host threads
+    struct Part {
+      uint32_t count[B200_TX_SIZES_ALL];
+      size_t lo[B200_TX_SIZES_ALL], hi[B200_TX_SIZES_ALL];
+      long long bad_type, bad_range;  // first offending block, or -1
+      bool in_order;
+    };
+    const unsigned hw = std::thread::hardware_concurrency();
+    const int n_parts = n < (1u << 16) ? 1 : (int)std::min<unsigned>(8, hw ? hw : 1);
+    std::vector<Part> parts(n_parts);
+    auto scan = [&](int pi) {
+      Part &pt = parts[pi];
+      for (int ts = 0; ts < B200_TX_SIZES_ALL; ++ts) pt.count[ts] = 0, pt.lo[ts] = (size_t)-1, pt.hi[ts] = 0;
+      pt.bad_type = pt.bad_range = -1;
+      pt.in_order = true;
+      const size_t i0 = n * pi / n_parts, i1 = n * (pi + 1) / n_parts;
+      unsigned prev = i0 ? blocks[i0 - 1].tx_size : 0;
+      for (size_t i = i0; i < i1; ++i) {
+        const unsigned ts = blocks[i].tx_size;
+        if (ts >= B200_TX_SIZES_ALL || blocks[i].tx_type >= 16 || !s_valid[ts * 16u + blocks[i].tx_type]) {
+          pt.bad_type = (long long)i;
+          return;
+        }
+        // the last sample a block reads must lie inside the input buffers
+        const size_t span = (size_t)(s_h[ts] - 1) * blocks[i].src_stride + s_w[ts];
+        if (((size_t)blocks[i].src_offset + span > src_elems ||
+             (has_pred && (size_t)preds[i].pred_offset + (size_t)(s_h[ts] - 1) * preds[i].pred_stride + s_w[ts] >
+                              pred_elems) ||
+             (has_q && blocks[i].qrow >= (unsigned)n_qrows)) && pt.bad_range < 0)
+          pt.bad_range = (long long)i;
+        pt.in_order = pt.in_order && ts >= prev;
+        prev = ts;
+        ++pt.count[ts];
+        const size_t o = blocks[i].out_offset;
+        pt.lo[ts] = o < pt.lo[ts] ? o : pt.lo[ts];
+        pt.hi[ts] = o > pt.hi[ts] ? o : pt.hi[ts];
+      }
+    };
+    if (n_parts == 1) {
+      scan(0);
+    } else {
+      std::vector<std::thread> th;
+      for (int pi = 1; pi < n_parts; ++pi) th.emplace_back(scan, pi);
+      scan(0);
+      for (auto &t : th) t.join();
     }
-    // the last sample a block reads must lie inside the input buffers
-    const size_t span = (size_t)(s_h[ts] - 1) * blocks[i].src_stride + s_w[ts];
-    if ((size_t)blocks[i].src_offset + span > src_elems ||
-        (has_pred && (size_t)preds[i].pred_offset + (size_t)(s_h[ts] - 1) * preds[i].pred_stride + s_w[ts] >
-                         pred_elems) ||
-        (has_q && blocks[i].qrow >= (unsigned)n_qrows)) {
-      set_error("b200_txq_batch_host: block %zu reads outside src / pred / qrows", i);
-      return B200_EINVAL;
+    for (const Part &pt : parts) {
+      if (pt.bad_type >= 0) {
+        const size_t i = (size_t)pt.bad_type;
+        set_error("b200_txq_batch_host: block %zu has invalid tx_size/tx_type %d/%d", i, (int)blocks[i].tx_size,
+                  (int)blocks[i].tx_type);
+        return B200_EINVAL;
+      }
+      if (pt.bad_range >= 0) {
+        set_error("b200_txq_batch_host: block %zu reads outside src / pred / qrows", (size_t)pt.bad_range);
+        return B200_EINVAL;
+      }
+      in_order = in_order && pt.in_order;
+      for (int ts = 0; ts < B200_TX_SIZES_ALL; ++ts) {
+        bucket[ts * 16 + 1] += pt.count[ts];
+        g_lo[ts] = pt.lo[ts] < g_lo[ts] ? pt.lo[ts] : g_lo[ts];
+        g_hi[ts] = pt.hi[ts] > g_hi[ts] ? pt.hi[ts] : g_hi[ts];
+      }
     }
-    in_order = in_order && key >= prev_key;
-    prev_key = key;
-    ++bucket[key + 1];
-    const size_t o = blocks[i].out_offset;
-    g_lo[ts] = o < g_lo[ts] ? o : g_lo[ts];
-    g_hi[ts] = o > g_hi[ts] ? o : g_hi[ts];
   }
   for (int k = 0; k < kKeys; ++k) bucket[k + 1] += bucket[k];
 
