@@ -57,6 +57,8 @@ struct Ctx {
   bool fast;                 // staged window with 16-byte aligned rows: vector-load SAD path
   bool staged;               // reference window is in shared memory (word-aligned rows at least)
   int win0_off;              // staged: byte offset inside me_smem of the reference pixel at mv (0,0)
+  int win_region_off;        // byte offset inside me_smem where the window region starts (after the source)
+  int win_budget;            // bytes of that region (0: none)
   int cost_fr, cost_fc;      // full-pel reference mv of the sad-domain mv cost
   int l1_mul;                // 32 / 15 / 8 for the L1 cost types, 0 otherwise
   int px;                    // bytes per pixel

@@ -686,8 +686,24 @@ __device__ __forceinline__ bool mesh_fast_ok(const Ctx &k, bool skip, int step, 
 // exhaustive_mesh_search (mcomp.c:1530-1599).  Candidates are visited row-major; at
 // step 1 the reference works in groups of four columns and its tail loop stops one short
 // of the last column (`i < end_col - c`, :1586) -- reproduced.
-__device__ int mesh_search(const Ctx &k, bool skip, Mv start, int range, int step, Mv *best,
+__device__ bool stage_window(Ctx &k, int wr0, int wc0, int wh, int ww);
+
+__device__ int mesh_search(const Ctx &k_in, bool skip, Mv start, int range, int step, Mv *best,
                            Mv *second, bool has_second) {
+  // A search whose mv limits are frame wide (temporal filter, TPL, first pass) cannot keep its whole
+  // reachable window on chip, but one mesh stage only visits start +- range: stage that box here and run
+  // the stage on the register-blocked maps instead of one warp per candidate through L1/L2 (ncu on the
+  // temporal-filter queue: 3.6-9.1 GB of L2->L1 traffic per launch, 0.5-0.9 us per 8x8 / 16x16 search).
+  Ctx km(k_in);
+  if (!k_in.staged && k_in.win_budget > 0) {
+    const Mv s0 = clamp_mv(k_in, start);
+    const int br0 = max(-range, k_in.d.row_min - s0.row), bc0 = max(-range, k_in.d.col_min - s0.col);
+    const int br1 = min(range, k_in.d.row_max - s0.row), bc1 = min(range, k_in.d.col_max - s0.col);
+    if (br1 >= br0 && bc1 >= bc0)
+      stage_window(km, s0.row + br0, s0.col + bc0, br1 - br0 + k_in.d.bh, bc1 - bc0 + k_in.d.bw);
+    __syncthreads();
+  }
+  const Ctx &k = km;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   start = clamp_mv(k, start);
   *best = start;
@@ -960,6 +976,38 @@ __device__ int refine_8p(const Ctx &k, bool skip, Mv *bestp) {
 // pitch in words that is 4 (mod 8): conflict-free uint4 access by 8 consecutive rows
 __host__ __device__ __forceinline__ int vec_pitch(int words) { return ((words + 3) & ~7) + 4 >= words ? ((words + 3) & ~7) + 4 : ((words + 11) & ~7) + 4; }
 
+// Cooperative copy of the reference window whose top-left pixel is at full-pel mv (wr0, wc0), wh x ww
+// pixels, into the window region of shared memory (when it fits k.win_budget); on success the pixel views
+// of `k` address the copy.  The caller synchronises the CTA afterwards.
+__device__ bool stage_window(Ctx &k, int wr0, int wc0, int wh, int ww) {
+  const B200MeLaunch &l = *k.l;
+  const int px = k.px;
+  const long long stride_b = (long long)l.ref_stride * px;
+  const unsigned char *g_ref0 = static_cast<const unsigned char *>(l.ref) + (size_t)k.d.ref_offset * px;
+  const unsigned char *g0 = g_ref0 + ((long long)wr0 * l.ref_stride + wc0) * px;
+  const bool vec = (stride_b & 15) == 0;
+  const int lead = (int)(reinterpret_cast<unsigned long long>(g0) & (vec ? 15 : 3));
+  // + 4 words: the vector path reads a 16-byte aligned superset of each candidate segment
+  const int words = vec ? vec_pitch((lead + ww * px + 3) / 4 + 4) : (lead + ww * px + 3) / 4 + 1;
+  const long long need = (long long)wh * words * 4;
+  if (!((stride_b & 3) == 0 && need <= k.win_budget && wh > 0 && ww > 0)) return false;
+  unsigned *s_win = reinterpret_cast<unsigned *>(me_smem + k.win_region_off);
+  const unsigned *ga = reinterpret_cast<const unsigned *>(g0 - lead);
+  // exactly the words that hold window bytes: nothing is read past the window's right edge
+  // (the funnel shifts also touch the following word; its value is shifted out)
+  const int copy_words = (lead + ww * px + 3) / 4;
+  for (int i = threadIdx.x; i < wh * (copy_words + 1); i += kThreads) {
+    const int y = i / (copy_words + 1), x = i - y * (copy_words + 1);
+    s_win[y * words + x] = x < copy_words ? ga[(long long)y * (stride_b >> 2) + x] : 0u;
+  }
+  k.ref_pitch = words * 4 / px;
+  k.ref0 = reinterpret_cast<unsigned char *>(s_win) + lead + ((long long)(-wr0) * k.ref_pitch + (-wc0)) * px;
+  k.fast = vec;
+  k.staged = true;
+  k.win0_off = k.win_region_off + lead + ((-wr0) * k.ref_pitch + (-wc0)) * px;
+  return true;
+}
+
 // Stage the source block and (when it fits) the reachable reference window; fills in the
 // pixel views of `k`.  Layout for the vector SAD path: row pitches of 4 (mod 8) words and
 // 16-byte aligned row starts (needs a reference stride that is a multiple of 16 bytes).
@@ -1002,6 +1050,8 @@ __device__ void stage_inputs(Ctx &k, unsigned char *smem, int window_budget, int
           tma_load_2d(smem + src_bytes + b * box_bytes, tm_ref, (wxb - lead) >> 2, wy + b * kTmaRows, &g_mbar);
       }
       k.src_pitch_w = tc.src_pitch_w;
+      k.win_region_off = src_bytes;
+      k.win_budget = window_budget;
       k.ref_pitch = tc.win_pitch_w * 4 / px;
       k.ref0 = smem + src_bytes + lead + ((long long)(-wr0) * k.ref_pitch + (-wc0)) * px;
       k.fast = true;
@@ -1018,29 +1068,9 @@ __device__ void stage_inputs(Ctx &k, unsigned char *smem, int window_budget, int
     s_src[y * k.src_pitch_w * 4 + x] = g_src[(size_t)y * l.cur_stride * px + x];
   }
   const int src_bytes = (bh * k.src_pitch_w * 4 + 15) & ~15;
-  const unsigned char *g0 = g_ref0 + ((long long)wr0 * l.ref_stride + wc0) * px;
-  const bool vec = (stride_b & 15) == 0;
-  const int lead = (int)(reinterpret_cast<unsigned long long>(g0) & (vec ? 15 : 3));
-  // + 4 words: the vector path reads a 16-byte aligned superset of each candidate segment
-  const int words = vec ? vec_pitch((lead + ww * px + 3) / 4 + 4) : (lead + ww * px + 3) / 4 + 1;
-  const long long need = (long long)wh * words * 4;
-  if ((stride_b & 3) == 0 && need <= window_budget && wh > 0 && ww > 0) {
-    unsigned *s_win = reinterpret_cast<unsigned *>(smem + src_bytes);
-    const unsigned *ga = reinterpret_cast<const unsigned *>(g0 - lead);
-    // exactly the words that hold window bytes: nothing is read past the window's right edge
-    // (the funnel shifts also touch the following word; its value is shifted out)
-    const int copy_words = (lead + ww * px + 3) / 4;
-    for (int i = threadIdx.x; i < wh * (copy_words + 1); i += kThreads) {
-      const int y = i / (copy_words + 1), x = i - y * (copy_words + 1);
-      s_win[y * words + x] = x < copy_words ? ga[(long long)y * (stride_b >> 2) + x] : 0u;
-    }
-    k.ref_pitch = words * 4 / px;
-    k.ref0 = reinterpret_cast<unsigned char *>(s_win) + lead +
-             ((long long)(-wr0) * k.ref_pitch + (-wc0)) * px;
-    k.fast = vec;
-    k.staged = true;
-    k.win0_off = src_bytes + lead + ((-wr0) * k.ref_pitch + (-wc0)) * px;
-  }
+  k.win_region_off = src_bytes;
+  k.win_budget = window_budget;
+  stage_window(k, wr0, wc0, wh, ww);
   __syncthreads();
 }
 

@@ -254,6 +254,17 @@ extern "C" int b200_queue_tf_describe(int width, int height, int pitch, int orig
   return n;
 }
 
+// Shared memory for the mesh-local window of a frame-wide search (me_fullpel.cuh mesh_search): the
+// largest mesh stage box is (2 * range + block) pixels square, rows padded to the vector pitch.
+static int mesh_window_bytes(const int *mesh_range, int bw, int bh, int px) {
+  int r = 0;
+  for (int i = 0; i < 4; ++i) r = mesh_range[i] > r ? mesh_range[i] : r;
+  if (r <= 0) return 0;
+  if (r > 64) r = 64;  // larger first stages (range scaled by the start mv, mcomp.c:1620) fall back to L1/L2
+  const int rows = 2 * r + bh, words = ((15 + (2 * r + bw) * px + 3) / 4 + 4 + 11) & ~3;
+  return rows * (words + 8) * 4;
+}
+
 extern "C" int b200_queue_tf_motion_search(b200_ctx *ctx, const b200_frame *cur, const b200_frame *ref,
                                            const B200TfParams *p, const int16_t *ref_mvs, B200TfResult *out) {
   if (!ctx || !cur || !ref || !p || !out) return B200_EINVAL;
@@ -300,6 +311,7 @@ extern "C" int b200_queue_tf_motion_search(b200_ctx *ctx, const b200_frame *cur,
     B200MeLaunch fl = l;
     fl.n_blocks = cnt;
     fl.max_bw = stage ? p->bw >> 1 : p->bw, fl.max_bh = stage ? p->bh >> 1 : p->bh;
+    fl.window_bytes = mesh_window_bytes(p->mesh_range, fl.max_bw, fl.max_bh, cur->bd > 8 ? 2 : 1);
     fl.blocks = d_desc + (stage ? 2 * n : 0);
     fl.results = stage ? r_full1 : r_full0;
     if (stage) fl.start_from = r_sub0, fl.start_group = 4;  // start_mv = get_fullmv_from_mv(ref_mv) (:198)
@@ -473,6 +485,7 @@ extern "C" int b200_queue_tpl_motion_estimation(b200_ctx *ctx, const b200_frame 
   l.families = p->search_method <= B200_ME_CLAMPED_DIAMOND ? B200_ME_FAMILY_NSTEP : B200_ME_FAMILY_PATTERN;
   l.n_blocks = n;
   l.max_bw = p->bw, l.max_bh = p->bh;
+  l.window_bytes = mesh_window_bytes(p->mesh_range, p->bw, p->bh, cur->bd > 8 ? 2 : 1);
   l.blocks = (const B200MeBlock *)(base + o_desc);
   l.results = (B200MeResult *)(base + o_res);
   rc = b200_me_fullpel_launch(ctx, &l, s);

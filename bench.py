@@ -980,7 +980,7 @@ def main():
     ap.add_argument("--no-extras", action="store_true", help="skip the config[3] / config[4] / Hadamard sections")
     ap.add_argument("--config5-frames", type=int, default=120, help="frames of the 4K 10-bit batch (all ranks)")
     ap.add_argument("--sizes", default="", help="comma list of tx sizes (debug)")
-    ap.add_argument("--only", default="", choices=["", "hbd4k", "itx", "hadamard"],
+    ap.add_argument("--only", default="", choices=["", "hbd4k", "itx", "hadamard", "tf"],
                     help="(profiling) run one extras section alone and print its JSON")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -1054,8 +1054,10 @@ def main():
             out = bench_hbd4k(ctx, dev, stream, args.steps, args.warmup, seed)
         elif args.only == "itx":
             out = bench_itx(ctx, dev, stream, args.steps, args.warmup, seed, hbm_peak_gbs())
+        elif args.only == "tf":
+            out = bench_tf_queue(ctx, make_residual_frames([0], seed)[2], seed, os.cpu_count() or 1)
         else:
-            d_src = torch.from_numpy(make_residual_frames(range(args.frames), seed).reshape(-1)).to(dev)
+            d_src = torch.from_numpy(make_residual_frames(range(args.frames), seed)[0].reshape(-1)).to(dev)
             out = bench_hadamard(ctx, dev, stream, args.steps, args.warmup, d_src, args.frames)
         print(json.dumps({"only": args.only, "result": out}))
         return 0
