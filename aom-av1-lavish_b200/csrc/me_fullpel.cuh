@@ -634,9 +634,15 @@ __device__ __forceinline__ void mesh_strided_band(const Ctx &k, int row0, int nr
 // strided stages.  Not inlined: its register allocation stays out of the 8-bit paths of the kernel.
 __device__ __noinline__ void mesh_band_fast_hbd(const Ctx &k, int row0, int nrows, int col0, int nc, int step) {
   if (step == 1) mesh1_band<4, 2, 4>(k, row0, nrows, col0, nc);
-  else if (step == 4) mesh_strided_band<8, 2, 2, 2>(k, row0, nrows, col0, nc, step);
-  else if (step == 8) mesh_strided_band<8, 4, 2, 2>(k, row0, nrows, col0, nc, step);
-  else mesh_strided_band<8, 8, 2, 2>(k, row0, nrows, col0, nc, step);
+  else if (k.d.bw >= 16) {
+    if (step == 4) mesh_strided_band<8, 2, 2, 2>(k, row0, nrows, col0, nc, step);
+    else if (step == 8) mesh_strided_band<8, 4, 2, 2>(k, row0, nrows, col0, nc, step);
+    else mesh_strided_band<8, 8, 2, 2>(k, row0, nrows, col0, nc, step);
+  } else {  // 8 pixels = 4 words
+    if (step == 4) mesh_strided_band<4, 2, 2, 2>(k, row0, nrows, col0, nc, step);
+    else if (step == 8) mesh_strided_band<4, 4, 2, 2>(k, row0, nrows, col0, nc, step);
+    else mesh_strided_band<4, 8, 2, 2>(k, row0, nrows, col0, nc, step);
+  }
   // raw block sums -> encoder SAD (>> 2 / >> 4, encoder_utils.h:153-208) + mv cost
   __syncthreads();
   for (int j = threadIdx.x; j < nrows * nc; j += kThreads) {
@@ -664,23 +670,24 @@ __device__ __forceinline__ bool mesh_band_fast(const Ctx &k, int row0, int nrows
     if (step == 4) mesh_strided_band<8, 1, 1, kJB>(k, row0, nrows, col0, nc, step);
     else if (step == 8) mesh_strided_band<8, 2, 1, kJB>(k, row0, nrows, col0, nc, step);
     else mesh_strided_band<8, 4, 1, kJB>(k, row0, nrows, col0, nc, step);
-  } else {
+  } else if (bw >= 16) {
     if (step == 4) mesh_strided_band<4, 1, 1, kJB>(k, row0, nrows, col0, nc, step);
     else if (step == 8) mesh_strided_band<4, 2, 1, kJB>(k, row0, nrows, col0, nc, step);
     else mesh_strided_band<4, 4, 1, kJB>(k, row0, nrows, col0, nc, step);
+  } else {  // 8-pixel blocks (the temporal filter's sub-blocks): 2-word segments
+    if (step == 4) mesh_strided_band<2, 1, 1, kJB>(k, row0, nrows, col0, nc, step);
+    else if (step == 8) mesh_strided_band<2, 2, 1, kJB>(k, row0, nrows, col0, nc, step);
+    else mesh_strided_band<2, 4, 1, kJB>(k, row0, nrows, col0, nc, step);
   }
   return true;
 }
 
 __device__ __forceinline__ bool mesh_fast_ok(const Ctx &k, bool skip, int step, int nc) {
   if (skip || !k.staged || (k.d.bh & 3) || nc > kMaxCand) return false;
-  if (k.px == 2) {
-    if (step == 1) return k.d.bw >= 8;  // 16 bytes = one 4-word segment
-    return k.fast && k.d.bw >= 16 && (step == 4 || step == 8 || step == 16);
-  }
-  if (step == 1) return k.d.bw >= 8;
+  if (k.d.bw < 8) return false;
+  if (step == 1) return true;  // 8 bytes = one 2-word segment (uint16: 16 bytes = one 4-word segment)
   // strided: 16-byte aligned window rows (vector loads), whole-word candidate spacing
-  return k.fast && k.d.bw >= 16 && (step == 4 || step == 8 || step == 16);
+  return k.fast && (step == 4 || step == 8 || step == 16);
 }
 
 // exhaustive_mesh_search (mcomp.c:1530-1599).  Candidates are visited row-major; at
