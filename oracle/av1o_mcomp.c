@@ -103,6 +103,29 @@ static unsigned me_sad(const Av1oMeParams *p, int row, int col, int skip) {
   return v;
 }
 
+/* the predictor of a compound search at mv (row, col) in 1/8 pel: reference sample (optionally
+ * interpolated), blended with second_pred by average or mask */
+static void compound_view(const Av1oMeParams *p, int fr, int fc, Av1oCompound *c) {
+  memset(c, 0, sizeof(*c));
+  c->w = p->bw, c->h = p->bh, c->highbd = p->highbd, c->bd = p->bd;
+  c->pre = (const char *)p->ref + ((long)fr * p->ref_stride + fc) * (p->highbd ? 2 : 1);
+  c->pre_stride = p->ref_stride;
+  c->tgt = p->src, c->tgt_stride = p->src_stride;
+  c->blend = p->mask ? AV1O_BLEND_MASK : AV1O_BLEND_AVG;
+  c->second_pred = p->second_pred;
+  c->mask = p->mask, c->mask_stride = p->mask_stride, c->invert_mask = p->inv_mask;
+}
+
+/* get_mvpred_compound_sad (mcomp.c:729): msdf / sdaf, with the encoder's >> 2 / >> 4 high-bit-depth
+ * wrappers (encoder_utils.h MAKE_BFP_SADAVG_WRAPPER / MAKE_MBFP_COMPOUND_SAD_WRAPPER) */
+static unsigned me_sad_compound(const Av1oMeParams *p, int row, int col) {
+  Av1oCompound c;
+  compound_view(p, row, col, &c);
+  unsigned v = av1o_compound_sad(&c);
+  if (p->highbd) v >>= p->bd == 10 ? 2 : (p->bd == 12 ? 4 : 0);
+  return v;
+}
+
 static unsigned me_var(const Av1oMeParams *p, int row, int col, unsigned *sse) {
   if (p->highbd) {
     const uint16_t *ref = (const uint16_t *)p->ref + row * p->ref_stride + col;
@@ -577,6 +600,30 @@ static unsigned pref_error(const Av1oMeParams *p, Mv mv, int upsampled, unsigned
   const int fr = mv.row >> 3, fc = mv.col >> 3, sx = mv.col & 7, sy = mv.row & 7;
   const int w = p->bw, h = p->bh;
   unsigned v;
+  if (p->second_pred) {
+    /* compound: svaf / msvf (bilinear estimate), or aom_comp_avg_upsampled_pred /
+     * aom_comp_mask_upsampled_pred (reconinter_enc.c:498-560) followed by vf */
+    Av1oCompound c;
+    if (!upsampled) {
+      compound_view(p, fr, fc, &c);
+      c.subpel = 1, c.xoff = sx, c.yoff = sy;
+      return av1o_compound_variance(&c, sse);
+    }
+    const int taps = p->subpel_search_type == AV1O_USE_2_TAPS ? 2
+                     : (p->subpel_search_type == AV1O_USE_4_TAPS ? 4 : 8);
+    void *up = malloc((size_t)(w * h) * 2);
+    if (p->highbd)
+      av1o_highbd_upsampled_pred((uint16_t *)up, w, h, sx, sy, (const uint16_t *)p->ref + fr * p->ref_stride + fc,
+                                 p->ref_stride, p->bd, taps);
+    else
+      av1o_upsampled_pred((uint8_t *)up, w, h, sx, sy, (const uint8_t *)p->ref + fr * p->ref_stride + fc,
+                          p->ref_stride, taps);
+    compound_view(p, 0, 0, &c);
+    c.pre = up, c.pre_stride = w;
+    v = av1o_compound_variance(&c, sse);
+    free(up);
+    return v;
+  }
   if (p->highbd) {
     const uint16_t *ref = (const uint16_t *)p->ref + fr * p->ref_stride + fc;
     const uint16_t *src = (const uint16_t *)p->src;
@@ -671,7 +718,11 @@ void av1o_find_best_sub_pixel_tree(const Av1oMeParams *p, Av1oMeResult *r) {
     /* vf(y, y_stride, src, src_stride): reference first -- the order matters at 10/12 bit
      * because the rounding of the (signed) sum is not symmetric (variance.c:361-379) */
     const int fr = s.best.row >> 3, fc = s.best.col >> 3;
-    if (p->highbd)
+    if (p->second_pred) { /* setup_center_error :2781: aom_comp_avg_pred / aom_comp_mask_pred, then vf */
+      Av1oCompound c;
+      compound_view(p, fr, fc, &c);
+      e = av1o_compound_variance(&c, &sse);
+    } else if (p->highbd)
       e = av1o_highbd_variance((const uint16_t *)p->ref + fr * p->ref_stride + fc, p->ref_stride,
                                (const uint16_t *)p->src, p->src_stride, p->bw, p->bh, p->bd, &sse);
     else
@@ -741,7 +792,11 @@ void av1o_find_best_sub_pixel_tree_pruned(const Av1oMeParams *p, Av1oMeResult *r
   unsigned sse, e;
   {
     const int fr = s.best.row >> 3, fc = s.best.col >> 3;
-    if (p->highbd)
+    if (p->second_pred) { /* setup_center_error :2781: aom_comp_avg_pred / aom_comp_mask_pred, then vf */
+      Av1oCompound c;
+      compound_view(p, fr, fc, &c);
+      e = av1o_compound_variance(&c, &sse);
+    } else if (p->highbd)
       e = av1o_highbd_variance((const uint16_t *)p->ref + fr * p->ref_stride + fc, p->ref_stride,
                                (const uint16_t *)p->src, p->src_stride, p->bw, p->bh, p->bd, &sse);
     else
@@ -792,7 +847,7 @@ void av1o_find_best_sub_pixel_tree_pruned(const Av1oMeParams *p, Av1oMeResult *r
 }
 
 /* ===================================== av1_refining_search_8p_c (:1683) ===== */
-/* single reference (second_pred == NULL, no mask): get_mvpred_compound_sad is sdf */
+/* get_mvpred_compound_sad (:729): sdf for a single reference, sdaf / msdf with second_pred / mask */
 void av1o_refining_search_8p(const Av1oMeParams *p, Av1oMeResult *r) {
   static const int nb[8][2] = { { -1, 0 }, { 0, -1 }, { 0, 1 }, { 1, 0 },
                                 { -1, -1 }, { 1, -1 }, { -1, 1 }, { 1, 1 } };
@@ -803,7 +858,8 @@ void av1o_refining_search_8p(const Av1oMeParams *p, Av1oMeResult *r) {
   int centre = RANGE * STRIDE + RANGE;
   Mv start = { p->start_row, p->start_col };
   Mv best = clamp_mv(p, start);
-  unsigned best_sad = me_sad(p, best.row, best.col, p->use_skip_sad);
+  unsigned best_sad = p->second_pred ? me_sad_compound(p, best.row, best.col)
+                                     : me_sad(p, best.row, best.col, p->use_skip_sad);
   best_sad += (unsigned)sad_cost(p, best.row, best.col);
   grid[centre] = 1;
   for (int i = 0; i < RANGE; ++i) {
@@ -815,7 +871,7 @@ void av1o_refining_search_8p(const Av1oMeParams *p, Av1oMeResult *r) {
       const Mv m = { best.row + nb[j][0], best.col + nb[j][1] };
       if (m.col < p->col_min || m.col > p->col_max || m.row < p->row_min || m.row > p->row_max)
         continue;
-      unsigned sad = me_sad(p, m.row, m.col, p->use_skip_sad);
+      unsigned sad = p->second_pred ? me_sad_compound(p, m.row, m.col) : me_sad(p, m.row, m.col, p->use_skip_sad);
       if (sad < best_sad) {
         sad += (unsigned)sad_cost(p, m.row, m.col);
         if (sad < best_sad) {

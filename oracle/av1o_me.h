@@ -68,6 +68,13 @@ typedef struct {
    * 2 _pruned_more (:2907); sp_have_cost_list = (ms_params->cost_list != NULL) */
   int sp_tree, sp_have_cost_list;
   int sp_cost_list[5];
+  /* compound search (av1_set_ms_compound_refs, mcomp.c:80-93; MSBuffers mcomp.h:64-90): second_pred =
+   * bw-pitch prediction from the other reference, mask = optional 6-bit blend weights.  Served by
+   * av1_refining_search_8p_c and the three sub-pel trees -- the two searches of one iteration of
+   * av1_joint_motion_search (motion_search_facade.c:594-652). */
+  const void *second_pred;
+  const uint8_t *mask;
+  int mask_stride, inv_mask;
 } Av1oMeParams;
 
 typedef struct {

@@ -66,9 +66,29 @@
     RF(aom_highbd_sad_skip_##W##x##H##x4d)(a, as, b, bs, o);                                   \
     for (int i = 0; i < 4; ++i) o[i] >>= 4;                                                    \
   }                                                                                            \
+  static unsigned sada##W##x##H##_b10(const uint8_t *a, int as, const uint8_t *b, int bs,      \
+                                      const uint8_t *sp) {                                     \
+    return RF(aom_highbd_sad##W##x##H##_avg)(a, as, b, bs, sp) >> 2;                           \
+  }                                                                                            \
+  static unsigned sada##W##x##H##_b12(const uint8_t *a, int as, const uint8_t *b, int bs,      \
+                                      const uint8_t *sp) {                                     \
+    return RF(aom_highbd_sad##W##x##H##_avg)(a, as, b, bs, sp) >> 4;                           \
+  }                                                                                            \
+  static unsigned msad##W##x##H##_b10(const uint8_t *a, int as, const uint8_t *b, int bs,      \
+                                      const uint8_t *sp, const uint8_t *m, int ms, int inv) {  \
+    return RF(aom_highbd_masked_sad##W##x##H)(a, as, b, bs, sp, m, ms, inv) >> 2;              \
+  }                                                                                            \
+  static unsigned msad##W##x##H##_b12(const uint8_t *a, int as, const uint8_t *b, int bs,      \
+                                      const uint8_t *sp, const uint8_t *m, int ms, int inv) {  \
+    return RF(aom_highbd_masked_sad##W##x##H)(a, as, b, bs, sp, m, ms, inv) >> 4;              \
+  }                                                                                            \
   static int fill##W##x##H(aom_variance_fn_ptr_t *f, int highbd, int bd) {                     \
     memset(f, 0, sizeof(*f));                                                                  \
     if (!highbd) {                                                                             \
+      f->sdaf = RF(aom_sad##W##x##H##_avg);                                                    \
+      f->svaf = RF(aom_sub_pixel_avg_variance##W##x##H);                                       \
+      f->msdf = RF(aom_masked_sad##W##x##H);                                                   \
+      f->msvf = RF(aom_masked_sub_pixel_variance##W##x##H);                                    \
       f->sdf = RF(aom_sad##W##x##H);                                                           \
       f->sdsf = RF(aom_sad_skip_##W##x##H);                                                    \
       f->vf = RF(aom_variance##W##x##H);                                                       \
@@ -77,6 +97,10 @@
       f->sdx3df = RF(aom_sad##W##x##H##x3d);                                                   \
       f->sdsx4df = RF(aom_sad_skip_##W##x##H##x4d);                                            \
     } else if (bd == 10) {                                                                     \
+      f->sdaf = sada##W##x##H##_b10;                                                           \
+      f->svaf = RF(aom_highbd_10_sub_pixel_avg_variance##W##x##H);                             \
+      f->msdf = msad##W##x##H##_b10;                                                           \
+      f->msvf = RF(aom_highbd_10_masked_sub_pixel_variance##W##x##H);                          \
       f->sdf = sad##W##x##H##_b10;                                                             \
       f->sdsf = sads##W##x##H##_b10;                                                           \
       f->vf = RF(aom_highbd_10_variance##W##x##H);                                             \
@@ -85,6 +109,10 @@
       f->sdx3df = sad4##W##x##H##_b10;                                                         \
       f->sdsx4df = sads4##W##x##H##_b10;                                                       \
     } else {                                                                                   \
+      f->sdaf = sada##W##x##H##_b12;                                                           \
+      f->svaf = RF(aom_highbd_12_sub_pixel_avg_variance##W##x##H);                             \
+      f->msdf = msad##W##x##H##_b12;                                                           \
+      f->msvf = RF(aom_highbd_12_masked_sub_pixel_variance##W##x##H);                          \
       f->sdf = sad##W##x##H##_b12;                                                             \
       f->sdsf = sads##W##x##H##_b12;                                                           \
       f->vf = RF(aom_highbd_12_variance##W##x##H);                                             \
@@ -145,6 +173,9 @@ static void fullpel_common(const Av1oMeParams *p, Av1oMeResult *r, int refine8p)
   ms.vfp = &vfp;
   ms.ms_buffers.src = &src;
   ms.ms_buffers.ref = &ref;
+  if (p->second_pred) /* av1_set_ms_compound_refs (mcomp.c:80) */
+    av1_set_ms_compound_refs(&ms.ms_buffers, as_ref_ptr(p->second_pred, p->highbd), p->mask, p->mask_stride,
+                             p->inv_mask);
   search_site_config *cfg = (search_site_config *)calloc(1, sizeof(*cfg));
   switch (p->search_method) {
     case AV1O_NSTEP:
@@ -259,6 +290,9 @@ static void subpel_common(const Av1oMeParams *p, Av1oMeResult *r, int tree) {
   ms.var_params.subpel_search_type = (SUBPEL_SEARCH_TYPE)p->subpel_search_type;
   ms.var_params.ms_buffers.src = &src;
   ms.var_params.ms_buffers.ref = &ref;
+  if (p->second_pred)
+    av1_set_ms_compound_refs(&ms.var_params.ms_buffers, as_ref_ptr(p->second_pred, p->highbd), p->mask,
+                             p->mask_stride, p->inv_mask);
   ms.var_params.w = p->bw;
   ms.var_params.h = p->bh;
 

@@ -220,7 +220,8 @@ class MeParams(C.Structure):
                 ("subpel_search_type", C.c_int), ("sp_col_min", C.c_int), ("sp_col_max", C.c_int),
                 ("sp_row_min", C.c_int), ("sp_row_max", C.c_int), ("sp_start_row", C.c_int),
                 ("sp_start_col", C.c_int), ("sp_tree", C.c_int), ("sp_have_cost_list", C.c_int),
-                ("sp_cost_list", C.c_int * 5)]
+                ("sp_cost_list", C.c_int * 5), ("second_pred", C.c_void_p), ("mask", C.c_void_p),
+                ("mask_stride", C.c_int), ("inv_mask", C.c_int)]
 
 
 class MeResult(C.Structure):

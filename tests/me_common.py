@@ -104,3 +104,18 @@ def random_cost_list(rng, p):
     for i in range(5):
         p.sp_cost_list[i] = vals[i]
     return p
+
+
+def add_compound(rng, p, bd, keep, masked):
+    """attach a second_pred block (bw-pitch, the other reference's prediction) and, when `masked`, a 6-bit
+    blend mask to a search descriptor; `keep` receives the arrays (they must outlive the call)"""
+    dt = np.uint16 if bd > 8 else np.uint8
+    second = rng.integers(0, 1 << bd, p.bw * p.bh).astype(dt)
+    keep.append(second)
+    p.second_pred = second.ctypes.data
+    if masked:
+        ms = p.bw + int(rng.integers(0, 3)) * 4
+        mask = rng.integers(0, 65, p.bh * ms).astype(np.uint8)
+        keep.append(mask)
+        p.mask, p.mask_stride, p.inv_mask = mask.ctypes.data, ms, int(rng.integers(0, 2))
+    return p
