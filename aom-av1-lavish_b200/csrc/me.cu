@@ -57,6 +57,7 @@ struct Ctx {
   bool fast;                 // staged window with 16-byte aligned rows: vector-load SAD path
   bool staged;               // reference window is in shared memory (word-aligned rows at least)
   int win0_off;              // staged: byte offset inside me_smem of the reference pixel at mv (0,0)
+  bool compound;             // compound search (B200MeLaunch.compound): its operands live in g_cmp
   int win_region_off;        // byte offset inside me_smem where the window region starts (after the source)
   int win_budget;            // bytes of that region (0: none)
   int cost_fr, cost_fc;      // full-pel reference mv of the sad-domain mv cost
@@ -546,8 +547,69 @@ __device__ __forceinline__ unsigned sad_finish(const Ctx &k, unsigned acc, bool 
   if (skip) acc *= 2;
   return acc >> k.sad_shift;
 }
+// Operands of a compound search: prediction from the other reference and optional blend mask.  Kept in
+// shared memory, not in Ctx: the context is copied and spilled by the hot single-reference paths.
+struct CompoundOps {
+  const unsigned char *second;
+  const unsigned char *cmask;  // nullptr: average
+  int cmask_stride;
+  int cinv;
+};
+__shared__ CompoundOps g_cmp;
+// compound descriptor of search `bi`; the CTA is synchronised by the staging that follows
+__device__ __forceinline__ void init_compound(Ctx &k, const B200MeLaunch &l, int bi) {
+  k.compound = l.compound != nullptr && l.second_pred != nullptr;
+  if (k.compound && threadIdx.x == 0) {
+    const B200MeCompound c = l.compound[bi];
+    CompoundOps o;
+    o.second = static_cast<const unsigned char *>(l.second_pred) + (size_t)c.second_offset * k.px;
+    o.cmask = nullptr;
+    o.cmask_stride = 0;
+    o.cinv = 0;
+    if (c.use_mask && l.mask) {
+      o.cmask = l.mask + c.mask_offset;
+      o.cmask_stride = c.mask_stride;
+      o.cinv = c.invert_mask != 0;
+    }
+    g_cmp = o;
+  }
+}
+// AOM_BLEND_AVG / AOM_BLEND_A64 (aom_dsp/blend.h:23-40) of predictor sample pv of pixel (x, y), i = y * bw + x
+__device__ __forceinline__ int compound_blend(const Ctx &k, int pv, int i, int y, int x) {
+  const unsigned char *second = g_cmp.second, *cmask = g_cmp.cmask;
+  const int s2 = k.px == 1 ? (int)second[i] : (int)reinterpret_cast<const unsigned short *>(second)[i];
+  if (!cmask) return (s2 + pv + 1) >> 1;
+  const int m = cmask[y * g_cmp.cmask_stride + x];
+  return g_cmp.cinv ? (m * s2 + (64 - m) * pv + 32) >> 6 : (m * pv + (64 - m) * s2 + 32) >> 6;
+}
+// get_mvpred_compound_sad (mcomp.c:729) with second_pred: vfp->sdaf / vfp->msdf, one warp per candidate
+__device__ __noinline__ unsigned warp_sad_compound(const Ctx &k, int row, int col) {
+  const int lane = threadIdx.x & 31, bw = k.d.bw, n = bw * k.d.bh;
+  const unsigned char *rp = k.ref0 + ((long long)row * k.ref_pitch + col) * k.px;
+  const int sp = k.src_pitch_w * 4 / k.px;  // source pitch in pixels (shared copy)
+  unsigned acc = 0;
+  for (int i = lane; i < n; i += 32) {
+    const int y = i / bw, x = i - y * bw;
+    int p, s;
+    if (k.px == 1) {
+      p = rp[(long long)y * k.ref_pitch + x];
+      s = k.src[y * sp + x];
+    } else {
+      p = reinterpret_cast<const unsigned short *>(rp)[(long long)y * k.ref_pitch + x];
+      s = reinterpret_cast<const unsigned short *>(k.src)[y * sp + x];
+    }
+    acc += (unsigned)abs(s - compound_blend(k, p, i, y, x));
+  }
+  return warp_sum_u(acc) >> k.sad_shift;
+}
 __device__ __forceinline__ unsigned warp_sad(const Ctx &k, int row, int col, bool skip, int lane) {
   return sad_finish(k, warp_sad_part(k, row, col, skip, 0, 1), skip);
+}
+// the SAD of av1_refining_search_8p_c: get_mvpred_compound_sad (the only full-pel search served with
+// second_pred; the branch stays out of the single-reference paths of the other kernel instances)
+__device__ __forceinline__ unsigned warp_sad_refine(const Ctx &k, int row, int col, bool skip, int lane) {
+  if (k.compound) return warp_sad_compound(k, row, col);
+  return warp_sad(k, row, col, skip, lane);
 }
 
 // ---- CTA-cooperative evaluation of a step's candidates (staged 8-bit path) ----------

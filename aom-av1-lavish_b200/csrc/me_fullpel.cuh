@@ -944,7 +944,7 @@ __device__ int refine_8p(const Ctx &k, bool skip, Mv *bestp) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const Mv start = { k.d.start_row, k.d.start_col };
   Mv best = clamp_mv(k, start);
-  unsigned best_sad = cta_value(k, [&](int ln) { return warp_sad(k, best.row, best.col, skip, ln); });
+  unsigned best_sad = cta_value(k, [&](int ln) { return warp_sad_refine(k, best.row, best.col, skip, ln); });
   best_sad += (unsigned)sad_cost(k, best.row, best.col);
   int centre = kRange * kStride + kRange;
   unsigned long long visited = 1ull << centre;
@@ -954,7 +954,7 @@ __device__ int refine_8p(const Ctx &k, bool skip, Mv *bestp) {
       const int g = centre + nb[warp][0] * kStride + nb[warp][1];
       const int r = best.row + nb[warp][0], c = best.col + nb[warp][1];
       unsigned v = 0xffffffffu;
-      if (!((visited >> g) & 1) && in_range(k, r, c)) v = warp_sad(k, r, c, skip, lane);
+      if (!((visited >> g) & 1) && in_range(k, r, c)) v = warp_sad_refine(k, r, c, skip, lane);
       if (lane == 0) g_cand[warp] = v;
     }
     __syncthreads();
@@ -1105,6 +1105,8 @@ __global__ void __launch_bounds__(kThreads, 3) fullpel_kernel(const B200MeLaunch
   k.sites = &g_sites;
   k.px = l.highbd ? 2 : 1;
   k.sad_shift = l.highbd ? (l.bd == 10 ? 2 : (l.bd == 12 ? 4 : 0)) : 0;
+  if constexpr (FAM == 2) init_compound(k, l, bi);  // compound refinement (av1_refining_search_8p_c)
+  else k.compound = false;
 #ifdef B200_ME_TIMING
   const long long t_start = clock64();
 #endif

@@ -80,6 +80,10 @@ static int me_check(const B200MeLaunch *l) {
     b200::set_error("b200_me_*_launch: missing buffer or stride");
     return B200_EINVAL;
   }
+  if (l->compound && !l->second_pred) {
+    b200::set_error("b200_me_*_launch: compound descriptors without second_pred");
+    return B200_EINVAL;
+  }
   if ((l->mvcost[0] == nullptr) != (l->mvcost[1] == nullptr) || (l->mvcost[0] && !l->mvjcost)) {
     b200::set_error("b200_me_*_launch: mvjcost / mvcost[0] / mvcost[1] must be given together");
     return B200_EINVAL;

@@ -54,7 +54,9 @@ __device__ unsigned cta_pref_error(const SubCtx &s, Mv mv, int mode, unsigned *s
   if (mode == 0) {
     for (int i = threadIdx.x; i < n; i += kThreads) {
       const int y = i / bw, x = i - y * bw;
-      const int df = ref_px(k, rp, (long long)y * k.ref_pitch + x) - src_px(k, i);
+      int pv = ref_px(k, rp, (long long)y * k.ref_pitch + x);
+      if (k.compound) pv = compound_blend(k, pv, i, y, x);  // setup_center_error (:2781)
+      const int df = pv - src_px(k, i);
       sum += df;
       sse += (unsigned)(df * df);
     }
@@ -67,6 +69,7 @@ __device__ unsigned cta_pref_error(const SubCtx &s, Mv mv, int mode, unsigned *s
       const int h1 = (ref_px(k, rp, o + k.ref_pitch) * f0 + ref_px(k, rp, o + k.ref_pitch + 1) * f1 + 64) >> 7;
       int pv = (h0 * g0 + h1 * g1 + 64) >> 7;
       if (k.px == 1) pv &= 0xff;  // uint8 store of the second pass (value <= 255 anyway)
+      if (k.compound) pv = compound_blend(k, pv, i, y, x);  // svaf / msvf
       const int df = pv - src_px(k, i);
       sum += df;
       sse += (unsigned)(df * df);
@@ -103,6 +106,7 @@ __device__ unsigned cta_pref_error(const SubCtx &s, Mv mv, int mode, unsigned *s
       } else {
         pv = s.tmp[i];
       }
+      if (k.compound) pv = compound_blend(k, pv, i, y, x);  // aom_comp_avg / comp_mask_upsampled_pred
       const int df = pv - src_px(k, i);
       sum += df;
       sse += (unsigned)(df * df);
@@ -502,6 +506,7 @@ __global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) 
   s.k.sites = nullptr;
   s.k.px = l.highbd ? 2 : 1;
   s.k.sad_shift = 0;
+  init_compound(s.k, l, bi);
   s.search_type = (s.k.d.subpel >> 4) & 3;
   s.start = Mv{ s.k.d.start_row, s.k.d.start_col };
   // the limits are sub-pel here: no window staging (window_budget 0), reference via L1/L2
@@ -527,7 +532,7 @@ __global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) 
     SubFast f;
     f.on = false;
     const int mbw = l.max_bw > 0 ? l.max_bw : 128, mbh = l.max_bh > 0 ? l.max_bh : 128;
-    if (s.search_type != B200_USE_2_TAPS_ORIG && !l.highbd && s.k.d.bw >= 4)
+    if (s.search_type != B200_USE_2_TAPS_ORIG && !l.highbd && s.k.d.bw >= 4 && !s.k.compound)
       subfast_init(s, f, (mbw * mbh + 16 + (mbh + 7) * mbw * 2 + 15) & ~15, mbw, mbh);
     subpel_search(s, f, st);
   } else {

@@ -295,7 +295,13 @@ class MeLaunch(C.Structure):
                 ("cost_lists", C.c_void_p), ("cost_list_stride", C.c_int), ("families", C.c_uint),
                 ("cur_rows", C.c_int), ("ref_rows", C.c_int), ("max_col_span", C.c_int),
                 ("max_row_span", C.c_int), ("start_from", C.c_void_p), ("stats", C.c_void_p),
-                ("start_group", C.c_int)]
+                ("start_group", C.c_int), ("compound", C.c_void_p), ("second_pred", C.c_void_p),
+                ("mask", C.c_void_p)]
+
+
+MECOMPOUND_DTYPE = np.dtype([("second_offset", "<u4"), ("mask_offset", "<u4"), ("mask_stride", "<u2"),
+                             ("invert_mask", "u1"), ("use_mask", "u1")])
+assert MECOMPOUND_DTYPE.itemsize == 12
 
 
 ME_FAMILY_NSTEP, ME_FAMILY_PATTERN, ME_FAMILY_REFINE = 1, 2, 4

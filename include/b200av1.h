@@ -598,7 +598,24 @@ typedef struct {
                                     the block starts at get_fullmv_from_mv() of it (mv.h:79) -- the
                                     4 sub-blocks of tf_motion_search start at their parent block's
                                     refined mv (temporal_filter.c:198), start_group = 4 */
+  /* ---- compound search (av1_set_ms_compound_refs, av1/encoder/mcomp.h:86): with `compound` set, block i
+   * is searched against blend(reference, second_pred) -- the average (vfp->sdaf / svaf,
+   * aom_comp_avg_upsampled_pred) or, with a mask, AOM_BLEND_A64 (vfp->msdf / msvf,
+   * aom_comp_mask_upsampled_pred) -- as get_mvpred_compound_sad (mcomp.c:729), setup_center_error (:2781),
+   * estimated_pref_error (:2371) and upsampled_pref_error (:2402) do.  Served by B200_ME_REFINE_8P
+   * (b200_me_fullpel_launch) and the three sub-pel trees (b200_me_subpel_launch): the two searches of one
+   * iteration of av1_joint_motion_search (motion_search_facade.c:594-652). ---- */
+  const struct B200MeCompound *compound; /* device, n_blocks entries, or NULL: single reference */
+  const void *second_pred;               /* device: bw-pitch prediction blocks from the other reference */
+  const uint8_t *mask;                   /* device: 6-bit blend weights (0..64), or NULL */
 } B200MeLaunch;
+typedef struct B200MeCompound {
+  uint32_t second_offset; /* pixels from second_pred to the block's bw x bh prediction */
+  uint32_t mask_offset;   /* bytes from mask to the block's first weight */
+  uint16_t mask_stride;
+  uint8_t invert_mask;    /* inv_mask: the weights apply to second_pred instead of the reference */
+  uint8_t use_mask;       /* 0: average, 1: masked blend */
+} B200MeCompound; /* 12 bytes */
 #define B200_ME_FAMILY_NSTEP 1u   /* NSTEP, NSTEP_8PT, DIAMOND, CLAMPED_DIAMOND */
 #define B200_ME_FAMILY_PATTERN 2u /* HEX .. VFAST_DIAMOND (pattern_search) */
 #define B200_ME_FAMILY_REFINE 4u  /* B200_ME_REFINE_8P */

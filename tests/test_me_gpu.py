@@ -28,7 +28,7 @@ def upload_tables(ctx, tables):
     return (dj, d0, d1), (dj.ptr.value, d0.ptr.value + 4 * H.MV_TABLE_HALF, d1.ptr.value + 4 * H.MV_TABLE_HALF)
 
 
-def me_launch(ctx, cur, refb, params, tables_dev, subpel, window_bytes, tma=True):
+def me_launch(ctx, cur, refb, params, tables_dev, subpel, window_bytes, tma=True, compound=None):
     import b200av1
     n = len(params)
     blocks = np.zeros(n, b200av1.MEBLOCK_DTYPE)
@@ -80,6 +80,23 @@ def me_launch(ctx, cur, refb, params, tables_dev, subpel, window_bytes, tma=True
         cls = np.array([list(p.sp_cost_list) for p in params], np.int32)
         d_cls = b200av1.to_device(ctx, cls)
         l.cost_lists, l.cost_list_stride = d_cls.ptr, 5
+    if compound is not None:
+        # compound[i] = (second_pred block, mask array or None): pooled into one buffer each
+        cd = np.zeros(n, b200av1.MECOMPOUND_DTYPE)
+        sec, msk, so, mo = [], [], 0, 0
+        for i, (p, (second, mask)) in enumerate(zip(params, compound)):
+            cd[i]["second_offset"] = so
+            sec.append(second)
+            so += second.size
+            if mask is not None:
+                cd[i]["mask_offset"], cd[i]["mask_stride"] = mo, p.mask_stride
+                cd[i]["invert_mask"], cd[i]["use_mask"] = p.inv_mask, 1
+                msk.append(mask)
+                mo += mask.size
+        d_cd = b200av1.to_device(ctx, cd)
+        d_sec = b200av1.to_device(ctx, np.concatenate(sec))
+        d_msk = b200av1.to_device(ctx, np.concatenate(msk) if msk else np.zeros(4, np.uint8))
+        l.compound, l.second_pred, l.mask = d_cd.ptr, d_sec.ptr, d_msk.ptr
     fn = b200av1.lib().b200_me_subpel_launch if subpel else b200av1.lib().b200_me_fullpel_launch
     b200av1.check(fn(ctx.h, C.byref(l), None))
     return b200av1.to_host(ctx, d_res, b200av1.MERESULT_DTYPE, n)
@@ -356,3 +373,55 @@ def test_refining_search_8p_batch_vs_oracle(ctx, bd):
                 g = got[i]
                 assert (int(g["best_row"]), int(g["best_col"]), int(g["ret"])) == \
                     (e.best_row, e.best_col, e.ret), (trial, i, p.bw, p.bh, p.use_skip_sad, window)
+
+
+@pytest.mark.parametrize("bd", [8, 10, 12])
+def test_compound_refine_and_subpel_vs_oracle(ctx, bd):
+    """compound search (second_pred / mask, av1_set_ms_compound_refs): av1_refining_search_8p_c and the
+    three sub-pel trees -- one iteration of av1_joint_motion_search (motion_search_facade.c:594-652) --
+    against the oracle, average and masked blends, all block sizes"""
+    import b200av1
+    O = H.oracle()
+    rng = np.random.default_rng(1900 + bd)
+    tables = H.make_mv_cost_tables(7)
+    keep, tdev = upload_tables(ctx, tables)
+    cur, refb = M.make_frames(rng, 320, 256, bd, flat=False)
+    sizes = [(64, 64), (32, 32), (16, 16), (8, 8), (16, 8), (32, 64), (128, 128), (4, 4), (8, 32), (4, 16)]
+    alive, params, comp = [], [], []
+    for (bw, bh) in sizes:
+        for rep in range(6):
+            p = M.random_fullpel_params(rng, cur, refb, bw, bh, bd, tables)
+            p.search_method = b200av1.ME_REFINE_8P
+            k = []
+            M.add_compound(rng, p, bd, k, masked=rep % 2 == 1)
+            alive.append(k)
+            params.append(p)
+            comp.append((k[0], k[1] if len(k) > 1 else None))
+    got = me_launch(ctx, cur, refb, params, tdev, False, 0, tma=False, compound=comp)
+    for i, p in enumerate(params):
+        e = H.MeResult()
+        O.av1o_refining_search_8p(C.byref(p), C.byref(e))
+        g = got[i]
+        assert (int(g["best_row"]), int(g["best_col"]), int(g["ret"])) == (e.best_row, e.best_col, e.ret), \
+            (bd, i, p.bw, p.bh)
+    for tree in (0, 1, 2):
+        params, comp = [], []
+        for (bw, bh) in sizes:
+            for rep in range(4):
+                p = M.random_subpel_params(rng, cur, refb, bw, bh, bd, tables, int(rng.integers(0, 4)))
+                p.sp_tree = tree
+                if tree:
+                    M.random_cost_list(rng, p)
+                k = []
+                M.add_compound(rng, p, bd, k, masked=rep % 2 == 1)
+                alive.append(k)
+                params.append(p)
+                comp.append((k[0], k[1] if len(k) > 1 else None))
+        got = me_launch(ctx, cur, refb, params, tdev, True, 0, compound=comp)
+        fo = O.av1o_find_best_sub_pixel_tree if tree == 0 else O.av1o_find_best_sub_pixel_tree_pruned
+        for i, p in enumerate(params):
+            e = H.MeResult()
+            fo(C.byref(p), C.byref(e))
+            g = got[i]
+            assert (int(g["best_row"]), int(g["best_col"]), int(g["ret"]), int(g["distortion"]), int(g["sse"])) == \
+                e.key(True), (bd, tree, i, p.bw, p.bh, p.subpel_search_type)
