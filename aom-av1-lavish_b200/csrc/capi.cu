@@ -5,7 +5,10 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <stdio.h>
+
 #include <algorithm>
+#include <chrono>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -43,6 +46,7 @@ extern "C" int b200_device_count(void) {
 static int ctx_init(b200_ctx *ctx) {
   B200_CUDA_TRY(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
   B200_CUDA_TRY(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+  B200_CUDA_TRY(cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking));
   for (int i = 0; i < B200_TX_SIZES_ALL; ++i)
     B200_CUDA_TRY(cudaEventCreateWithFlags(&ctx->group_done[i], cudaEventDisableTiming));
   B200_CUDA_TRY(cudaEventCreateWithFlags(&ctx->copy_done, cudaEventDisableTiming));
@@ -95,6 +99,7 @@ extern "C" void b200_ctx_destroy(b200_ctx *ctx) {
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
+  if (ctx->aux_stream) cudaStreamSynchronize(ctx->aux_stream);
   if (ctx->d_iscan) cudaFree(ctx->d_iscan);
   if (ctx->d_scan) cudaFree(ctx->d_scan);
   if (ctx->d_pmask) cudaFree(ctx->d_pmask);
@@ -106,6 +111,7 @@ extern "C" void b200_ctx_destroy(b200_ctx *ctx) {
     if (ctx->group_done[i]) cudaEventDestroy(ctx->group_done[i]);
   if (ctx->copy_done) cudaEventDestroy(ctx->copy_done);
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+  if (ctx->aux_stream) cudaStreamDestroy(ctx->aux_stream);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   cudaGetLastError();
   free(ctx);
@@ -202,6 +208,24 @@ extern "C" int b200_txq_launch(b200_ctx *ctx, const B200TxqLaunch *launch, void 
 }
 
 static size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
+// B200_HOST_TIMING=1: per-phase wall clock of the host-buffer tier on stderr (measurement aid)
+struct HostPhases {
+  bool on;
+  std::chrono::steady_clock::time_point t0;
+  char line[512];
+  int len;
+  HostPhases() : on(getenv("B200_HOST_TIMING") != nullptr), t0(std::chrono::steady_clock::now()), len(0) { line[0] = 0; }
+  void mark(const char *name) {
+    if (!on) return;
+    const auto t1 = std::chrono::steady_clock::now();
+    len += snprintf(line + len, sizeof(line) - len, " %s %.3f", name,
+                    std::chrono::duration<double, std::milli>(t1 - t0).count());
+    t0 = t1;
+  }
+  ~HostPhases() {
+    if (on) fprintf(stderr, "[b200 host ms]%s\n", line);
+  }
+};
 
 // Host-buffer wrapper of the fused kernel -- the reference-facing call of the frame tier
 // (what `e2e` in bench.py times).  Pipeline per call:
@@ -256,6 +280,7 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
     return B200_EINVAL;
   }
   const size_t n = (size_t)n_blocks;
+  HostPhases ph;
 
   // ---- one pass over the queue: validate, bucket by tx_size (one launch per size; the caller's order
   // inside a size is kept -- it is the caller that knows how to keep blocks of one tx type and of one
@@ -345,6 +370,7 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
     }
   }
   for (int k = 0; k < kKeys; ++k) bucket[k + 1] += bucket[k];
+  ph.mark("validate");
 
   // pinned staging: [sorted blocks][sorted preds][eob][dist][level offsets]
   size_t hoff = 0;
@@ -418,6 +444,7 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
     for (size_t i = 0; i + 1 < by_lo.size(); ++i) dense = dense && by_lo[i]->hi <= by_lo[i + 1]->lo;
   }
 
+  ph.mark("sort+groups");
   // ---- device carve-out
   const bool wide = q_kind == B200_Q_FP_HBD || q_kind == B200_Q_B_HBD;
   const size_t lv_bytes = wide ? 4 : 2;
@@ -499,6 +526,7 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
       }
     }
   }
+  ph.mark("enqueue");
   size_t d2h = 0;
   if (cmp) {
     // pack the levels on the device; the host learns the total before it sizes the read-back
@@ -523,6 +551,7 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
     if (want_coeff)
       B200_CUDA_TRY(cudaMemcpyAsync(coeff, base + o_coeff, out_elems * 4, cudaMemcpyDeviceToHost, cs));
     B200_CUDA_TRY(cudaStreamSynchronize(s));
+    ph.mark("kernels+offsets");
     const size_t total = h_loff[n];
     if (total > cmp->levels_cap) {
       cudaStreamSynchronize(cs);
@@ -563,6 +592,7 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
   }
   B200_CUDA_TRY(cudaStreamSynchronize(cs));
   B200_CUDA_TRY(cudaStreamSynchronize(s));
+  ph.mark("readback");
   const uint16_t *eob_s = (const uint16_t *)(hbase + ho_eob);
   const int64_t *dist_s = (const int64_t *)(hbase + ho_dist);
   if (in_order) {
@@ -582,6 +612,7 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
     }
     if (cmp) cmp->level_offset[n] = loff_s[n];
   }
+  ph.mark("scatter");
   if (cmp && cmp->d2h_bytes) *cmp->d2h_bytes = d2h;
   return B200_OK;
 }

@@ -62,6 +62,7 @@ struct b200_ctx {
   cudaStream_t copy_stream;            // device->host leg of the host-buffer tier
   cudaEvent_t group_done[B200_TX_SIZES_ALL];  // one per tx-size group of a batch
   cudaEvent_t copy_done;
+  cudaStream_t aux_stream;             // second compute stream of b200_me_batch_host (alternating chunks)
   void *d_me_sites;   // search-site tables of the four served methods, see me_host.cuh
 };
 

@@ -484,8 +484,9 @@ __device__ __forceinline__ void var8_wo(int wo, int s_off, int r_off, int it0, i
 // Per-lane partial sums of (src - ref) and (src - ref)^2 over the whole block, the rows
 // dealt out to all `n_warps` warps of the CTA (iteration `it` goes to warp it % n_warps).
 __device__ __noinline__ void var8_staged(int cand_off, int src_pitch_b, int win_pitch_b, int bw, int bh,
-                                         int n_warps, int *sum_out, unsigned *sse_out) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+                                         int n_warps, int *sum_out, unsigned *sse_out, int warp_in = -1) {
+  // warp_in >= 0: the rows are dealt out to a group of n_warps warps, this one being its warp_in-th
+  const int lane = threadIdx.x & 31, warp = warp_in >= 0 ? warp_in : (int)(threadIdx.x >> 5);
   const unsigned sh = (unsigned)(cand_off & 3) * 8;
   const int wo = (cand_off >> 2) & 3, base = cand_off & ~15;
   unsigned ss = 0, sr = 0, sse = 0;
@@ -641,6 +642,9 @@ __device__ __forceinline__ void load_words(const unsigned *p, unsigned (&o)[N]) 
   }
 }
 
+#ifndef B200_ME_SEG_ACC
+#define B200_ME_SEG_ACC 8
+#endif
 template <int SEGW, int WO>
 __device__ __forceinline__ unsigned seg_sad_regs(const unsigned (&sv)[SEGW], int addr, unsigned sh) {
   constexpr int NV = SEGW / 4 + 1;
@@ -650,13 +654,20 @@ __device__ __forceinline__ unsigned seg_sad_regs(const unsigned (&sv)[SEGW], int
     const uint4 t = *reinterpret_cast<const uint4 *>(me_smem + addr + 16 * v);
     r[4 * v] = t.x, r[4 * v + 1] = t.y, r[4 * v + 2] = t.z, r[4 * v + 3] = t.w;
   }
-  unsigned a0 = 0, a1 = 0;
+  // one accumulator chain per word up to kAcc: a candidate is a single dependent pass over the lane's
+  // segment, so the chain depth (SEGW / kAcc VABSDIFF4.ACC) is latency the warp cannot hide
+  constexpr int kAcc = SEGW < B200_ME_SEG_ACC ? SEGW : B200_ME_SEG_ACC;
+  unsigned a[kAcc];
 #pragma unroll
-  for (int i = 0; i < SEGW; i += 2) {
-    a0 = sad4_acc(sv[i], __funnelshift_r(r[WO + i], r[WO + i + 1], sh), a0);
-    a1 = sad4_acc(sv[i + 1], __funnelshift_r(r[WO + i + 1], r[WO + i + 2], sh), a1);
-  }
-  return a0 + a1;
+  for (int i = 0; i < kAcc; ++i) a[i] = 0;
+#pragma unroll
+  for (int i = 0; i < SEGW; ++i)
+    a[i % kAcc] = sad4_acc(sv[i], __funnelshift_r(r[WO + i], r[WO + i + 1], sh), a[i % kAcc]);
+#pragma unroll
+  for (int w = kAcc / 2; w > 0; w >>= 1)
+#pragma unroll
+    for (int i = 0; i < w; ++i) a[i] += a[i + w];
+  return a[0];
 }
 
 __device__ __forceinline__ bool multi_ok(const Ctx &k) { return k.fast && k.px == 1 && k.d.bw >= 16; }

@@ -131,8 +131,15 @@ __device__ void diamond_runs(const Ctx &k, bool skip, Mv start, unsigned start_s
   if (warp == 0) publish(0);
   __syncthreads();
   int ring = 0;
+#ifdef B200_ME_TIMING3
+  long long t3_eval = 0, t3_ctrl = 0, t3_a, t3_b;
+  int t3_rounds = 0;
+#endif
   for (int round = 0;; ++round) {
     if (round >= nruns && !__any_sync(0xffffffffu, lane < nruns && g_runn[lane] > 0)) break;
+#ifdef B200_ME_TIMING3
+    t3_a = clock64();
+#endif
     unsigned *cand = g_cand + ring * (kMaxRuns * 16);
     for (int r = 0; r < nruns; ++r) {
       const int n = g_runn[r];
@@ -141,6 +148,10 @@ __device__ void diamond_runs(const Ctx &k, bool skip, Mv start, unsigned start_s
 #endif
     }
     __syncthreads();
+#ifdef B200_ME_TIMING3
+    t3_b = clock64();
+    t3_eval += t3_b - t3_a;
+#endif
 #pragma unroll
     for (int s = 0; s < kSlots; ++s) {
       const int r = warp + s * kWarps;
@@ -192,7 +203,178 @@ __device__ void diamond_runs(const Ctx &k, bool skip, Mv start, unsigned start_s
     }
     ring = (ring + 1) % 3;
     __syncthreads();
+#ifdef B200_ME_TIMING3
+    t3_ctrl += clock64() - t3_b;
+    ++t3_rounds;
+#endif
   }
+#ifdef B200_ME_TIMING3
+  if (threadIdx.x == 0) g_bcast[13] = (int)(t3_eval >> 4), g_bcast[15] = (int)(t3_ctrl >> 4), g_bcast[14] = t3_rounds;
+#endif
+}
+
+// ---- the same runs, one WARP GROUP per run (staged 8-bit windows, SEGW > 0) -------------
+// diamond_runs keeps the whole CTA in lock step: two CTA-wide barriers per round, one warp deciding
+// while seven wait -- measured (tools/me_phase_timing.py) the n-step phase took 58 % of a 64x64
+// search for a quarter of its SADs, 2.8x its shared-memory / ALU floor.  Here the np warps that
+// together cover one candidate block (LaneShare: np = passes) form a group that owns a run from
+// its first step to its last: per step the lanes derive the step's candidates in registers
+// (lane i = candidate i, fetched by shuffle: nothing is published), every warp adds its rows of
+// each candidate, the group meets at ITS named barrier (a __syncwarp when np == 1), every warp
+// sums the np partial totals and replays the decision redundantly -- no CTA-wide barrier, no
+// atomics, no idle warps; the kWarps / np groups run different runs side by side (run r on group
+// r mod G, then r + G, ...).  Run r > 0 is wanted only if run 0 left its centre within its first r
+// steps (else num00 >= r and the reference never executes it): group 0 publishes run 0's
+// progress in g_bcast[25] = steps done << 16 | step at which it left the centre (0xffff: not
+// yet), the other groups poll it before they start a run.  Results: g_runres[r], as diamond_runs.
+__device__ __forceinline__ void group_sync(int id, int nthreads) {
+  if (nthreads <= 32) __syncwarp();
+  else asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+template <int SEGW>
+__device__ void diamond_runs_grouped(const Ctx &k, bool skip, Mv start, unsigned start_sad, int step_param,
+                                     int nruns, const LaneShare<SEGW> &ls) {
+  static_assert(SEGW > 0, "register-resident lane share only");
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const Sites &cfg = g_sites;
+  start = clamp_mv(k, start);
+  const int G = ls.cstep, np = kWarps / G;  // groups, warps per group (= passes)
+  const int grp = ls.c0, pass = warp & (np - 1);
+  const bool leader = pass == 0 && lane == 0;
+  unsigned *part = g_cand;  // [2][kWarps][16] partial totals of a step
+  volatile int *progress = &g_bcast[25];
+  __syncthreads();  // g_cand may still be read by the previous stage
+  if (threadIdx.x == 0) *progress = 0xffff;
+  __syncthreads();
+  // runs -> groups: longest run first onto the least loaded group (run r has n_steps - step_param - r steps),
+  // lane g < G keeps group g's load and run set; every warp derives the same table
+  unsigned my_runs;
+  {
+    unsigned load = lane < G ? 0u : 0xfffffu, mask = 0;
+    for (int r = 0; r < nruns; ++r) {
+      const int g = (int)(__reduce_min_sync(0xffffffffu, (load << 5) | (unsigned)lane) & 31u);
+      if (lane == g) load += (unsigned)max(cfg.n_steps - (step_param + r), 1), mask |= 1u << r;
+    }
+    my_runs = __shfl_sync(0xffffffffu, mask, grp);
+  }
+  int buf = 0;
+  while (my_runs) {
+    const int r = __ffs(my_runs) - 1;
+    my_runs &= my_runs - 1;
+    if (r > 0) {
+      // group 0 finished run 0 before it gets here; the others wait until run 0 has done r steps
+      int v = *progress;
+      while ((v & 0xffff) > r && (v >> 16) < r) {
+        __nanosleep(64);
+        v = *progress;
+      }
+      if ((v & 0xffff) > r) {  // still on its centre after r steps: never executed
+        if (leader) g_runres[r][5] = 0, g_runres[r][6] = 0;
+        continue;
+      }
+    }
+    Mv cur = start, sec = start;
+    unsigned bestsad = start_sad;
+    int off_center = 0, center_steps = 0, steps_done = 0, left_at = 0xffff;
+    int step = cfg.n_steps - (step_param + r) - 1;
+    while (step >= 0) {
+      const int st = step, n = cfg.per_step[st];
+      // lane i < n: candidate i of the step around the run's centre
+      int a = -1, prow = 0, pcol = 0;
+      if (lane < n) {
+        prow = cur.row + cfg.site[st][lane + 1][0];
+        pcol = cur.col + cfg.site[st][lane + 1][1];
+        if (in_range(k, prow, pcol)) a = k.win0_off + prow * k.ref_pitch + pcol;
+      }
+      unsigned mine = 0;
+      for (int j = 0; j < n; ++j) {
+        const int aj = __shfl_sync(0xffffffffu, a, j);
+        if (aj < 0) continue;  // warp-uniform
+        const int addr = (aj & ~15) + ls.l_off;
+        const unsigned sh = (unsigned)(aj & 3) * 8;
+        unsigned acc;
+        switch ((aj >> 2) & 3) {
+          case 0: acc = seg_sad_regs<SEGW, 0>(ls.sv, addr, sh); break;
+          case 1: acc = seg_sad_regs<SEGW, 1>(ls.sv, addr, sh); break;
+          case 2: acc = seg_sad_regs<SEGW, 2>(ls.sv, addr, sh); break;
+          default: acc = seg_sad_regs<SEGW, 3>(ls.sv, addr, sh); break;
+        }
+        acc = warp_sum_u(ls.act ? acc : 0u);
+        if (lane == j) mine = acc;
+      }
+      unsigned total = mine;
+      if (np > 1) {
+        if (lane < 16) part[(buf * kWarps + warp) * 16 + lane] = mine;
+        group_sync(1 + grp, np * 32);
+        total = 0;
+        if (lane < 16)
+          for (int p = 0; p < np; ++p) total += part[(buf * kWarps + grp * np + p) * 16 + lane];
+        buf ^= 1;  // the next step writes the other half: a slower warp of the group may still be reading
+      }
+      if (skip) total *= 2;
+      if (leader) atomicAdd(&g_bcast[24], n);
+#ifdef B200_ME_TIMING
+      if (leader) atomicAdd(&g_bcast[11], 1 + (n << 8));  // steps | candidates << 8
+#endif
+      const unsigned t = (lane < n && a >= 0) ? total + (unsigned)sad_cost(k, prow, pcol) : 0xffffffffu;
+      const unsigned tmin = __reduce_min_sync(0xffffffffu, t);
+      const bool moved = tmin < bestsad;
+      if (moved) {
+        const int site = 1 + (int)__reduce_min_sync(0xffffffffu, t == tmin ? (unsigned)lane : 99u);
+        bestsad = tmin;
+        sec = cur;
+        cur.row += cfg.site[st][site][0];
+        cur.col += cfg.site[st][site][1];
+        off_center = 1;
+      }
+      if (!off_center) center_steps++;
+      int ns = st;
+      if (!moved && ns > 2) {
+        int next = cfg.radius[ns - 1];
+        while (next == cfg.radius[ns] && ns > 2) {
+          center_steps++;
+          --ns;
+          next = cfg.radius[ns - 1];
+        }
+      }
+      step = ns - 1;
+      ++steps_done;
+      if (r == 0) {
+        if (off_center && left_at == 0xffff) left_at = steps_done;
+        if (leader) {
+          __threadfence_block();
+          *progress = ((step >= 0 ? steps_done : 0x7fff) << 16) | left_at;
+        }
+      }
+    }
+    if (r == 0 && steps_done == 0 && leader) *progress = (0x7fff << 16) | 0xffff;  // run 0 had no step at all
+    // get_mvpred_var_cost (mcomp.c:665) of the run's result, which the replay of full_pixel_diamond compares
+    // between runs: measured here by the group (its rows dealt out to the np warps) instead of by the whole
+    // CTA once the runs are over
+    int lsum;
+    unsigned lsse;
+    var8_staged(k.win0_off + cur.row * k.ref_pitch + cur.col, k.src_pitch_w * 4, k.ref_pitch, k.d.bw, k.d.bh, np,
+                &lsum, &lsse, pass);
+    long long vsum = warp_sum_ll((long long)lsum);
+    unsigned long long vsse = (unsigned long long)warp_sum_ll((long long)lsse);
+    if (np > 1) {
+      if (lane == 0) g_red[warp] = vsum, g_red[kWarps + warp] = (long long)vsse;
+      group_sync(1 + grp, np * 32);
+      vsum = 0, vsse = 0;
+      for (int p = 0; p < np; ++p)
+        vsum += g_red[grp * np + p], vsse += (unsigned long long)g_red[kWarps + grp * np + p];
+    }
+    if (leader) {
+      unsigned sse32;
+      const unsigned v = finish_var(vsum, vsse, k.d.bw * k.d.bh, false, 8, &sse32);
+      g_runres[r][0] = cur.row, g_runres[r][1] = cur.col;
+      g_runres[r][2] = sec.row, g_runres[r][3] = sec.col;
+      g_runres[r][4] = (int)bestsad, g_runres[r][5] = center_steps, g_runres[r][6] = off_center;
+      g_runres[r][7] = (int)v + err_cost(k, cur.row * 8, cur.col * 8);
+    }
+  }
+  __syncthreads();
 }
 
 // calc_int_sad_list (mcomp.c:791) with costlist_has_sad == 0
@@ -240,7 +422,8 @@ __device__ int full_pixel_diamond_t(const Ctx &k, bool skip, Mv start, int step_
 #ifdef B200_ME_TIMING2
   const long long tr0 = clock64();
 #endif
-  diamond_runs<SEGW>(k, skip, start, start_sad, step_param, nruns, ls);
+  if constexpr (SEGW > 0) diamond_runs_grouped<SEGW>(k, skip, start, start_sad, step_param, nruns, ls);
+  else diamond_runs<SEGW>(k, skip, start, start_sad, step_param, nruns, ls);
 #ifdef B200_ME_TIMING2
   const long long tr1 = clock64();
   if (threadIdx.x == 0) g_bcast[14] = (int)((tr1 - tr0) >> 4);
@@ -251,12 +434,26 @@ __device__ int full_pixel_diamond_t(const Ctx &k, bool skip, Mv start, int step_
   int n = g_runres[0][5];
   best->row = g_runres[0][0], best->col = g_runres[0][1];
   take_second(0);
-  int bestsme = var_cost(k, *best);
+  // the grouped runs left their variance in g_runres[r][7]; the lock-step path measures it here
+  int bestsme = SEGW > 0 ? g_runres[0][7] : var_cost(k, *best);
+  // runs that end on an mv already measured (the usual case: they converge) reuse its variance
+  Mv last = *best;
+  int last_sme = bestsme;
   while (n < further) {
     ++n;
     const Mv tmp = { g_runres[n][0], g_runres[n][1] };
     take_second(n);
-    const int sme = var_cost(k, tmp);
+    int sme;
+    if constexpr (SEGW > 0) {
+      sme = g_runres[n][7];
+    } else if (tmp.row == best->row && tmp.col == best->col) {
+      sme = bestsme;
+    } else if (tmp.row == last.row && tmp.col == last.col) {
+      sme = last_sme;
+    } else {
+      sme = var_cost(k, tmp);
+      last = tmp, last_sme = sme;
+    }
     if (sme < bestsme) {
       bestsme = sme;
       *best = tmp;
@@ -844,7 +1041,7 @@ __device__ int full_pixel_exhaustive(const Ctx &k, bool skip, Mv start, int *cl,
   long long tm = clock64();
 #endif
   int bestsme = mesh_search(k, skip, *best, range, interval, best, second, has_second);
-#if defined(B200_ME_TIMING) && !defined(B200_ME_TIMING2)
+#if defined(B200_ME_TIMING) && !defined(B200_ME_TIMING2) && !defined(B200_ME_TIMING3)
   g_bcast[13] = (int)((clock64() - tm) >> 4);
 #endif
   if (interval > 1 && range > 7) {
@@ -854,7 +1051,7 @@ __device__ int full_pixel_exhaustive(const Ctx &k, bool skip, Mv start, int *cl,
 #endif
       bestsme = mesh_search(k, skip, *best, k.l->mesh_range[i], k.l->mesh_interval[i], best, second,
                             has_second);
-#if defined(B200_ME_TIMING) && !defined(B200_ME_TIMING2)
+#if defined(B200_ME_TIMING) && !defined(B200_ME_TIMING2) && !defined(B200_ME_TIMING3)
       if (i < 3) g_bcast[13 + i] = (int)((clock64() - tm) >> 4);
 #endif
       if (k.l->mesh_interval[i] == 1) break;

@@ -233,10 +233,57 @@ extern "C" int b200_measure_sad_peak(b200_ctx *ctx, double *gabsdiff_per_s) {
   return B200_OK;
 }
 
+// b200_me_batch_host pipelines the call: the descriptors are cut into up to kMeHostChunks chunks of at least
+// two waves of CTAs; the copy stream brings each chunk's part of the planes up (the byte range its searches
+// can touch: limits box + block + the sub-pel filter margin; ranges already on the device are not copied
+// again) while the two compute streams, alternating, run the previous chunks' full-pel + sub-pel kernels and
+// read their results back -- so the step costs max(copy, compute) instead of their sum, and the tail of one
+// chunk's kernels overlaps the head of the next chunk's.
+namespace {
+constexpr int kMeHostChunks = 8;
+constexpr long long kMeHostMargin = 9;  // pixels around the limits box: 8-tap filter (4) + the last sub-pel step, rounded up
+struct ByteSpan {
+  long long lo, hi;
+};
+// copies what [want.lo, want.hi) adds to the contiguous span `have` already on the device (256-byte granules)
+int copy_new_part(char *dst, const char *src, long long total, ByteSpan want, ByteSpan &have, cudaStream_t s,
+                  size_t *copied) {
+  want.lo = want.lo < 0 ? 0 : (want.lo & ~255ll);
+  want.hi = want.hi > total ? total : ((want.hi + 255) & ~255ll);
+  if (want.hi > total) want.hi = total;
+  if (want.lo >= want.hi) return B200_OK;
+  auto put = [&](long long lo, long long hi) -> int {
+    if (lo >= hi) return B200_OK;
+    B200_CUDA_TRY(cudaMemcpyAsync(dst + lo, src + lo, (size_t)(hi - lo), cudaMemcpyHostToDevice, s));
+    *copied += (size_t)(hi - lo);
+    return B200_OK;
+  };
+  int rc = B200_OK;
+  if (have.lo >= have.hi) {
+    rc = put(want.lo, want.hi);
+    have = want;
+    return rc;
+  }
+  if (want.lo < have.lo) {
+    rc = put(want.lo, have.lo);
+    have.lo = want.lo;
+  }
+  if (rc == B200_OK && want.hi > have.hi) {
+    rc = put(have.hi, want.hi);
+    have.hi = want.hi;
+  }
+  return rc;
+}
+}  // namespace
+
 extern "C" int b200_me_batch_host(b200_ctx *ctx, const B200MeLaunch *hl, size_t cur_bytes, size_t ref_bytes,
                                   const B200MeBlock *subpel_blocks, B200MeResult *fullpel_out,
                                   B200MeResult *subpel_out) {
   if (!ctx || !hl || hl->n_blocks < 0 || !hl->blocks || !hl->cur || !hl->ref) return B200_EINVAL;
+  if (hl->compound || hl->second_pred || hl->mask) {
+    b200::set_error("b200_me_batch_host: compound searches go through b200_me_fullpel_launch / b200_me_subpel_launch");
+    return B200_EINVAL;
+  }
   if (hl->n_blocks == 0) return B200_OK;
   B200_CUDA_TRY(cudaSetDevice(ctx->device));
   const size_t n = (size_t)hl->n_blocks;
@@ -255,47 +302,91 @@ extern "C" int b200_me_batch_host(b200_ctx *ctx, const B200MeLaunch *hl, size_t 
   int rc = b200::scratch_reserve(ctx, off);
   if (rc != B200_OK) return rc;
   char *base = (char *)ctx->d_scratch;
-  cudaStream_t s = ctx->stream;
-  B200_CUDA_TRY(cudaMemcpyAsync(base + o_cur, hl->cur, cur_bytes, cudaMemcpyHostToDevice, s));
-  B200_CUDA_TRY(cudaMemcpyAsync(base + o_ref, hl->ref, ref_bytes, cudaMemcpyHostToDevice, s));
-  B200_CUDA_TRY(cudaMemcpyAsync(base + o_blk, hl->blocks, n * sizeof(B200MeBlock), cudaMemcpyHostToDevice, s));
+  cudaStream_t cs = ctx->copy_stream;
+  cudaStream_t st[2] = { ctx->stream, ctx->aux_stream };
+  B200_CUDA_TRY(cudaMemcpyAsync(base + o_blk, hl->blocks, n * sizeof(B200MeBlock), cudaMemcpyHostToDevice, cs));
   if (subpel_blocks)
-    B200_CUDA_TRY(cudaMemcpyAsync(base + o_sub, subpel_blocks, n * sizeof(B200MeBlock), cudaMemcpyHostToDevice, s));
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_sub, subpel_blocks, n * sizeof(B200MeBlock), cudaMemcpyHostToDevice, cs));
   B200MeLaunch dl = *hl;
-  dl.blocks = (const B200MeBlock *)(base + o_blk);
   dl.cur = base + o_cur;
   dl.ref = base + o_ref;
-  dl.results = (B200MeResult *)(base + o_rf);
   dl.cost_lists = nullptr;
   dl.start_from = nullptr;
   dl.stats = nullptr;
   dl.mvjcost = nullptr;
   dl.mvcost[0] = dl.mvcost[1] = nullptr;
   if (costs) {
-    B200_CUDA_TRY(cudaMemcpyAsync(base + o_j, hl->mvjcost, 4 * sizeof(int), cudaMemcpyHostToDevice, s));
-    B200_CUDA_TRY(cudaMemcpyAsync(base + o_c0, hl->mvcost[0] - 16383, tab, cudaMemcpyHostToDevice, s));
-    B200_CUDA_TRY(cudaMemcpyAsync(base + o_c1, hl->mvcost[1] - 16383, tab, cudaMemcpyHostToDevice, s));
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_j, hl->mvjcost, 4 * sizeof(int), cudaMemcpyHostToDevice, cs));
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_c0, hl->mvcost[0] - 16383, tab, cudaMemcpyHostToDevice, cs));
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_c1, hl->mvcost[1] - 16383, tab, cudaMemcpyHostToDevice, cs));
     dl.mvjcost = (const int *)(base + o_j);
     dl.mvcost[0] = (const int *)(base + o_c0) + 16383;
     dl.mvcost[1] = (const int *)(base + o_c1) + 16383;
   }
-  rc = b200_me_fullpel_launch(ctx, &dl, s);
-  if (rc != B200_OK) return rc;
-  if (fullpel_out)
-    B200_CUDA_TRY(cudaMemcpyAsync(fullpel_out, base + o_rf, n * sizeof(B200MeResult), cudaMemcpyDeviceToHost, s));
-  if (subpel_blocks) {
-    B200MeLaunch sl = dl;
-    sl.blocks = (const B200MeBlock *)(base + o_sub);
-    sl.start_from = (const B200MeResult *)(base + o_rf);
-    sl.results = (B200MeResult *)(base + o_rs);
-    // the pruned trees read the full-pel cost list in place
-    sl.cost_lists = &((const B200MeResult *)(base + o_rf))->cost_list[0];
-    sl.cost_list_stride = sizeof(B200MeResult) / sizeof(int32_t);
-    rc = b200_me_subpel_launch(ctx, &sl, s);
+  // chunks of >= two waves of resident CTAs; a sub-pel queue that does not mirror the full-pel one
+  // (other block positions) is served unpipelined: every plane byte is up before the first kernel
+  const long long px = hl->highbd ? 2 : 1;
+  bool mirror = true;
+  if (subpel_blocks)
+    for (size_t i = 0; i < n && mirror; ++i)
+      mirror = subpel_blocks[i].src_offset == hl->blocks[i].src_offset &&
+               subpel_blocks[i].ref_offset == hl->blocks[i].ref_offset;
+  const size_t waves2 = (size_t)ctx->sm_count * 6;
+  int n_chunks = !mirror ? 1 : (int)std::min<size_t>(kMeHostChunks, std::max<size_t>(1, n / waves2));
+  const size_t chunk = (n + n_chunks - 1) / n_chunks;
+  ByteSpan have_cur = { 0, 0 }, have_ref = { 0, 0 };
+  size_t copied = 0;
+  for (int c = 0; c < n_chunks; ++c) {
+    const size_t b0 = chunk * c, b1 = std::min(n, b0 + chunk);
+    if (b0 >= b1) break;
+    ByteSpan wc = { 0, (long long)cur_bytes }, wr = { 0, (long long)ref_bytes };
+    if (n_chunks > 1) {
+      wc.lo = wr.lo = LLONG_MAX, wc.hi = wr.hi = 0;
+      const long long mbh = hl->max_bh > 0 ? hl->max_bh : 128, mbw = hl->max_bw > 0 ? hl->max_bw : 128;
+      for (size_t i = b0; i < b1; ++i) {
+        const B200MeBlock &d = hl->blocks[i];
+        // the source box the kernels stage is max_bh x max_bw from the block's origin
+        const long long s0 = (long long)d.src_offset, s1 = s0 + (mbh - 1) * hl->cur_stride + mbw + 16;
+        const long long r0 = (long long)d.ref_offset + (d.row_min - kMeHostMargin) * hl->ref_stride + d.col_min - kMeHostMargin;
+        const long long r1 = (long long)d.ref_offset + (d.row_max + d.bh + kMeHostMargin) * hl->ref_stride + d.col_max +
+                             d.bw + kMeHostMargin;
+        wc.lo = std::min(wc.lo, s0), wc.hi = std::max(wc.hi, s1);
+        wr.lo = std::min(wr.lo, r0), wr.hi = std::max(wr.hi, r1);
+      }
+      wc.lo *= px, wc.hi *= px, wr.lo *= px, wr.hi *= px;
+    }
+    rc = copy_new_part(base + o_cur, (const char *)hl->cur, (long long)cur_bytes, wc, have_cur, cs, &copied);
+    if (rc == B200_OK)
+      rc = copy_new_part(base + o_ref, (const char *)hl->ref, (long long)ref_bytes, wr, have_ref, cs, &copied);
     if (rc != B200_OK) return rc;
-    if (subpel_out)
-      B200_CUDA_TRY(cudaMemcpyAsync(subpel_out, base + o_rs, n * sizeof(B200MeResult), cudaMemcpyDeviceToHost, s));
+    B200_CUDA_TRY(cudaEventRecord(ctx->group_done[c], cs));
+    cudaStream_t s = st[c & 1];
+    B200_CUDA_TRY(cudaStreamWaitEvent(s, ctx->group_done[c], 0));
+    dl.n_blocks = (int)(b1 - b0);
+    dl.blocks = (const B200MeBlock *)(base + o_blk) + b0;
+    dl.results = (B200MeResult *)(base + o_rf) + b0;
+    rc = b200_me_fullpel_launch(ctx, &dl, s);
+    if (rc != B200_OK) return rc;
+    if (fullpel_out)
+      B200_CUDA_TRY(cudaMemcpyAsync(fullpel_out + b0, base + o_rf + b0 * sizeof(B200MeResult),
+                                    (b1 - b0) * sizeof(B200MeResult), cudaMemcpyDeviceToHost, s));
+    if (subpel_blocks) {
+      B200MeLaunch sl = dl;
+      sl.blocks = (const B200MeBlock *)(base + o_sub) + b0;
+      sl.start_from = (const B200MeResult *)(base + o_rf) + b0;
+      sl.results = (B200MeResult *)(base + o_rs) + b0;
+      // the pruned trees read the full-pel cost list in place
+      sl.cost_lists = &((const B200MeResult *)(base + o_rf) + b0)->cost_list[0];
+      sl.cost_list_stride = sizeof(B200MeResult) / sizeof(int32_t);
+      rc = b200_me_subpel_launch(ctx, &sl, s);
+      if (rc != B200_OK) return rc;
+      if (subpel_out)
+        B200_CUDA_TRY(cudaMemcpyAsync(subpel_out + b0, base + o_rs + b0 * sizeof(B200MeResult),
+                                      (b1 - b0) * sizeof(B200MeResult), cudaMemcpyDeviceToHost, s));
+    }
   }
-  B200_CUDA_TRY(cudaStreamSynchronize(s));
+  B200_CUDA_TRY(cudaStreamSynchronize(cs));
+  B200_CUDA_TRY(cudaStreamSynchronize(st[0]));
+  B200_CUDA_TRY(cudaStreamSynchronize(st[1]));
   return B200_OK;
 }

@@ -425,3 +425,102 @@ def test_compound_refine_and_subpel_vs_oracle(ctx, bd):
             g = got[i]
             assert (int(g["best_row"]), int(g["best_col"]), int(g["ret"]), int(g["distortion"]), int(g["sse"])) == \
                 e.key(True), (bd, tree, i, p.bw, p.bh, p.subpel_search_type)
+
+
+@pytest.mark.parametrize("bd,shuffle", [(8, False), (8, True), (10, False)])
+def test_me_batch_host_pipelined_vs_launch_tier_and_oracle(ctx, bd, shuffle):
+    """b200_me_batch_host cuts a large queue into chunks whose plane ranges are copied while the
+    previous chunks' kernels run: the results must equal those of ONE device-resident launch pair
+    over the same descriptors (any descriptor order), and the oracle's on a sample."""
+    import b200av1
+    O = H.oracle()
+    rng = np.random.default_rng(4100 + bd + shuffle)
+    w, h, B = 1024, 576, M.BORDER
+    dt = np.uint8 if bd == 8 else np.uint16
+    hi = (1 << bd) - 1
+    base = rng.integers(0, hi + 1, (h // 8, w // 8)).astype(np.float32)
+    cur = np.clip(np.kron(base, np.ones((8, 8), np.float32)) + rng.integers(-6, 7, (h, w)), 0, hi).astype(dt)
+    rs, rh = w + 2 * B, h + 2 * B
+    refs = np.zeros((2, rh, rs), dt)
+    for r in range(2):
+        dy, dx = int(rng.integers(-5, 6)), int(rng.integers(-5, 6))
+        ref = np.roll(cur, (dy, dx), (0, 1)).astype(np.int32) + rng.integers(-2, 3, (h, w))
+        refs[r] = np.pad(np.clip(ref, 0, hi).astype(dt), B, mode="edge")
+    sites = [(r, bx, by) for r in range(2) for by in range(0, h, 16) for bx in range(0, w, 16)]
+    if shuffle:
+        sites = [sites[i] for i in rng.permutation(len(sites))]
+    n = len(sites)
+    assert n >= 4 * 148 * 6  # several chunks of two waves on a B200
+    blocks = np.zeros(n, b200av1.MEBLOCK_DTYPE)
+    blocks["src_offset"] = [by * w + bx for (_, bx, by) in sites]
+    blocks["ref_offset"] = [(r * rh + by + B) * rs + bx + B for (r, bx, by) in sites]
+    blocks["col_min"], blocks["col_max"], blocks["row_min"], blocks["row_max"] = -12, 12, -12, 12
+    blocks["bw"], blocks["bh"] = 16, 16
+    blocks["search_method"] = 0
+    blocks["step_param"] = 6
+    blocks["mv_cost_type"] = 3
+    blocks["sad_per_bit"], blocks["error_per_bit"] = 40, 90
+    sub = blocks.copy()
+    sub["col_min"], sub["col_max"], sub["row_min"], sub["row_max"] = -96, 96, -96, 96
+    sub["flags"] = b200av1.ME_ALLOW_HP
+    sub["subpel"] = 0 | (2 << 2) | (3 << 4)
+
+    def launch_struct(pb, pc, pr, pres):
+        l = b200av1.MeLaunch()
+        l.highbd, l.bd, l.n_blocks = int(bd > 8), bd, n
+        l.blocks, l.cur, l.ref, l.results = pb, pc, pr, pres
+        l.cur_stride, l.ref_stride = w, rs
+        l.window_bytes, l.max_bw, l.max_bh = 16 * 1024, 16, 16
+        l.families = b200av1.ME_FAMILY_NSTEP
+        l.cur_rows, l.ref_rows = h, 2 * rh
+        l.max_col_span, l.max_row_span = 24, 24
+        return l
+
+    lib = b200av1.lib()
+    # host tier
+    rf = np.zeros(n, b200av1.MERESULT_DTYPE)
+    rsub = np.zeros(n, b200av1.MERESULT_DTYPE)
+    hl = launch_struct(blocks.ctypes.data, cur.ctypes.data, refs.ctypes.data, None)
+    for _ in range(2):  # the second call reuses the scratch of the first
+        rf[:] = 0
+        rsub[:] = 0
+        b200av1.check(lib.b200_me_batch_host(ctx.h, C.byref(hl), C.c_size_t(cur.nbytes), C.c_size_t(refs.nbytes),
+                                             C.c_void_p(sub.ctypes.data), C.c_void_p(rf.ctypes.data),
+                                             C.c_void_p(rsub.ctypes.data)))
+    # launch tier, everything resident
+    d_cur, d_ref = b200av1.to_device(ctx, cur), b200av1.to_device(ctx, refs)
+    d_blk, d_sub = b200av1.to_device(ctx, blocks), b200av1.to_device(ctx, sub)
+    d_rf, d_rs = b200av1.DevBuf(ctx, n * 40), b200av1.DevBuf(ctx, n * 40)
+    l = launch_struct(d_blk.ptr, d_cur.ptr, d_ref.ptr, d_rf.ptr)
+    b200av1.check(lib.b200_me_fullpel_launch(ctx.h, C.byref(l), None))
+    l.blocks, l.results, l.start_from = d_sub.ptr, d_rs.ptr, d_rf.ptr
+    b200av1.check(lib.b200_me_subpel_launch(ctx.h, C.byref(l), None))
+    ef = b200av1.to_host(ctx, d_rf, b200av1.MERESULT_DTYPE, n)
+    es = b200av1.to_host(ctx, d_rs, b200av1.MERESULT_DTYPE, n)
+    assert rf.tobytes() == ef.tobytes()
+    assert rsub.tobytes() == es.tobytes()
+    assert np.any(rf["best_row"] != 0) and np.all(rsub["ret"] < 2 ** 30)
+    # oracle on a sample (first, last and random searches)
+    esz = cur.itemsize
+    for i in [0, n - 1] + [int(v) for v in rng.integers(0, n, 40)]:
+        r, bx, by = sites[i]
+        p = H.MeParams()
+        p.src = cur.ctypes.data + (by * w + bx) * esz
+        p.ref = refs.ctypes.data + ((r * rh + by + B) * rs + bx + B) * esz
+        p.src_stride, p.ref_stride = w, rs
+        p.bw, p.bh, p.highbd, p.bd = 16, 16, int(bd > 8), bd
+        p.col_min, p.col_max, p.row_min, p.row_max = -12, 12, -12, 12
+        p.search_method, p.step_param = 0, 6
+        p.mv_cost_type, p.sad_per_bit, p.error_per_bit = 3, 40, 90
+        p.want_cost_list = p.want_second_best = 1
+        p.allow_hp, p.forced_stop, p.iters_per_step, p.subpel_search_type = 1, 0, 2, 3
+        p.sp_col_min, p.sp_col_max, p.sp_row_min, p.sp_row_max = -96, 96, -96, 96
+        e = H.MeResult()
+        O.av1o_full_pixel_search(C.byref(p), C.byref(e))
+        assert (int(rf[i]["best_row"]), int(rf[i]["best_col"]), int(rf[i]["ret"])) == (e.best_row, e.best_col, e.ret), i
+        p.sp_start_row, p.sp_start_col = e.best_row * 8, e.best_col * 8
+        e2 = H.MeResult()
+        O.av1o_find_best_sub_pixel_tree(C.byref(p), C.byref(e2))
+        assert (int(rsub[i]["best_row"]), int(rsub[i]["best_col"]), int(rsub[i]["ret"]),
+                int(rsub[i]["distortion"]), int(rsub[i]["sse"])) == \
+            (e2.best_row, e2.best_col, e2.ret, e2.distortion, e2.sse), i
