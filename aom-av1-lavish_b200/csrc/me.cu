@@ -670,6 +670,35 @@ __device__ __forceinline__ unsigned seg_sad_regs(const unsigned (&sv)[SEGW], int
   return a[0];
 }
 
+// The same with the loads addressed through a 32-bit shared-window address (no per-call S2UR / ULEA of the
+// dynamic shared array) and the PREVIOUS candidate's warp reduction issued while they are in flight: the
+// grouped n-step loop is one dependent pass per candidate, so the REDUX latency would otherwise be exposed
+// once per candidate.  prev: this lane's sum of the previous candidate; prev_total: its warp total.
+template <int SEGW, int WO>
+__device__ __forceinline__ unsigned seg_sad_regs_p(const unsigned (&sv)[SEGW], unsigned saddr, unsigned sh,
+                                                   unsigned prev, unsigned &prev_total) {
+  constexpr int NV = SEGW / 4 + 1;
+  unsigned r[4 * NV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[4 * v]), "=r"(r[4 * v + 1]), "=r"(r[4 * v + 2]), "=r"(r[4 * v + 3])
+                 : "r"(saddr + 16u * v));
+  prev_total = __reduce_add_sync(0xffffffffu, prev);
+  constexpr int kAcc = SEGW < B200_ME_SEG_ACC ? SEGW : B200_ME_SEG_ACC;
+  unsigned a[kAcc];
+#pragma unroll
+  for (int i = 0; i < kAcc; ++i) a[i] = 0;
+#pragma unroll
+  for (int i = 0; i < SEGW; ++i)
+    a[i % kAcc] = sad4_acc(sv[i], __funnelshift_r(r[WO + i], r[WO + i + 1], sh), a[i % kAcc]);
+#pragma unroll
+  for (int w = kAcc / 2; w > 0; w >>= 1)
+#pragma unroll
+    for (int i = 0; i < w; ++i) a[i] += a[i + w];
+  return a[0];
+}
+
 __device__ __forceinline__ bool multi_ok(const Ctx &k) { return k.fast && k.px == 1 && k.d.bw >= 16; }
 
 // A lane's share of the block, fixed for one search and skip mode: hoisted out of the step

@@ -244,6 +244,7 @@ __device__ void diamond_runs_grouped(const Ctx &k, bool skip, Mv start, unsigned
   const bool leader = pass == 0 && lane == 0;
   unsigned *part = g_cand;  // [2][kWarps][16] partial totals of a step
   volatile int *progress = &g_bcast[25];
+  const unsigned smem_base = (unsigned)__cvta_generic_to_shared(me_smem);
   __syncthreads();  // g_cand may still be read by the previous stage
   if (threadIdx.x == 0) *progress = 0xffff;
   __syncthreads();
@@ -276,7 +277,7 @@ __device__ void diamond_runs_grouped(const Ctx &k, bool skip, Mv start, unsigned
     }
     Mv cur = start, sec = start;
     unsigned bestsad = start_sad;
-    int off_center = 0, center_steps = 0, steps_done = 0, left_at = 0xffff;
+    int off_center = 0, center_steps = 0, steps_done = 0, left_at = 0xffff, n_cand = 0;
     int step = cfg.n_steps - (step_param + r) - 1;
     while (step >= 0) {
       const int st = step, n = cfg.per_step[st];
@@ -287,21 +288,32 @@ __device__ void diamond_runs_grouped(const Ctx &k, bool skip, Mv start, unsigned
         pcol = cur.col + cfg.site[st][lane + 1][1];
         if (in_range(k, prow, pcol)) a = k.win0_off + prow * k.ref_pitch + pcol;
       }
-      unsigned mine = 0;
+      // candidate j's address comes from lane j one iteration ahead; its lane sums are reduced while
+      // candidate j + 1's window rows are being loaded
+      unsigned mine = 0, pend = 0;
+      int pend_j = -1;
+      int aj = __shfl_sync(0xffffffffu, a, 0);
       for (int j = 0; j < n; ++j) {
-        const int aj = __shfl_sync(0xffffffffu, a, j);
-        if (aj < 0) continue;  // warp-uniform
-        const int addr = (aj & ~15) + ls.l_off;
-        const unsigned sh = (unsigned)(aj & 3) * 8;
-        unsigned acc;
-        switch ((aj >> 2) & 3) {
-          case 0: acc = seg_sad_regs<SEGW, 0>(ls.sv, addr, sh); break;
-          case 1: acc = seg_sad_regs<SEGW, 1>(ls.sv, addr, sh); break;
-          case 2: acc = seg_sad_regs<SEGW, 2>(ls.sv, addr, sh); break;
-          default: acc = seg_sad_regs<SEGW, 3>(ls.sv, addr, sh); break;
+        const int an = __shfl_sync(0xffffffffu, a, j + 1);
+        if (aj >= 0) {  // warp-uniform
+          const unsigned saddr = smem_base + (unsigned)((aj & ~15) + ls.l_off);
+          const unsigned sh = (unsigned)(aj & 3) * 8;
+          unsigned acc, tot;
+          switch ((aj >> 2) & 3) {
+            case 0: acc = seg_sad_regs_p<SEGW, 0>(ls.sv, saddr, sh, pend, tot); break;
+            case 1: acc = seg_sad_regs_p<SEGW, 1>(ls.sv, saddr, sh, pend, tot); break;
+            case 2: acc = seg_sad_regs_p<SEGW, 2>(ls.sv, saddr, sh, pend, tot); break;
+            default: acc = seg_sad_regs_p<SEGW, 3>(ls.sv, saddr, sh, pend, tot); break;
+          }
+          if (lane == pend_j) mine = tot;
+          pend = ls.act ? acc : 0u;
+          pend_j = j;
         }
-        acc = warp_sum_u(ls.act ? acc : 0u);
-        if (lane == j) mine = acc;
+        aj = an;
+      }
+      {
+        const unsigned tot = warp_sum_u(pend);
+        if (lane == pend_j) mine = tot;
       }
       unsigned total = mine;
       if (np > 1) {
@@ -313,7 +325,7 @@ __device__ void diamond_runs_grouped(const Ctx &k, bool skip, Mv start, unsigned
         buf ^= 1;  // the next step writes the other half: a slower warp of the group may still be reading
       }
       if (skip) total *= 2;
-      if (leader) atomicAdd(&g_bcast[24], n);
+      n_cand += n;
 #ifdef B200_ME_TIMING
       if (leader) atomicAdd(&g_bcast[11], 1 + (n << 8));  // steps | candidates << 8
 #endif
@@ -372,6 +384,7 @@ __device__ void diamond_runs_grouped(const Ctx &k, bool skip, Mv start, unsigned
       g_runres[r][2] = sec.row, g_runres[r][3] = sec.col;
       g_runres[r][4] = (int)bestsad, g_runres[r][5] = center_steps, g_runres[r][6] = off_center;
       g_runres[r][7] = (int)v + err_cost(k, cur.row * 8, cur.col * 8);
+      atomicAdd(&g_bcast[24], n_cand);
     }
   }
   __syncthreads();
