@@ -8,7 +8,10 @@
 #include <stdio.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
+#include <condition_variable>
+#include <functional>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -251,6 +254,84 @@ struct CompactOut {
 };
 }  // namespace
 
+// A few persistent host threads for the per-descriptor passes of the host-buffer tier: a frame's queue is
+// ~10^6 descriptors, and spawning std::threads per call cost more (~0.5 ms) than the pass itself.
+namespace {
+class HostPool {
+ public:
+  static HostPool &get() {
+    static HostPool p;
+    return p;
+  }
+  int width() const { return (int)workers_.size() + 1; }
+  // f(0 .. n_parts) on the pool and the calling thread; returns when all parts are done
+  void run(int n_parts, const std::function<void(int)> &f) {
+    if (n_parts <= 1 || workers_.empty()) {
+      for (int i = 0; i < n_parts; ++i) f(i);
+      return;
+    }
+    std::lock_guard<std::mutex> one_job(job_mu_);
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      fn_ = &f;
+      n_.store(n_parts);
+      pending_.store(n_parts);
+      next_.store(0);
+      ++gen_;
+    }
+    cv_.notify_all();
+    work();
+    std::unique_lock<std::mutex> g(mu_);
+    done_cv_.wait(g, [&] { return pending_.load() == 0; });
+  }
+
+ private:
+  HostPool() {
+    const unsigned hw = std::thread::hardware_concurrency();
+    const int n = (int)std::min<unsigned>(16, hw ? hw : 1) - 1;
+    for (int i = 0; i < n; ++i) workers_.emplace_back([this] { loop(); });
+  }
+  ~HostPool() {
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      stop_ = true;
+    }
+    cv_.notify_all();
+    for (auto &t : workers_) t.join();
+  }
+  void work() {
+    for (;;) {
+      const int i = next_.fetch_add(1);
+      if (i >= n_.load()) return;
+      (*fn_)(i);
+      if (pending_.fetch_sub(1) == 1) {
+        std::lock_guard<std::mutex> g(mu_);
+        done_cv_.notify_all();
+      }
+    }
+  }
+  void loop() {
+    unsigned long long seen = 0;
+    for (;;) {
+      {
+        std::unique_lock<std::mutex> g(mu_);
+        cv_.wait(g, [&] { return stop_ || gen_ != seen; });
+        if (stop_) return;
+        seen = gen_;
+      }
+      work();
+    }
+  }
+  std::vector<std::thread> workers_;
+  std::mutex mu_, job_mu_;
+  std::condition_variable cv_, done_cv_;
+  const std::function<void(int)> *fn_ = nullptr;
+  std::atomic<int> n_{ 0 }, next_{ 0 }, pending_{ 0 };
+  unsigned long long gen_ = 0;
+  bool stop_ = false;
+};
+}  // namespace
+
 static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, unsigned flags,
                                const B200TxBlock *blocks, const B200TxPred *preds, int n_blocks,
                                const void *src, size_t src_elems, const void *pred, size_t pred_elems,
@@ -282,6 +363,49 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
   const size_t n = (size_t)n_blocks;
   HostPhases ph;
 
+  // ---- device carve-out
+  const bool wide = q_kind == B200_Q_FP_HBD || q_kind == B200_Q_B_HBD;
+  const size_t lv_bytes = wide ? 4 : 2;
+  size_t off = 0;
+  auto carve = [&](size_t bytes) {
+    size_t o = off;
+    off += align_up(bytes);
+    return o;
+  };
+  const size_t o_blocks = carve(sizeof(B200TxBlock) * n);
+  const size_t o_preds = carve(has_pred ? sizeof(B200TxPred) * n : 0);
+  const size_t o_src = carve(src_elems * px);
+  const size_t o_pred = carve(has_pred ? pred_elems * px : 0);
+  const size_t o_q = carve(has_q ? sizeof(B200QRow) * n_qrows : 0);
+  const size_t o_coeff = carve(want_coeff ? out_elems * 4 : 0);
+  const size_t o_qc = carve(has_q ? out_elems * 4 : 0);
+  const size_t o_dq = carve(has_q ? out_elems * 4 : 0);
+  const size_t o_eob = carve(has_q ? n * 2 : 0);
+  const size_t o_dist = carve(want_err ? n * 16 : 0);
+  const size_t o_loff = carve(cmp ? (n + 1) * 4 : 0);
+  const size_t o_lv = carve(cmp ? out_elems * lv_bytes : 0);
+  int rc = scratch_reserve(ctx, off);
+  if (rc != B200_OK) return rc;
+  char *base = (char *)ctx->d_scratch;
+  cudaStream_t s = ctx->stream, cs = ctx->copy_stream;
+
+  // the inputs go up while the host validates and buckets the queue (nothing below depends on the
+  // descriptors' contents); the descriptors too, as they are: a queue that turns out not to be grouped by
+  // tx_size is overwritten by its sorted copy later.  Every early return from here on drains the stream.
+  B200_CUDA_TRY(cudaMemcpyAsync(base + o_src, src, src_elems * px, cudaMemcpyHostToDevice, s));
+  B200_CUDA_TRY(cudaMemcpyAsync(base + o_blocks, blocks, sizeof(B200TxBlock) * n, cudaMemcpyHostToDevice, s));
+  if (has_pred)
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_preds, preds, sizeof(B200TxPred) * n, cudaMemcpyHostToDevice, s));
+  if (has_pred)
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_pred, pred, pred_elems * px, cudaMemcpyHostToDevice, s));
+  if (has_q)
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_q, qrows, sizeof(B200QRow) * n_qrows,
+                                  cudaMemcpyHostToDevice, s));
+  auto bail = [&](int code) {
+    cudaStreamSynchronize(s);
+    return code;
+  };
+
   // ---- one pass over the queue: validate, bucket by tx_size (one launch per size; the caller's order
   // inside a size is kept -- it is the caller that knows how to keep blocks of one tx type and of one
   // neighbourhood together, e.g. type groups inside ~1 MB bands, see bench.py make_descriptors), and find
@@ -311,8 +435,7 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
       long long bad_type, bad_range;  // first offending block, or -1
       bool in_order;
     };
-    const unsigned hw = std::thread::hardware_concurrency();
-    const int n_parts = n < (1u << 16) ? 1 : (int)std::min<unsigned>(8, hw ? hw : 1);
+    const int n_parts = (int)std::max<size_t>(1, std::min<size_t>(n >> 14, (size_t)HostPool::get().width()));
     std::vector<Part> parts(n_parts);
     auto scan = [&](int pi) {
       Part &pt = parts[pi];
@@ -342,24 +465,17 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
         pt.hi[ts] = o > pt.hi[ts] ? o : pt.hi[ts];
       }
     };
-    if (n_parts == 1) {
-      scan(0);
-    } else {
-      std::vector<std::thread> th;
-      for (int pi = 1; pi < n_parts; ++pi) th.emplace_back(scan, pi);
-      scan(0);
-      for (auto &t : th) t.join();
-    }
+    HostPool::get().run(n_parts, scan);
     for (const Part &pt : parts) {
       if (pt.bad_type >= 0) {
         const size_t i = (size_t)pt.bad_type;
         set_error("b200_txq_batch_host: block %zu has invalid tx_size/tx_type %d/%d", i, (int)blocks[i].tx_size,
                   (int)blocks[i].tx_type);
-        return B200_EINVAL;
+        return bail(B200_EINVAL);
       }
       if (pt.bad_range >= 0) {
         set_error("b200_txq_batch_host: block %zu reads outside src / pred / qrows", (size_t)pt.bad_range);
-        return B200_EINVAL;
+        return bail(B200_EINVAL);
       }
       in_order = in_order && pt.in_order;
       for (int ts = 0; ts < B200_TX_SIZES_ALL; ++ts) {
@@ -384,9 +500,14 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
   const size_t ho_eob = hcarve(has_q ? n * 2 : 0);
   const size_t ho_dist = hcarve(want_err ? n * 16 : 0);
   const size_t ho_loff = hcarve(cmp ? (n + 1) * 4 : 0);
-  int rc = host_scratch_reserve(ctx, hoff);
-  if (rc != B200_OK) return rc;
+  rc = host_scratch_reserve(ctx, hoff);
+  if (rc != B200_OK) return bail(rc);
   char *hbase = (char *)ctx->h_scratch;
+  // a queue already grouped by tx_size needs no scatter: eob, distortion and the level offsets are read
+  // back straight into the caller's arrays
+  char *eob_dst = in_order && eob ? (char *)eob : hbase + ho_eob;
+  char *dist_dst = in_order && dist ? (char *)dist : hbase + ho_dist;
+  char *loff_dst = in_order && cmp ? (char *)cmp->level_offset : hbase + ho_loff;
   std::vector<uint32_t> order;  // sorted position -> caller's index
   const B200TxBlock *sblocks = blocks;
   const B200TxPred *spreds = preds;
@@ -418,7 +539,7 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
     Group g = { ts, first, last - first, g_lo[ts], g_hi[ts] + me, (last - first) * me };
     if (g.hi > out_elems) {
       set_error("b200_txq_batch_host: a %s block writes past out_elems", "queued");
-      return B200_EINVAL;
+      return bail(B200_EINVAL);
     }
     groups.push_back(g);
   }
@@ -445,38 +566,6 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
   }
 
   ph.mark("sort+groups");
-  // ---- device carve-out
-  const bool wide = q_kind == B200_Q_FP_HBD || q_kind == B200_Q_B_HBD;
-  const size_t lv_bytes = wide ? 4 : 2;
-  size_t off = 0;
-  auto carve = [&](size_t bytes) {
-    size_t o = off;
-    off += align_up(bytes);
-    return o;
-  };
-  const size_t o_blocks = carve(sizeof(B200TxBlock) * n);
-  const size_t o_preds = carve(has_pred ? sizeof(B200TxPred) * n : 0);
-  const size_t o_src = carve(src_elems * px);
-  const size_t o_pred = carve(has_pred ? pred_elems * px : 0);
-  const size_t o_q = carve(has_q ? sizeof(B200QRow) * n_qrows : 0);
-  const size_t o_coeff = carve(want_coeff ? out_elems * 4 : 0);
-  const size_t o_qc = carve(has_q ? out_elems * 4 : 0);
-  const size_t o_dq = carve(has_q ? out_elems * 4 : 0);
-  const size_t o_eob = carve(has_q ? n * 2 : 0);
-  const size_t o_dist = carve(want_err ? n * 16 : 0);
-  const size_t o_loff = carve(cmp ? (n + 1) * 4 : 0);
-  const size_t o_lv = carve(cmp ? out_elems * lv_bytes : 0);
-  rc = scratch_reserve(ctx, off);
-  if (rc != B200_OK) return rc;
-  char *base = (char *)ctx->d_scratch;
-  cudaStream_t s = ctx->stream, cs = ctx->copy_stream;
-
-  B200_CUDA_TRY(cudaMemcpyAsync(base + o_src, src, src_elems * px, cudaMemcpyHostToDevice, s));
-  if (has_pred)
-    B200_CUDA_TRY(cudaMemcpyAsync(base + o_pred, pred, pred_elems * px, cudaMemcpyHostToDevice, s));
-  if (has_q)
-    B200_CUDA_TRY(cudaMemcpyAsync(base + o_q, qrows, sizeof(B200QRow) * n_qrows,
-                                  cudaMemcpyHostToDevice, s));
   if (!dense && !cmp) {
     // regions of the output arrays that no block covers read back as zero
     if (want_coeff) B200_CUDA_TRY(cudaMemsetAsync(base + o_coeff, 0, out_elems * 4, s));
@@ -486,13 +575,13 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
     }
   }
   if (cmp && want_coeff) B200_CUDA_TRY(cudaMemsetAsync(base + o_coeff, 0, out_elems * 4, s));
+  if (!in_order) {  // the sorted queue replaces the caller's order sent up ahead of the validation
+    B200_CUDA_TRY(cudaMemcpyAsync(base + o_blocks, sblocks, n * sizeof(B200TxBlock), cudaMemcpyHostToDevice, s));
+    if (has_pred)
+      B200_CUDA_TRY(cudaMemcpyAsync(base + o_preds, spreds, n * sizeof(B200TxPred), cudaMemcpyHostToDevice, s));
+  }
   for (size_t gi = 0; gi < groups.size(); ++gi) {
     const Group &g = groups[gi];
-    B200_CUDA_TRY(cudaMemcpyAsync(base + o_blocks + g.first * sizeof(B200TxBlock), sblocks + g.first,
-                                  g.count * sizeof(B200TxBlock), cudaMemcpyHostToDevice, s));
-    if (has_pred)
-      B200_CUDA_TRY(cudaMemcpyAsync(base + o_preds + g.first * sizeof(B200TxPred), spreds + g.first,
-                                    g.count * sizeof(B200TxPred), cudaMemcpyHostToDevice, s));
     B200TxqLaunch l;
     memset(&l, 0, sizeof(l));
     l.tx_size = g.ts;
@@ -512,7 +601,7 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
     l.eob = has_q ? (uint16_t *)(base + o_eob) + g.first : nullptr;
     l.dist = want_err ? (int64_t *)(base + o_dist) + 2 * g.first : nullptr;
     rc = txq_launch(ctx, l, s);
-    if (rc != B200_OK) return rc;
+    if (rc != B200_OK) return bail(rc);
     if (cmp) continue;
     B200_CUDA_TRY(cudaEventRecord(ctx->group_done[gi], s));
     B200_CUDA_TRY(cudaStreamWaitEvent(cs, ctx->group_done[gi], 0));
@@ -539,15 +628,15 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
     cl.levels = base + o_lv;
     cl.level_offset = (uint32_t *)(base + o_loff);
     rc = b200_txq_compact_launch(ctx, &cl, s);
-    if (rc != B200_OK) return rc;
-    uint32_t *h_loff = (uint32_t *)(hbase + ho_loff);
+    if (rc != B200_OK) return bail(rc);
+    uint32_t *h_loff = (uint32_t *)loff_dst;
     B200_CUDA_TRY(cudaMemcpyAsync(h_loff, base + o_loff, (n + 1) * 4, cudaMemcpyDeviceToHost, s));
-    B200_CUDA_TRY(cudaMemcpyAsync(hbase + ho_eob, base + o_eob, n * 2, cudaMemcpyDeviceToHost, s));
+    B200_CUDA_TRY(cudaMemcpyAsync(eob_dst, base + o_eob, n * 2, cudaMemcpyDeviceToHost, s));
     B200_CUDA_TRY(cudaEventRecord(ctx->group_done[0], s));
     B200_CUDA_TRY(cudaStreamWaitEvent(cs, ctx->group_done[0], 0));
     // meanwhile the second stream brings the per-block distortion and the dense coeff back
     if (want_err)
-      B200_CUDA_TRY(cudaMemcpyAsync(hbase + ho_dist, base + o_dist, n * 16, cudaMemcpyDeviceToHost, cs));
+      B200_CUDA_TRY(cudaMemcpyAsync(dist_dst, base + o_dist, n * 16, cudaMemcpyDeviceToHost, cs));
     if (want_coeff)
       B200_CUDA_TRY(cudaMemcpyAsync(coeff, base + o_coeff, out_elems * 4, cudaMemcpyDeviceToHost, cs));
     B200_CUDA_TRY(cudaStreamSynchronize(s));
@@ -571,9 +660,9 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
       }
     }
     if (has_q)
-      B200_CUDA_TRY(cudaMemcpyAsync(hbase + ho_eob, base + o_eob, n * 2, cudaMemcpyDeviceToHost, cs));
+      B200_CUDA_TRY(cudaMemcpyAsync(eob_dst, base + o_eob, n * 2, cudaMemcpyDeviceToHost, cs));
     if (want_err)
-      B200_CUDA_TRY(cudaMemcpyAsync(hbase + ho_dist, base + o_dist, n * 16, cudaMemcpyDeviceToHost, cs));
+      B200_CUDA_TRY(cudaMemcpyAsync(dist_dst, base + o_dist, n * 16, cudaMemcpyDeviceToHost, cs));
     if (dense) {
       // zero what no group covers, on the host, while the copies run
       size_t at = 0;
@@ -595,11 +684,7 @@ static int txq_batch_host_impl(b200_ctx *ctx, int in_kind, int q_kind, int bd, u
   ph.mark("readback");
   const uint16_t *eob_s = (const uint16_t *)(hbase + ho_eob);
   const int64_t *dist_s = (const int64_t *)(hbase + ho_dist);
-  if (in_order) {
-    if (has_q && eob) memcpy(eob, eob_s, n * 2);
-    if (want_err) memcpy(dist, dist_s, n * 16);
-    if (cmp) memcpy(cmp->level_offset, hbase + ho_loff, (n + 1) * 4);
-  } else {
+  if (!in_order) {
     const uint32_t *loff_s = (const uint32_t *)(hbase + ho_loff);
     for (size_t i = 0; i < n; ++i) {
       if (has_q && eob) eob[order[i]] = eob_s[i];
