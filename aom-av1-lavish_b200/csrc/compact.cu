@@ -24,6 +24,15 @@ constexpr int kChunk = 2048;   // blocks per CTA of the prefix-sum kernels
 constexpr int kScanThreads = 256;
 constexpr int kMaxChunks = 1 << 16;
 
+// Scratch of b200_txq_compact_launch_noalloc: the per-chunk sums, in a file-scope device array instead of the
+// context's cudaMalloc'ed d_partials.  kStaticMaxChunks * 4 B = 16 KB, held by every GPU that loads the library
+// until the process exits.  In HOST code this name is only the host-side stand-in of the symbol, never a
+// device address: compact_init_device asks the runtime for the address (cudaGetSymbolAddress, once per context
+// with its device current) and the launches below pass that pointer.
+constexpr int kStaticMaxChunks = B200_COMPACT_NOALLOC_MAX_BLOCKS / kChunk;
+static_assert(kStaticMaxChunks * kChunk == B200_COMPACT_NOALLOC_MAX_BLOCKS, "maximum is a whole number of chunks");
+static __device__ __align__(256) uint32_t g_static_partials[kStaticMaxChunks];
+
 __constant__ uint32_t c_scan_off[B200_TX_SIZES_ALL];  // element offset of the size's tables in d_scan
 __constant__ uint16_t c_scan_n[B200_TX_SIZES_ALL];    // max_eob of the size
 
@@ -140,6 +149,10 @@ int compact_init_device(b200_ctx *ctx) {
   B200_CUDA_TRY(cudaMemcpyToSymbol(c_scan_off, off, sizeof(off)));
   B200_CUDA_TRY(cudaMemcpyToSymbol(c_scan_n, cnt, sizeof(cnt)));
   B200_CUDA_TRY(cudaMalloc(&ctx->d_partials, sizeof(uint32_t) * kMaxChunks));
+  // device address of the static scratch on THIS context's device (ctx_init runs with it current)
+  void *p = nullptr;
+  B200_CUDA_TRY(cudaGetSymbolAddress(&p, g_static_partials));
+  ctx->d_static_partials = static_cast<uint32_t *>(p);
   return B200_OK;
 }
 
@@ -168,6 +181,49 @@ extern "C" int b200_txq_compact_launch(b200_ctx *ctx, const B200CompactLaunch *l
   compact_sums<<<n_chunks, kScanThreads, 0, s>>>(l->eob, n, ctx->d_partials);
   compact_scan<<<1, 1024, 0, s>>>(ctx->d_partials, n_chunks, l->level_offset + n);
   compact_offsets<<<n_chunks, kScanThreads, 0, s>>>(l->eob, n, ctx->d_partials, l->level_offset);
+  if (l->wide)
+    compact_gather<int32_t><<<(n + 7) / 8, 256, 0, s>>>(l->blocks, l->qcoeff, l->eob, l->level_offset,
+                                                        ctx->d_scan, static_cast<int32_t *>(l->levels), n);
+  else
+    compact_gather<int16_t><<<(n + 7) / 8, 256, 0, s>>>(l->blocks, l->qcoeff, l->eob, l->level_offset,
+                                                        ctx->d_scan, static_cast<int16_t *>(l->levels), n);
+  B200_CUDA_TRY(cudaGetLastError());
+  return B200_OK;
+}
+
+// The same packing without any allocation (no counterpart in the reference; see include/b200av1.h): the
+// per-chunk sums live in g_static_partials.  Nothing in the scratch has to start at zero -- compact_sums writes
+// every entry [0, n_chunks) the two later kernels read -- so nothing is cleared; the array keeps the previous
+// call's sums.  All calls on a device share it: two calls whose kernels overlap on the GPU (different streams
+// without an ordering between them) race.
+extern "C" int b200_txq_compact_launch_noalloc(b200_ctx *ctx, const B200CompactLaunch *l, void *stream) {
+  if (!ctx || !l || l->n_blocks < 0) return B200_EINVAL;
+  if (!l->blocks || !l->qcoeff || !l->eob || !l->levels || !l->level_offset) {
+    set_error("b200_txq_compact_launch_noalloc: missing buffer");
+    return B200_EINVAL;
+  }
+  const int n = l->n_blocks;
+  if (n > B200_COMPACT_NOALLOC_MAX_BLOCKS) {
+    set_error("b200_txq_compact_launch_noalloc: %d blocks exceed the static scratch's maximum of %d "
+              "(B200_COMPACT_NOALLOC_MAX_BLOCKS); use b200_txq_compact_launch or split the batch",
+              n, B200_COMPACT_NOALLOC_MAX_BLOCKS);
+    return B200_EINVAL;
+  }
+  if (!ctx->d_static_partials) {
+    set_error("b200_txq_compact_launch_noalloc: static scratch not resolved on device %d", ctx->device);
+    return B200_EINVAL;
+  }
+  B200_CUDA_TRY(cudaSetDevice(ctx->device));
+  cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+  if (n == 0) {
+    B200_CUDA_TRY(cudaMemsetAsync(l->level_offset, 0, sizeof(uint32_t), s));
+    return B200_OK;
+  }
+  const int n_chunks = (n + kChunk - 1) / kChunk;
+  uint32_t *partials = ctx->d_static_partials;
+  compact_sums<<<n_chunks, kScanThreads, 0, s>>>(l->eob, n, partials);
+  compact_scan<<<1, 1024, 0, s>>>(partials, n_chunks, l->level_offset + n);
+  compact_offsets<<<n_chunks, kScanThreads, 0, s>>>(l->eob, n, partials, l->level_offset);
   if (l->wide)
     compact_gather<int32_t><<<(n + 7) / 8, 256, 0, s>>>(l->blocks, l->qcoeff, l->eob, l->level_offset,
                                                         ctx->d_scan, static_cast<int32_t *>(l->levels), n);

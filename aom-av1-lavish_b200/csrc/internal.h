@@ -53,6 +53,7 @@ struct b200_ctx {
   int16_t *d_iscan;   // all inverse scan tables, see txq.cu
   int16_t *d_scan;    // all forward scan tables, same layout (compact.cu)
   uint32_t *d_partials;  // per-chunk sums of the compaction prefix sum (compact.cu)
+  uint32_t *d_static_partials;  // device address of compact.cu's file-scope scratch (no-alloc entry point)
   unsigned long long *d_pmask;  // scan prefix masks of the <= 64-sample sizes, see txq.cu
   // scratch for the host-buffer (drop-in) tier
   void *d_scratch;

@@ -276,6 +276,17 @@ typedef struct {
   uint32_t *level_offset;    /* device out: n_blocks + 1 entries */
 } B200CompactLaunch;
 int b200_txq_compact_launch(b200_ctx *ctx, const B200CompactLaunch *launch, void *stream);
+/* The same packing for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.  Its
+ * scratch (the per-chunk sums of the prefix sum) is a file-scope device array of
+ * B200_COMPACT_NOALLOC_MAX_BLOCKS / 2048 * 4 bytes = 16 KB, resident on every GPU that loads the library;
+ * the call itself performs no cudaMalloc / cudaFree and no allocating library call (the context must exist
+ * already).  n_blocks beyond B200_COMPACT_NOALLOC_MAX_BLOCKS is refused with B200_EINVAL and a message in
+ * b200_last_error().  Every call on a device shares the array (it keeps the last call's sums; nothing in it
+ * needs to start at zero): calls whose kernels overlap on the GPU race -- order them on one stream or with
+ * events.  Results are identical to b200_txq_compact_launch. */
+#define B200_COMPACT_NOALLOC_MAX_BLOCKS (1 << 23) /* 8 388 608 transform blocks per call */
+int b200_txq_compact_launch_noalloc(b200_ctx *ctx, const B200CompactLaunch *launch, void *stream);
 
 /* Host-buffer call returning the compact form: like b200_txq_batch_host, but the dense
  * qcoeff / dqcoeff stay on the device; the host receives eob, level_offset (n_blocks + 1),
