@@ -18,7 +18,8 @@ from harness import i16p, i32p, ptr  # noqa: E402
 
 R = H.ref()
 assert R is not None, "oracle/_ref not built"
-FIELDS = [n for n, _ in H.MeParams._fields_ if n not in ("src", "ref", "mvjcost", "mvcost0", "mvcost1")]
+FIELDS = [n for n, _ in H.MeParams._fields_ if n not in ("src", "ref", "mvjcost", "mvcost0", "mvcost1",
+          "second_pred", "mask", "mask_stride", "inv_mask")]  # compound operands: not part of these vectors
 
 
 def pack(p):
