@@ -287,9 +287,11 @@ class HostPool {
 
  private:
   HostPool() {
+    // B200_HOST_THREADS: width of the pool (a process per GPU on one host should divide the cores between them)
     const unsigned hw = std::thread::hardware_concurrency();
-    const int n = (int)std::min<unsigned>(16, hw ? hw : 1) - 1;
-    for (int i = 0; i < n; ++i) workers_.emplace_back([this] { loop(); });
+    int n = (int)std::min<unsigned>(16, hw ? hw : 1);
+    if (const char *e = getenv("B200_HOST_THREADS")) n = std::max(1, std::min(64, atoi(e)));
+    for (int i = 0; i < n - 1; ++i) workers_.emplace_back([this] { loop(); });
   }
   ~HostPool() {
     {

@@ -986,6 +986,8 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    # one process per GPU on one host: the host-buffer tier's validation threads divide the cores between the ranks
+    os.environ.setdefault("B200_HOST_THREADS", str(max(1, min(16, (os.cpu_count() or 1) // max(world, 1)))))
     sizes = [int(s) for s in args.sizes.split(",")] if args.sizes else list(range(19))
     seed = 2001
     metric = "1080p frame-equiv/s for txfm+quant+ME SAD; HBM GB/s as % of B200 peak"
