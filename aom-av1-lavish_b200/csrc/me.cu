@@ -674,9 +674,12 @@ __device__ __forceinline__ unsigned seg_sad_regs(const unsigned (&sv)[SEGW], int
 // dynamic shared array) and the PREVIOUS candidate's warp reduction issued while they are in flight: the
 // grouped n-step loop is one dependent pass per candidate, so the REDUX latency would otherwise be exposed
 // once per candidate.  prev: this lane's sum of the previous candidate; prev_total: its warp total.
-template <int SEGW, int WO>
+// PX == 2 (uint16 pixels): |s - r| per half word = max - min (VIMNMX.U16x2) added into packed 16-bit sums -- a
+// lane adds at most 16 terms of at most 12 bits per half (16 * 4095 < 65536) -- folded by one IDP.2A at the end.
+template <int SEGW, int WO, int PX = 1>
 __device__ __forceinline__ unsigned seg_sad_regs_p(const unsigned (&sv)[SEGW], unsigned saddr, unsigned sh,
                                                    unsigned prev, unsigned &prev_total) {
+  static_assert(PX == 1 || SEGW <= 16, "packed 16-bit sums hold 16 terms");
   constexpr int NV = SEGW / 4 + 1;
   unsigned r[4 * NV];
 #pragma unroll
@@ -690,12 +693,16 @@ __device__ __forceinline__ unsigned seg_sad_regs_p(const unsigned (&sv)[SEGW], u
 #pragma unroll
   for (int i = 0; i < kAcc; ++i) a[i] = 0;
 #pragma unroll
-  for (int i = 0; i < SEGW; ++i)
-    a[i % kAcc] = sad4_acc(sv[i], __funnelshift_r(r[WO + i], r[WO + i + 1], sh), a[i % kAcc]);
+  for (int i = 0; i < SEGW; ++i) {
+    const unsigned rv = __funnelshift_r(r[WO + i], r[WO + i + 1], sh);
+    if constexpr (PX == 1) a[i % kAcc] = sad4_acc(sv[i], rv, a[i % kAcc]);
+    else a[i % kAcc] = a[i % kAcc] + __vmaxu2(sv[i], rv) - __vminu2(sv[i], rv);
+  }
 #pragma unroll
   for (int w = kAcc / 2; w > 0; w >>= 1)
 #pragma unroll
     for (int i = 0; i < w; ++i) a[i] += a[i + w];
+  if constexpr (PX == 2) return __dp2a_lo(a[0], 0x0101u, 0u);
   return a[0];
 }
 
@@ -717,14 +724,14 @@ template <int SEGW>
 __device__ __forceinline__ void lane_share_init(const Ctx &k, bool skip, LaneShare<SEGW> &ls) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int R = skip ? k.d.bh >> 1 : k.d.bh, rmul = skip ? 2 : 1;
-  const int lS = k.d.bw > 4 * SEGW ? 1 : 0;            // log2(segments per row): 128-wide blocks have two
+  const int lS = k.d.bw * k.px > 4 * SEGW ? 1 : 0;     // log2(segments per row): 128-byte rows have two
   const int np = ((R << lS) + 31) >> 5;                // passes: 1, 2, 4 or 8
   const int lP = np <= 1 ? 0 : 32 - __clz(np - 1);
   const int T = ((warp & ((1 << lP) - 1)) << 5) + lane, q = T >> 3;
   const int seg = q & ((1 << lS) - 1), row = ((q >> lS) << 3) + (T & 7);
   ls.act = row < R;
   const int yy = ls.act ? row * rmul : 0;
-  ls.l_off = yy * k.ref_pitch + seg * (4 * SEGW);
+  ls.l_off = yy * k.ref_pitch * k.px + seg * (4 * SEGW);
   ls.c0 = warp >> lP;
   ls.cstep = kWarps >> lP;
   load_words<SEGW>(smem_words(yy * k.src_pitch_w * 4 + seg * (4 * SEGW)), ls.sv);
@@ -766,6 +773,15 @@ struct LaneShare<0> {};
 __device__ __forceinline__ int multi_segw(const Ctx &k) {
   if (!multi_ok(k)) return 0;
   return k.d.bw >= 64 ? 16 : (k.d.bw == 32 ? 8 : 4);
+}
+
+// Lane share of the warp-group n-step (diamond_runs_grouped), which also serves uint16 planes: words per lane
+// by the row's BYTES; rows of more than 128 bytes (128-pixel wide blocks at high bit depth) do not fit its
+// 8 passes and keep the lock-step path.
+__device__ __forceinline__ int grouped_segw(const Ctx &k) {
+  if (k.px == 1) return multi_segw(k);
+  if (!(k.fast && k.d.bw >= 16 && k.d.bw <= 64)) return 0;
+  return k.d.bw >= 32 ? 16 : 8;
 }
 
 // The step's candidates (g_cda / g_cdp, n of them) -> out[i] = SAD (finished: doubled when rows

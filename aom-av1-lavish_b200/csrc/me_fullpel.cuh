@@ -232,7 +232,7 @@ __device__ __forceinline__ void group_sync(int id, int nthreads) {
   else asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
-template <int SEGW>
+template <int SEGW, int PX>
 __device__ void diamond_runs_grouped(const Ctx &k, bool skip, Mv start, unsigned start_sad, int step_param,
                                      int nruns, const LaneShare<SEGW> &ls) {
   static_assert(SEGW > 0, "register-resident lane share only");
@@ -286,7 +286,7 @@ __device__ void diamond_runs_grouped(const Ctx &k, bool skip, Mv start, unsigned
       if (lane < n) {
         prow = cur.row + cfg.site[st][lane + 1][0];
         pcol = cur.col + cfg.site[st][lane + 1][1];
-        if (in_range(k, prow, pcol)) a = k.win0_off + prow * k.ref_pitch + pcol;
+        if (in_range(k, prow, pcol)) a = k.win0_off + (prow * k.ref_pitch + pcol) * PX;
       }
       // candidate j's address comes from lane j one iteration ahead; its lane sums are reduced while
       // candidate j + 1's window rows are being loaded
@@ -300,10 +300,10 @@ __device__ void diamond_runs_grouped(const Ctx &k, bool skip, Mv start, unsigned
           const unsigned sh = (unsigned)(aj & 3) * 8;
           unsigned acc, tot;
           switch ((aj >> 2) & 3) {
-            case 0: acc = seg_sad_regs_p<SEGW, 0>(ls.sv, saddr, sh, pend, tot); break;
-            case 1: acc = seg_sad_regs_p<SEGW, 1>(ls.sv, saddr, sh, pend, tot); break;
-            case 2: acc = seg_sad_regs_p<SEGW, 2>(ls.sv, saddr, sh, pend, tot); break;
-            default: acc = seg_sad_regs_p<SEGW, 3>(ls.sv, saddr, sh, pend, tot); break;
+            case 0: acc = seg_sad_regs_p<SEGW, 0, PX>(ls.sv, saddr, sh, pend, tot); break;
+            case 1: acc = seg_sad_regs_p<SEGW, 1, PX>(ls.sv, saddr, sh, pend, tot); break;
+            case 2: acc = seg_sad_regs_p<SEGW, 2, PX>(ls.sv, saddr, sh, pend, tot); break;
+            default: acc = seg_sad_regs_p<SEGW, 3, PX>(ls.sv, saddr, sh, pend, tot); break;
           }
           if (lane == pend_j) mine = tot;
           pend = ls.act ? acc : 0u;
@@ -325,6 +325,7 @@ __device__ void diamond_runs_grouped(const Ctx &k, bool skip, Mv start, unsigned
         buf ^= 1;  // the next step writes the other half: a slower warp of the group may still be reading
       }
       if (skip) total *= 2;
+      if constexpr (PX == 2) total >>= k.sad_shift;  // aom_highbd_sadMxN_bits10 / _bits12 (encoder_utils.h:153-208)
       n_cand += n;
 #ifdef B200_ME_TIMING
       if (leader) atomicAdd(&g_bcast[11], 1 + (n << 8));  // steps | candidates << 8
@@ -364,13 +365,15 @@ __device__ void diamond_runs_grouped(const Ctx &k, bool skip, Mv start, unsigned
     // get_mvpred_var_cost (mcomp.c:665) of the run's result, which the replay of full_pixel_diamond compares
     // between runs: measured here by the group (its rows dealt out to the np warps) instead of by the whole
     // CTA once the runs are over
-    int lsum;
-    unsigned lsse;
-    var8_staged(k.win0_off + cur.row * k.ref_pitch + cur.col, k.src_pitch_w * 4, k.ref_pitch, k.d.bw, k.d.bh, np,
-                &lsum, &lsse, pass);
+    // (uint16 planes: the replay measures the few distinct results with the CTA-wide var_cost instead)
+    int lsum = 0;
+    unsigned lsse = 0;
+    if constexpr (PX == 1)
+      var8_staged(k.win0_off + cur.row * k.ref_pitch + cur.col, k.src_pitch_w * 4, k.ref_pitch, k.d.bw, k.d.bh, np,
+                  &lsum, &lsse, pass);
     long long vsum = warp_sum_ll((long long)lsum);
     unsigned long long vsse = (unsigned long long)warp_sum_ll((long long)lsse);
-    if (np > 1) {
+    if (PX == 1 && np > 1) {
       if (lane == 0) g_red[warp] = vsum, g_red[kWarps + warp] = (long long)vsse;
       group_sync(1 + grp, np * 32);
       vsum = 0, vsse = 0;
@@ -422,7 +425,7 @@ __device__ void sad_list(const Ctx &k, bool skip, Mv best, int *cl) {
 // sequential bookkeeping replayed on their results -- which runs count (num00 skips), the
 // variance comparison between them, and second_best_mv handed from run to run (a run that
 // never moved leaves it as it found it).
-template <int SEGW>
+template <int SEGW, int PX = 1>
 __device__ int full_pixel_diamond_t(const Ctx &k, bool skip, Mv start, int step_param, int *cl,
                                     Mv *best, Mv *second, bool has_second) {
   LaneShare<SEGW> ls;
@@ -435,7 +438,7 @@ __device__ int full_pixel_diamond_t(const Ctx &k, bool skip, Mv start, int step_
 #ifdef B200_ME_TIMING2
   const long long tr0 = clock64();
 #endif
-  if constexpr (SEGW > 0) diamond_runs_grouped<SEGW>(k, skip, start, start_sad, step_param, nruns, ls);
+  if constexpr (SEGW > 0) diamond_runs_grouped<SEGW, PX>(k, skip, start, start_sad, step_param, nruns, ls);
   else diamond_runs<SEGW>(k, skip, start, start_sad, step_param, nruns, ls);
 #ifdef B200_ME_TIMING2
   const long long tr1 = clock64();
@@ -448,7 +451,8 @@ __device__ int full_pixel_diamond_t(const Ctx &k, bool skip, Mv start, int step_
   best->row = g_runres[0][0], best->col = g_runres[0][1];
   take_second(0);
   // the grouped runs left their variance in g_runres[r][7]; the lock-step path measures it here
-  int bestsme = SEGW > 0 ? g_runres[0][7] : var_cost(k, *best);
+  constexpr bool kGroupVar = SEGW > 0 && PX == 1;
+  int bestsme = kGroupVar ? g_runres[0][7] : var_cost(k, *best);
   // runs that end on an mv already measured (the usual case: they converge) reuse its variance
   Mv last = *best;
   int last_sme = bestsme;
@@ -457,7 +461,7 @@ __device__ int full_pixel_diamond_t(const Ctx &k, bool skip, Mv start, int step_
     const Mv tmp = { g_runres[n][0], g_runres[n][1] };
     take_second(n);
     int sme;
-    if constexpr (SEGW > 0) {
+    if constexpr (kGroupVar) {
       sme = g_runres[n][7];
     } else if (tmp.row == best->row && tmp.col == best->col) {
       sme = bestsme;
@@ -483,13 +487,23 @@ __device__ int full_pixel_diamond_t(const Ctx &k, bool skip, Mv start, int step_
   return bestsme;
 }
 
+// HBD: the kernel instance of uint16 planes (fullpel_kernel<3>); the 8-bit instance does not carry its code
+template <bool HBD>
 __device__ int full_pixel_diamond(const Ctx &k, bool skip, Mv start, int step_param, int *cl,
                                   Mv *best, Mv *second, bool has_second) {
-  switch (multi_segw(k)) {  // CTA-uniform
-    case 16: return full_pixel_diamond_t<16>(k, skip, start, step_param, cl, best, second, has_second);
-    case 8: return full_pixel_diamond_t<8>(k, skip, start, step_param, cl, best, second, has_second);
-    case 4: return full_pixel_diamond_t<4>(k, skip, start, step_param, cl, best, second, has_second);
-    default: return full_pixel_diamond_t<0>(k, skip, start, step_param, cl, best, second, has_second);
+  if constexpr (HBD) {
+    switch (grouped_segw(k)) {  // CTA-uniform
+      case 16: return full_pixel_diamond_t<16, 2>(k, skip, start, step_param, cl, best, second, has_second);
+      case 8: return full_pixel_diamond_t<8, 2>(k, skip, start, step_param, cl, best, second, has_second);
+      default: return full_pixel_diamond_t<0>(k, skip, start, step_param, cl, best, second, has_second);
+    }
+  } else {
+    switch (multi_segw(k)) {
+      case 16: return full_pixel_diamond_t<16>(k, skip, start, step_param, cl, best, second, has_second);
+      case 8: return full_pixel_diamond_t<8>(k, skip, start, step_param, cl, best, second, has_second);
+      case 4: return full_pixel_diamond_t<4>(k, skip, start, step_param, cl, best, second, has_second);
+      default: return full_pixel_diamond_t<0>(k, skip, start, step_param, cl, best, second, has_second);
+    }
   }
 }
 
@@ -1107,7 +1121,7 @@ __device__ int full_pixel_search(const Ctx &k, bool skip, int *cl, Mv *best, Mv 
           var = pattern_search(k, skip, start, max(kMaxSteps - 1, sp), false, pcl, best);
       } else {
         (void)m, (void)pcl;
-        var = full_pixel_diamond(k, skip, start, sp, cl, best, second, true);
+        var = full_pixel_diamond<FAM == 3>(k, skip, start, sp, cl, best, second, true);
       }
     }
 #ifdef B200_ME_TIMING
@@ -1304,7 +1318,7 @@ __global__ void __launch_bounds__(kThreads, 3) fullpel_kernel(const B200MeLaunch
   load_desc<true>(l, bi);
   Ctx k(g_desc);
   k.l = &l;
-  if (me_family(k.d.search_method) != FAM) return;
+  if (me_family(k.d.search_method) != (FAM == 3 ? 0 : FAM)) return;  // instance 3 = family 0 on uint16 planes
   if (threadIdx.x == 0) g_bcast[24] = 0;  // served by another instance of the launch
   init_costs(k);
   {  // the method's site table: read at every step of the search, keep it on chip

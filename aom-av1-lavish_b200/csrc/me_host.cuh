@@ -68,6 +68,8 @@ int me_init_device(b200_ctx *ctx) {
                                      200 * 1024));
   B200_CUDA_TRY(cudaFuncSetAttribute(me::fullpel_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      200 * 1024));
+  B200_CUDA_TRY(cudaFuncSetAttribute(me::fullpel_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     200 * 1024));
   B200_CUDA_TRY(cudaFuncSetAttribute(me::subpel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      200 * 1024));
   return B200_OK;
@@ -167,8 +169,10 @@ extern "C" int b200_me_fullpel_launch(b200_ctx *ctx, const B200MeLaunch *l, void
   // other families exit at once)
   const unsigned fam = (l->families & 7u) ? (l->families & 7u) : 7u;
   const b200::me::Sites *sites = static_cast<const b200::me::Sites *>(ctx->d_me_sites);
-  if (fam & B200_ME_FAMILY_NSTEP)
+  if ((fam & B200_ME_FAMILY_NSTEP) && !l->highbd)
     b200::me::fullpel_kernel<0><<<l->n_blocks, b200::me::kThreads, smem, s>>>(*l, sites, budget, tc, tm_cur, tm_ref);
+  if ((fam & B200_ME_FAMILY_NSTEP) && l->highbd)  // uint16 planes: the n-step family's own instance
+    b200::me::fullpel_kernel<3><<<l->n_blocks, b200::me::kThreads, smem, s>>>(*l, sites, budget, tc, tm_cur, tm_ref);
   if (fam & B200_ME_FAMILY_PATTERN)
     b200::me::fullpel_kernel<1><<<l->n_blocks, b200::me::kThreads, smem, s>>>(*l, sites, budget, tc, tm_cur, tm_ref);
   if (fam & B200_ME_FAMILY_REFINE)

@@ -18,7 +18,10 @@ import bench  # noqa: E402
 def main():
     F = 4
     _, _, luma = bench.make_residual_frames(list(range(F)), 5)
-    work = bench.MeWork(luma, list(range(F)), 5)
+    bd = 10 if "--hbd" in sys.argv else 8
+    if bd > 8:  # the 10-bit searches of configs[4] (same per-search work on 1080p planes)
+        luma = (luma.astype(np.uint16) << 2) | (np.random.default_rng(6).integers(0, 4, luma.shape).astype(np.uint16))
+    work = bench.MeWork(luma, list(range(F)), 5, bd=bd)
     if "--no-mesh" in sys.argv:
         work.blocks["flags"] = 0
         work.blocks["force_mesh_thresh"] = 2 ** 31 - 1
