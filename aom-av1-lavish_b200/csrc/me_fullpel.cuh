@@ -32,6 +32,23 @@ __device__ int var_cost(const Ctx &k, Mv m) {
     sum = lsum;
     sse = lsse;
   } else
+  if (k.px == 2 && (bw & 1) == 0) {
+    // uint16 planes: a thread takes pixel PAIRS (block widths are powers of two: shifts, 32-bit loads where
+    // the pair is word aligned -- the source copy always is, the reference when its column is even)
+    const int lw = 31 - __clz(bw >> 1), np2 = n >> 1;
+    const unsigned short *sp16 = reinterpret_cast<const unsigned short *>(k.src);
+    const unsigned short *rp16 = reinterpret_cast<const unsigned short *>(rp);
+    const bool ral = ((reinterpret_cast<size_t>(rp16) | (size_t)(k.ref_pitch * 2)) & 3) == 0;
+    for (int i = threadIdx.x; i < np2; i += kThreads) {
+      const int y = i >> lw, x = (i - (y << lw)) * 2;
+      const unsigned s2 = *reinterpret_cast<const unsigned *>(sp16 + y * k.src_pitch_w * 2 + x);
+      const unsigned short *rq = rp16 + (long long)y * k.ref_pitch + x;
+      const unsigned r2 = ral ? *reinterpret_cast<const unsigned *>(rq) : ((unsigned)rq[0] | ((unsigned)rq[1] << 16));
+      const int d0 = (int)(s2 & 0xffff) - (int)(r2 & 0xffff), d1 = (int)(s2 >> 16) - (int)(r2 >> 16);
+      sum += d0 + d1;
+      sse += (unsigned)(d0 * d0) + (unsigned)(d1 * d1);
+    }
+  } else
   for (int i = threadIdx.x; i < n; i += kThreads) {
     const int y = i / bw, x = i - y * bw;
     int sv, rv;
