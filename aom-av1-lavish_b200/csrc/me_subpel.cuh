@@ -44,7 +44,7 @@ __device__ __forceinline__ int src_px(const Ctx &k, int i) {
 // 2: aom_upsampled_pred with 2/4/8 taps then vf (upsampled_pref_error).
 __device__ unsigned cta_pref_error(const SubCtx &s, Mv mv, int mode, unsigned *sse_out) {
   const Ctx &k = s.k;
-  const int bw = k.d.bw, bh = k.d.bh, n = bw * bh;
+  const int bw = k.d.bw, bh = k.d.bh, n = bw * bh, lw = 31 - __clz(bw);
   const int fr = mv.row >> 3, fc = mv.col >> 3, sx = mv.col & 7, sy = mv.row & 7;
   const unsigned char *rp = k.ref0 + ((long long)fr * k.ref_pitch + fc) * k.px;
   const int maxv = k.px == 1 ? 255 : (1 << k.l->bd) - 1;
@@ -53,7 +53,7 @@ __device__ unsigned cta_pref_error(const SubCtx &s, Mv mv, int mode, unsigned *s
   __syncthreads();
   if (mode == 0) {
     for (int i = threadIdx.x; i < n; i += kThreads) {
-      const int y = i / bw, x = i - y * bw;
+      const int y = i >> lw, x = i & (bw - 1);  // block widths are powers of two
       int pv = ref_px(k, rp, (long long)y * k.ref_pitch + x);
       if (k.compound) pv = compound_blend(k, pv, i, y, x);  // setup_center_error (:2781)
       const int df = pv - src_px(k, i);
@@ -63,7 +63,7 @@ __device__ unsigned cta_pref_error(const SubCtx &s, Mv mv, int mode, unsigned *s
   } else if (mode == 1) {
     const int f0 = c_me_bil[sx][0], f1 = c_me_bil[sx][1], g0 = c_me_bil[sy][0], g1 = c_me_bil[sy][1];
     for (int i = threadIdx.x; i < n; i += kThreads) {
-      const int y = i / bw, x = i - y * bw;
+      const int y = i >> lw, x = i & (bw - 1);  // block widths are powers of two
       const long long o = (long long)y * k.ref_pitch + x;
       const int h0 = (ref_px(k, rp, o) * f0 + ref_px(k, rp, o + 1) * f1 + 64) >> 7;
       const int h1 = (ref_px(k, rp, o + k.ref_pitch) * f0 + ref_px(k, rp, o + k.ref_pitch + 1) * f1 + 64) >> 7;
@@ -81,7 +81,7 @@ __device__ unsigned cta_pref_error(const SubCtx &s, Mv mv, int mode, unsigned *s
     // rows -3..bh+3 only when a vertical filter follows
     const int top = sy ? 3 : 0, ih = sy ? bh + 7 : bh;
     for (int i = threadIdx.x; i < ih * bw; i += kThreads) {
-      const int y = i / bw, x = i - y * bw;
+      const int y = i >> lw, x = i & (bw - 1);  // block widths are powers of two
       const long long o = (long long)(y - top) * k.ref_pitch + x;
       int v;
       if (sx) {
@@ -96,7 +96,7 @@ __device__ unsigned cta_pref_error(const SubCtx &s, Mv mv, int mode, unsigned *s
     }
     __syncthreads();
     for (int i = threadIdx.x; i < n; i += kThreads) {
-      const int y = i / bw, x = i - y * bw;
+      const int y = i >> lw, x = i & (bw - 1);  // block widths are powers of two
       int pv;
       if (sy) {
         int a = 0;
