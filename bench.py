@@ -901,15 +901,15 @@ def bench_config5(ctx, dev, stream, rank, world, seed, total_frames, batch, e2e_
         eblocks = pinned_copy(np.concatenate(one_frame_blocks))
         epreds = pinned_copy(np.concatenate(one_frame_preds))
         h_levels = pinned(out_off * 4, np.int32)
-        h_loff = np.zeros(eblocks.size + 1, np.uint32)
-        h_eob = np.zeros(eblocks.size, np.uint16)
-        h_dist = np.zeros((eblocks.size, 2), np.int64)
+        h_loff = pinned((eblocks.size + 1) * 4, np.uint32)
+        h_eob = pinned(eblocks.size * 2, np.uint16)
+        h_dist = pinned(eblocks.size * 16, np.int64).reshape(-1, 2)
         h_src, h_pred = pinned(frame_elems * 2, np.uint16), pinned(frame_elems * 2, np.uint16)
         h_refs = pinned(2 * rh * rs * 2, np.uint16)
         emb = pinned_copy(me_blocks(1, frame_elems))
         esub = pinned_copy(MeWork._sub(emb))
-        h_rf = np.zeros(emb.size, b200av1.MERESULT_DTYPE)
-        h_rs = np.zeros(emb.size, b200av1.MERESULT_DTYPE)
+        h_rf = pinned(emb.size * 40, b200av1.MERESULT_DTYPE)
+        h_rs = pinned(emb.size * 40, b200av1.MERESULT_DTYPE)
     for b0 in range(0, len(ids), batch):
         chunk = ids[b0:b0 + batch]
         hs = np.zeros((batch, frame_elems), np.uint16)
@@ -921,24 +921,29 @@ def bench_config5(ctx, dev, stream, rank, world, seed, total_frames, batch, e2e_
             if e2e_n < e2e_frames:
                 # ---- e2e: this frame through the host-buffer calls, copies inside the timed region
                 h_src[:], h_pred[:], h_refs[:] = hs[j], hp[j], hr[2 * j:2 * j + 2].reshape(-1)
+                def e2e_frame():
+                    d2h = ctx.txq_batch_host_compact(b200av1.IN_PIXELS16, b200av1.Q_FP_HBD, 10,
+                                                     b200av1.TXQ_BLOCK_ERROR, eblocks, epreds, h_src, h_pred, qrows,
+                                                     out_off, h_levels, h_loff, h_eob, h_dist)
+                    hl = b200av1.MeLaunch()
+                    hl.highbd, hl.bd, hl.n_blocks = 1, 10, int(emb.size)
+                    hl.blocks, hl.cur, hl.ref = emb.ctypes.data, h_src.ctypes.data, h_refs.ctypes.data
+                    hl.cur_stride, hl.ref_stride = w, rs
+                    for k, (rg, it) in enumerate(ME_MESH):
+                        hl.mesh_range[k], hl.mesh_interval[k] = rg, it
+                    hl.window_bytes, hl.max_bw, hl.max_bh = 88 * 1024, 64, 64
+                    hl.families = b200av1.ME_FAMILY_NSTEP
+                    hl.cur_rows, hl.ref_rows = h, 2 * rh
+                    hl.max_col_span, hl.max_row_span = 128, 128
+                    b200av1.check(lib.b200_me_batch_host(ctx.h, C.byref(hl), C.c_size_t(w * h * 2),
+                                                         C.c_size_t(h_refs.nbytes), C.c_void_p(esub.ctypes.data),
+                                                         C.c_void_p(h_rf.ctypes.data), C.c_void_p(h_rs.ctypes.data)))
+                    return d2h
+                if e2e_n == 0:
+                    e2e_frame()  # untimed once: scratch growth, lazy kernel loading of the uint16 instances
                 torch.cuda.synchronize(dev)
                 t0 = time.perf_counter()
-                d2h = ctx.txq_batch_host_compact(b200av1.IN_PIXELS16, b200av1.Q_FP_HBD, 10,
-                                                 b200av1.TXQ_BLOCK_ERROR, eblocks, epreds, h_src, h_pred, qrows,
-                                                 out_off, h_levels, h_loff, h_eob, h_dist)
-                hl = b200av1.MeLaunch()
-                hl.highbd, hl.bd, hl.n_blocks = 1, 10, int(emb.size)
-                hl.blocks, hl.cur, hl.ref = emb.ctypes.data, h_src.ctypes.data, h_refs.ctypes.data
-                hl.cur_stride, hl.ref_stride = w, rs
-                for k, (rg, it) in enumerate(ME_MESH):
-                    hl.mesh_range[k], hl.mesh_interval[k] = rg, it
-                hl.window_bytes, hl.max_bw, hl.max_bh = 88 * 1024, 64, 64
-                hl.families = b200av1.ME_FAMILY_NSTEP
-                hl.cur_rows, hl.ref_rows = h, 2 * rh
-                hl.max_col_span, hl.max_row_span = 128, 128
-                b200av1.check(lib.b200_me_batch_host(ctx.h, C.byref(hl), C.c_size_t(w * h * 2),
-                                                     C.c_size_t(h_refs.nbytes), C.c_void_p(esub.ctypes.data),
-                                                     C.c_void_p(h_rf.ctypes.data), C.c_void_p(h_rs.ctypes.data)))
+                d2h = e2e_frame()
                 e2e_t += time.perf_counter() - t0
                 e2e_n += 1
                 e2e_h2d += 2 * frame_elems * 2 + eblocks.nbytes + epreds.nbytes + w * h * 2 + h_refs.nbytes + 2 * emb.nbytes
@@ -1210,7 +1215,7 @@ def main():
         if work is not None:
             # one host-buffer call carries E frames (their planes stacked like the resident pool): a single
             # 1080p frame is 960 searches = 2.2 waves of resident CTAs, so calls of one frame time the tail
-            E = min(4, args.frames)
+            E = min(8, args.frames)
             e_mblk = pinned_copy(work._blocks(range(E), pooled=True))
             e_msub = pinned_copy(MeWork._sub(e_mblk))
             h_cur = pinned_copy(work.cur[0:E])
