@@ -784,6 +784,32 @@ __device__ __forceinline__ int grouped_segw(const Ctx &k) {
   return k.d.bw >= 32 ? 16 : 8;
 }
 
+// Small 8-bit blocks on the share-less path (8x8 .. 16x16: the temporal filter's blocks, whose frame-wide
+// n-step reads the reference through L1/L2): one warp per candidate leaves 16 or 24 of its lanes idle and pays
+// the load latency once per candidate.  Here a lane owns one row and a warp evaluates 32 / bh candidates at a
+// time (segmented shuffle sum over the bh lanes of a candidate).  W = words per row.
+template <int W>
+__device__ __noinline__ void eval_small_rows(const Ctx &k, int n, unsigned *out, int slot0) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int bh = k.d.bh, lb = 31 - __clz(bh), cpw = 32 >> lb;  // bh is 8 or 16
+  const int sub = lane >> lb, y = lane & (bh - 1);
+  unsigned sv[W];
+#pragma unroll
+  for (int j = 0; j < W; ++j) sv[j] = reinterpret_cast<const unsigned *>(k.src)[y * k.src_pitch_w + j];
+  for (int i0 = warp * cpw; i0 < n; i0 += kWarps * cpw) {
+    const int i = i0 + sub;
+    const bool ok = i < n && g_cda[slot0 + i] >= 0;
+    unsigned acc = 0;
+    if (ok) {
+      const int p = g_cdp[slot0 + i];
+      const int row = (short)(p & 0xffff), col = p >> 16;
+      acc = seg_sad<W, 1>(sv, k.ref0 + (long long)(row + y) * k.ref_pitch + col);
+    }
+    for (int o = bh >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (ok && y == 0) out[i] = acc;
+  }
+}
+
 // The step's candidates (g_cda / g_cdp, n of them) -> out[i] = SAD (finished: doubled when rows
 // are skipped, shifted at high bit depth); slots of candidates outside the limits are left
 // untouched.  out[0 .. n) must be zero on entry; the caller synchronises the CTA before reading.
@@ -793,6 +819,11 @@ __device__ __forceinline__ void eval_candidates(const Ctx &k, bool skip, int n, 
   if constexpr (SEGW > 0) {
     cta_sad_multi_t<SEGW>(skip, n, g_cda + slot0, out, ls);
   } else {
+    if (k.px == 1 && !skip && (k.d.bh == 8 || k.d.bh == 16) && (k.d.bw == 8 || k.d.bw == 16)) {  // CTA-uniform
+      if (k.d.bw == 8) eval_small_rows<2>(k, n, out, slot0);
+      else eval_small_rows<4>(k, n, out, slot0);
+      return;
+    }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int i = warp; i < n; i += kWarps) {
       if (g_cda[slot0 + i] < 0) continue;
