@@ -1327,7 +1327,7 @@ __host__ __device__ __forceinline__ int me_family(int method) {
 }
 
 template <int FAM>
-__global__ void __launch_bounds__(kThreads, 3) fullpel_kernel(const B200MeLaunch l, const Sites *sites4,
+__global__ void __launch_bounds__(kThreads, FAM == 3 ? 2 : 3) fullpel_kernel(const B200MeLaunch l, const Sites *sites4,
                                                            int window_budget, const TmaCfg tc,
                                                            const __grid_constant__ CUtensorMap tm_cur,
                                                            const __grid_constant__ CUtensorMap tm_ref) {

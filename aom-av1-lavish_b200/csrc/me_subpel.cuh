@@ -497,7 +497,7 @@ __device__ void subpel_search_pruned(const SubCtx &s, SubState &st, int tree, co
   }
 }
 
-__global__ void __launch_bounds__(kThreads) subpel_kernel(const B200MeLaunch l) {
+__global__ void __launch_bounds__(kThreads, 4) subpel_kernel(const B200MeLaunch l) {
   const int bi = blockIdx.x;
   load_desc<false>(l, bi);
   SubCtx s(g_desc);
